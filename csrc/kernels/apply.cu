@@ -1,0 +1,261 @@
+// K9/K10: gradient push fused with the owning shard's optimizer apply.
+//
+// The worker launches ONE kernel per step. For every (variable slice, gradient slice) pair it
+// reads the local fp32 gradient, reads the slice's optimizer state from the owning PS shard
+// (local HBM, or a peer GPU's HBM through the NVLink mapping), applies the TF1 update rule and
+// writes var / slots back together with the bf16 serving copy that workers pull. Plain SGD can
+// instead be pushed with red.global.add.f32 (write-only over NVLink, exact under concurrency).
+// The last CTA to retire performs TF's "_finish": beta1_power/beta2_power *= beta, then bumps the
+// shared global_step with ONE system-scope 64-bit atomic and publishes the worker's heartbeat.
+// Updates are deliberately unlocked (use_locking=False, Hogwild), as in the reference's
+// AdamOptimizer(...).minimize (run_mnist_distributed.py:116).
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../../include/dtf_b200.h"
+
+namespace dtf {
+
+constexpr int APPLY_THREADS = 256;
+constexpr int APPLY_VEC = 4;
+constexpr int APPLY_UNROLL = 4;
+constexpr int APPLY_CHUNK = APPLY_THREADS * APPLY_VEC * APPLY_UNROLL;  // 4096 elements / CTA
+
+struct ApplyArgs {
+  dtf_apply_item items[DTF_MAX_APPLY_ITEMS];
+  int block_start[DTF_MAX_APPLY_ITEMS + 1];
+  int n_items;
+  int total_blocks;
+  dtf_apply_hyper h;
+  dtf_ps_ctrl* ctrl_powers;
+  dtf_ps_ctrl* ctrl_step;
+  int finish;
+  int worker_id;
+  unsigned long long* step_out;
+  unsigned int* block_counter;
+};
+
+template <int OPT>
+__device__ __forceinline__ void update_one(float g, float& var, float& s0, float& s1,
+                                           const dtf_apply_hyper& h, float lr_t) {
+  if (OPT == DTF_OPT_SGD) {
+    var -= h.lr * g;
+  } else if (OPT == DTF_OPT_MOMENTUM) {
+    s0 = s0 * h.momentum + g;
+    if (h.use_nesterov)
+      var -= g * h.lr + s0 * h.momentum * h.lr;
+    else
+      var -= h.lr * s0;
+  } else if (OPT == DTF_OPT_ADAGRAD) {
+    s0 += g * g;
+    var -= h.lr * g * rsqrtf(s0);
+  } else {  // Adam, TF1 "epsilon hat" form
+    s0 += (g - s0) * (1.f - h.beta1);
+    s1 += (g * g - s1) * (1.f - h.beta2);
+    var -= lr_t * s0 / (sqrtf(s1) + h.epsilon);
+  }
+}
+
+template <int OPT>
+__global__ void __launch_bounds__(APPLY_THREADS)
+push_apply_kernel(const __grid_constant__ ApplyArgs a) {
+  __shared__ int s_item;
+  __shared__ float s_lr_t;
+  __shared__ unsigned int s_last;
+  if (threadIdx.x == 0) {
+    int it = 0;
+    while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
+    s_item = it;
+    float lr_t = a.h.lr;
+    if (OPT == DTF_OPT_ADAM) {
+      // beta powers live on the PS (shared by all workers): t counts applies from everyone.
+      const float b1p = *reinterpret_cast<volatile float*>(&a.ctrl_powers->beta1_power);
+      const float b2p = *reinterpret_cast<volatile float*>(&a.ctrl_powers->beta2_power);
+      lr_t = a.h.lr * sqrtf(1.f - b2p) / (1.f - b1p);
+    }
+    s_lr_t = lr_t;
+  }
+  __syncthreads();
+  const dtf_apply_item& it = a.items[s_item];
+  const float lr_t = s_lr_t;
+  const long long base = static_cast<long long>(blockIdx.x - a.block_start[s_item]) * APPLY_CHUNK;
+  const bool vec_ok =
+      ((reinterpret_cast<uintptr_t>(it.var) | reinterpret_cast<uintptr_t>(it.grad) |
+        reinterpret_cast<uintptr_t>(it.slot0) | reinterpret_cast<uintptr_t>(it.slot1)) & 15) == 0;
+  __nv_bfloat16* shadow = reinterpret_cast<__nv_bfloat16*>(it.shadow);
+  const bool shadow_vec = shadow != nullptr && (it.cols % 4 == 0) && (it.shadow_ld % 4 == 0) &&
+                          (it.first % 4 == 0) &&
+                          ((reinterpret_cast<uintptr_t>(shadow) & 7) == 0);
+
+#pragma unroll
+  for (int u = 0; u < APPLY_UNROLL; ++u) {
+    const long long i = base + (static_cast<long long>(u) * APPLY_THREADS + threadIdx.x) * APPLY_VEC;
+    if (i >= it.n) continue;
+    if (vec_ok && i + APPLY_VEC <= it.n) {
+      const float4 g4 = *reinterpret_cast<const float4*>(it.grad + i);
+      float g[4] = {g4.x * a.h.grad_scale, g4.y * a.h.grad_scale, g4.z * a.h.grad_scale,
+                    g4.w * a.h.grad_scale};
+      if (OPT == DTF_OPT_SGD && a.h.atomic_sgd) {
+        // write-only push: var += -lr * g via reduction atomics at the owner's L2
+#pragma unroll
+        for (int j = 0; j < 4; ++j) red_add_f32_sys(it.var + i + j, -a.h.lr * g[j]);
+        continue;  // shadow is refreshed by the owner in this mode
+      }
+      float4 v4 = *reinterpret_cast<float4*>(it.var + i);
+      float v[4] = {v4.x, v4.y, v4.z, v4.w};
+      float s0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0};
+      if (OPT != DTF_OPT_SGD) {
+        const float4 t = *reinterpret_cast<float4*>(it.slot0 + i);
+        s0[0] = t.x; s0[1] = t.y; s0[2] = t.z; s0[3] = t.w;
+      }
+      if (OPT == DTF_OPT_ADAM) {
+        const float4 t = *reinterpret_cast<float4*>(it.slot1 + i);
+        s1[0] = t.x; s1[1] = t.y; s1[2] = t.z; s1[3] = t.w;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) update_one<OPT>(g[j], v[j], s0[j], s1[j], a.h, lr_t);
+      *reinterpret_cast<float4*>(it.var + i) = make_float4(v[0], v[1], v[2], v[3]);
+      if (OPT != DTF_OPT_SGD)
+        *reinterpret_cast<float4*>(it.slot0 + i) = make_float4(s0[0], s0[1], s0[2], s0[3]);
+      if (OPT == DTF_OPT_ADAM)
+        *reinterpret_cast<float4*>(it.slot1 + i) = make_float4(s1[0], s1[1], s1[2], s1[3]);
+      if (shadow != nullptr) {
+        const long long f = it.first + i;
+        if (shadow_vec) {
+          const long long r = f / it.cols, c = f % it.cols;
+          uint2 o;
+          o.x = pack_bf16x2(v[0], v[1]);
+          o.y = pack_bf16x2(v[2], v[3]);
+          *reinterpret_cast<uint2*>(shadow + r * it.shadow_ld + c) = o;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const long long r = (f + j) / it.cols, c = (f + j) % it.cols;
+            shadow[r * it.shadow_ld + c] = __float2bfloat16(v[j]);
+          }
+        }
+      }
+    } else {
+      for (int j = 0; j < APPLY_VEC && i + j < it.n; ++j) {
+        const float g = it.grad[i + j] * a.h.grad_scale;
+        if (OPT == DTF_OPT_SGD && a.h.atomic_sgd) {
+          red_add_f32_sys(it.var + i + j, -a.h.lr * g);
+          continue;
+        }
+        float v = it.var[i + j];
+        float s0 = (OPT != DTF_OPT_SGD) ? it.slot0[i + j] : 0.f;
+        float s1 = (OPT == DTF_OPT_ADAM) ? it.slot1[i + j] : 0.f;
+        update_one<OPT>(g, v, s0, s1, a.h, lr_t);
+        it.var[i + j] = v;
+        if (OPT != DTF_OPT_SGD) it.slot0[i + j] = s0;
+        if (OPT == DTF_OPT_ADAM) it.slot1[i + j] = s1;
+        if (shadow != nullptr) {
+          const long long f = it.first + i + j;
+          shadow[(f / it.cols) * it.shadow_ld + (f % it.cols)] = __float2bfloat16(v);
+        }
+      }
+    }
+  }
+
+  if (!a.finish) return;
+  // ---- elect the last CTA; it performs _finish (K10) ----
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int old = atomicInc(a.block_counter, static_cast<unsigned int>(a.total_blocks - 1));
+    s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    if (OPT == DTF_OPT_ADAM) {
+      volatile float* b1 = &a.ctrl_powers->beta1_power;
+      volatile float* b2 = &a.ctrl_powers->beta2_power;
+      *b1 = *b1 * a.h.beta1;
+      *b2 = *b2 * a.h.beta2;
+    }
+    const unsigned long long old = atom_add_u64_sys(&a.ctrl_step->global_step, 1ull);
+    if (a.step_out != nullptr) *a.step_out = old + 1ull;
+    if (a.worker_id >= 0 && a.worker_id < DTF_MAX_WORKERS)
+      *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[a.worker_id]) =
+          old + 1ull;
+    atomicAdd(&a.ctrl_step->apply_count, 1u);
+    __threadfence_system();
+  }
+}
+
+__global__ void refresh_shadow_kernel(const float* __restrict__ var,
+                                      __nv_bfloat16* __restrict__ shadow, long long n,
+                                      long long first, int cols, int shadow_ld) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long f = first + i;
+    shadow[(f / cols) * shadow_ld + (f % cols)] = __float2bfloat16(var[i]);
+  }
+}
+
+}  // namespace dtf
+
+using namespace dtf;
+
+extern "C" int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
+                              const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
+                              dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
+                              unsigned long long* step_out, unsigned int* block_counter,
+                              void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "push_apply: %d items (max %d)",
+              n_items, DTF_MAX_APPLY_ITEMS);
+  DTF_REQUIRE(!finish || (ctrl_for_step != nullptr && block_counter != nullptr),
+              "push_apply: finish needs ctrl_for_step and block_counter");
+  DTF_REQUIRE(opt != DTF_OPT_ADAM || ctrl_for_powers != nullptr,
+              "push_apply: Adam needs the control block that owns the beta powers");
+  ApplyArgs a;
+  memset(&a, 0, sizeof(a));
+  int blocks = 0;
+  for (int i = 0; i < n_items; ++i) {
+    a.items[i] = items[i];
+    a.block_start[i] = blocks;
+    DTF_REQUIRE(items[i].n >= 0 && items[i].var && items[i].grad, "push_apply: item %d invalid", i);
+    DTF_REQUIRE(opt == DTF_OPT_SGD || items[i].slot0, "push_apply: item %d lacks slot0", i);
+    DTF_REQUIRE(opt != DTF_OPT_ADAM || items[i].slot1, "push_apply: item %d lacks slot1", i);
+    blocks += static_cast<int>((items[i].n + APPLY_CHUNK - 1) / APPLY_CHUNK);
+  }
+  a.block_start[n_items] = blocks;
+  if (blocks == 0) {  // nothing to apply but the step may still need its _finish
+    DTF_REQUIRE(n_items > 0 || finish, "push_apply: nothing to do");
+    blocks = 1;
+    if (n_items == 0) {
+      a.items[0].n = 0;
+      n_items = 1;
+      a.block_start[1] = 1;
+    }
+  }
+  a.n_items = n_items;
+  a.total_blocks = blocks;
+  a.h = *hyper;
+  a.ctrl_powers = ctrl_for_powers;
+  a.ctrl_step = ctrl_for_step;
+  a.finish = finish;
+  a.worker_id = worker_id;
+  a.step_out = step_out;
+  a.block_counter = block_counter;
+  switch (opt) {
+    case DTF_OPT_SGD: push_apply_kernel<DTF_OPT_SGD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_MOMENTUM: push_apply_kernel<DTF_OPT_MOMENTUM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_ADAGRAD: push_apply_kernel<DTF_OPT_ADAGRAD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_ADAM: push_apply_kernel<DTF_OPT_ADAM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    default: DTF_REQUIRE(false, "push_apply: unknown optimizer %d", opt);
+  }
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dtf_refresh_shadow(const float* var, void* shadow, long long n, long long first,
+                                  int cols, int shadow_ld, void* stream) {
+  if (n <= 0) return 0;
+  int blocks = static_cast<int>((n + 1023) / 1024);
+  if (blocks > 1184) blocks = 1184;
+  refresh_shadow_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      var, reinterpret_cast<__nv_bfloat16*>(shadow), n, first, cols, shadow_ld);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}

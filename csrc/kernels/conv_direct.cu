@@ -1,0 +1,206 @@
+// K6/K7/K8 for the reference CNN's FIRST conv block (run_mnist_distributed.py:52-58) and the
+// pooling gradients. conv1 has Cin = 1 (implicit-GEMM K = 25): too thin for the tensor cores, so
+// it is a direct CUDA-core kernel with the whole image, the 5x5x32 filter bank and the bias in
+// shared memory, fused with bias + ReLU + 2x2 max-pool (+argmax) and with the input
+// normalisation uint8 -> [0,1] (dataset.py:92-100). Outputs land in the zero-bordered NHWC bf16
+// layout that conv2's TMA boxes read.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../../include/dtf_b200.h"
+
+namespace dtf {
+
+constexpr int C1_IMG = 28, C1_PAD = 32, C1_OUT = 14, C1_CH = 32, C1_HP = 18;
+
+__device__ __forceinline__ void load_image_padded(float (*img)[C1_PAD], const unsigned char* x_u8,
+                                                  const float* x_f32, float scale, int n) {
+  for (int i = threadIdx.x; i < C1_PAD * C1_PAD; i += blockDim.x) {
+    const int y = i / C1_PAD - 2, x = i % C1_PAD - 2;
+    float v = 0.f;
+    if (y >= 0 && y < C1_IMG && x >= 0 && x < C1_IMG) {
+      const size_t o = static_cast<size_t>(n) * (C1_IMG * C1_IMG) + y * C1_IMG + x;
+      v = (x_u8 != nullptr) ? static_cast<float>(x_u8[o]) * scale : x_f32[o] * scale;
+    }
+    img[i / C1_PAD][i % C1_PAD] = v;
+  }
+}
+
+// One CTA per image. Work item = (pooled pixel, group of 8 output channels).
+__global__ void __launch_bounds__(256)
+conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
+                 float scale, const float* __restrict__ w1, const float* __restrict__ b1,
+                 __nv_bfloat16* __restrict__ pool1p, unsigned char* __restrict__ amax1) {
+  __shared__ float img[C1_PAD][C1_PAD];
+  __shared__ float w[25][C1_CH];
+  __shared__ float bias[C1_CH];
+  const int n = blockIdx.x;
+  load_image_padded(img, x_u8, x_f32, scale, n);
+  for (int i = threadIdx.x; i < 25 * C1_CH; i += blockDim.x) w[i / C1_CH][i % C1_CH] = w1[i];
+  if (threadIdx.x < C1_CH) bias[threadIdx.x] = b1[threadIdx.x];
+  __syncthreads();
+
+  for (int item = threadIdx.x; item < C1_OUT * C1_OUT * 4; item += blockDim.x) {
+    const int pp = item >> 2, cg = item & 3;
+    const int py = pp / C1_OUT, px = pp % C1_OUT;
+    float patch[6][6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = 0; j < 6; ++j) patch[i][j] = img[2 * py + i][2 * px + j];
+    float acc[4][8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[q][c] = 0.f;
+#pragma unroll
+    for (int r = 0; r < 5; ++r)
+#pragma unroll
+      for (int s = 0; s < 5; ++s) {
+        float wv[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) wv[c] = w[r * 5 + s][cg * 8 + c];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float xv = patch[(q >> 1) + r][(q & 1) + s];
+#pragma unroll
+          for (int c = 0; c < 8; ++c) acc[q][c] = fmaf(xv, wv[c], acc[q][c]);
+        }
+      }
+    uint32_t packed[4];
+    uint32_t am[2] = {0, 0};
+    float o[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      float best = acc[0][c];
+      uint32_t bi = 0;
+#pragma unroll
+      for (int q = 1; q < 4; ++q)
+        if (acc[q][c] > best) { best = acc[q][c]; bi = q; }
+      o[c] = fmaxf(best + bias[cg * 8 + c], 0.f);
+      am[c >> 2] |= bi << (8 * (c & 3));
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) packed[c] = pack_bf16x2(o[2 * c], o[2 * c + 1]);
+    const size_t op = ((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + cg * 8;
+    *reinterpret_cast<uint4*>(pool1p + op) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+    const size_t oa = ((static_cast<size_t>(n) * C1_OUT + py) * C1_OUT + px) * C1_CH + cg * 8;
+    *reinterpret_cast<uint2*>(amax1 + oa) = make_uint2(am[0], am[1]);
+  }
+}
+
+// One CTA (800 threads = 25 taps x 32 channels) per image: thread (tap, c) accumulates
+// dW1[tap, c] over the image's 196 pooled pixels; warp 0 also accumulates db1.
+__global__ void __launch_bounds__(800)
+conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
+                 float scale, const __nv_bfloat16* __restrict__ dpool1,
+                 const __nv_bfloat16* __restrict__ pool1p, const unsigned char* __restrict__ amax1,
+                 float* __restrict__ dw1_accum, float* __restrict__ db1_accum) {
+  __shared__ float img[C1_PAD][C1_PAD];
+  __shared__ float g[C1_OUT * C1_OUT][C1_CH];          // 25 KB
+  __shared__ unsigned char am[C1_OUT * C1_OUT][C1_CH]; // 6 KB
+  const int n = blockIdx.x;
+  load_image_padded(img, x_u8, x_f32, scale, n);
+  for (int i = threadIdx.x; i < C1_OUT * C1_OUT * C1_CH; i += blockDim.x) {
+    const int pp = i / C1_CH, c = i % C1_CH;
+    const int py = pp / C1_OUT, px = pp % C1_OUT;
+    const float act = __bfloat162float(
+        pool1p[((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + c]);
+    const float d = __bfloat162float(dpool1[static_cast<size_t>(n) * (C1_OUT * C1_OUT * C1_CH) + i]);
+    g[pp][c] = (act > 0.f) ? d : 0.f;  // ReLU gradient through the max-pool
+    am[pp][c] = amax1[static_cast<size_t>(n) * (C1_OUT * C1_OUT * C1_CH) + i];
+  }
+  __syncthreads();
+  const int tap = threadIdx.x >> 5, c = threadIdx.x & 31;
+  const int r = tap / 5, s = tap % 5;
+  float acc = 0.f, accb = 0.f;
+  for (int pp = 0; pp < C1_OUT * C1_OUT; ++pp) {
+    const int py = pp / C1_OUT, px = pp % C1_OUT;
+    const int a = am[pp][c];
+    const float gv = g[pp][c];
+    acc = fmaf(img[2 * py + (a >> 1) + r][2 * px + (a & 1) + s], gv, acc);
+    accb += gv;
+  }
+  atomicAdd(&dw1_accum[tap * C1_CH + c], acc);
+  if (tap == 0) atomicAdd(&db1_accum[c], accb);
+}
+
+// pool2 gradient + ReLU gradient, scattered into the zero-bordered [B,18,18,64] layout conv2's
+// dgrad / wgrad TMA boxes read; db2 = column sums. Work item = (pooled pixel, 8 channels).
+__global__ void __launch_bounds__(256)
+pool2_bwd_kernel(const __nv_bfloat16* __restrict__ dpool2, int ld, const __nv_bfloat16* __restrict__ pool2,
+                 const unsigned char* __restrict__ amax2, __nv_bfloat16* __restrict__ dconv2p,
+                 float* __restrict__ db2_accum, int B) {
+  __shared__ float s_db[64];
+  if (threadIdx.x < 64) s_db[threadIdx.x] = 0.f;
+  __syncthreads();
+  const int total = B * 49 * 8;
+  for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < total; item += gridDim.x * blockDim.x) {
+    const int cg = item & 7;
+    const int pp = (item >> 3) % 49;
+    const int n = (item >> 3) / 49;
+    const int py = pp / 7, px = pp % 7;
+    const uint4 dv = *reinterpret_cast<const uint4*>(dpool2 + static_cast<size_t>(n) * ld + pp * 64 + cg * 8);
+    const uint4 av = *reinterpret_cast<const uint4*>(pool2 + (static_cast<size_t>(n) * 49 + pp) * 64 + cg * 8);
+    const uint2 mv = *reinterpret_cast<const uint2*>(amax2 + (static_cast<size_t>(n) * 49 + pp) * 64 + cg * 8);
+    const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(&dv);
+    const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(&av);
+    const unsigned char* m = reinterpret_cast<const unsigned char*>(&mv);
+    __nv_bfloat16 out[4][8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const bool on = __bfloat162float(a[c]) > 0.f;
+      const __nv_bfloat16 gv = on ? d[c] : __float2bfloat16(0.f);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) out[q][c] = (m[c] == q) ? gv : __float2bfloat16(0.f);
+      if (on) atomicAdd(&s_db[cg * 8 + c], __bfloat162float(d[c]));
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int y = 2 * py + (q >> 1) + 2, x = 2 * px + (q & 1) + 2;
+      *reinterpret_cast<uint4*>(dconv2p + ((static_cast<size_t>(n) * 18 + y) * 18 + x) * 64 + cg * 8) =
+          *reinterpret_cast<const uint4*>(out[q]);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 64) atomicAdd(&db2_accum[threadIdx.x], s_db[threadIdx.x]);
+}
+
+}  // namespace dtf
+
+using namespace dtf;
+
+extern "C" int dtf_conv1_fwd(const unsigned char* x_u8, const float* x_f32, float scale,
+                             const float* w1, const float* b1, void* pool1p,
+                             unsigned char* amax1, int B, void* stream) {
+  DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_fwd: pass exactly one of x_u8/x_f32");
+  conv1_fwd_kernel<<<B, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x_u8, x_f32, scale, w1, b1, reinterpret_cast<__nv_bfloat16*>(pool1p), amax1);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, float scale,
+                             const void* dpool1, const void* pool1p, const unsigned char* amax1,
+                             float* dw1_accum, float* db1_accum, int B, void* stream) {
+  DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_bwd: pass exactly one of x_u8/x_f32");
+  conv1_bwd_kernel<<<B, 800, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x_u8, x_f32, scale, reinterpret_cast<const __nv_bfloat16*>(dpool1),
+      reinterpret_cast<const __nv_bfloat16*>(pool1p), amax1, dw1_accum, db1_accum);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dtf_pool2_bwd(const void* dpool2, int ld_dpool2, const void* pool2,
+                             const unsigned char* amax2, void* dconv2p, float* db2_accum, int B,
+                             void* stream) {
+  DTF_REQUIRE(ld_dpool2 % 8 == 0, "pool2_bwd: ld_dpool2=%d must be a multiple of 8", ld_dpool2);
+  const int total = B * 49 * 8;
+  int blocks = ceil_div(total, 256);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  pool2_bwd_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(dpool2), ld_dpool2,
+      reinterpret_cast<const __nv_bfloat16*>(pool2), amax2,
+      reinterpret_cast<__nv_bfloat16*>(dconv2p), db2_accum, B);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,107 @@
+// K13 + small helpers: input normalisation (uint8 -> bf16 * 1/255, dataset.py:92-100 done on the
+// device so only 1 byte/pixel crosses PCIe), fp32 -> bf16 cast into a row-padded TMA operand,
+// column sums (BiasAddGrad, K3) and a 32-bit fill used to clear the per-step scratch block.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../../include/dtf_b200.h"
+
+namespace dtf {
+
+__global__ void u8_to_bf16_kernel(const unsigned char* __restrict__ src,
+                                  __nv_bfloat16* __restrict__ dst, int rows, int cols, int ldd,
+                                  float scale) {
+  const long long total = static_cast<long long>(rows) * ldd;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / ldd), c = static_cast<int>(i % ldd);
+    const float v = (c < cols) ? static_cast<float>(src[static_cast<long long>(r) * cols + c]) * scale : 0.f;
+    dst[i] = __float2bfloat16(v);
+  }
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ src, int lds,
+                                   __nv_bfloat16* __restrict__ dst, int ldd, int rows, int cols) {
+  const long long total = static_cast<long long>(rows) * ldd;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / ldd), c = static_cast<int>(i % ldd);
+    dst[i] = __float2bfloat16((c < cols) ? src[static_cast<long long>(r) * lds + c] : 0.f);
+  }
+}
+
+// out_accum[c] += sum_r x[r, c]. Block = 32 columns x 8 row-lanes; grid.y splits the rows.
+__global__ void __launch_bounds__(256)
+colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int rows, int cols,
+                   float* __restrict__ out_accum, int rows_per_block) {
+  __shared__ float s[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float acc = 0.f;
+  if (c < cols)
+    for (int r = r0 + ty; r < r1; r += 8) acc += __bfloat162float(x[static_cast<long long>(r) * ldx + c]);
+  s[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += s[i][tx];
+    atomicAdd(&out_accum[c], t);
+  }
+}
+
+__global__ void fill_u32_kernel(unsigned int* __restrict__ dst, unsigned int v, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    dst[i] = v;
+}
+
+static inline int grid_for(long long n, int threads) {
+  long long b = (n + threads - 1) / threads;
+  if (b > 148 * 8) b = 148 * 8;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+}  // namespace dtf
+
+using namespace dtf;
+
+extern "C" int dtf_u8_to_bf16(const unsigned char* src, void* dst, int rows, int cols, int ldd,
+                              float scale, void* stream) {
+  const long long total = static_cast<long long>(rows) * ldd;
+  u8_to_bf16_kernel<<<grid_for(total, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      src, reinterpret_cast<__nv_bfloat16*>(dst), rows, cols, ldd, scale);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dtf_f32_to_bf16(const float* src, int lds, void* dst, int ldd, int rows, int cols,
+                               void* stream) {
+  const long long total = static_cast<long long>(rows) * ldd;
+  f32_to_bf16_kernel<<<grid_for(total, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, rows, cols);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dtf_colsum_bf16(const void* x, int ldx, int rows, int cols, float* out_accum,
+                               void* stream) {
+  int ysplit = ceil_div(rows, 256);
+  if (ysplit > 64) ysplit = 64;
+  const int rpb = ceil_div(rows, ysplit);
+  dim3 grid(ceil_div(cols, 32), ceil_div(rows, rpb));
+  colsum_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), ldx, rows, cols, out_accum, rpb);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dtf_fill_u32(void* dst, unsigned int value, long long n_words, void* stream) {
+  if (n_words <= 0) return 0;
+  fill_u32_kernel<<<grid_for(n_words, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<unsigned int*>(dst), value, n_words);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}

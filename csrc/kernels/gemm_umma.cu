@@ -1,0 +1,340 @@
+// Dense GEMM on the 5th-generation tensor cores.
+//
+//   D[M,N] = A[M,K] * B[N,K]^T      bf16 operands, fp32 accumulation in TMEM
+//
+// One CTA per 128 x BN output tile (optionally one K-slice of it: split-K):
+//   warp 0     TMA producer   cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx-count
+//   warp 1     MMA issuer     one elected thread issues tcgen05.mma (UMMA 128 x BN x 16), the
+//                             ring slot is released by tcgen05.commit -> mbarrier
+//   warp 2     TMEM allocator tcgen05.alloc / dealloc of BN fp32 columns
+//   warps 4-7  epilogue       tcgen05.ld (thread = accumulator row), fused bias / ReLU /
+//                             ReLU-grad mask / scale, bf16 or fp32 store, or red.global.add
+//                             (split-K and gradient accumulation into peer memory)
+//
+// Both operands may be K-major (the reduction dim is contiguous in memory) or MN-major (the
+// M/N dim is contiguous), so forward (X*W), input-gradient (dY*W^T) and weight-gradient (X^T*dY)
+// all run without a transpose pass:
+//   fwd   Y = X W      A = X  [M,K] K-major      B = W  [K,N] MN-major
+//   dX    = dY W^T     A = dY [M,K] K-major      B = W  [N,K] K-major   (W stored [in,out])
+//   dW    = X^T dY     A = X  [K,M] MN-major     B = dY [K,N] MN-major
+// The B operand of the forward GEMM may live in another GPU's memory (the PS shard's bf16
+// serving copy): the TMA descriptor is simply encoded on the peer-mapped address, which fuses the
+// parameter pull into the first GEMM (reference: the _Recv of hid_w feeding MatMul,
+// templates/00_mnist_replica.py:160 / run_mnist_distributed.py:67).
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../../include/dtf_b200.h"
+
+namespace dtf {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 64;  // 64 bf16 = 128 B = one swizzle row
+constexpr int GEMM_THREADS = 256;
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;  // 16 KB
+  static constexpr int B_BYTES = BN * GEMM_BK * 2;       // 8 / 16 KB
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN <= 64) ? 6 : 5;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct GemmParams {
+  int M, N, K;
+  int kb_per_split;  // k-blocks (of 64) handled by one blockIdx.z
+  // epilogue
+  void* out;
+  int ldo;
+  int out_f32;
+  int n_store;  // columns [0, n_store) are written (N rounded up into the row padding)
+  const float* bias;
+  int relu;
+  const __nv_bfloat16* mask;
+  int ldmask;
+  int reduce;  // red.global.add.f32 into out instead of a store
+  float alpha;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                 const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int S = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + S;
+  uint64_t* tmem_full_bar = empty_bar + S;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int n0 = blockIdx.x * BN;
+  const int m0 = blockIdx.y * GEMM_BM;
+  const int num_kb_total = (p.K + GEMM_BK - 1) / GEMM_BK;
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int kb_end = min(num_kb_total, kb_begin + p.kb_per_split);
+  const int num_kb = max(0, kb_end - kb_begin);
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < S; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (elect_one()) {
+      for (int i = 0; i < num_kb; ++i) {
+        const int s = i % S;
+        const uint32_t ph = (i / S) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        uint8_t* a_dst = smem + s * Cfg::STAGE_BYTES;
+        uint8_t* b_dst = a_dst + Cfg::A_BYTES;
+        mbar_arrive_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+        const int k0 = (kb_begin + i) * GEMM_BK;
+        if constexpr (!A_MN) {
+          tma_load_2d(a_dst, &tmap_a, &full_bar[s], k0, m0);  // box {64 k, 128 m}
+        } else {
+#pragma unroll
+          for (int c = 0; c < GEMM_BM / 64; ++c)  // box {64 m, 64 k}
+            tma_load_2d(a_dst + c * 8192, &tmap_a, &full_bar[s], m0 + c * 64, k0);
+        }
+        if constexpr (!B_MN) {
+          tma_load_2d(b_dst, &tmap_b, &full_bar[s], k0, n0);  // box {64 k, BN n}
+        } else {
+#pragma unroll
+          for (int c = 0; c < BN / 64; ++c)  // box {64 n, 64 k}
+            tma_load_2d(b_dst + c * 8192, &tmap_b, &full_bar[s], n0 + c * 64, k0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer --------------------------------
+    if (elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
+      for (int i = 0; i < num_kb; ++i) {
+        const int s = i % S;
+        const uint32_t ph = (i / S) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + s * Cfg::STAGE_BYTES);
+        const uint32_t b_base = a_base + Cfg::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < GEMM_BK / 16; ++k) {
+          // K-major, 128B swizzle: rows of 128 B, 8-row groups 1024 B apart; a K=16 slice is 32 B
+          // inside the swizzled row. MN-major: 64-element chunks 8192 B apart (LBO), 8 k-rows per
+          // 1024 B group (SBO); a K=16 slice is 16 rows = 2048 B.
+          const uint64_t adesc = A_MN ? umma_smem_desc(a_base + k * 2048, 8192, 1024, 2)
+                                      : umma_smem_desc(a_base + k * 32, 16, 1024, 2);
+          const uint64_t bdesc = B_MN ? umma_smem_desc(b_base + k * 2048, 8192, 1024, 2)
+                                      : umma_smem_desc(b_base + k * 32, 16, 1024, 2);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+      }
+      umma_commit(tmem_full_bar);  // accumulator complete
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ epilogue ----------------------------------
+    const int q = warp - 4;  // TMEM lane quarter == warp_id % 4
+    const int lane = threadIdx.x & 31;
+    const int m = m0 + q * 32 + lane;
+    if (num_kb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    const bool row_ok = m < p.M;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t r[32];
+      if (num_kb > 0) {
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c * 32, r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0;
+      }
+      const int nb = n0 + c * 32;
+      if (!row_ok || nb >= p.n_store) continue;
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+      }
+      if (p.mask != nullptr) {
+        const __nv_bfloat16* mrow = p.mask + static_cast<size_t>(m) * p.ldmask + nb;
+        if ((p.ldmask & 7) == 0 && nb + 32 <= p.ldmask) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 mv = *reinterpret_cast<const uint4*>(mrow + g * 8);
+            const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (!(__bfloat162float(mb[j]) > 0.f)) v[g * 8 + j] = 0.f;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.ldmask && !(__bfloat162float(mrow[j]) > 0.f)) v[j] = 0.f;
+        }
+      }
+      if (p.out_f32) {
+        float* orow = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
+        if (p.reduce) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.n_store) red_add_f32_sys(orow + j, v[j]);
+        } else if ((p.ldo & 3) == 0 && nb + 32 <= p.n_store) {
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            *reinterpret_cast<float4*>(orow + g * 4) =
+                make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.n_store) orow[j] = v[j];
+        }
+      } else {
+        __nv_bfloat16* orow =
+            reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
+        if ((p.ldo & 7) == 0 && nb + 32 <= p.n_store) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 o;
+            o.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
+            o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
+            o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
+            o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
+            *reinterpret_cast<uint4*>(orow + g * 8) = o;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.n_store) orow[j] = __float2bfloat16(v[j]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BN);
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
+                       int splits, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = gemm_umma_kernel<BN, A_MN, B_MN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DTF_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  dim3 grid(ceil_div(p.N, BN), ceil_div(p.M, GEMM_BM), splits);
+  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace dtf
+
+using namespace dtf;
+
+extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int b_mn,
+                             int M, int N, int K, const dtf_gemm_epilogue* epi, int splits,
+                             int block_n, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
+  DTF_REQUIRE(epi != nullptr && epi->out != nullptr, "gemm: epilogue/out is null");
+  DTF_REQUIRE(lda % 8 == 0 && ldb % 8 == 0,
+              "gemm: lda=%d ldb=%d must be multiples of 8 elements (TMA 16 B rule)", lda, ldb);
+  const int BN = (block_n == 64 || block_n == 128) ? block_n : (N > 64 ? 128 : 64);
+  const int num_kb = ceil_div(K, GEMM_BK);
+  if (splits < 1) splits = 1;
+  if (splits > num_kb) splits = num_kb;
+  DTF_REQUIRE(splits == 1 || (epi->reduce && epi->out_f32),
+              "gemm: split-K needs an fp32 reduce epilogue");
+
+  CUtensorMap ta, tb;
+  {
+    uint64_t dims[2], str[1];
+    uint32_t box[2];
+    if (!a_mn) {  // memory [M, K]
+      dims[0] = K; dims[1] = M; box[0] = 64; box[1] = GEMM_BM;
+    } else {      // memory [K, M]
+      dims[0] = M; dims[1] = K; box[0] = 64; box[1] = 64;
+    }
+    str[0] = static_cast<uint64_t>(lda) * 2;
+    if (encode_tmap_bf16(&ta, A, 2, dims, str, box, 128) != 0) return -1;
+    if (!b_mn) {  // memory [N, K]
+      dims[0] = K; dims[1] = N; box[0] = 64; box[1] = BN;
+    } else {      // memory [K, N]
+      dims[0] = N; dims[1] = K; box[0] = 64; box[1] = 64;
+    }
+    str[0] = static_cast<uint64_t>(ldb) * 2;
+    if (encode_tmap_bf16(&tb, B, 2, dims, str, box, 128) != 0) return -1;
+  }
+
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.kb_per_split = ceil_div(num_kb, splits);
+  splits = ceil_div(num_kb, p.kb_per_split);
+  p.out = epi->out;
+  p.ldo = epi->ldo;
+  p.out_f32 = epi->out_f32;
+  {
+    const int pad = epi->out_f32 ? 1 : 8;
+    int ns = round_up(N, pad);
+    p.n_store = ns < epi->ldo ? ns : epi->ldo;
+  }
+  p.bias = epi->bias;
+  p.relu = epi->relu;
+  p.mask = reinterpret_cast<const __nv_bfloat16*>(epi->mask);
+  p.ldmask = epi->ldmask;
+  p.reduce = epi->reduce;
+  p.alpha = epi->alpha;
+
+#define DTF_DISPATCH(BN_, AM_, BM_) return launch_gemm<BN_, AM_, BM_>(ta, tb, p, splits, stream)
+  if (BN == 64) {
+    if (!a_mn && !b_mn) DTF_DISPATCH(64, false, false);
+    if (!a_mn && b_mn) DTF_DISPATCH(64, false, true);
+    if (a_mn && !b_mn) DTF_DISPATCH(64, true, false);
+    DTF_DISPATCH(64, true, true);
+  } else {
+    if (!a_mn && !b_mn) DTF_DISPATCH(128, false, false);
+    if (!a_mn && b_mn) DTF_DISPATCH(128, false, true);
+    if (a_mn && !b_mn) DTF_DISPATCH(128, true, false);
+    DTF_DISPATCH(128, true, true);
+  }
+#undef DTF_DISPATCH
+}

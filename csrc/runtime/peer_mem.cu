@@ -1,0 +1,111 @@
+// Peer-memory runtime: the data plane that replaces tf.train.Server's gRPC RecvTensor path
+// (run_mnist_distributed.py:96-98). A PS task allocates its shard arena with cudaMalloc, exports
+// a 64-byte CUDA IPC handle through the TCP control plane, and every worker maps it into its own
+// address space; from then on parameters and gradients move by loads/stores/atomics issued from
+// inside kernels over NVLink 5 / NVSwitch. Same-process shards (one process driving several
+// GPUs, or PS and worker colocated on one GPU) use the pointer directly after
+// cudaDeviceEnablePeerAccess.
+#include "../kernels/common.cuh"
+#include "../../include/dtf_b200.h"
+
+using namespace dtf;
+
+extern "C" int dtf_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+extern "C" int dtf_set_device(int device) {
+  DTF_CHECK_CUDA(cudaSetDevice(device));
+  return 0;
+}
+
+extern "C" int dtf_arena_alloc(void** ptr_out, size_t bytes) {
+  DTF_REQUIRE(ptr_out != nullptr && bytes > 0, "arena_alloc: bad arguments");
+  void* p = nullptr;
+  DTF_CHECK_CUDA(cudaMalloc(&p, bytes));
+  DTF_CHECK_CUDA(cudaMemset(p, 0, bytes));
+  DTF_CHECK_CUDA(cudaDeviceSynchronize());
+  *ptr_out = p;
+  return 0;
+}
+
+extern "C" int dtf_arena_free(void* ptr) {
+  if (ptr == nullptr) return 0;
+  DTF_CHECK_CUDA(cudaFree(ptr));
+  return 0;
+}
+
+extern "C" int dtf_ipc_export(void* ptr, unsigned char* handle_out) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == DTF_IPC_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  DTF_CHECK_CUDA(cudaIpcGetMemHandle(&h, ptr));
+  memcpy(handle_out, &h, sizeof(h));
+  return 0;
+}
+
+extern "C" int dtf_ipc_import(const unsigned char* handle, void** ptr_out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  void* p = nullptr;
+  DTF_CHECK_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  *ptr_out = p;
+  return 0;
+}
+
+extern "C" int dtf_ipc_close(void* ptr) {
+  if (ptr == nullptr) return 0;
+  DTF_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+
+extern "C" int dtf_can_access_peer(int device, int peer_device) {
+  int ok = 0;
+  if (cudaDeviceCanAccessPeer(&ok, device, peer_device) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return ok;
+}
+
+extern "C" int dtf_enable_peer_access(int peer_device) {
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    return 0;
+  }
+  DTF_CHECK_CUDA(e);
+  return 0;
+}
+
+extern "C" int dtf_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes, void* stream) {
+  DTF_CHECK_CUDA(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost,
+                                 reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int dtf_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes, void* stream) {
+  DTF_CHECK_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice,
+                                 reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int dtf_stream_sync(void* stream) {
+  DTF_CHECK_CUDA(cudaStreamSynchronize(reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int dtf_host_alloc_pinned(void** ptr_out, size_t bytes) {
+  DTF_CHECK_CUDA(cudaHostAlloc(ptr_out, bytes, cudaHostAllocDefault));
+  return 0;
+}
+
+extern "C" int dtf_host_free_pinned(void* ptr) {
+  if (ptr == nullptr) return 0;
+  DTF_CHECK_CUDA(cudaFreeHost(ptr));
+  return 0;
+}

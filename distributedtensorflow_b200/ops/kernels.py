@@ -1,0 +1,258 @@
+"""Torch-tensor front ends of the hand-written sm_100a kernels.
+
+Each function validates shapes/dtypes, then enqueues exactly one kernel of
+``libdtf_b200_cuda.so`` on the current CUDA stream. ``LAUNCHES`` counts those launches (bench.py
+reports it as ``gpu_launches``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib as L
+
+LAUNCHES = 0
+
+
+def _count(n: int = 1) -> None:
+    global LAUNCHES
+    LAUNCHES += n
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+# ------------------------------------------------------------------------------------------------
+# GEMM
+# ------------------------------------------------------------------------------------------------
+def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *,
+         a_mn: bool = False, b_mn: bool = False, bias: Optional[torch.Tensor] = None,
+         relu: bool = False, mask: Optional[torch.Tensor] = None, reduce: bool = False,
+         alpha: float = 1.0, splits: int = 1, block_n: int = 0,
+         a_ptr: Optional[int] = None, b_ptr: Optional[int] = None, lda: Optional[int] = None,
+         ldb: Optional[int] = None) -> None:
+    """out[M,N] = alpha * A @ B^T with the fused epilogue of ``dtf_gemm_bf16``.
+
+    ``a``/``b`` are 2-D bf16 tensors whose row pitch (stride(0)) is a multiple of 8; with
+    ``a_mn``/``b_mn`` they are stored transposed ([K,M] / [K,N]). ``a_ptr``/``b_ptr`` override
+    the base address (peer-mapped PS memory) while ``lda``/``ldb`` give its pitch.
+    """
+    assert out.dim() == 2 and out.stride(1) == 1
+    if a_ptr is None:
+        assert a.dtype == torch.bfloat16 and a.stride(1) == 1
+        a_ptr, lda = a.data_ptr(), a.stride(0)
+    if b_ptr is None:
+        assert b.dtype == torch.bfloat16 and b.stride(1) == 1
+        b_ptr, ldb = b.data_ptr(), b.stride(0)
+    epi = L.GemmEpilogue()
+    epi.out = out.data_ptr()
+    epi.ldo = out.stride(0)
+    epi.out_f32 = 1 if out.dtype == torch.float32 else 0
+    assert out.dtype in (torch.float32, torch.bfloat16)
+    epi.bias = _ptr(bias)
+    epi.relu = int(relu)
+    epi.mask = _ptr(mask)
+    epi.ldmask = mask.stride(0) if mask is not None else 0
+    epi.reduce = int(reduce)
+    epi.alpha = float(alpha)
+    rc = L.lib().dtf_gemm_bf16(a_ptr, lda, int(a_mn), b_ptr, ldb, int(b_mn), M, N, K,
+                               C.byref(epi), splits, block_n, L.current_stream())
+    L.check(rc, "dtf_gemm_bf16")
+    _count()
+
+
+# ------------------------------------------------------------------------------------------------
+# loss
+# ------------------------------------------------------------------------------------------------
+def softmax_xent_sparse(logits: torch.Tensor, labels: torch.Tensor, loss_accum: torch.Tensor,
+                        dlogits: torch.Tensor, dbias_accum: Optional[torch.Tensor] = None,
+                        num_classes: Optional[int] = None) -> None:
+    B = logits.shape[0]
+    Cn = num_classes or logits.shape[1]
+    assert logits.dtype == torch.float32 and labels.dtype == torch.int32
+    assert dlogits.dtype == torch.bfloat16
+    rc = L.lib().dtf_softmax_xent_sparse(logits.data_ptr(), logits.stride(0), labels.data_ptr(),
+                                         B, Cn, loss_accum.data_ptr(), dlogits.data_ptr(),
+                                         dlogits.stride(0), _ptr(dbias_accum), L.current_stream())
+    L.check(rc, "dtf_softmax_xent_sparse")
+    _count()
+
+
+def softmax_xent_dense(logits: torch.Tensor, labels: torch.Tensor, loss_accum: torch.Tensor,
+                       dlogits: torch.Tensor, dbias_accum: Optional[torch.Tensor] = None,
+                       num_classes: Optional[int] = None) -> None:
+    B = logits.shape[0]
+    Cn = num_classes or logits.shape[1]
+    assert logits.dtype == torch.float32 and labels.dtype == torch.float32
+    rc = L.lib().dtf_softmax_xent_dense(logits.data_ptr(), logits.stride(0), labels.data_ptr(),
+                                        labels.stride(0), B, Cn, loss_accum.data_ptr(),
+                                        dlogits.data_ptr(), dlogits.stride(0),
+                                        _ptr(dbias_accum), L.current_stream())
+    L.check(rc, "dtf_softmax_xent_dense")
+    _count()
+
+
+# ------------------------------------------------------------------------------------------------
+# push + apply, pull
+# ------------------------------------------------------------------------------------------------
+def make_apply_items(entries: Sequence[dict]) -> "C.Array":
+    arr = (L.ApplyItem * max(1, len(entries)))()
+    for i, e in enumerate(entries):
+        it = arr[i]
+        it.var = e["var"]
+        it.slot0 = e.get("slot0")
+        it.slot1 = e.get("slot1")
+        it.shadow = e.get("shadow")
+        it.grad = e["grad"]
+        it.n = e["n"]
+        it.first = e.get("first", 0)
+        it.cols = e.get("cols", 1)
+        it.shadow_ld = e.get("shadow_ld", e.get("cols", 1))
+    return arr
+
+
+def make_hyper(lr: float, beta1: float = 0.9, beta2: float = 0.999, epsilon: float = 1e-8,
+               momentum: float = 0.0, grad_scale: float = 1.0, use_nesterov: bool = False,
+               atomic_sgd: bool = False) -> L.ApplyHyper:
+    h = L.ApplyHyper()
+    h.lr, h.beta1, h.beta2, h.epsilon = lr, beta1, beta2, epsilon
+    h.momentum, h.grad_scale = momentum, grad_scale
+    h.use_nesterov, h.atomic_sgd = int(use_nesterov), int(atomic_sgd)
+    return h
+
+
+def push_apply(opt: int, items, n_items: int, hyper: L.ApplyHyper, ctrl_powers: Optional[int],
+               ctrl_step: Optional[int], finish: bool, worker_id: int,
+               step_out: Optional[int], block_counter: Optional[int]) -> None:
+    rc = L.lib().dtf_push_apply(opt, items, n_items, C.byref(hyper), ctrl_powers, ctrl_step,
+                                int(finish), worker_id, step_out, block_counter,
+                                L.current_stream())
+    L.check(rc, "dtf_push_apply")
+    _count()
+
+
+def pull_bulk(copies: Sequence[tuple], ctrl_step: Optional[int] = None,
+              pulled_step_out: Optional[int] = None) -> None:
+    """copies: (src_ptr, dst_ptr, nbytes) triples, nbytes % 16 == 0."""
+    n = len(copies)
+    for start in range(0, max(n, 1), L.MAX_COPY_ITEMS):
+        chunk = copies[start:start + L.MAX_COPY_ITEMS]
+        arr = (L.CopyItem * max(1, len(chunk)))()
+        for i, (s, d, b) in enumerate(chunk):
+            arr[i].src, arr[i].dst, arr[i].bytes = s, d, b
+        first = start == 0
+        if not chunk and not (first and pulled_step_out):
+            break
+        rc = L.lib().dtf_pull_bulk(arr, len(chunk), ctrl_step if first else None,
+                                   pulled_step_out if first else None, L.current_stream())
+        L.check(rc, "dtf_pull_bulk")
+        _count()
+
+
+def refresh_shadow(var_ptr: int, shadow_ptr: int, n: int, first: int, cols: int,
+                   shadow_ld: int) -> None:
+    rc = L.lib().dtf_refresh_shadow(var_ptr, shadow_ptr, n, first, cols, shadow_ld,
+                                    L.current_stream())
+    L.check(rc, "dtf_refresh_shadow")
+    _count()
+
+
+# ------------------------------------------------------------------------------------------------
+# elementwise helpers
+# ------------------------------------------------------------------------------------------------
+def u8_to_bf16(src: torch.Tensor, dst: torch.Tensor, scale: float = 1.0 / 255.0) -> None:
+    rows, cols = src.shape
+    rc = L.lib().dtf_u8_to_bf16(src.data_ptr(), dst.data_ptr(), rows, cols, dst.stride(0), scale,
+                                L.current_stream())
+    L.check(rc, "dtf_u8_to_bf16")
+    _count()
+
+
+def f32_to_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    rows, cols = src.shape
+    rc = L.lib().dtf_f32_to_bf16(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0),
+                                 rows, cols, L.current_stream())
+    L.check(rc, "dtf_f32_to_bf16")
+    _count()
+
+
+def colsum_bf16(x: torch.Tensor, rows: int, cols: int, out_accum: torch.Tensor) -> None:
+    rc = L.lib().dtf_colsum_bf16(x.data_ptr(), x.stride(0), rows, cols, out_accum.data_ptr(),
+                                 L.current_stream())
+    L.check(rc, "dtf_colsum_bf16")
+    _count()
+
+
+def fill_u32(t: torch.Tensor, value: int = 0) -> None:
+    nbytes = t.numel() * t.element_size()
+    assert nbytes % 4 == 0
+    rc = L.lib().dtf_fill_u32(t.data_ptr(), value, nbytes // 4, L.current_stream())
+    L.check(rc, "dtf_fill_u32")
+    _count()
+
+
+# ------------------------------------------------------------------------------------------------
+# CNN layers
+# ------------------------------------------------------------------------------------------------
+def conv1_fwd(x: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, pool1p: torch.Tensor,
+              amax1: torch.Tensor, scale: float) -> None:
+    B = x.shape[0]
+    u8 = x.dtype == torch.uint8
+    rc = L.lib().dtf_conv1_fwd(x.data_ptr() if u8 else None, None if u8 else x.data_ptr(), scale,
+                               w1.data_ptr(), b1.data_ptr(), pool1p.data_ptr(), amax1.data_ptr(),
+                               B, L.current_stream())
+    L.check(rc, "dtf_conv1_fwd")
+    _count()
+
+
+def conv1_bwd(x: torch.Tensor, dpool1: torch.Tensor, pool1p: torch.Tensor, amax1: torch.Tensor,
+              dw1_accum: torch.Tensor, db1_accum: torch.Tensor, scale: float) -> None:
+    B = x.shape[0]
+    u8 = x.dtype == torch.uint8
+    rc = L.lib().dtf_conv1_bwd(x.data_ptr() if u8 else None, None if u8 else x.data_ptr(), scale,
+                               dpool1.data_ptr(), pool1p.data_ptr(), amax1.data_ptr(),
+                               dw1_accum.data_ptr(), db1_accum.data_ptr(), B, L.current_stream())
+    L.check(rc, "dtf_conv1_bwd")
+    _count()
+
+
+def conv2_fwd(pool1p: torch.Tensor, w2_ptr: int, b2: torch.Tensor, pool2: torch.Tensor,
+              amax2: torch.Tensor) -> None:
+    B = pool1p.shape[0]
+    rc = L.lib().dtf_conv2_fwd(pool1p.data_ptr(), w2_ptr, b2.data_ptr(), pool2.data_ptr(),
+                               amax2.data_ptr(), B, L.current_stream())
+    L.check(rc, "dtf_conv2_fwd")
+    _count()
+
+
+def pool2_bwd(dpool2: torch.Tensor, pool2: torch.Tensor, amax2: torch.Tensor,
+              dconv2p: torch.Tensor, db2_accum: torch.Tensor) -> None:
+    B = pool2.shape[0]
+    rc = L.lib().dtf_pool2_bwd(dpool2.data_ptr(), dpool2.stride(0), pool2.data_ptr(),
+                               amax2.data_ptr(), dconv2p.data_ptr(), db2_accum.data_ptr(), B,
+                               L.current_stream())
+    L.check(rc, "dtf_pool2_bwd")
+    _count()
+
+
+def conv2_wgrad(pool1p: torch.Tensor, dconv2p: torch.Tensor, dw2_accum: torch.Tensor) -> None:
+    B = pool1p.shape[0]
+    rc = L.lib().dtf_conv2_wgrad(pool1p.data_ptr(), dconv2p.data_ptr(), dw2_accum.data_ptr(), B,
+                                 L.current_stream())
+    L.check(rc, "dtf_conv2_wgrad")
+    _count()
+
+
+def conv2_dgrad(dconv2p: torch.Tensor, w2_ptr: int, dpool1: torch.Tensor) -> None:
+    B = dconv2p.shape[0]
+    rc = L.lib().dtf_conv2_dgrad(dconv2p.data_ptr(), w2_ptr, dpool1.data_ptr(), B,
+                                 L.current_stream())
+    L.check(rc, "dtf_conv2_dgrad")
+    _count()

@@ -1,0 +1,203 @@
+/* C ABI of libdtf_b200_cuda.so — the hand-written sm_100a kernels and the peer-memory runtime of
+ * the B200-native parameter-server framework. Every entry point returns 0 on success and a
+ * negative value on failure (dtf_last_error() gives the reason). Pointers are device pointers
+ * unless stated; `stream` is a cudaStream_t passed as void*. Nothing here links against PyTorch;
+ * the Python package binds these with ctypes (distributedtensorflow_b200/ops/_lib.py).
+ *
+ * Reference citations are file:line under the upstream reference tree. */
+#ifndef DTF_B200_H_
+#define DTF_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dtf_last_error(void);
+int dtf_abi_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * PS shard control block. Lives at the start of every shard arena (peer-mapped into every
+ * worker). Replaces the TF resource-manager scalars: global_step
+ * (run_mnist_distributed.py:114), Adam's beta1_power/beta2_power (:116), the "variables
+ * initialised" readiness poll of MonitoredTrainingSession (:128-132) and SyncReplicasOptimizer's
+ * token queue (templates/00_mnist_replica.py:174-191).
+ * ------------------------------------------------------------------------------------------ */
+#define DTF_MAX_WORKERS 16
+#define DTF_MAX_SHARDS 8
+typedef struct dtf_ps_ctrl {
+  unsigned long long global_step;               /* +0   shared step counter (device atomics) */
+  float beta1_power;                            /* +8   */
+  float beta2_power;                            /* +12  */
+  unsigned int initialized;                     /* +16  chief sets 1 after init / restore */
+  unsigned int epoch;                           /* +20  sync mode: completed rounds */
+  unsigned int shutdown;                        /* +24  */
+  unsigned int apply_count;                     /* +28  applies seen by this shard */
+  unsigned long long heartbeat[DTF_MAX_WORKERS];/* +32  last global step each worker published */
+  unsigned int arrive[DTF_MAX_WORKERS];         /* +160 sync mode: worker w pushed round r */
+  unsigned int done[DTF_MAX_SHARDS];            /* +224 sync mode: shard s finished round r */
+} dtf_ps_ctrl;                                  /* 256 bytes */
+
+/* ------------------------------------------------------------------------------------------
+ * K1/K2/K3: tcgen05 GEMM  D[M,N] = A * B^T, bf16 in, fp32 accumulate in TMEM.
+ *   a_mn = 0: A is stored [M, K] (K contiguous), 1: stored [K, M] (M contiguous)
+ *   b_mn = 0: B is stored [N, K] (K contiguous), 1: stored [K, N] (N contiguous)
+ *   lda/ldb: row pitch in elements (multiple of 8).
+ * (MatMul / BiasAdd / Relu / ReluGrad of run_mnist_distributed.py:67-69 and
+ *  templates/00_mnist_replica.py:160-163, plus their autodiff.)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dtf_gemm_epilogue {
+  void* out;          /* [M, ldo] bf16 (out_f32 = 0) or fp32 (out_f32 = 1); may be peer memory */
+  int ldo;            /* row pitch of out in elements */
+  int out_f32;
+  const float* bias;  /* [N] or NULL: out = acc + bias */
+  int relu;           /* out = max(out, 0) */
+  const void* mask;   /* bf16 [M, ldmask] or NULL: out = (mask > 0) ? out : 0  (ReLU gradient) */
+  int ldmask;
+  int reduce;         /* 1: red.global.add.f32 into out (split-K / gradient accumulation) */
+  float alpha;        /* out = alpha * acc (applied first) */
+} dtf_gemm_epilogue;
+
+int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int b_mn, int M,
+                  int N, int K, const dtf_gemm_epilogue* epi, int splits, int block_n,
+                  void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K4/K5: softmax cross-entropy, loss and dlogits in one pass.
+ *   sparse: loss = mean_b(lse - logit[label])          (run_mnist_distributed.py:113)
+ *   dense : loss = -sum(y * log(clip(softmax,1e-10,1))) (templates/00_mnist_replica.py:163-164)
+ * loss_accum (fp32 scalar) and dbias_accum ([C] fp32, may be NULL) are ACCUMULATED with atomics:
+ * zero them before the call. dlogits is bf16 [B, ldd] (columns C..ldd-1 are written as 0).
+ * ------------------------------------------------------------------------------------------ */
+int dtf_softmax_xent_sparse(const float* logits, int ldl, const int* labels, int B, int C,
+                            float* loss_accum, void* dlogits, int ldd, float* dbias_accum,
+                            void* stream);
+int dtf_softmax_xent_dense(const float* logits, int ldl, const float* labels, int ldy, int B,
+                           int C, float* loss_accum, void* dlogits, int ldd, float* dbias_accum,
+                           void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K9/K10: gradient push fused with the owning shard's optimizer apply. One launch walks a list
+ * of (variable slice, gradient) pairs; var/slots/shadow may be peer (NVLink) pointers. The last
+ * CTA to finish performs the "_finish" step: beta powers, heartbeat and the global_step device
+ * atomic. use_locking=False semantics (Hogwild): concurrent workers interleave element-wise.
+ * TF1 formulas (python/training/{adam,adagrad,momentum,gradient_descent}.py via
+ * run_mnist_distributed.py:116, templates/00_between_graph_replication_async_mnist.py:34).
+ * ------------------------------------------------------------------------------------------ */
+enum { DTF_OPT_SGD = 0, DTF_OPT_MOMENTUM = 1, DTF_OPT_ADAGRAD = 2, DTF_OPT_ADAM = 3 };
+#define DTF_MAX_APPLY_ITEMS 24
+typedef struct dtf_apply_item {
+  float* var;          /* fp32 master slice on the owning shard */
+  float* slot0;        /* m / accum / momentum (NULL for SGD) */
+  float* slot1;        /* v (Adam only) */
+  void* shadow;        /* bf16 serving copy (row-padded), or NULL */
+  const float* grad;   /* local fp32 gradient slice */
+  long long n;         /* elements in this slice */
+  long long first;     /* flat index of the slice's first element inside the variable */
+  int cols;            /* variable's innermost dim (for the padded shadow layout) */
+  int shadow_ld;       /* shadow row pitch in elements */
+} dtf_apply_item;
+typedef struct dtf_apply_hyper {
+  float lr, beta1, beta2, epsilon, momentum, grad_scale;
+  int use_nesterov;
+  int atomic_sgd;      /* SGD only: red.global.add.f32 of -lr*g (exact under concurrency) */
+} dtf_apply_hyper;
+/* ctrl_for_powers: control block holding beta powers (shard of the first variable).
+ * ctrl_for_step: control block holding global_step. finish: 1 = bump global_step, update beta
+ * powers, heartbeat[worker_id]. step_out (device u64, local) receives the new global step.
+ * block_counter: a zero-initialised local u32 the kernel uses to elect the last CTA. */
+int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
+                   const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
+                   dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
+                   unsigned long long* step_out, unsigned int* block_counter, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K11: bulk parameter pull, peer -> local (one launch for a list of tensors). Reference: the
+ * per-tensor RecvTensor RPCs of every mon_sess.run (run_mnist_distributed.py:150,161).
+ * ------------------------------------------------------------------------------------------ */
+#define DTF_MAX_COPY_ITEMS 32
+typedef struct dtf_copy_item {
+  const void* src;
+  void* dst;
+  long long bytes;     /* multiple of 16 */
+} dtf_copy_item;
+int dtf_pull_bulk(const dtf_copy_item* items, int n_items, const dtf_ps_ctrl* ctrl_for_step,
+                  unsigned long long* pulled_step_out, void* stream);
+
+/* fp32 master -> bf16 row-padded serving copy (used at init / restore). */
+int dtf_refresh_shadow(const float* var, void* shadow, long long n, long long first, int cols,
+                       int shadow_ld, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K13 and small elementwise helpers.
+ * ------------------------------------------------------------------------------------------ */
+int dtf_u8_to_bf16(const unsigned char* src, void* dst, int rows, int cols, int ldd, float scale,
+                   void* stream);                                    /* dataset.py:92-100 */
+int dtf_f32_to_bf16(const float* src, int lds, void* dst, int ldd, int rows, int cols,
+                    void* stream);
+int dtf_colsum_bf16(const void* x, int ldx, int rows, int cols, float* out_accum, void* stream);
+int dtf_fill_u32(void* dst, unsigned int value, long long n_words, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K6/K7/K8: the reference CNN's conv / pool layers (run_mnist_distributed.py:52-65), NHWC.
+ * conv1 (Cin = 1) is a direct CUDA-core kernel fused with bias + ReLU + 2x2 max-pool; conv2
+ * (Cin = 32) is an implicit GEMM on tcgen05 fed by 4-D TMA boxes over a zero-padded NHWC
+ * activation, fused with bias + ReLU + pool in the TMEM epilogue.
+ * ------------------------------------------------------------------------------------------ */
+/* x: u8 [B,28,28] (scale applied) -> pool1p bf16 [B,18,18,32] interior (zero border kept by the
+ * caller), amax1 u8 [B,14,14,32] (argmax position 0..3). w1: fp32 [5,5,1,32], b1: fp32 [32]. */
+int dtf_conv1_fwd(const unsigned char* x_u8, const float* x_f32, float scale, const float* w1,
+                  const float* b1, void* pool1p, unsigned char* amax1, int B, void* stream);
+/* dpool1 bf16 [B,14,14,32] + amax1 + pooled output -> dW1 fp32 [25,32], db1 fp32 [32]
+ * (accumulated with atomics: zero first). */
+int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, float scale,
+                  const void* dpool1, const void* pool1p, const unsigned char* amax1,
+                  float* dw1_accum, float* db1_accum, int B, void* stream);
+/* conv2 forward: pool1p [B,18,18,32] (*) w2 bf16 [800,64] -> pool2 bf16 [B,7,7,64],
+ * amax2 u8 [B,7,7,64]. */
+int dtf_conv2_fwd(const void* pool1p, const void* w2, const float* b2, void* pool2,
+                  unsigned char* amax2, int B, void* stream);
+/* pool2 gradient + ReLU gradient: dpool2 bf16 [B,7,7,64] -> dconv2p bf16 [B,18,18,64] interior
+ * (zero border kept by the caller); db2 fp32 [64] accumulated. */
+int dtf_pool2_bwd(const void* dpool2, int ld_dpool2, const void* pool2,
+                  const unsigned char* amax2, void* dconv2p, float* db2_accum, int B,
+                  void* stream);
+/* conv2 weight gradient: dW2 fp32 [800,64] += im2col(pool1p)^T * dconv2 (split-K, atomics). */
+int dtf_conv2_wgrad(const void* pool1p, const void* dconv2p, float* dw2_accum, int B,
+                    void* stream);
+/* conv2 input gradient: dpool1 bf16 [B,14,14,32] = fullcorr(dconv2p, w2). */
+int dtf_conv2_dgrad(const void* dconv2p, const void* w2, void* dpool1, int B, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K12: synchronous round (SyncReplicasOptimizer, templates/00_mnist_replica.py:174-191):
+ * reduce-scatter of the workers' gradients fused with mean + optimizer apply on the owning
+ * shard, followed by an all-gather of the updated bf16 serving copy into every worker, all in
+ * ONE cooperative kernel per rank over NVLink peer memory (no NCCL).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dtf_sync_plan dtf_sync_plan; /* opaque, see csrc/kernels/sync_step.cu */
+
+/* ------------------------------------------------------------------------------------------
+ * Peer-memory runtime (replaces tf.train.Server's gRPC data plane, run_mnist_distributed.py:96).
+ * ------------------------------------------------------------------------------------------ */
+#define DTF_IPC_HANDLE_BYTES 64
+int dtf_arena_alloc(void** ptr_out, size_t bytes);            /* cudaMalloc + zero */
+int dtf_arena_free(void* ptr);
+int dtf_ipc_export(void* ptr, unsigned char* handle_out);     /* 64-byte cudaIpcMemHandle_t */
+int dtf_ipc_import(const unsigned char* handle, void** ptr_out);
+int dtf_ipc_close(void* ptr);
+int dtf_enable_peer_access(int peer_device);                  /* same-process multi-GPU */
+int dtf_can_access_peer(int device, int peer_device);
+int dtf_device_count(void);
+int dtf_set_device(int device);
+int dtf_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes, void* stream);
+int dtf_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes, void* stream);
+int dtf_stream_sync(void* stream);
+int dtf_host_alloc_pinned(void** ptr_out, size_t bytes);
+int dtf_host_free_pinned(void* ptr);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTF_B200_H_ */

@@ -1,0 +1,392 @@
+"""Numerics of every hand-written sm_100a kernel against a plain PyTorch fp32 reference of the
+same op. All tests need a B200 (``-m gpu``)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def K():
+    from distributedtensorflow_b200.ops import kernels
+    from distributedtensorflow_b200.ops import _lib
+    _lib.lib()  # fail loudly if the extension is missing on a GPU box
+    return kernels
+
+
+def _bf16(t):
+    return t.to(torch.bfloat16)
+
+
+def _rel_err(got, ref):
+    got, ref = got.float(), ref.float()
+    return (got - ref).abs().max().item() / max(ref.abs().max().item(), 1e-6)
+
+
+def _padded(rows, cols, dtype=torch.bfloat16, fill=None):
+    from distributedtensorflow_b200.ops.kernels import pad8
+    t = torch.zeros(rows, pad8(cols), dtype=dtype, device="cuda")
+    if fill is not None:
+        t[:, :cols] = fill.to(dtype)
+    return t
+
+
+# ------------------------------------------------------------------------------------------------
+# GEMM: all four operand layouts, ragged shapes, fused epilogues
+# ------------------------------------------------------------------------------------------------
+GEMM_SHAPES = [
+    (128, 128, 64), (128, 64, 128), (256, 256, 512), (100, 100, 784), (100, 10, 100),
+    (128, 1024, 3136), (128, 10, 1024), (784, 100, 100), (3136, 1024, 128), (384, 192, 200),
+]
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K_", GEMM_SHAPES)
+def test_gemm_layouts(K, M, N, K_, a_mn, b_mn):
+    torch.manual_seed(M * 7 + N * 3 + K_)
+    A = torch.randn(M, K_, device="cuda")
+    Bm = torch.randn(N, K_, device="cuda")
+    a_store = _padded(K_, M, fill=A.t()) if a_mn else _padded(M, K_, fill=A)
+    b_store = _padded(K_, N, fill=Bm.t()) if b_mn else _padded(N, K_, fill=Bm)
+    out = torch.full((M, N), float("nan"), device="cuda")
+    K.gemm(a_store, b_store, out, M, N, K_, a_mn=a_mn, b_mn=b_mn)
+    torch.cuda.synchronize()
+    ref = _bf16(A).float() @ _bf16(Bm).float().t()
+    err = _rel_err(out, ref)
+    assert err < 2e-3, f"rel err {err}"
+
+
+@pytest.mark.parametrize("block_n", [64, 128])
+def test_gemm_bias_relu_bf16_out(K, block_n):
+    torch.manual_seed(0)
+    M, N, K_ = 128, 200, 320
+    A = torch.randn(M, K_, device="cuda")
+    W = torch.randn(K_, N, device="cuda") * 0.1
+    bias = torch.randn(N, device="cuda")
+    a = _padded(M, K_, fill=A)
+    w = _padded(K_, N, fill=W)  # [K, N] row-major == MN-major B
+    out = torch.full((M, w.shape[1]), 7.0, dtype=torch.bfloat16, device="cuda")
+    K.gemm(a, w, out, M, N, K_, b_mn=True, bias=bias, relu=True, block_n=block_n)
+    torch.cuda.synchronize()
+    ref = torch.relu(_bf16(A).float() @ _bf16(W).float() + bias)
+    assert _rel_err(out[:, :N], ref) < 1e-2
+    assert (out[:, N:] == 0).all(), "row padding must be written as zeros"
+
+
+def test_gemm_relu_grad_mask(K):
+    torch.manual_seed(1)
+    M, N, K_ = 128, 104, 16
+    dY = torch.randn(M, K_, device="cuda")
+    W = torch.randn(N, K_, device="cuda")
+    act = torch.randn(M, N, device="cuda")
+    a = _padded(M, K_, fill=dY)
+    w = _padded(N, K_, fill=W)
+    mask = _padded(M, N, fill=torch.relu(act))
+    out = torch.zeros(M, mask.shape[1], dtype=torch.bfloat16, device="cuda")
+    K.gemm(a, w, out, M, N, K_, mask=mask)
+    torch.cuda.synchronize()
+    ref = (_bf16(dY).float() @ _bf16(W).float().t()) * (act > 0)
+    assert _rel_err(out[:, :N], ref) < 1e-2
+
+
+def test_gemm_split_k_reduce(K):
+    torch.manual_seed(2)
+    M, N, K_ = 256, 64, 4096
+    A = torch.randn(M, K_, device="cuda")
+    Bm = torch.randn(N, K_, device="cuda")
+    a, b = _padded(M, K_, fill=A), _padded(N, K_, fill=Bm)
+    out = torch.zeros(M, N, device="cuda")
+    K.gemm(a, b, out, M, N, K_, reduce=True, splits=8, alpha=0.5)
+    torch.cuda.synchronize()
+    ref = 0.5 * (_bf16(A).float() @ _bf16(Bm).float().t())
+    assert _rel_err(out, ref) < 2e-3
+
+
+# ------------------------------------------------------------------------------------------------
+# loss
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("B,Cn", [(128, 10), (100, 10), (37, 33)])
+def test_softmax_xent_sparse(K, B, Cn):
+    torch.manual_seed(3)
+    logits = torch.randn(B, Cn, device="cuda") * 3
+    labels = torch.randint(0, Cn, (B,), device="cuda", dtype=torch.int32)
+    loss = torch.zeros(1, device="cuda")
+    dl = _padded(B, Cn)
+    db = torch.zeros(Cn, device="cuda")
+    K.softmax_xent_sparse(logits, labels, loss, dl, db)
+    torch.cuda.synchronize()
+    lref = logits.clone().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(lref, labels.long())
+    ref.backward()
+    assert abs(loss.item() - ref.item()) < 1e-4 * max(1.0, abs(ref.item()))
+    assert (dl[:, :Cn].float() - lref.grad).abs().max().item() < 1e-2 / B + 1e-4
+    assert (db - lref.grad.sum(0)).abs().max().item() < 2e-2
+    assert (dl[:, Cn:] == 0).all()
+
+
+def test_softmax_xent_dense_clipped_sum(K):
+    torch.manual_seed(4)
+    B, Cn = 100, 10
+    logits = torch.randn(B, Cn, device="cuda") * 4
+    logits[0, 3] = 60.0  # forces probabilities below the 1e-10 clip for the other classes
+    labels = torch.nn.functional.one_hot(torch.randint(0, Cn, (B,), device="cuda"), Cn).float()
+    loss = torch.zeros(1, device="cuda")
+    dl = _padded(B, Cn)
+    K.softmax_xent_dense(logits, labels, loss, dl)
+    torch.cuda.synchronize()
+    lref = logits.clone().requires_grad_(True)
+    y = torch.softmax(lref, dim=1)
+    ref = -(labels * torch.log(torch.clamp(y, 1e-10, 1.0))).sum()
+    ref.backward()
+    assert abs(loss.item() - ref.item()) < 1e-3 * max(1.0, abs(ref.item()))
+    assert (dl[:, :Cn].float() - lref.grad).abs().max().item() < 2e-2
+
+
+# ------------------------------------------------------------------------------------------------
+# push + apply (TF1 update rules, fp64 restatement as oracle)
+# ------------------------------------------------------------------------------------------------
+def _apply_ref(opt, var, s0, s1, g, h, b1p, b2p):
+    var, s0, s1, g = (t.double() for t in (var, s0, s1, g))
+    if opt == "sgd":
+        var = var - h["lr"] * g
+    elif opt == "momentum":
+        s0 = s0 * h["momentum"] + g
+        var = var - h["lr"] * s0
+    elif opt == "adagrad":
+        s0 = s0 + g * g
+        var = var - h["lr"] * g / s0.sqrt()
+    else:
+        lr_t = h["lr"] * math.sqrt(1 - b2p) / (1 - b1p)
+        s0 = s0 + (g - s0) * (1 - h["beta1"])
+        s1 = s1 + (g * g - s1) * (1 - h["beta2"])
+        var = var - lr_t * s0 / (s1.sqrt() + h["epsilon"])
+    return var, s0, s1
+
+
+@pytest.mark.parametrize("opt", ["sgd", "momentum", "adagrad", "adam"])
+def test_push_apply_matches_tf1_rules(K, opt):
+    from distributedtensorflow_b200.ops import _lib as L
+    torch.manual_seed(5)
+    code = {"sgd": L.OPT_SGD, "momentum": L.OPT_MOMENTUM, "adagrad": L.OPT_ADAGRAD, "adam": L.OPT_ADAM}[opt]
+    shapes = [(3136, 1024), (1024,), (1024, 10), (10,), (5, 5, 1, 32), (4099,)]
+    h = dict(lr=0.01, beta1=0.9, beta2=0.999, epsilon=1e-8, momentum=0.9)
+    ctrl = torch.zeros(64, dtype=torch.int32, device="cuda")  # 256-byte control block
+    ctrl_f = ctrl.view(torch.float32)
+    b1p, b2p = 0.9 ** 3, 0.999 ** 3
+    ctrl_f[2], ctrl_f[3] = b1p, b2p
+    ctrl.view(torch.int64)[0] = 41
+    step_out = torch.zeros(1, dtype=torch.int64, device="cuda")
+    counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+    entries, refs, keep = [], [], []
+    for shp in shapes:
+        n = math.prod(shp)
+        cols = shp[-1]
+        ld = K.pad8(cols)
+        var = torch.randn(n, device="cuda")
+        s0 = torch.rand(n, device="cuda") * (0.1 if opt != "adagrad" else 1.0) + (0.1 if opt == "adagrad" else 0)
+        s1 = torch.rand(n, device="cuda") * 0.01
+        g = torch.randn(n, device="cuda")
+        shadow = torch.zeros(n // cols, ld, dtype=torch.bfloat16, device="cuda")
+        refs.append(_apply_ref(opt, var, s0, s1, g, h, b1p, b2p))
+        keep.append((var, s0, s1, g, shadow, cols))
+        entries.append(dict(var=var.data_ptr(), slot0=s0.data_ptr(), slot1=s1.data_ptr(),
+                            shadow=shadow.data_ptr(), grad=g.data_ptr(), n=n, first=0, cols=cols,
+                            shadow_ld=ld))
+    items = K.make_apply_items(entries)
+    hyper = K.make_hyper(h["lr"], h["beta1"], h["beta2"], h["epsilon"], h["momentum"])
+    K.push_apply(code, items, len(entries), hyper, ctrl.data_ptr(), ctrl.data_ptr(), True, 2,
+                 step_out.data_ptr(), counter.data_ptr())
+    torch.cuda.synchronize()
+    for (var, s0, s1, g, shadow, cols), (rv, r0, r1) in zip(keep, refs):
+        assert (var.double() - rv).abs().max().item() < 1e-5
+        if opt != "sgd":
+            assert (s0.double() - r0).abs().max().item() < 1e-5
+        if opt == "adam":
+            assert (s1.double() - r1).abs().max().item() < 1e-5
+        assert (shadow[:, :cols].reshape(-1).float() - var).abs().max().item() < 2e-2
+    assert ctrl.view(torch.int64)[0].item() == 42 and step_out.item() == 42
+    assert counter.item() == 0, "last-CTA election counter must wrap back to zero"
+    if opt == "adam":
+        assert abs(ctrl_f[2].item() - b1p * 0.9) < 1e-7 and abs(ctrl_f[3].item() - b2p * 0.999) < 1e-7
+    hb = ctrl.view(torch.int64)[4 + 2].item()
+    assert hb == 42
+
+
+def test_push_apply_atomic_sgd_is_exact_sum(K):
+    from distributedtensorflow_b200.ops import _lib as L
+    torch.manual_seed(6)
+    n = 100003
+    var = torch.zeros(n, device="cuda")
+    ctrl = torch.zeros(64, dtype=torch.int32, device="cuda")
+    counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+    grads = [torch.randn(n, device="cuda") for _ in range(4)]
+    hyper = K.make_hyper(0.5, atomic_sgd=True)
+    streams = [torch.cuda.Stream() for _ in grads]
+    torch.cuda.synchronize()
+    for g, s in zip(grads, streams):  # concurrent writers on different streams
+        with torch.cuda.stream(s):
+            items = K.make_apply_items([dict(var=var.data_ptr(), grad=g.data_ptr(), n=n, cols=1)])
+            K.push_apply(L.OPT_SGD, items, 1, hyper, None, ctrl.data_ptr(), False, 0, None,
+                         counter.data_ptr())
+    torch.cuda.synchronize()
+    ref = -0.5 * torch.stack(grads).double().sum(0)
+    assert (var.double() - ref).abs().max().item() < 1e-5
+
+
+def test_pull_bulk_and_refresh_shadow(K):
+    torch.manual_seed(7)
+    srcs = [torch.randn(n, device="cuda") for n in (4, 1024, 3136 * 1024, 12)]
+    dsts = [torch.zeros_like(s) for s in srcs]
+    ctrl = torch.zeros(64, dtype=torch.int32, device="cuda")
+    ctrl.view(torch.int64)[0] = 1234
+    pulled = torch.zeros(1, dtype=torch.int64, device="cuda")
+    K.pull_bulk([(s.data_ptr(), d.data_ptr(), s.numel() * 4) for s, d in zip(srcs, dsts)],
+                ctrl.data_ptr(), pulled.data_ptr())
+    torch.cuda.synchronize()
+    for s, d in zip(srcs, dsts):
+        assert torch.equal(s, d)
+    assert pulled.item() == 1234
+    var = torch.randn(1024 * 10, device="cuda")
+    shadow = torch.zeros(1024, 16, dtype=torch.bfloat16, device="cuda")
+    K.refresh_shadow(var.data_ptr(), shadow.data_ptr(), var.numel(), 0, 10, 16)
+    torch.cuda.synchronize()
+    assert torch.equal(shadow[:, :10], var.view(1024, 10).to(torch.bfloat16))
+
+
+def test_elementwise_helpers(K):
+    torch.manual_seed(8)
+    x = torch.randint(0, 256, (100, 784), dtype=torch.uint8, device="cuda")
+    dst = _padded(100, 784)
+    K.u8_to_bf16(x, dst)
+    f = torch.randn(33, 10, device="cuda")
+    fd = _padded(33, 10)
+    K.f32_to_bf16(f, fd)
+    m = _padded(300, 70, fill=torch.randn(300, 70, device="cuda"))
+    cs = torch.zeros(70, device="cuda")
+    K.colsum_bf16(m, 300, 70, cs)
+    z = torch.ones(1000, device="cuda")
+    K.fill_u32(z, 0)
+    torch.cuda.synchronize()
+    assert torch.equal(dst[:, :784], (x.float() * (1.0 / 255.0)).to(torch.bfloat16))
+    assert torch.equal(fd[:, :10], f.to(torch.bfloat16)) and (fd[:, 10:] == 0).all()
+    assert (cs - m[:, :70].float().sum(0)).abs().max().item() < 1e-3
+    assert (z == 0).all()
+
+
+# ------------------------------------------------------------------------------------------------
+# CNN layers (run_mnist_distributed.py:52-65)
+# ------------------------------------------------------------------------------------------------
+def _conv1_ref(x_u8, w1, b1):
+    x = (x_u8.float() / 255.0).view(-1, 1, 28, 28)
+    w = w1.view(5, 5, 1, 32).permute(3, 2, 0, 1).contiguous()
+    conv = torch.nn.functional.conv2d(x, w, b1, padding=2)
+    return x, w, conv
+
+
+@pytest.mark.parametrize("B", [128, 6])
+def test_conv1_fwd_bwd(K, B):
+    torch.manual_seed(9)
+    x_u8 = torch.randint(0, 256, (B, 28, 28), dtype=torch.uint8, device="cuda")
+    w1 = torch.randn(25, 32, device="cuda") * 0.2
+    b1 = torch.randn(32, device="cuda") * 0.1
+    pool1p = torch.zeros(B, 18, 18, 32, dtype=torch.bfloat16, device="cuda")
+    amax1 = torch.zeros(B, 14, 14, 32, dtype=torch.uint8, device="cuda")
+    K.conv1_fwd(x_u8, w1, b1, pool1p, amax1, 1.0 / 255.0)
+    torch.cuda.synchronize()
+    x, w, conv = _conv1_ref(x_u8, w1, b1)
+    w.requires_grad_(True)
+    b = b1.clone().requires_grad_(True)
+    conv = torch.nn.functional.conv2d(x, w, b, padding=2)
+    pooled = torch.nn.functional.max_pool2d(torch.relu(conv), 2)
+    got = pool1p[:, 2:16, 2:16, :].permute(0, 3, 1, 2).float()
+    assert (got - pooled).abs().max().item() < 2e-2 * max(1.0, pooled.abs().max().item())
+    assert (pool1p[:, :2] == 0).all() and (pool1p[:, :, 16:] == 0).all()
+    # backward: random upstream gradient
+    dpool1 = (torch.randn(B, 14, 14, 32, device="cuda") * 0.1).to(torch.bfloat16)
+    dw = torch.zeros(25, 32, device="cuda")
+    db = torch.zeros(32, device="cuda")
+    K.conv1_bwd(x_u8, dpool1, pool1p, amax1, dw, db, 1.0 / 255.0)
+    torch.cuda.synchronize()
+    pooled.backward(dpool1.float().permute(0, 3, 1, 2))
+    dw_ref = w.grad.permute(2, 3, 1, 0).reshape(25, 32)
+    assert _rel_err(dw, dw_ref) < 2e-2
+    assert _rel_err(db, b.grad) < 2e-2
+
+
+def _conv2_setup(B):
+    torch.manual_seed(10 + B)
+    a = torch.relu(torch.randn(B, 14, 14, 32, device="cuda"))
+    pool1p = torch.zeros(B, 18, 18, 32, dtype=torch.bfloat16, device="cuda")
+    pool1p[:, 2:16, 2:16, :] = a.to(torch.bfloat16)
+    w2 = (torch.randn(5, 5, 32, 64, device="cuda") * 0.05).to(torch.bfloat16)
+    b2 = torch.randn(64, device="cuda") * 0.1
+    return pool1p, w2, b2
+
+
+@pytest.mark.parametrize("B", [128, 4, 6])
+def test_conv2_fwd(K, B):
+    pool1p, w2, b2 = _conv2_setup(B)
+    pool2 = torch.zeros(B, 7, 7, 64, dtype=torch.bfloat16, device="cuda")
+    amax2 = torch.zeros(B, 7, 7, 64, dtype=torch.uint8, device="cuda")
+    K.conv2_fwd(pool1p, w2.data_ptr(), b2, pool2, amax2)
+    torch.cuda.synchronize()
+    x = pool1p[:, 2:16, 2:16, :].float().permute(0, 3, 1, 2)
+    w = w2.float().permute(3, 2, 0, 1)
+    conv = torch.nn.functional.conv2d(x, w, b2, padding=2)
+    pooled, idx = torch.nn.functional.max_pool2d(torch.relu(conv), 2, return_indices=True)
+    got = pool2.float().permute(0, 3, 1, 2)
+    err = (got - pooled).abs().max().item()
+    assert err < 2e-2 * max(1.0, pooled.abs().max().item()), f"abs err {err}"
+    # argmax agrees wherever the window has a unique, clearly separated maximum
+    convw = conv.view(B, 64, 7, 2, 7, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, 64, 7, 7, 4)
+    top2 = convw.topk(2, dim=-1).values
+    clear = (top2[..., 0] - top2[..., 1]) > 0.05
+    ref_am = convw.argmax(-1)
+    got_am = amax2.permute(0, 3, 1, 2).long()
+    assert (got_am[clear] == ref_am[clear]).all()
+
+
+@pytest.mark.parametrize("B", [128, 6])
+def test_conv2_backward(K, B):
+    pool1p, w2, b2 = _conv2_setup(B)
+    # upstream gradient w.r.t. the conv2 pre-activation, in the zero-bordered layout
+    dy = (torch.randn(B, 14, 14, 64, device="cuda") * 0.1).to(torch.bfloat16)
+    dconv2p = torch.zeros(B, 18, 18, 64, dtype=torch.bfloat16, device="cuda")
+    dconv2p[:, 2:16, 2:16, :] = dy
+    x = pool1p[:, 2:16, 2:16, :].float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    w = w2.float().permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    conv = torch.nn.functional.conv2d(x, w, None, padding=2)
+    conv.backward(dy.float().permute(0, 3, 1, 2))
+    dw = torch.zeros(800, 64, device="cuda")
+    K.conv2_wgrad(pool1p, dconv2p, dw)
+    dpool1 = torch.zeros(B, 14, 14, 32, dtype=torch.bfloat16, device="cuda")
+    K.conv2_dgrad(dconv2p, w2.data_ptr(), dpool1)
+    torch.cuda.synchronize()
+    dw_ref = w.grad.permute(2, 3, 1, 0).reshape(800, 64)
+    assert _rel_err(dw, dw_ref) < 1e-2, f"wgrad rel err {_rel_err(dw, dw_ref)}"
+    dx_ref = x.grad.permute(0, 2, 3, 1)
+    assert _rel_err(dpool1, dx_ref) < 2e-2, f"dgrad rel err {_rel_err(dpool1, dx_ref)}"
+
+
+def test_pool2_bwd(K):
+    torch.manual_seed(11)
+    B = 16
+    conv = torch.randn(B, 64, 14, 14, device="cuda", requires_grad=True)
+    pooled, idx = torch.nn.functional.max_pool2d(torch.relu(conv), 2, return_indices=True)
+    # our argmax encoding: position inside the 2x2 window
+    convw = conv.detach().view(B, 64, 7, 2, 7, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, 64, 7, 7, 4)
+    amax2 = convw.argmax(-1).permute(0, 2, 3, 1).contiguous().to(torch.uint8)
+    pool2 = pooled.detach().permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
+    d = (torch.randn(B, 7, 7, 64, device="cuda")).to(torch.bfloat16)
+    dpool2 = d.reshape(B, 3136).contiguous()
+    dconv2p = torch.zeros(B, 18, 18, 64, dtype=torch.bfloat16, device="cuda")
+    db2 = torch.zeros(64, device="cuda")
+    K.pool2_bwd(dpool2, pool2, amax2, dconv2p, db2)
+    torch.cuda.synchronize()
+    pooled.backward(d.float().permute(0, 3, 1, 2))
+    ref = conv.grad.permute(0, 2, 3, 1)
+    got = dconv2p[:, 2:16, 2:16, :].float()
+    assert (got - ref).abs().max().item() < 1e-2
+    assert (db2 - ref.sum((0, 1, 2))).abs().max().item() < 0.05
