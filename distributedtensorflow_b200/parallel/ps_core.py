@@ -1,0 +1,321 @@
+"""Host-side state machine of ONE parameter-server task (CPU backends).
+
+This is what lives behind ``server.join()`` in a ``--job_name ps`` process
+(run_mnist_distributed.py:100-103) when the cluster runs on CPUs: the variables (slices) placed
+on this task, their optimizer slots, Adam's beta powers, the shared ``global_step``, and — for
+synchronous training — the ``ConditionalAccumulator`` per variable and the token ``FIFOQueue`` of
+``SyncReplicasOptimizer`` (templates/00_mnist_replica.py:174-191). State survives worker exits and
+restarts; it is lost when the PS dies unless a checkpoint was written (TF1 semantics, T2).
+
+Concurrency: apply is intentionally unlocked (``use_locking=False`` Hogwild) unless the optimizer
+spec asks for locking; accumulators and queues are properly synchronised because their TF
+counterparts are.
+"""
+from __future__ import annotations
+
+import threading
+import time
+from collections import deque
+from typing import Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ..train.optimizers import Optimizer, OptimizerSpec
+
+_TORCH_DTYPES = {"float32": torch.float32, "int32": torch.int32, "int64": torch.int64}
+
+
+class AbortedError(RuntimeError):
+    """A PS/worker task went away (tf.errors.AbortedError / UnavailableError equivalent)."""
+
+
+class OutOfRangeError(RuntimeError):
+    """A closed queue was dequeued (tf.errors.OutOfRangeError)."""
+
+
+class ConditionalAccumulator:
+    """tf.ConditionalAccumulator: sums gradients whose ``local_step >= global_step`` (stale ones
+    are silently dropped); ``take_grad(n)`` blocks until ``n`` were applied, returns their MEAN,
+    resets the sum and advances the accumulator's global_step by one."""
+
+    def __init__(self, shape, dtype=torch.float32):
+        self._sum = torch.zeros(shape, dtype=dtype)
+        self._count = 0
+        self._global_step = 0
+        self._cv = threading.Condition()
+        self.dropped = 0
+
+    def apply_grad(self, grad: torch.Tensor, local_step: int) -> bool:
+        with self._cv:
+            if local_step < self._global_step:
+                self.dropped += 1
+                return False
+            self._sum.add_(grad.reshape(self._sum.shape))
+            self._count += 1
+            self._cv.notify_all()
+            return True
+
+    def take_grad(self, num_required: int, timeout: Optional[float] = None) -> torch.Tensor:
+        deadline = None if timeout is None else time.monotonic() + timeout
+        with self._cv:
+            while self._count < num_required:
+                remaining = None if deadline is None else deadline - time.monotonic()
+                if remaining is not None and remaining <= 0:
+                    raise TimeoutError("take_grad timed out")
+                self._cv.wait(remaining if remaining is not None else 1.0)
+            avg = self._sum / float(self._count)
+            self._sum.zero_()
+            self._count = 0
+            self._global_step += 1
+            return avg
+
+    def set_global_step(self, new_step: int) -> None:
+        with self._cv:
+            if new_step > self._global_step:
+                self._global_step = new_step
+
+    def num_accumulated(self) -> int:
+        with self._cv:
+            return self._count
+
+    @property
+    def global_step(self) -> int:
+        return self._global_step
+
+
+class FIFOQueue:
+    """Unbounded scalar FIFO with blocking dequeue (the ``sync_token_q``)."""
+
+    def __init__(self):
+        self._q = deque()
+        self._cv = threading.Condition()
+        self._closed = False
+
+    def enqueue_many(self, values: Iterable[int]) -> None:
+        with self._cv:
+            self._q.extend(values)
+            self._cv.notify_all()
+
+    def dequeue(self, timeout: Optional[float] = None) -> int:
+        deadline = None if timeout is None else time.monotonic() + timeout
+        with self._cv:
+            while not self._q:
+                if self._closed:
+                    raise OutOfRangeError("queue is closed and empty")
+                remaining = None if deadline is None else deadline - time.monotonic()
+                if remaining is not None and remaining <= 0:
+                    raise TimeoutError("dequeue timed out")
+                self._cv.wait(remaining if remaining is not None else 1.0)
+            return self._q.popleft()
+
+    def size(self) -> int:
+        with self._cv:
+            return len(self._q)
+
+    def close(self) -> None:
+        with self._cv:
+            self._closed = True
+            self._cv.notify_all()
+
+
+class PsShard:
+    """All state of PS task ``task_index``. Methods are the RPC surface."""
+
+    def __init__(self, task_index: int):
+        self.task_index = task_index
+        self.vars: Dict[str, torch.Tensor] = {}          # slice tensors (flat 1-D)
+        self.meta: Dict[str, dict] = {}                  # name -> {first, n, dtype}
+        self.slots: Dict[str, List[torch.Tensor]] = {}
+        self.slot_spec: Optional[OptimizerSpec] = None
+        self.powers: Dict[str, torch.Tensor] = {}
+        self.initialized = False
+        self.accumulators: Dict[str, ConditionalAccumulator] = {}
+        self.queues: Dict[str, FIFOQueue] = {}
+        self.heartbeats: Dict[int, Tuple[int, float]] = {}
+        self.apply_count = 0
+        self.shutdown_requested = threading.Event()
+        self._lock = threading.Lock()        # structure changes + locked applies
+        self._step_lock = threading.Lock()   # AssignAdd on global_step is atomic in TF too
+        self.incarnation = int(time.time() * 1e6)
+
+    # -- creation / init --------------------------------------------------------------------------
+    def create(self, defs: Sequence[dict], spec: Optional[dict]) -> bool:
+        """defs: [{name, first, n, dtype}] slices owned by this shard. Idempotent: re-creating an
+        existing variable keeps its value (PS state outlives workers)."""
+        with self._lock:
+            for d in defs:
+                name = d["name"]
+                if name not in self.vars:
+                    self.vars[name] = torch.zeros(int(d["n"]), dtype=_TORCH_DTYPES[d["dtype"]])
+                    self.meta[name] = dict(d)
+            if spec is not None:
+                ospec = _spec_from(spec)
+                self.slot_spec = ospec
+                for d in defs:
+                    name = d["name"]
+                    if not d.get("trainable", True) or d["dtype"] != "float32":
+                        continue
+                    if name not in self.slots or len(self.slots[name]) != ospec.num_slots:
+                        self.slots[name] = [
+                            torch.full((int(d["n"]),), ospec.slot_init(i), dtype=torch.float32)
+                            for i in range(ospec.num_slots)]
+                if ospec.kind == "adam" and spec.get("_owns_powers"):
+                    if "beta1_power" not in self.powers:
+                        self.powers["beta1_power"] = torch.tensor(ospec.beta1, dtype=torch.float32)
+                        self.powers["beta2_power"] = torch.tensor(ospec.beta2, dtype=torch.float32)
+        return True
+
+    def assign(self, name: str, value: np.ndarray) -> None:
+        t = self.vars[name]
+        with torch.no_grad():
+            t.copy_(torch.from_numpy(np.ascontiguousarray(value)).reshape(-1).to(t.dtype))
+
+    def assign_slot(self, name: str, slot: int, value: np.ndarray) -> None:
+        with torch.no_grad():
+            self.slots[name][slot].copy_(torch.from_numpy(np.ascontiguousarray(value)).reshape(-1))
+
+    def assign_power(self, name: str, value: float) -> None:
+        self.powers[name] = torch.tensor(float(value), dtype=torch.float32)
+
+    def reset_slots(self) -> None:
+        spec = self.slot_spec
+        if spec is None:
+            return
+        for name, sl in self.slots.items():
+            for i, s in enumerate(sl):
+                s.fill_(spec.slot_init(i))
+        if spec.kind == "adam" and self.powers:
+            self.powers["beta1_power"].fill_(spec.beta1)
+            self.powers["beta2_power"].fill_(spec.beta2)
+
+    def mark_initialized(self, value: bool = True) -> None:
+        self.initialized = value
+
+    def is_initialized(self, names: Optional[Sequence[str]] = None) -> bool:
+        if not self.initialized:
+            return False
+        return all(n in self.vars for n in (names or ()))
+
+    def uninitialized(self, names: Sequence[str]) -> List[str]:
+        """report_uninitialized_variables for the slices this shard should hold."""
+        if not self.initialized:
+            return list(names)
+        return [n for n in names if n not in self.vars]
+
+    # -- data plane ---------------------------------------------------------------------------------
+    def pull(self, names: Sequence[str]) -> List[np.ndarray]:
+        # Unlocked reads: a pull can observe a half-applied update, exactly like TF's PS.
+        return [self.vars[n].numpy().copy() for n in names]
+
+    def read_powers(self) -> Dict[str, float]:
+        return {k: float(v) for k, v in self.powers.items()}
+
+    def push_apply(self, spec: dict, grads: Dict[str, np.ndarray],
+                   powers: Optional[Dict[str, float]]) -> None:
+        ospec = _spec_from(spec)
+        pw = None
+        if ospec.kind == "adam":
+            pw = powers if powers is not None else self.powers
+        ctx = self._lock if ospec.use_locking else _NullCtx()
+        with ctx:
+            for name, g in grads.items():
+                gt = torch.from_numpy(np.ascontiguousarray(g)).reshape(-1)
+                Optimizer.apply_dense(ospec, self.vars[name], gt, self.slots.get(name, ()), pw)
+        self.apply_count += 1
+
+    def finish(self, spec: dict) -> None:
+        ospec = _spec_from(spec)
+        if self.powers:
+            Optimizer.finish(ospec, self.powers)
+
+    def step_add(self, name: str, delta: int = 1) -> int:
+        with self._step_lock:
+            t = self.vars[name]
+            t.add_(delta)
+            return int(t.item())
+
+    def read_scalar(self, name: str) -> int:
+        return int(self.vars[name].item())
+
+    def heartbeat(self, worker: int, step: int) -> None:
+        self.heartbeats[worker] = (step, time.time())
+
+    # -- sync-replicas objects --------------------------------------------------------------------
+    def accum_create(self, names_shapes: Sequence[Tuple[str, int]]) -> None:
+        with self._lock:
+            for name, n in names_shapes:
+                if name not in self.accumulators:
+                    self.accumulators[name] = ConditionalAccumulator((int(n),))
+
+    def accum_apply(self, grads: Dict[str, np.ndarray], local_step: int) -> int:
+        ok = 0
+        for name, g in grads.items():
+            ok += bool(self.accumulators[name].apply_grad(torch.from_numpy(np.ascontiguousarray(g)), local_step))
+        return ok
+
+    def accum_take(self, names: Sequence[str], num_required: int,
+                   timeout: Optional[float] = None) -> List[np.ndarray]:
+        return [self.accumulators[n].take_grad(num_required, timeout).numpy() for n in names]
+
+    def accum_take_apply(self, names: Sequence[str], num_required: int, spec: dict,
+                         powers: Optional[Dict[str, float]], timeout: Optional[float] = None) -> int:
+        """The chief's sync_op as it executes ON this PS: block until ``num_required`` fresh
+        gradients were accumulated for every listed variable, apply their mean once."""
+        grads = {n: self.accumulators[n].take_grad(num_required, timeout).numpy() for n in names}
+        self.push_apply(spec, grads, powers)
+        return len(grads)
+
+    def accum_set_global_step(self, step: int) -> None:
+        for a in self.accumulators.values():
+            a.set_global_step(step)
+
+    def accum_stats(self) -> Dict[str, Tuple[int, int, int]]:
+        return {n: (a.num_accumulated(), a.global_step, a.dropped) for n, a in self.accumulators.items()}
+
+    def queue_create(self, name: str) -> None:
+        with self._lock:
+            self.queues.setdefault(name, FIFOQueue())
+
+    def queue_enqueue_many(self, name: str, values: Sequence[int]) -> None:
+        self.queues[name].enqueue_many(values)
+
+    def queue_dequeue(self, name: str, timeout: Optional[float] = None) -> int:
+        return self.queues[name].dequeue(timeout)
+
+    def queue_size(self, name: str) -> int:
+        return self.queues[name].size()
+
+    def queue_close(self, name: str) -> None:
+        if name in self.queues:
+            self.queues[name].close()
+
+    # -- checkpoint support ---------------------------------------------------------------------------
+    def snapshot(self) -> Dict[str, np.ndarray]:
+        """Every tensor this shard would write into its checkpoint data shard."""
+        out = {n: t.numpy().copy() for n, t in self.vars.items()}
+        spec = self.slot_spec
+        if spec is not None:
+            for n, sl in self.slots.items():
+                for sname, s in zip(spec.slot_names(), sl):
+                    out[f"{n}/{sname}"] = s.numpy().copy()
+        for k, v in self.powers.items():
+            out[k] = np.asarray(float(v), np.float32)
+        return out
+
+    def request_shutdown(self) -> None:
+        self.shutdown_requested.set()
+        for q in self.queues.values():
+            q.close()
+
+
+def _spec_from(d: dict) -> OptimizerSpec:
+    return OptimizerSpec(**{k: v for k, v in d.items() if not k.startswith("_")})
+
+
+class _NullCtx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
