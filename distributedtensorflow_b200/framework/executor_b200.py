@@ -1,0 +1,681 @@
+"""B200 executor: compiles the reference's model graphs into the hand-written sm_100a kernels and
+replays one CUDA graph per training step.
+
+What ``mon_sess.run(train_op)`` costs in the reference: a Python -> gRPC RunStep,
+graph partitions on worker and PS, 8 RecvTensor RPCs down and 8 up through host memory, CPU conv /
+matmul, ApplyAdam on the PS. Here the same step is ONE graph launch on the worker's GPU:
+
+    H2D(batch) -> clear scratch -> [pull_bulk from remote shards] -> forward (tcgen05 GEMMs /
+    implicit-GEMM conv, first layer reading its weights straight from the PS arena) -> fused
+    softmax-xent fwd+bwd -> backward GEMMs -> push+apply on the owning shards (+ global_step
+    atomic) -> D2H(loss, step)
+
+The graph is pattern-compiled from the TF1-style IR (framework/graph.py). Supported families:
+dense stacks (the MLP of templates/00_mnist_replica.py:138-164 with its clipped-sum loss, the wide
+MLP) and the CNN of run_mnist_distributed.py:46-70 with the mean sparse softmax loss. Anything
+else raises and can run with ``ConfigProto(backend="cpu")``.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ..ops import _lib as L
+from ..ops import kernels as K
+from ..parallel.nvl import NvlStore, SliceRegion, pad8
+from . import graph as G
+
+
+# ------------------------------------------------------------------------------------------------
+# graph -> plan
+# ------------------------------------------------------------------------------------------------
+@dataclass
+class DenseLayer:
+    w: G.Variable
+    b: Optional[G.Variable]
+    relu: bool
+    out_node: G.Tensor
+
+
+@dataclass
+class ConvLayer:
+    k: G.Variable
+    b: Optional[G.Variable]
+    relu: bool
+    padding: str
+
+
+@dataclass
+class Plan:
+    kind: str                       # "mlp" | "cnn"
+    input_node: G.Tensor
+    labels_node: G.Tensor
+    logits_node: G.Tensor
+    loss_node: G.Tensor
+    loss_kind: str                  # "sparse_mean" | "dense_clipped_sum"
+    dense: List[DenseLayer]
+    convs: List[ConvLayer]
+    in_features: int
+    num_classes: int
+
+
+class UnsupportedGraphError(NotImplementedError):
+    pass
+
+
+def _is_input(n: G.Tensor) -> bool:
+    return n.op in ("Placeholder", "IteratorGetNext")
+
+
+def parse_loss(loss: G.Tensor) -> Tuple[str, G.Tensor, G.Tensor]:
+    if loss.op == "Mean" and loss.attrs.get("axis") is None and loss.inputs[0].op == "SparseSoftmaxXent":
+        x = loss.inputs[0]
+        return "sparse_mean", x.inputs[0], x.inputs[1]
+    if loss.op == "Neg" and loss.inputs[0].op == "Sum" and loss.inputs[0].attrs.get("axis") is None:
+        mul = loss.inputs[0].inputs[0]
+        if mul.op == "Mul":
+            for a, b in ((mul.inputs[0], mul.inputs[1]), (mul.inputs[1], mul.inputs[0])):
+                if a.op == "Log" and a.inputs[0].op == "ClipByValue":
+                    clip = a.inputs[0]
+                    if (clip.inputs[0].op == "Softmax" and abs(clip.attrs["min"] - 1e-10) < 1e-16
+                            and clip.attrs["max"] == 1.0 and _is_input(b)):
+                        return "dense_clipped_sum", clip.inputs[0].inputs[0], b
+    raise UnsupportedGraphError("loss expression is not one of the B200-compiled forms "
+                                "(mean sparse softmax xent / clipped sum dense xent)")
+
+
+def parse_plan(loss: G.Tensor) -> Plan:
+    loss_kind, logits, labels = parse_loss(loss)
+    layers: List[Any] = []
+    node = logits
+    while True:
+        if _is_input(node):
+            input_node = node
+            break
+        if node.op == "Reshape":
+            layers.append(("reshape", node.attrs["shape"]))
+            node = node.inputs[0]
+            continue
+        if node.op == "MaxPool":
+            if node.attrs["pool_size"] != (2, 2) or node.attrs["strides"] != (2, 2):
+                raise UnsupportedGraphError("only 2x2/2 max-pool is compiled for B200")
+            layers.append(("pool",))
+            node = node.inputs[0]
+            continue
+        out_node = node
+        relu = False
+        if node.op == "Relu":
+            relu, node = True, node.inputs[0]
+        bias = None
+        if node.op == "BiasAdd":
+            bias, node = node.inputs[1], node.inputs[0]
+        if node.op == "MatMul":
+            layers.append(DenseLayer(node.inputs[1], bias, relu, out_node))
+            node = node.inputs[0]
+        elif node.op == "Conv2D":
+            layers.append(ConvLayer(node.inputs[1], bias, relu, node.attrs["padding"]))
+            node = node.inputs[0]
+        else:
+            raise UnsupportedGraphError(f"op {node.op} ({node.name}) is not compiled for B200")
+    layers.reverse()
+    seq = [l for l in layers if not (isinstance(l, tuple) and l[0] == "reshape")]
+    dense = [l for l in seq if isinstance(l, DenseLayer)]
+    convs = [l for l in seq if isinstance(l, ConvLayer)]
+    for l in dense + convs:
+        if not isinstance(l.w if isinstance(l, DenseLayer) else l.k, G.Variable):
+            raise UnsupportedGraphError("layer weights must be Variables")
+    if not dense or dense[-1].relu:
+        raise UnsupportedGraphError("the graph must end in a linear (logits) dense layer")
+    if convs:
+        kinds = ["conv" if isinstance(l, ConvLayer) else "pool" if isinstance(l, tuple) else "dense" for l in seq]
+        ok = (kinds[:4] == ["conv", "pool", "conv", "pool"] and all(k == "dense" for k in kinds[4:])
+              and tuple(convs[0].k.shape) == (5, 5, 1, 32) and tuple(convs[1].k.shape) == (5, 5, 32, 64)
+              and all(c.relu and c.padding == "SAME" and c.b is not None for c in convs)
+              and dense[0].w.shape[0] == 3136)
+        if not ok:
+            raise UnsupportedGraphError("only the reference CNN topology (conv5x5x32-pool-conv5x5x64-"
+                                        "pool-dense...) is compiled for B200")
+        kind, in_features = "cnn", 784
+    else:
+        if any(isinstance(l, tuple) for l in seq):
+            raise UnsupportedGraphError("pooling without convolutions is not compiled for B200")
+        kind, in_features = "mlp", int(dense[0].w.shape[0])
+    for a, b in zip(dense[:-1], dense[1:]):
+        if a.w.shape[1] != b.w.shape[0] or not a.relu:
+            raise UnsupportedGraphError("hidden dense layers must chain and use ReLU")
+    return Plan(kind, input_node, labels, logits, loss, loss_kind, dense, convs, in_features,
+                int(dense[-1].w.shape[1]))
+
+
+# ------------------------------------------------------------------------------------------------
+# per-batch-size device state
+# ------------------------------------------------------------------------------------------------
+class _Zero:
+    """One contiguous fp32 region holding every atomically accumulated buffer of a step, cleared
+    by a single fill kernel."""
+
+    def __init__(self):
+        self.sizes: List[Tuple[str, int]] = []
+
+    def add(self, name: str, n: int) -> None:
+        self.sizes.append((name, (n + 63) // 64 * 64))
+
+    def build(self, device) -> Dict[str, torch.Tensor]:
+        total = sum(n for _, n in self.sizes)
+        self.buf = torch.zeros(max(total, 64), dtype=torch.float32, device=device)
+        out, o = {}, 0
+        for name, n in self.sizes:
+            out[name] = self.buf[o:o + n]
+            o += n
+        return out
+
+
+class StepState:
+    def __init__(self, runner: "B200StepRunner", B: int, train: bool, x_dtype, y_dtype):
+        self.B, self.train = B, train
+        p, dev = runner.plan, runner.device
+        bf, f32 = torch.bfloat16, torch.float32
+        self.x_pin = torch.zeros((B, p.in_features), dtype=x_dtype).pin_memory()
+        ysh = (B,) if p.loss_kind == "sparse_mean" else (B, p.num_classes)
+        self.y_pin = torch.zeros(ysh, dtype=y_dtype).pin_memory()
+        self.x_dev = torch.zeros((B, p.in_features), dtype=x_dtype, device=dev)
+        self.y_dev = torch.zeros(ysh, dtype=y_dtype, device=dev)
+        self.out_pin = torch.zeros(4, dtype=torch.float32).pin_memory()      # loss
+        self.step_pin = torch.zeros(2, dtype=torch.int64).pin_memory()       # global_step, pulled
+        self.step_dev = torch.zeros(2, dtype=torch.int64, device=dev)
+        self.counter = torch.zeros(4, dtype=torch.int32, device=dev)
+        dims = [int(d.w.shape[0]) for d in p.dense] + [p.num_classes]
+        self.dims = dims
+        nl = len(p.dense)
+        # activations: act[i] is the input of dense layer i (act[0] = network / conv output)
+        self.act = [torch.zeros((B, pad8(dims[i])), dtype=bf, device=dev) for i in range(nl)]
+        self.logits = torch.zeros((B, p.num_classes), dtype=f32, device=dev)
+        zero = _Zero()
+        zero.add("loss", 1)
+        if train:
+            self.dlogits = torch.zeros((B, pad8(p.num_classes)), dtype=bf, device=dev)
+            self.dact = [None] + [torch.zeros((B, pad8(dims[i])), dtype=bf, device=dev) for i in range(1, nl)]
+            self.gw = [torch.zeros((dims[i], dims[i + 1]), dtype=f32, device=dev) for i in range(nl)]
+            for i in range(nl):
+                zero.add(f"gb{i}", dims[i + 1])
+        if p.kind == "cnn":
+            self.pool1p = torch.zeros((B, 18, 18, 32), dtype=bf, device=dev)
+            self.amax1 = torch.zeros((B, 14, 14, 32), dtype=torch.uint8, device=dev)
+            self.amax2 = torch.zeros((B, 7, 7, 64), dtype=torch.uint8, device=dev)
+            if train:
+                self.dpool2 = torch.zeros((B, 3136), dtype=bf, device=dev)
+                self.dconv2p = torch.zeros((B, 18, 18, 64), dtype=bf, device=dev)
+                self.dpool1 = torch.zeros((B, 14, 14, 32), dtype=bf, device=dev)
+                zero.add("gk1", 25 * 32)
+                zero.add("gkb1", 32)
+                zero.add("gk2", 800 * 64)
+                zero.add("gkb2", 64)
+        self.z = zero.build(dev)
+        self.zero = zero
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.launches_per_step = 0
+
+
+# ------------------------------------------------------------------------------------------------
+# the runner
+# ------------------------------------------------------------------------------------------------
+class B200StepRunner:
+    def __init__(self, graph: G.Graph, client, layout, worker_id: int, config, cluster=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("backend 'b200' needs a CUDA device")
+        L.lib()  # fail loudly when the extension is missing
+        self.graph, self.client, self.layout = graph, client, layout
+        self.worker_id, self.config, self.cluster = worker_id, config, cluster
+        opts = getattr(config, "b200_options", {}) or {}
+        self.use_cuda_graph = bool(opts.get("cuda_graph", True))
+        self.fused_first_pull = bool(opts.get("fused_first_pull", True))
+        self.atomic_sgd = bool(opts.get("atomic_sgd", False))
+        self.device = torch.device(self._pick_device())
+        torch.cuda.set_device(self.device)
+        self.store: Optional[NvlStore] = None
+        self.plan: Optional[Plan] = None
+        self.spec = None
+        self.train_op = None
+        self.states: Dict[Tuple[int, bool], StepState] = {}
+        self.local: Dict[str, torch.Tensor] = {}     # pulled copies of remote tensors
+        self.stream = torch.cuda.Stream(device=self.device)
+
+    def _pick_device(self) -> str:
+        if getattr(self.config, "device", None):
+            return self.config.device
+        if self.cluster is not None and "worker" in self.cluster.jobs:
+            try:
+                d = self.cluster.parsed_address("worker", self.worker_id).device
+                if d and d.startswith("cuda"):
+                    return d
+            except Exception:
+                pass
+        return "cuda:%d" % torch.cuda.current_device()
+
+    def _shard_devices(self) -> List[Optional[int]]:
+        out: List[Optional[int]] = []
+        for s in range(self.client.num_shards):
+            dev = None
+            if self.cluster is not None and "ps" in self.cluster.jobs:
+                try:
+                    d = self.cluster.parsed_address("ps", s).device
+                    if d and d.startswith("cuda:"):
+                        dev = int(d.split(":")[1])
+                except Exception:
+                    dev = None
+            out.append(dev)
+        return out
+
+    # -- variable lifecycle (called by Session) ---------------------------------------------------
+    def create_variables(self, spec, trainable_names: Sequence[str]) -> None:
+        self.spec = spec
+        self.trainable_names = list(trainable_names)
+        self.store = NvlStore(self.client, self.layout, spec, trainable_names, self.device.index or 0,
+                              self._shard_devices())
+
+    def init_variables(self, values: Dict[str, np.ndarray]) -> None:
+        st = self.store
+        for name, arr in values.items():
+            if name in st.arena.regions:
+                st.write_variable(name, arr)
+        if self.spec is not None:
+            for name in self.trainable_names:
+                for i in range(self.spec.num_slots):
+                    st.write_slot(name, i, self.spec.slot_init(i))
+        step0 = int(values[st.arena.step_var]) if st.arena.step_var in values else 0
+        for s in range(st.num_shards):
+            b1 = self.spec.beta1 if (self.spec is not None and self.spec.kind == "adam") else 0.0
+            b2 = self.spec.beta2 if (self.spec is not None and self.spec.kind == "adam") else 0.0
+            st.write_ctrl(s, global_step=step0 if s == st.arena.step_shard else 0, beta1_power=b1,
+                          beta2_power=b2, initialized=1)
+        self.client.mark_initialized(True)
+
+    def uninitialized_variables(self) -> List[str]:
+        return self.client.uninitialized_variables(self.layout)
+
+    def snapshot_shards(self) -> List[Dict[str, np.ndarray]]:
+        st = self.store
+        shards: List[Dict[str, np.ndarray]] = [dict() for _ in range(st.num_shards)]
+        slot_names = self.spec.slot_names() if self.spec is not None else []
+        for name, regs in st.arena.regions.items():
+            for r in regs:
+                shards[r.shard][name] = st._d2h(st.var_ptr(r), r.sl.n * 4, np.float32)
+                for i, sn in enumerate(slot_names):
+                    if i < len(r.slot_off):
+                        shards[r.shard][f"{name}/{sn}"] = st._d2h(st.slot_ptr(r, i), r.sl.n * 4, np.float32)
+        if st.arena.step_var:
+            vl = self.layout[st.arena.step_var]
+            npdt = np.int64 if vl.dtype == "int64" else np.int32
+            shards[st.arena.step_shard][st.arena.step_var] = np.asarray([st.read_global_step()], npdt)
+        if self.spec is not None and self.spec.kind == "adam":
+            c = st.read_ctrl(st.arena.powers_shard)
+            shards[st.arena.powers_shard]["beta1_power"] = np.asarray(c["beta1_power"], np.float32)
+            shards[st.arena.powers_shard]["beta2_power"] = np.asarray(c["beta2_power"], np.float32)
+        return shards
+
+    def restore_tensors(self, tensors: Dict[str, np.ndarray], var_names, slot_names: Sequence[str]) -> None:
+        st = self.store
+        missing = [n for n in var_names if n in st.arena.regions and n not in tensors]
+        if missing:
+            raise KeyError("Tensors not found in checkpoint: %s" % missing)
+        for name in st.arena.regions:
+            if name in tensors:
+                st.write_variable(name, tensors[name])
+            for i, sn in enumerate(slot_names):
+                key = f"{name}/{sn}"
+                if key in tensors:
+                    st.write_slot(name, i, tensors[key])
+        step = int(np.asarray(tensors.get(st.arena.step_var, 0)).reshape(-1)[0]) if st.arena.step_var else 0
+        adam = self.spec is not None and self.spec.kind == "adam"
+        for s in range(st.num_shards):
+            b1 = float(tensors.get("beta1_power", self.spec.beta1 if adam else 0.0)) if adam else 0.0
+            b2 = float(tensors.get("beta2_power", self.spec.beta2 if adam else 0.0)) if adam else 0.0
+            st.write_ctrl(s, global_step=step if s == st.arena.step_shard else 0, beta1_power=b1,
+                          beta2_power=b2, initialized=1)
+        self.client.mark_initialized(True)
+
+    # -- parameter access ---------------------------------------------------------------------------
+    def _regions(self, var: G.Variable) -> List[SliceRegion]:
+        return self.store.arena.regions[var.name]
+
+    def _single_local(self, var: G.Variable) -> Optional[SliceRegion]:
+        regs = self._regions(var)
+        if len(regs) == 1 and self.store.is_local[regs[0].shard]:
+            return regs[0]
+        return None
+
+    def _setup_params(self) -> None:
+        """Decide, per tensor the kernels read, whether to alias the arena (local shard), read it
+        in place over NVLink (fused pull) or copy it with pull_bulk. Builds ``self.copies``."""
+        st, p = self.store, self.plan
+        self.copies: List[Tuple[int, int, int]] = []
+        self.wptr: Dict[str, Tuple[int, int]] = {}    # bf16 serving copy: name -> (ptr, ld)
+        self.fptr: Dict[str, int] = {}                # fp32 tensor: name -> ptr
+
+        def want_shadow(var: G.Variable, allow_in_place: bool) -> None:
+            regs = self._regions(var)
+            ld = regs[0].shadow_ld
+            if len(regs) == 1 and (st.is_local[regs[0].shard] or (allow_in_place and self.fused_first_pull)):
+                self.wptr[var.name] = (st.shadow_ptr(regs[0]), ld)
+                return
+            rows = sum(r.rows for r in regs)
+            buf = torch.zeros((rows, ld), dtype=torch.bfloat16, device=self.device)
+            self.local["w:" + var.name] = buf
+            row = 0
+            for r in regs:
+                self.copies.append((st.shadow_ptr(r), buf.data_ptr() + row * ld * 2, r.rows * ld * 2))
+                row += r.rows
+            self.wptr[var.name] = (buf.data_ptr(), ld)
+
+        def want_f32(var: G.Variable, allow_in_place: bool) -> None:
+            regs = self._regions(var)
+            if len(regs) == 1 and (st.is_local[regs[0].shard] or allow_in_place):
+                self.fptr[var.name] = st.var_ptr(regs[0])
+                return
+            n = self.layout[var.name].num_elements
+            buf = torch.zeros(((n + 63) // 64 * 64,), dtype=torch.float32, device=self.device)
+            self.local["f:" + var.name] = buf
+            for r in regs:
+                nbytes = (r.sl.n * 4 + 15) // 16 * 16
+                self.copies.append((st.var_ptr(r), buf.data_ptr() + r.sl.first * 4, nbytes))
+            self.fptr[var.name] = buf.data_ptr()
+
+        if p.kind == "cnn":
+            want_f32(p.convs[0].k, True)       # conv1 reads w1/b1 in place (3.3 KB)
+            want_f32(p.convs[0].b, True)
+            want_shadow(p.convs[1].k, False)   # w2 is read by fwd AND dgrad: needs one snapshot
+            want_f32(p.convs[1].b, False)
+        for i, d in enumerate(p.dense):
+            # first GEMM layer of an MLP: weights are used by the forward only -> fused pull
+            want_shadow(d.w, allow_in_place=(p.kind == "mlp" and i == 0))
+            if d.b is not None:
+                want_f32(d.b, False)
+
+    # -- kernels of one step ------------------------------------------------------------------------
+    def _forward(self, s: StepState) -> None:
+        p = self.plan
+        if p.kind == "cnn":
+            scale = 1.0 / 255.0 if s.x_dev.dtype == torch.uint8 else 1.0
+            c1, c2 = p.convs
+            K_conv1_fwd(s.x_dev, self.fptr[c1.k.name], self.fptr[c1.b.name], s.pool1p, s.amax1, scale)
+            K_conv2_fwd(s.pool1p, self.wptr[c2.k.name][0], self.fptr[c2.b.name],
+                        s.act[0].view(s.B, 7, 7, 64), s.amax2)
+        else:
+            if s.x_dev.dtype == torch.uint8:
+                K.u8_to_bf16(s.x_dev, s.act[0])
+            else:
+                K.f32_to_bf16(s.x_dev, s.act[0])
+        nl = len(p.dense)
+        for i, d in enumerate(p.dense):
+            wp, ld = self.wptr[d.w.name]
+            out = s.act[i + 1] if i + 1 < nl else s.logits
+            bias = _PtrTensor(self.fptr[d.b.name]) if d.b is not None else None
+            K.gemm(s.act[i], None, out, s.B, s.dims[i + 1], s.dims[i], b_mn=True, bias=bias,
+                   relu=d.relu, b_ptr=wp, ldb=ld)
+
+    def _loss(self, s: StepState) -> None:
+        p = self.plan
+        dl = s.dlogits if s.train else self._scratch_dlogits(s)
+        gb = s.z[f"gb{len(p.dense) - 1}"] if s.train else None
+        if p.loss_kind == "sparse_mean":
+            K.softmax_xent_sparse(s.logits, s.y_dev, s.z["loss"], dl, gb, p.num_classes)
+        else:
+            K.softmax_xent_dense(s.logits, s.y_dev, s.z["loss"], dl, gb, p.num_classes)
+
+    def _scratch_dlogits(self, s: StepState) -> torch.Tensor:
+        if not hasattr(s, "_dl"):
+            s._dl = torch.zeros((s.B, pad8(self.plan.num_classes)), dtype=torch.bfloat16, device=self.device)
+        return s._dl
+
+    def _backward(self, s: StepState) -> None:
+        p = self.plan
+        nl = len(p.dense)
+        dz = s.dlogits
+        for i in range(nl - 1, -1, -1):
+            d = p.dense[i]
+            din, dout = s.dims[i], s.dims[i + 1]
+            # dW_i = act_i^T dZ_i
+            K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
+            wp, ld = self.wptr[d.w.name]
+            if i > 0:
+                # dZ_{i-1} = (dZ_i W_i^T) * relu'(act_i);  db_{i-1} = colsum
+                K.gemm(dz, None, s.dact[i], s.B, din, dout, mask=s.act[i], b_ptr=wp, ldb=ld)
+                K.colsum_bf16(s.dact[i], s.B, din, s.z[f"gb{i - 1}"])
+                dz = s.dact[i]
+            elif p.kind == "cnn":
+                K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld)
+        if p.kind == "cnn":
+            c1, c2 = p.convs
+            scale = 1.0 / 255.0 if s.x_dev.dtype == torch.uint8 else 1.0
+            K.pool2_bwd(s.dpool2, s.act[0].view(s.B, 7, 7, 64), s.amax2, s.dconv2p, s.z["gkb2"])
+            K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
+            K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
+            K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
+
+    def _grad_ptr(self, s: StepState, var: G.Variable) -> int:
+        p = self.plan
+        if p.kind == "cnn":
+            c1, c2 = p.convs
+            m = {c1.k.name: "gk1", c1.b.name: "gkb1", c2.k.name: "gk2", c2.b.name: "gkb2"}
+            if var.name in m:
+                return s.z[m[var.name]].data_ptr()
+        for i, d in enumerate(p.dense):
+            if var is d.w:
+                return s.gw[i].data_ptr()
+            if d.b is not None and var is d.b:
+                return s.z[f"gb{i}"].data_ptr()
+        raise KeyError(var.name)
+
+    def _apply(self, s: StepState) -> None:
+        st, spec = self.store, self.spec
+        entries = []
+        for var in self.train_op.var_list:
+            gptr = self._grad_ptr(s, var)
+            for r in self._regions(var):
+                entries.append(dict(var=st.var_ptr(r), slot0=st.slot_ptr(r, 0), slot1=st.slot_ptr(r, 1),
+                                    shadow=st.shadow_ptr(r), grad=gptr + r.sl.first * 4, n=r.sl.n,
+                                    first=0, cols=r.cols, shadow_ld=r.shadow_ld))
+        hyper = K.make_hyper(spec.learning_rate, spec.beta1, spec.beta2, spec.epsilon, spec.momentum,
+                             1.0, spec.use_nesterov, self.atomic_sgd and spec.kind == "sgd")
+        chunks = [entries[i:i + L.MAX_APPLY_ITEMS] for i in range(0, len(entries), L.MAX_APPLY_ITEMS)]
+        for ci, ch in enumerate(chunks):
+            last = ci == len(chunks) - 1
+            items = K.make_apply_items(ch)
+            K.push_apply(spec.code, items, len(ch), hyper, st.powers_ctrl, st.step_ctrl, last,
+                         self.worker_id, s.step_dev.data_ptr() if last else None,
+                         s.counter.data_ptr())
+
+    def _pull(self, s: StepState) -> None:
+        if self.copies:
+            K.pull_bulk(self.copies, self.store.step_ctrl, s.step_dev.data_ptr() + 8)
+
+    def _enqueue_step(self, s: StepState, with_io: bool = True) -> None:
+        """Everything one ``sess.run(train_op)`` does on the device, in stream order."""
+        if with_io:
+            s.x_dev.copy_(s.x_pin, non_blocking=True)
+            s.y_dev.copy_(s.y_pin, non_blocking=True)
+        K.fill_u32(s.zero.buf, 0)
+        self._pull(s)
+        self._forward(s)
+        self._loss(s)
+        if s.train:
+            self._backward(s)
+            self._apply(s)
+        if with_io:
+            s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
+            s.step_pin.copy_(s.step_dev, non_blocking=True)
+
+    # -- state management ---------------------------------------------------------------------------
+    def _ensure_plan(self, loss: G.Tensor, train_op=None) -> None:
+        if self.plan is None:
+            self.plan = parse_plan(loss)
+            if train_op is not None:
+                self.train_op = train_op
+            else:
+                for n in self.graph.nodes:
+                    if type(n).__name__ == "TrainOp":
+                        self.train_op = n
+            self._setup_params()
+        elif train_op is not None and self.train_op is None:
+            self.train_op = train_op
+
+    def _state(self, B: int, train: bool, x: np.ndarray, y: np.ndarray) -> StepState:
+        key = (B, train, str(x.dtype), str(y.dtype))
+        s = self.states.get(key)
+        if s is None:
+            xdt = torch.uint8 if x.dtype == np.uint8 else torch.float32
+            ydt = torch.int32 if self.plan.loss_kind == "sparse_mean" else torch.float32
+            with torch.cuda.stream(self.stream):
+                s = StepState(self, B, train, xdt, ydt)
+            self.stream.synchronize()
+            self.states[key] = s
+        return s
+
+    def _stage(self, s: StepState, x: np.ndarray, y: np.ndarray) -> None:
+        xn = s.x_pin.numpy()
+        np.copyto(xn, x.reshape(xn.shape), casting="same_kind" if x.dtype != xn.dtype else "no")
+        yn = s.y_pin.numpy()
+        np.copyto(yn, np.asarray(y).reshape(yn.shape), casting="unsafe")
+
+    def _launch(self, s: StepState) -> None:
+        with torch.cuda.stream(self.stream):
+            if not self.use_cuda_graph:
+                self._enqueue_step(s)
+                return
+            if s.graph is None:
+                # one eager step first (sets kernel attributes, warms the allocator), then capture
+                before = K.LAUNCHES
+                self._enqueue_step(s)
+                s.launches_per_step = K.LAUNCHES - before
+                self.stream.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.stream):
+                    self._enqueue_step(s)
+                s.graph = g
+                return  # the eager step already did this run's work
+            s.graph.replay()
+
+    # -- Session.run entry ---------------------------------------------------------------------------
+    def run(self, fetches: Sequence[G.Tensor], feeds: Dict[G.Tensor, Any]) -> List[Any]:
+        from ..train.optimizers import TrainOp
+        train_ops = [f for f in fetches if isinstance(f, TrainOp)]
+        plain = [f for f in fetches if not isinstance(f, TrainOp)]
+        gs_var = G.get_global_step(self.graph)
+        if not train_ops and all(f is gs_var for f in plain):
+            step = self.store.read_global_step()
+            return [self._as_step(step) for _ in fetches]
+        top = train_ops[0] if train_ops else None
+        if top is not None and top.sync is not None:
+            raise NotImplementedError("sync replicas on the B200 backend goes through "
+                                      "parallel/nvl_sync.py (session option sync_mode='b200')")
+        loss_node = top.loss if top is not None else self._find_loss(plain)
+        self._ensure_plan(loss_node, top)
+        p = self.plan
+        if p.input_node not in feeds or p.labels_node not in feeds:
+            raise ValueError("feed the model input and labels (or initialise the iterator)")
+        x, y = np.asarray(feeds[p.input_node]), np.asarray(feeds[p.labels_node])
+        B = int(x.shape[0])
+        if x.dtype not in (np.uint8, np.float32):
+            x = x.astype(np.float32)
+        s = self._state(B, top is not None, x.reshape(B, -1), y)
+        self._stage(s, x.reshape(B, -1), y)
+        if top is not None:
+            self._launch(s)
+        else:
+            with torch.cuda.stream(self.stream):
+                self._enqueue_step(s)
+        self.stream.synchronize()
+        loss_val = np.float32(s.out_pin[0].item())
+        step_val = int(s.step_pin[0].item()) if top is not None else None
+        out: List[Any] = []
+        extra: Optional[Dict[int, Any]] = None
+        for f in fetches:
+            if isinstance(f, TrainOp):
+                out.append(None)
+            elif f is p.loss_node:
+                out.append(loss_val)
+            elif f is gs_var:
+                out.append(self._as_step(step_val if step_val is not None else self.store.read_global_step()))
+            elif f is p.logits_node:
+                out.append(s.logits.cpu().numpy())
+            else:
+                if extra is None:
+                    extra = self._eval_rest([g for g in plain if g not in (p.loss_node, gs_var, p.logits_node)],
+                                            feeds, s)
+                out.append(extra[id(f)])
+        return out
+
+    def _as_step(self, step: int):
+        gs = G.get_global_step(self.graph)
+        return np.int64(step) if gs is None or gs.dtype == "int64" else np.int32(step)
+
+    def _find_loss(self, fetches: Sequence[G.Tensor]) -> G.Tensor:
+        if self.plan is not None:
+            return self.plan.loss_node
+        for f in fetches:
+            try:
+                parse_loss(f)
+                return f
+            except UnsupportedGraphError:
+                continue
+        for n in self.graph.nodes:
+            if type(n).__name__ == "TrainOp":
+                return n.loss
+        raise UnsupportedGraphError("cannot find a compiled loss among the fetches")
+
+    def _eval_rest(self, nodes: Sequence[G.Tensor], feeds, s: StepState) -> Dict[int, Any]:
+        """Fetches that hang off the logits (accuracy, softmax ...) are finished on the host."""
+        from .executor_cpu import evaluate, _to_numpy
+        f2 = dict(feeds)
+        f2[self.plan.logits_node] = s.logits.cpu().numpy()
+        f2[self.plan.loss_node] = np.float32(s.out_pin[0].item())
+        vals = evaluate(list(nodes), f2, {})
+        return {id(n): _to_numpy(v) for n, v in zip(nodes, vals)}
+
+    # -- benchmarking hooks ---------------------------------------------------------------------------
+    def train_state(self) -> StepState:
+        for (B, train, *_), s in self.states.items():
+            if train:
+                return s
+        raise RuntimeError("no training step has run yet")
+
+    def replay(self, n: int) -> None:
+        """n back-to-back device steps on the current staged batch (no host round trip)."""
+        s = self.train_state()
+        with torch.cuda.stream(self.stream):
+            for _ in range(n):
+                if s.graph is not None:
+                    s.graph.replay()
+                else:
+                    self._enqueue_step(s)
+
+    def close(self) -> None:
+        try:
+            self.stream.synchronize()
+        except Exception:
+            pass
+        self.states.clear()
+        if self.store is not None:
+            self.store.close()
+
+
+class _PtrTensor:
+    """Minimal stand-in so raw arena pointers can be passed where kernels.py expects a tensor."""
+
+    def __init__(self, ptr: int):
+        self._ptr = ptr
+
+    def data_ptr(self) -> int:
+        return self._ptr
+
+
+def K_conv1_fwd(x, w1_ptr, b1_ptr, pool1p, amax1, scale):
+    K.conv1_fwd(x, _PtrTensor(w1_ptr), _PtrTensor(b1_ptr), pool1p, amax1, scale)
+
+
+def K_conv2_fwd(pool1p, w2_ptr, b2_ptr, pool2, amax2):
+    K.conv2_fwd(pool1p, w2_ptr, _PtrTensor(b2_ptr), pool2, amax2)

@@ -1,0 +1,281 @@
+"""NVLink peer-memory parameter store — the B200 product path's data plane.
+
+Every PS shard owns ONE device arena (``cudaMalloc`` on the shard's GPU):
+
+    [ dtf_ps_ctrl (256 B) | var slice fp32 | slot0 | slot1 | bf16 serving copy | next variable ... ]
+
+whose layout every task derives independently from the graph's variables + placement + optimizer
+(between-graph replication: nobody ships a graph). The owning process exports a 64-byte CUDA IPC
+handle through the TCP control plane (``PsShard.nvl_alloc``) and every worker maps the arena into
+its own address space; from then on parameters and gradients move ONLY by loads / stores /
+atomics issued from inside kernels over NVLink 5 / NVSwitch:
+
+* pull   — ``dtf_pull_bulk`` (one launch, 16-byte peer loads) or, for the first layer, TMA
+  straight from the peer-mapped bf16 serving copy into the tcgen05 GEMM's smem ring;
+* push   — ``dtf_push_apply``: the worker's kernel reads its local gradient, reads the slice's
+  optimizer state from the owner, applies the TF1 update and writes var / slots / serving copy
+  back; the last CTA bumps ``global_step`` with a system-scope atomic.
+
+This replaces the reference's per-tensor gRPC ``RecvTensor`` traffic: 8
+parameter tensors down and 8 gradient tensors up per step per worker, through host memory,
+protobuf and TCP.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import struct
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from ..ops import _lib as L
+from ..train.optimizers import OptimizerSpec
+from .layout import VarLayout, VarSlice, powers_shard
+
+ALIGN = 256
+
+
+def _align(n: int, a: int = ALIGN) -> int:
+    return (n + a - 1) // a * a
+
+
+def pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+@dataclass
+class SliceRegion:
+    """Byte offsets of one variable slice inside its shard's arena."""
+    name: str
+    shard: int
+    sl: VarSlice
+    cols: int
+    rows: int            # rows of the serving copy held by this slice
+    shadow_ld: int       # elements
+    var_off: int
+    slot_off: List[int]
+    shadow_off: Optional[int]
+
+    @property
+    def var_bytes(self) -> int:
+        return self.sl.n * 4
+
+    @property
+    def shadow_bytes(self) -> int:
+        return self.rows * self.shadow_ld * 2
+
+
+@dataclass
+class ArenaLayout:
+    num_shards: int
+    shard_bytes: List[int]
+    regions: Dict[str, List[SliceRegion]]   # variable name -> regions of its non-empty slices
+    step_var: Optional[str]                 # the global_step variable (lives in ctrl.global_step)
+    step_shard: int
+    powers_shard: int
+    num_slots: int
+
+
+def build_arena_layout(layout: Dict[str, VarLayout], num_shards: int, spec: Optional[OptimizerSpec],
+                       trainable_names: Sequence[str]) -> ArenaLayout:
+    num_slots = spec.num_slots if spec is not None else 0
+    offs = [L.CTRL_BYTES] * num_shards
+    regions: Dict[str, List[SliceRegion]] = {}
+    step_var, step_shard = None, 0
+    tset = set(trainable_names)
+    for vl in sorted(layout.values(), key=lambda v: v.index):
+        if vl.dtype in ("int64", "int32") and vl.num_elements == 1:
+            if vl.name == "global_step" or step_var is None:
+                step_var, step_shard = vl.name, vl.home_shard
+            continue
+        if vl.dtype != "float32":
+            raise NotImplementedError(f"variable {vl.name} has dtype {vl.dtype}; the device arena "
+                                      "holds float32 tensors and the integer global_step")
+        want_shadow = len(vl.shape) >= 2
+        cols = vl.cols
+        out = []
+        for sl in vl.slices:
+            if sl.n == 0:
+                continue
+            s = sl.shard
+            var_off = _align(offs[s])
+            o = var_off + _align(sl.n * 4)
+            slot_off = []
+            if vl.name in tset:
+                for _ in range(num_slots):
+                    slot_off.append(o)
+                    o += _align(sl.n * 4)
+            rows = sl.n // cols
+            ld = pad8(cols)
+            shadow_off = None
+            if want_shadow:
+                shadow_off = o
+                o += _align(rows * ld * 2)
+            offs[s] = o
+            out.append(SliceRegion(vl.name, s, sl, cols, rows, ld, var_off, slot_off, shadow_off))
+        regions[vl.name] = out
+    pshard = powers_shard(layout, list(trainable_names)) if trainable_names else 0
+    return ArenaLayout(num_shards, [_align(o, 4096) for o in offs], regions, step_var, step_shard,
+                       pshard, num_slots)
+
+
+class NvlStore:
+    """Maps every shard's arena into this process and answers "where is X" with raw pointers."""
+
+    def __init__(self, client, layout: Dict[str, VarLayout], spec: Optional[OptimizerSpec],
+                 trainable_names: Sequence[str], local_device: int,
+                 shard_devices: Optional[Sequence[Optional[int]]] = None):
+        self.client = client
+        self.layout = layout
+        self.spec = spec
+        self.num_shards = client.num_shards
+        self.local_device = local_device
+        self.arena = build_arena_layout(layout, self.num_shards, spec, trainable_names)
+        self.base: List[int] = [0] * self.num_shards
+        self.is_local: List[bool] = [False] * self.num_shards
+        self.shard_device: List[int] = [local_device] * self.num_shards
+        self._imported: List[int] = []
+        lib = L.lib()
+        for s in range(self.num_shards):
+            dev = local_device
+            if shard_devices is not None and shard_devices[s] is not None:
+                dev = int(shard_devices[s])
+            info = client.call(s, "nvl_alloc", int(self.arena.shard_bytes[s]), dev)
+            self.shard_device[s] = int(info["device"])
+            if int(info["pid"]) == os.getpid():
+                self.base[s] = int(info["ptr"])
+                if self.shard_device[s] != local_device:
+                    L.check(lib.dtf_set_device(local_device), "set_device")
+                    L.check(lib.dtf_enable_peer_access(self.shard_device[s]), "enable_peer_access")
+            else:
+                L.check(lib.dtf_set_device(local_device), "set_device")
+                ptr = C.c_void_p()
+                L.check(lib.dtf_ipc_import(bytes(info["handle"]), C.byref(ptr)), "ipc_import")
+                self.base[s] = int(ptr.value)
+                self._imported.append(self.base[s])
+            self.is_local[s] = self.shard_device[s] == local_device
+        L.check(lib.dtf_set_device(local_device), "set_device")
+        names_per_shard: Dict[int, List[str]] = {}
+        for name, regs in self.arena.regions.items():
+            for r in regs:
+                names_per_shard.setdefault(r.shard, []).append(name)
+        if self.arena.step_var:
+            names_per_shard.setdefault(self.arena.step_shard, []).append(self.arena.step_var)
+        for s, names in names_per_shard.items():
+            client.call(s, "declare", names)
+
+    # -- pointers -----------------------------------------------------------------------------------
+    def ctrl_ptr(self, shard: int) -> int:
+        return self.base[shard]
+
+    def var_ptr(self, r: SliceRegion) -> int:
+        return self.base[r.shard] + r.var_off
+
+    def slot_ptr(self, r: SliceRegion, i: int) -> Optional[int]:
+        return self.base[r.shard] + r.slot_off[i] if i < len(r.slot_off) else None
+
+    def shadow_ptr(self, r: SliceRegion) -> Optional[int]:
+        return None if r.shadow_off is None else self.base[r.shard] + r.shadow_off
+
+    @property
+    def step_ctrl(self) -> int:
+        return self.ctrl_ptr(self.arena.step_shard)
+
+    @property
+    def powers_ctrl(self) -> int:
+        return self.ctrl_ptr(self.arena.powers_shard)
+
+    # -- host <-> arena (init, restore, checkpoint): plain synchronous copies ------------------------
+    def _h2d(self, dst: int, arr: np.ndarray) -> None:
+        a = np.ascontiguousarray(arr)
+        lib = L.lib()
+        L.check(lib.dtf_memcpy_h2d(dst, a.ctypes.data_as(C.c_void_p), a.nbytes, None), "h2d")
+        L.check(lib.dtf_stream_sync(None), "sync")
+
+    def _d2h(self, src: int, nbytes: int, dtype) -> np.ndarray:
+        out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype)
+        lib = L.lib()
+        L.check(lib.dtf_memcpy_d2h(out.ctypes.data_as(C.c_void_p), src, nbytes, None), "d2h")
+        L.check(lib.dtf_stream_sync(None), "sync")
+        return out
+
+    def write_ctrl(self, shard: int, global_step: int = 0, beta1_power: float = 0.0,
+                   beta2_power: float = 0.0, initialized: int = 0) -> None:
+        buf = bytearray(L.CTRL_BYTES)
+        struct.pack_into("<QffI", buf, 0, int(global_step), float(beta1_power), float(beta2_power),
+                         int(initialized))
+        self._h2d(self.ctrl_ptr(shard), np.frombuffer(bytes(buf), np.uint8))
+
+    def read_ctrl(self, shard: int) -> dict:
+        raw = self._d2h(self.ctrl_ptr(shard), L.CTRL_BYTES, np.uint8).tobytes()
+        gs, b1, b2, init, epoch, shutdown, applies = struct.unpack_from("<QffIIII", raw, 0)
+        hb = struct.unpack_from("<%dQ" % L.MAX_WORKERS, raw, L.CTRL_OFF_HEARTBEAT)
+        return dict(global_step=gs, beta1_power=b1, beta2_power=b2, initialized=init, epoch=epoch,
+                    shutdown=shutdown, apply_count=applies, heartbeat=list(hb))
+
+    def set_field(self, shard: int, offset: int, fmt: str, value) -> None:
+        self._h2d(self.ctrl_ptr(shard) + offset, np.frombuffer(struct.pack(fmt, value), np.uint8))
+
+    def read_global_step(self) -> int:
+        raw = self._d2h(self.step_ctrl, 8, np.uint8).tobytes()
+        return struct.unpack("<Q", raw)[0]
+
+    def write_variable(self, name: str, value: np.ndarray) -> None:
+        """fp32 master + refreshed bf16 serving copy, slice by slice."""
+        from ..ops import kernels as K
+        flat = np.ascontiguousarray(value, np.float32).reshape(-1)
+        for r in self.arena.regions[name]:
+            self._h2d(self.var_ptr(r), flat[r.sl.first:r.sl.first + r.sl.n])
+            if r.shadow_off is not None:
+                K.refresh_shadow(self.var_ptr(r), self.shadow_ptr(r), r.sl.n, 0, r.cols, r.shadow_ld)
+        import torch
+        torch.cuda.synchronize()
+
+    def write_slot(self, name: str, slot: int, value) -> None:
+        for r in self.arena.regions[name]:
+            if slot >= len(r.slot_off):
+                continue
+            if np.isscalar(value):
+                arr = np.full(r.sl.n, value, np.float32)
+            else:
+                arr = np.ascontiguousarray(value, np.float32).reshape(-1)[r.sl.first:r.sl.first + r.sl.n]
+            self._h2d(self.slot_ptr(r, slot), arr)
+
+    def read_variable(self, name: str) -> np.ndarray:
+        vl = self.layout[name]
+        out = np.empty(vl.num_elements, np.float32)
+        for r in self.arena.regions[name]:
+            out[r.sl.first:r.sl.first + r.sl.n] = self._d2h(self.var_ptr(r), r.sl.n * 4, np.float32)
+        return out.reshape(vl.shape)
+
+    def read_slot(self, name: str, slot: int) -> Optional[np.ndarray]:
+        vl = self.layout[name]
+        regs = self.arena.regions[name]
+        if not regs or slot >= len(regs[0].slot_off):
+            return None
+        out = np.empty(vl.num_elements, np.float32)
+        for r in regs:
+            out[r.sl.first:r.sl.first + r.sl.n] = self._d2h(self.slot_ptr(r, slot), r.sl.n * 4, np.float32)
+        return out.reshape(vl.shape)
+
+    def read_shadow(self, name: str) -> np.ndarray:
+        """bf16 serving copy as float32 (tests)."""
+        import torch
+        vl = self.layout[name]
+        rows = []
+        for r in self.arena.regions[name]:
+            raw = self._d2h(self.shadow_ptr(r), r.shadow_bytes, np.uint16)
+            t = torch.from_numpy(raw.view(np.int16).copy()).view(torch.bfloat16)
+            rows.append(t.float().numpy().reshape(r.rows, r.shadow_ld)[:, :r.cols])
+        return np.concatenate(rows, 0).reshape(vl.shape)
+
+    def close(self) -> None:
+        lib = L.lib()
+        for p in self._imported:
+            try:
+                lib.dtf_ipc_close(p)
+            except Exception:
+                pass
+        self._imported = []

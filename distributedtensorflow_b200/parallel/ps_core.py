@@ -138,6 +138,9 @@ class PsShard:
         self._lock = threading.Lock()        # structure changes + locked applies
         self._step_lock = threading.Lock()   # AssignAdd on global_step is atomic in TF too
         self.incarnation = int(time.time() * 1e6)
+        self.declared: set = set()           # names whose storage lives in a device arena
+        self.device: Optional[str] = None    # "cuda:N" when this PS task owns a GPU arena
+        self._arena: Optional[dict] = None
 
     # -- creation / init --------------------------------------------------------------------------
     def create(self, defs: Sequence[dict], spec: Optional[dict]) -> bool:
@@ -201,7 +204,34 @@ class PsShard:
         """report_uninitialized_variables for the slices this shard should hold."""
         if not self.initialized:
             return list(names)
-        return [n for n in names if n not in self.vars]
+        return [n for n in names if n not in self.vars and n not in self.declared]
+
+    # -- device arena (B200 path): the shard's variables live in GPU memory that workers map ----
+    def declare(self, names: Sequence[str]) -> None:
+        self.declared.update(names)
+
+    def nvl_alloc(self, nbytes: int, device_index: int) -> dict:
+        """Allocate (once) this shard's arena on ``cuda:device_index`` and return what a peer
+        needs to map it: a 64-byte CUDA IPC handle, plus pid/pointer for same-process users."""
+        import os
+        from ..ops import _lib as L
+        with self._lock:
+            if self._arena is not None and self._arena["nbytes"] >= nbytes:
+                return self._arena
+            import ctypes as C
+            lib = L.lib()
+            L.check(lib.dtf_set_device(device_index), "set_device")
+            ptr = C.c_void_p()
+            L.check(lib.dtf_arena_alloc(C.byref(ptr), nbytes), "arena_alloc")
+            handle = C.create_string_buffer(L.IPC_HANDLE_BYTES)
+            L.check(lib.dtf_ipc_export(ptr, handle), "ipc_export")
+            self._arena = dict(handle=bytes(handle.raw), pid=os.getpid(), ptr=int(ptr.value),
+                               device=int(device_index), nbytes=int(nbytes))
+            self.initialized = False
+            return self._arena
+
+    def nvl_info(self) -> Optional[dict]:
+        return self._arena
 
     # -- data plane ---------------------------------------------------------------------------------
     def pull(self, names: Sequence[str]) -> List[np.ndarray]:

@@ -90,7 +90,7 @@ _ALLOWED = {
     "is_initialized", "uninitialized", "pull", "read_powers", "push_apply", "finish", "step_add",
     "read_scalar", "heartbeat", "accum_create", "accum_apply", "accum_take", "accum_take_apply",
     "accum_set_global_step", "accum_stats", "queue_create", "queue_enqueue_many", "queue_dequeue",
-    "queue_size", "queue_close", "snapshot", "request_shutdown", "ping", "kv_set", "kv_get",
+    "queue_size", "queue_close", "snapshot", "declare", "nvl_alloc", "nvl_info", "request_shutdown", "ping", "kv_set", "kv_get",
 }
 
 

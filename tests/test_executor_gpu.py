@@ -1,0 +1,142 @@
+"""End-to-end training through the public session API on the B200 backend, checked against the
+CPU executor (PyTorch fp32 autograd) started from the same initial values."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(backend, build, steps, batches, num_ps=1, strategy=None, options=None):
+    import distributedtensorflow_b200 as tf
+    tf.reset_default_graph()
+    tf.set_random_seed(1234)
+    server = tf.train.Server.create_local_server(num_ps=num_ps)
+    cluster = tf.train.ClusterSpec({"ps": ["localhost:%d" % (1000 + i) for i in range(num_ps)],
+                                    "worker": ["localhost:2000"]})
+    ps_strategy = None
+    if strategy == "flat":
+        ps_strategy = tf.train.FlatSlicedStrategy(num_ps)
+    with tf.device(tf.train.replica_device_setter(worker_device="/job:worker/task:0", cluster=cluster,
+                                                  ps_strategy=ps_strategy)):
+        x_ph, y_ph, loss, gs, train_op = build(tf)
+    cfg = tf.ConfigProto(backend=backend, device="cuda:0" if backend == "b200" else None, **(options or {}))
+    losses, gsteps = [], []
+    with tf.train.MonitoredTrainingSession(master=server.target, is_chief=True, config=cfg) as sess:
+        for i in range(steps):
+            bx, by = batches[i % len(batches)]
+            _, l, g = sess.run([train_op, loss, gs], feed_dict={x_ph: bx, y_ph: by})
+            losses.append(float(l))
+            gsteps.append(int(g))
+        raw = sess._tf_sess()
+        names = [v.name for v in tf.trainable_variables()]
+        if backend == "b200":
+            finals = {n: raw._runner.store.read_variable(n) for n in names}
+            shadows = {n: raw._runner.store.read_shadow(n) for n in names if len(finals[n].shape) >= 2}
+        else:
+            finals = raw.ps_client.pull_all(raw.layout, names)
+            shadows = {}
+    server.stop()
+    return losses, gsteps, finals, shadows
+
+
+def _build_cnn(tf):
+    from distributedtensorflow_b200.models import mnist_cnn
+    x = tf.placeholder(tf.float32, [None, 784])
+    y = tf.placeholder(tf.int32, [None])
+    _, loss, gs, train_op = mnist_cnn.build_train_graph(x, y, learning_rate=0.0005)
+    return x, y, loss, gs, train_op
+
+
+def _build_mlp(opt_name):
+    def build(tf):
+        from distributedtensorflow_b200.models import mnist_mlp
+        x = tf.placeholder(tf.float32, [None, 784])
+        y_ = tf.placeholder(tf.float32, [None, 10])
+        gs, xent, _ = mnist_mlp.build_model(x, y_, hidden_units=100)
+        opt = {"adam": lambda: tf.train.AdamOptimizer(0.01),
+               "sgd": lambda: tf.train.GradientDescentOptimizer(0.001),
+               "momentum": lambda: tf.train.MomentumOptimizer(0.001, 0.9),
+               "adagrad": lambda: tf.train.AdagradOptimizer(0.01)}[opt_name]()
+        train_op = opt.minimize(xent, global_step=gs)
+        return x, y_, xent, gs, train_op
+    return build
+
+
+def _batches(n, B, one_hot):
+    from distributedtensorflow_b200.data import mnist
+    imgs, labels = mnist.synthetic_arrays(n * B, seed=3)
+    x = imgs.astype(np.float32) / 255.0
+    out = []
+    for i in range(n):
+        lab = labels[i * B:(i + 1) * B]
+        y = np.eye(10, dtype=np.float32)[lab] if one_hot else lab.astype(np.int32)
+        out.append((x[i * B:(i + 1) * B], y))
+    return out
+
+
+@pytest.mark.parametrize("opt", ["adam", "sgd", "momentum", "adagrad"])
+def test_mlp_matches_cpu_oracle(opt):
+    batches = _batches(4, 100, one_hot=True)
+    ref_l, ref_g, ref_v, _ = _run("cpu", _build_mlp(opt), 12, batches)
+    got_l, got_g, got_v, shadows = _run("b200", _build_mlp(opt), 12, batches)
+    assert got_g == ref_g == list(range(1, 13))
+    for a, b in zip(got_l, ref_l):
+        assert abs(a - b) <= 0.05 * abs(b) + 0.5, (got_l, ref_l)
+    assert got_l[-1] < got_l[0]
+    for n in ref_v:
+        scale = max(1e-3, float(np.abs(ref_v[n]).max()))
+        assert float(np.abs(got_v[n] - ref_v[n]).max()) < 0.08 * scale + 2e-2, n
+    for n, sh in shadows.items():  # the bf16 serving copy tracks the fp32 master
+        assert float(np.abs(sh - got_v[n]).max()) <= 0.01 * float(np.abs(got_v[n]).max()) + 1e-6
+
+
+def test_cnn_matches_cpu_oracle():
+    batches = _batches(3, 128, one_hot=False)
+    ref_l, ref_g, ref_v, _ = _run("cpu", _build_cnn, 8, batches)
+    got_l, got_g, got_v, _ = _run("b200", _build_cnn, 8, batches)
+    assert got_g == ref_g == list(range(1, 9))
+    for a, b in zip(got_l, ref_l):
+        assert abs(a - b) <= 0.06 * abs(b) + 0.03, (got_l, ref_l)
+    assert got_l[-1] < got_l[0]
+
+
+def test_cnn_sharded_round_robin_and_flat_sliced_agree():
+    """8 shards on one GPU: TF round-robin placement and the flat-sliced layout train alike."""
+    batches = _batches(2, 128, one_hot=False)
+    base_l, _, base_v, _ = _run("b200", _build_cnn, 6, batches, num_ps=1)
+    rr_l, rr_g, rr_v, _ = _run("b200", _build_cnn, 6, batches, num_ps=8)
+    fl_l, fl_g, fl_v, _ = _run("b200", _build_cnn, 6, batches, num_ps=8, strategy="flat")
+    assert rr_g == fl_g == list(range(1, 7))
+    for a, b, c in zip(base_l, rr_l, fl_l):
+        assert abs(a - b) <= 0.03 * abs(a) + 0.02 and abs(a - c) <= 0.03 * abs(a) + 0.02
+
+
+def test_eager_mode_equals_cuda_graph_mode():
+    batches = _batches(2, 128, one_hot=False)
+    a, _, va, _ = _run("b200", _build_cnn, 5, batches, options={"cuda_graph": True})
+    b, _, vb, _ = _run("b200", _build_cnn, 5, batches, options={"cuda_graph": False})
+    for x, y in zip(a, b):
+        assert abs(x - y) <= 0.02 * abs(x) + 0.01
+
+
+def test_eval_fetch_and_validation_batch():
+    """Fetching only the loss runs a forward pass at any batch size (the MLP template's
+    validation cross-entropy, templates/00_mnist_replica.py:267-271)."""
+    import distributedtensorflow_b200 as tf
+    from distributedtensorflow_b200.models import mnist_mlp
+    tf.reset_default_graph()
+    tf.set_random_seed(7)
+    server = tf.train.Server.create_local_server()
+    x = tf.placeholder(tf.float32, [None, 784])
+    y_ = tf.placeholder(tf.float32, [None, 10])
+    gs, xent, _ = mnist_mlp.build_model(x, y_)
+    train_op = tf.train.AdamOptimizer(0.01).minimize(xent, global_step=gs)
+    (bx, by), = _batches(1, 100, one_hot=True)
+    (vx, vy), = _batches(1, 1000, one_hot=True)
+    with tf.train.MonitoredTrainingSession(master=server.target, config=tf.ConfigProto(backend="b200")) as sess:
+        v0 = float(sess.run(xent, feed_dict={x: vx, y_: vy}))
+        for _ in range(30):
+            sess.run(train_op, feed_dict={x: bx, y_: by})
+        v1 = float(sess.run(xent, feed_dict={x: vx, y_: vy}))
+        assert int(sess.run(gs)) == 30
+    assert v1 < v0
