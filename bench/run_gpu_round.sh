@@ -8,5 +8,5 @@ echo "=== smoke"
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1
 echo "exit=$? $(tail -n 5 gpurun_out/smoke.log)"
 echo "=== bench"
-timeout 600 python bench.py --steps 200 --warmup 10 > gpurun_out/bench.log 2>&1
+timeout 300 python bench.py --steps 200 --warmup 10 > gpurun_out/bench.log 2>&1
 echo "exit=$? $(tail -n 5 gpurun_out/bench.log)"

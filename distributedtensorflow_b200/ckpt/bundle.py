@@ -33,7 +33,8 @@ class BundleWriter:
         self.bytes_written = 0
 
     def add(self, name: str, array: np.ndarray, dtype_enum: Optional[int] = None) -> None:
-        a = np.ascontiguousarray(array)
+        src = np.asarray(array)
+        a = np.ascontiguousarray(src).reshape(src.shape)  # ascontiguousarray promotes 0-d to 1-d
         dt = dtype_enum if dtype_enum is not None else _NP_TO_DT[a.dtype]
         dims = (C.c_int64 * max(1, a.ndim))(*a.shape)
         rc = self._lib.dtf_bundle_writer_add(self._h, name.encode(), dt, a.ndim, dims,

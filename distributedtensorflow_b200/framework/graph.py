@@ -77,18 +77,21 @@ class Graph:
         return self.get_collection(GraphKeys.TRAINABLE_VARIABLES)
 
 
-_default = threading.local()
+class _Default:
+    # process-wide, like TF's global default graph: helper threads (queue runners, in-process
+    # worker threads of the fake cluster) see the graph the main thread built
+    graph: Optional[Graph] = None
 
 
 def get_default_graph() -> Graph:
-    if not hasattr(_default, "graph"):
-        _default.graph = Graph()
-    return _default.graph
+    if _Default.graph is None:
+        _Default.graph = Graph()
+    return _Default.graph
 
 
 def reset_default_graph() -> Graph:
-    _default.graph = Graph()
-    return _default.graph
+    _Default.graph = Graph()
+    return _Default.graph
 
 
 def set_random_seed(seed: int) -> None:

@@ -59,7 +59,8 @@ def pack(obj) -> bytes:
 
 def unpack(data: bytes):
     return msgpack.unpackb(data, ext_hook=_ext_hook, raw=False, strict_map_key=False,
-                           max_bin_len=_MAX_MSG, max_ext_len=_MAX_MSG, max_buffer_size=_MAX_MSG)
+                           max_bin_len=_MAX_MSG, max_ext_len=_MAX_MSG, max_str_len=_MAX_MSG,
+                           max_array_len=1 << 24, max_map_len=1 << 24)
 
 
 def _recv_exact(sock: socket.socket, n: int) -> bytes:
@@ -130,6 +131,8 @@ class PsRpcServer:
     def __init__(self, shard: PsShard, host: str, port: int):
         self.shard = shard
         self.kv: dict = {}
+        self.last_activity = time.monotonic()
+        self.drain_idle, self.drain_max = 1.0, 10.0
         self._kv_cv = threading.Condition()
         self._srv = _TcpServer((host, port), _Handler)
         self._srv.owner = self  # type: ignore[attr-defined]
@@ -139,6 +142,7 @@ class PsRpcServer:
         self._thread.start()
 
     def dispatch(self, method: str, args: Sequence[Any]):
+        self.last_activity = time.monotonic()
         if method == "ping":
             return {"task": self.shard.task_index, "incarnation": self.shard.incarnation}
         if method == "kv_set":
@@ -159,9 +163,14 @@ class PsRpcServer:
         return getattr(self.shard, method)(*args)
 
     def join(self, poll: float = 0.1) -> None:
-        """Block until a shutdown request arrives (``server.join()``)."""
+        """Block until a shutdown request arrives (``server.join()``), then drain: keep serving
+        until the other tasks have been quiet for ``drain_idle`` seconds (bounded), so workers
+        that are mid-step when the chief says "done" can finish that step and stop by themselves."""
         while not self.shard.shutdown_requested.wait(poll):
             pass
+        deadline = time.monotonic() + self.drain_max
+        while time.monotonic() < deadline and time.monotonic() - self.last_activity < self.drain_idle:
+            time.sleep(poll)
 
     def stop(self) -> None:
         self._srv.shutdown()

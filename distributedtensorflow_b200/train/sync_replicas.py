@@ -62,10 +62,14 @@ class ChiefQueueRunner:
         self.opt = opt
         self._thread: Optional[threading.Thread] = None
         self._stop = threading.Event()
+        self._client = None
+        self._layout = None
         self.rounds = 0
         self.error: Optional[BaseException] = None
 
     def start(self, client, layout) -> threading.Thread:
+        self._client, self._layout = client, layout
+
         def loop():
             try:
                 while not self._stop.is_set():
@@ -77,10 +81,18 @@ class ChiefQueueRunner:
         self._thread.start()
         return self._thread
 
-    def stop(self, join: bool = True) -> None:
+    def stop(self, join: bool = True, close_queue: bool = True) -> None:
+        """Stops the thread and (like TF's queue runner on coordinator stop) closes the token
+        queue, so replicas blocked in ``dequeue`` end with OutOfRangeError instead of hanging."""
         self._stop.set()
         if join and self._thread is not None:
             self._thread.join(timeout=5.0)
+        if close_queue and self._client is not None:
+            try:
+                gname = self.opt._train_op.global_step.name
+                self._client.call(self._layout[gname].home_shard, "queue_close", SYNC_TOKEN_QUEUE)
+            except Exception:
+                pass
 
 
 class SyncReplicasOptimizer(Optimizer):
@@ -97,7 +109,9 @@ class SyncReplicasOptimizer(Optimizer):
         self._gradients_applied = False
         self._train_op: Optional[TrainOp] = None
         self._chief_queue_runner: Optional[ChiefQueueRunner] = None
-        self.local_step = 0            # the LOCAL variable sync_rep_local_step
+        # sync_rep_local_step is a LOCAL variable: one per worker session (keyed by its client),
+        # so threads sharing one graph object behave like separate worker processes
+        self._local_steps: Dict[int, int] = {}
         self._setup_done = False
 
     kind = property(lambda self: self._opt.kind)  # type: ignore[assignment]
@@ -180,7 +194,10 @@ class SyncReplicasOptimizer(Optimizer):
         self._setup_done = True
 
     def init_local_step(self, client, layout) -> None:
-        self.local_step = client.read_global_step(layout, self._train_op.global_step.name)
+        self._local_steps[id(client)] = client.read_global_step(layout, self._train_op.global_step.name)
+
+    def get_local_step(self, client) -> int:
+        return self._local_steps.get(id(client), 0)
 
     def init_tokens(self, client, layout, num_tokens: int) -> None:
         gname = self._train_op.global_step.name
@@ -199,11 +216,11 @@ class SyncReplicasOptimizer(Optimizer):
                 if sl.n > 0:
                     per_shard.setdefault(sl.shard, {})[n] = flat[sl.first:sl.first + sl.n]
         for s, gs in per_shard.items():
-            client.call(s, "accum_apply", gs, int(self.local_step))
+            client.call(s, "accum_apply", gs, int(self.get_local_step(client)))
         gname = self._train_op.global_step.name
         gshard = layout[gname].home_shard
         token = client.call(gshard, "queue_dequeue", SYNC_TOKEN_QUEUE, token_timeout)
-        self.local_step = int(token)
+        self._local_steps[id(client)] = int(token)
         return client.read_global_step(layout, gname)
 
     def run_sync_op(self, client, layout, timeout: Optional[float] = None) -> bool:

@@ -83,9 +83,14 @@ def test_mlp_matches_cpu_oracle(opt):
     for a, b in zip(got_l, ref_l):
         assert abs(a - b) <= 0.05 * abs(b) + 0.5, (got_l, ref_l)
     assert got_l[-1] < got_l[0]
+    # Adam's update is ~lr*sign(g) where |g| is tiny, so bf16 rounding flips individual elements:
+    # compare the bulk (mean abs error) tightly and the worst element loosely
+    steps_lr = 12 * {"adam": 0.01, "sgd": 0.001, "momentum": 0.001, "adagrad": 0.01}[opt]
     for n in ref_v:
+        diff = np.abs(got_v[n] - ref_v[n])
         scale = max(1e-3, float(np.abs(ref_v[n]).max()))
-        assert float(np.abs(got_v[n] - ref_v[n]).max()) < 0.08 * scale + 2e-2, n
+        assert float(diff.mean()) < 0.02 * scale + 0.05 * steps_lr, n
+        assert float(diff.max()) < 0.1 * scale + 1.5 * steps_lr, n
     for n, sh in shadows.items():  # the bf16 serving copy tracks the fp32 master
         assert float(np.abs(sh - got_v[n]).max()) <= 0.01 * float(np.abs(got_v[n]).max()) + 1e-6
 

@@ -1,0 +1,123 @@
+"""BASELINE config 1 as an integration test: 1 PS + 2 workers as three OS processes on localhost
+over the TCP transport, driven through the same CLI as the reference."""
+import json
+import os
+import re
+import signal
+import socket
+import subprocess
+import sys
+import time
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_ports(n):
+    socks, ports = [], []
+    for _ in range(n):
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        socks.append(s)
+        ports.append(s.getsockname()[1])
+    for s in socks:
+        s.close()
+    return ports
+
+
+def _cluster_file(tmp_path, n_ps, n_workers):
+    ports = _free_ports(n_ps + n_workers)
+    cfg = {"ps": {"ps:%d" % i: "127.0.0.1:%d" % ports[i] for i in range(n_ps)},
+           "workers": {"worker:%d" % i: "127.0.0.1:%d" % ports[n_ps + i] for i in range(n_workers)}}
+    path = tmp_path / "config.json"
+    path.write_text(json.dumps(cfg))
+    return str(path)
+
+
+def _launch(job, idx, cfg_path, tmp_path, extra=()):
+    env = dict(os.environ, PYTHONPATH=ROOT, PYTHONUNBUFFERED="1", OMP_NUM_THREADS="2")
+    cmd = [sys.executable, os.path.join(ROOT, "run_mnist_distributed.py"), "--job_name", job, "--task_index",
+           str(idx), "--config_file", cfg_path, "--backend", "cpu", "--data_dir", str(tmp_path / "data"),
+           "--log_root", str(tmp_path / "logs"), *extra]
+    return subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, cwd=ROOT)
+
+
+def _finish(p, timeout):
+    try:
+        out, _ = p.communicate(timeout=timeout)
+    except subprocess.TimeoutExpired:
+        p.kill()
+        out, _ = p.communicate()
+        out += "\n<<killed after timeout>>"
+    return out
+
+
+@pytest.mark.slow
+def test_one_ps_two_workers_async(tmp_path):
+    from distributedtensorflow_b200.data import mnist
+    mnist.synthetic_mnist(str(tmp_path / "data"), num_train=2048, num_test=256)
+    cfg = _cluster_file(tmp_path, 1, 2)
+    steps = 40
+    ps = _launch("ps", 0, cfg, tmp_path)
+    w1 = _launch("worker", 1, cfg, tmp_path, ["--max_steps", str(steps)])     # non-chief first: must wait
+    time.sleep(1.0)
+    w0 = _launch("worker", 0, cfg, tmp_path, ["--max_steps", str(steps), "--shutdown_ps_when_done", "true"])
+    out0 = _finish(w0, 240)
+    out1 = _finish(w1, 60)
+    outp = _finish(ps, 30)
+    assert w0.returncode == 0, out0
+    assert w1.returncode == 0, out1
+    assert ps.returncode == 0 and "Close Parameter Server" in outp, outp   # clean PS shutdown
+    pairs = [(float(a), int(b)) for a, b in re.findall(r"loss = ([0-9.]+) \(global step: (\d+)\)", out0)]
+    steps_seen = [s for _, s in pairs]
+    assert steps_seen == sorted(steps_seen) and len(set(steps_seen)) == len(steps_seen)   # monotone
+    assert steps <= steps_seen[-1] <= steps + 1           # StopAtStepHook overshoot <= W - 1
+    assert pairs[-1][0] < pairs[0][0]                     # loss decreases
+    m0 = re.search(r"Worker 0: (\d+) local steps", out0)
+    m1 = re.search(r"Worker 1: (\d+) local steps", out1)
+    total_local = int(m0.group(1)) + int(m1.group(1))
+    # global_step counts applies from ALL workers: sum of local steps == final global step
+    final = max(steps_seen[-1], int(re.search(r"\(global step (\d+)\)", out1).group(1)) if "global step" in out1 else 0)
+    assert steps <= total_local <= steps + 2, (total_local, out0[-400:], out1[-400:])
+    assert int(m1.group(1)) > 0, "the second worker contributed steps"
+    assert os.listdir(tmp_path / "logs"), "chief wrote TensorBoard events"
+
+
+@pytest.mark.slow
+def test_ps_survives_worker_exit_and_worker_reattaches(tmp_path):
+    from distributedtensorflow_b200.data import mnist
+    mnist.synthetic_mnist(str(tmp_path / "data"), num_train=1024, num_test=128)
+    cfg = _cluster_file(tmp_path, 1, 1)
+    ps = _launch("ps", 0, cfg, tmp_path)
+    try:
+        w = _launch("worker", 0, cfg, tmp_path, ["--max_steps", "6"])
+        out_a = _finish(w, 180)
+        assert w.returncode == 0 and "global step: 6" in out_a, out_a
+        # a new chief re-attaches: the PS still holds the variables but this chief re-runs init_op
+        # (no checkpoint_dir), exactly like the reference; training proceeds again to the target
+        w = _launch("worker", 0, cfg, tmp_path, ["--max_steps", "4", "--shutdown_ps_when_done", "true"])
+        out_b = _finish(w, 180)
+        assert w.returncode == 0 and "global step: 4" in out_b, out_b
+        outp = _finish(ps, 30)
+        assert ps.returncode == 0, outp
+    finally:
+        if ps.poll() is None:
+            ps.kill()
+
+
+def test_ps_clean_shutdown_on_sigint(tmp_path):
+    """The reference's README TODO: Ctrl-C must end a parameter server cleanly."""
+    cfg = _cluster_file(tmp_path, 1, 1)
+    ps = _launch("ps", 0, cfg, tmp_path)
+    deadline = time.time() + 60
+    line = ""
+    while time.time() < deadline:
+        line = ps.stdout.readline()
+        if "Started Parameter Server" in line or not line:
+            break
+    assert "Started Parameter Server" in line
+    time.sleep(0.3)
+    ps.send_signal(signal.SIGINT)
+    out = _finish(ps, 20)
+    assert ps.returncode == 0 and "Close Parameter Server" in out, out
