@@ -259,3 +259,116 @@ extern "C" int dtf_refresh_shadow(const float* var, void* shadow, long long n, l
   DTF_LAUNCH_CHECK();
   return 0;
 }
+
+// ================================================================================================
+// dtf_push_apply_static — the same push+apply, for callers that must not allocate.
+//
+// dtf_push_apply needs one word of device scratch (the counter that elects the last CTA) and
+// makes its caller provide it. Some callers have nowhere to get that word from: a parameter-server
+// task that handed the whole HBM budget to its shard arena at start-up, a host thread that must
+// not enter cudaMalloc while the workers' kernels are in flight (cudaMalloc synchronises the
+// device and takes the driver's allocator lock), or a foreign runtime that reaches this library
+// only through the C ABI and owns no allocator we could call. For them the scratch lives inside
+// the library image: a file-scope __device__ array of DTF_PUSH_APPLY_STATIC_SCRATCH_BYTES (256)
+// bytes, which every GPU that loads the library keeps until the process exits.
+//
+// Rules that follow from sharing one array:
+//   * the first call on a device looks up the array's device address (cudaGetSymbolAddress, with
+//     that device current) and caches it; make that first call before starting any stream
+//     capture on that device;
+//   * every call clears the counter on `stream` before its kernel, because the array keeps
+//     whatever the previous call (or an aborted launch) left in it;
+//   * two calls whose kernels overlap on one GPU — different streams, or different host threads —
+//     race on the counter and may elect the wrong "last" CTA: keep calls on one GPU ordered;
+//   * requests beyond DTF_MAX_APPLY_ITEMS slices or DTF_PUSH_APPLY_STATIC_MAX_ELEMS elements per
+//     call are refused; split them or use dtf_push_apply with caller-owned scratch.
+// Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+// ================================================================================================
+namespace dtf {
+
+constexpr int kStaticScratchWords = DTF_PUSH_APPLY_STATIC_SCRATCH_BYTES / 4;
+constexpr int kStaticMaxDevices = 64;
+
+// In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device pointer.
+static __device__ __align__(256) unsigned int g_push_apply_static_scratch[kStaticScratchWords];
+
+static unsigned int* g_static_scratch_dev_ptr[kStaticMaxDevices];  // per device, filled lazily
+
+static int static_scratch_for_current_device(unsigned int** out) {
+  int dev = -1;
+  DTF_CHECK_CUDA(cudaGetDevice(&dev));
+  DTF_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "push_apply_static: device %d out of range", dev);
+  unsigned int* p = __atomic_load_n(&g_static_scratch_dev_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* addr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&addr, g_push_apply_static_scratch);
+    if (e != cudaSuccess || addr == nullptr) {
+      set_error("push_apply_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                cudaGetErrorString(e));
+      return -1;
+    }
+    p = static_cast<unsigned int*>(addr);
+    // concurrent first calls resolve the same address, so a plain publish is enough
+    __atomic_store_n(&g_static_scratch_dev_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace dtf
+
+extern "C" int dtf_push_apply_static(int opt, const dtf_apply_item* items, int n_items,
+                                     const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
+                                     dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
+                                     unsigned long long* step_out, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(items != nullptr && hyper != nullptr, "push_apply_static: items/hyper is null");
+  DTF_REQUIRE(n_items >= 1 && n_items <= DTF_MAX_APPLY_ITEMS,
+              "push_apply_static: %d slices in one call, the limit is %d (split the call)", n_items,
+              DTF_MAX_APPLY_ITEMS);
+  DTF_REQUIRE(!finish || ctrl_for_step != nullptr, "push_apply_static: finish needs ctrl_for_step");
+  DTF_REQUIRE(opt != DTF_OPT_ADAM || ctrl_for_powers != nullptr,
+              "push_apply_static: Adam needs the control block that owns the beta powers");
+  ApplyArgs a;
+  memset(&a, 0, sizeof(a));
+  long long total = 0;
+  int blocks = 0;
+  for (int i = 0; i < n_items; ++i) {
+    DTF_REQUIRE(items[i].n >= 0 && items[i].var && items[i].grad,
+                "push_apply_static: item %d invalid", i);
+    DTF_REQUIRE(opt == DTF_OPT_SGD || items[i].slot0, "push_apply_static: item %d lacks slot0", i);
+    DTF_REQUIRE(opt != DTF_OPT_ADAM || items[i].slot1, "push_apply_static: item %d lacks slot1", i);
+    total += items[i].n;
+    DTF_REQUIRE(total <= DTF_PUSH_APPLY_STATIC_MAX_ELEMS,
+                "push_apply_static: more than %lld elements in one call (limit of the "
+                "no-allocation entry point; split the call or use dtf_push_apply)",
+                (long long)DTF_PUSH_APPLY_STATIC_MAX_ELEMS);
+    a.items[i] = items[i];
+    a.block_start[i] = blocks;
+    blocks += static_cast<int>((items[i].n + APPLY_CHUNK - 1) / APPLY_CHUNK);
+  }
+  a.block_start[n_items] = blocks;
+  if (blocks == 0) blocks = 1;  // all slices empty: one CTA still performs the _finish
+  a.n_items = n_items;
+  a.total_blocks = blocks;
+  a.h = *hyper;
+  a.ctrl_powers = ctrl_for_powers;
+  a.ctrl_step = ctrl_for_step;
+  a.finish = finish;
+  a.worker_id = worker_id;
+  a.step_out = step_out;
+  unsigned int* scratch = nullptr;
+  if (static_scratch_for_current_device(&scratch) != 0) return -1;
+  a.block_counter = scratch;
+  // the array keeps the previous call's contents: the election counter must start at zero
+  DTF_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(unsigned int), stream));
+  switch (opt) {
+    case DTF_OPT_SGD: push_apply_kernel<DTF_OPT_SGD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_MOMENTUM: push_apply_kernel<DTF_OPT_MOMENTUM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_ADAGRAD: push_apply_kernel<DTF_OPT_ADAGRAD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_ADAM: push_apply_kernel<DTF_OPT_ADAM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    default: DTF_REQUIRE(false, "push_apply_static: unknown optimizer %d", opt);
+  }
+  DTF_LAUNCH_CHECK();
+  return 0;
+}

@@ -113,6 +113,29 @@ int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
                    dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                    unsigned long long* step_out, unsigned int* block_counter, void* stream);
 
+/* dtf_push_apply for callers that cannot allocate device memory (no counterpart in the reference:
+ * TensorFlow's ApplyAdam kernels allocate through the TF runtime). Same arguments and result as
+ * dtf_push_apply minus `block_counter`: the CTA-election counter lives in a 256-byte __device__
+ * array inside this library, resident on every GPU that loads it until the process exits.
+ * Meant for a PS task whose whole HBM budget is already committed to its shard arena, for a host
+ * thread that must not enter cudaMalloc (a device-wide synchronisation) while worker kernels are
+ * in flight, and for foreign runtimes that reach this library only through the C ABI.
+ *   - The first call on each device resolves the array's address (that device must be current);
+ *     issue it before any stream capture on that device.
+ *   - The counter is cleared on `stream` by every call; the array otherwise keeps the previous
+ *     call's contents.
+ *   - All calls on one GPU share the array: calls whose kernels overlap there race. Keep them
+ *     ordered (one stream, or events between streams).
+ *   - More than DTF_MAX_APPLY_ITEMS slices or DTF_PUSH_APPLY_STATIC_MAX_ELEMS elements per call
+ *     are refused with an error; split the call or use dtf_push_apply.
+ * It never calls cudaMalloc / cudaFree or an allocating library routine. */
+#define DTF_PUSH_APPLY_STATIC_SCRATCH_BYTES 256
+#define DTF_PUSH_APPLY_STATIC_MAX_ELEMS (1LL << 28)   /* 268 435 456 elements (1 GiB of fp32) */
+int dtf_push_apply_static(int opt, const dtf_apply_item* items, int n_items,
+                          const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
+                          dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
+                          unsigned long long* step_out, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * K11: bulk parameter pull, peer -> local (one launch for a list of tensors). Reference: the
  * per-tensor RecvTensor RPCs of every mon_sess.run (run_mnist_distributed.py:150,161).
