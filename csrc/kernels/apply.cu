@@ -61,6 +61,8 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
   __shared__ int s_item;
   __shared__ float s_lr_t;
   __shared__ unsigned int s_last;
+  griddep_wait();
+  griddep_launch();
   if (threadIdx.x == 0) {
     int it = 0;
     while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
@@ -86,31 +88,42 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
                           (it.first % 4 == 0) &&
                           ((reinterpret_cast<uintptr_t>(shadow) & 7) == 0);
 
+  // Phase 1: issue every 16-byte load of this thread's APPLY_UNROLL vectors before using any of
+  // them (up to 16 requests in flight per thread; over NVLink each one is a ~2 us round trip).
+  const bool rmw = !(OPT == DTF_OPT_SGD && a.h.atomic_sgd);
+  float4 ldg_[APPLY_UNROLL], ldv_[APPLY_UNROLL], ld0_[APPLY_UNROLL], ld1_[APPLY_UNROLL];
+#pragma unroll
+  for (int u = 0; u < APPLY_UNROLL; ++u) {
+    const long long i = base + (static_cast<long long>(u) * APPLY_THREADS + threadIdx.x) * APPLY_VEC;
+    ldg_[u] = ldv_[u] = ld0_[u] = ld1_[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (vec_ok && i + APPLY_VEC <= it.n) {
+      ldg_[u] = *reinterpret_cast<const float4*>(it.grad + i);
+      if (rmw) {
+        ldv_[u] = *reinterpret_cast<const float4*>(it.var + i);
+        if (OPT != DTF_OPT_SGD) ld0_[u] = *reinterpret_cast<const float4*>(it.slot0 + i);
+        if (OPT == DTF_OPT_ADAM) ld1_[u] = *reinterpret_cast<const float4*>(it.slot1 + i);
+      }
+    }
+  }
+  // Phase 2: update + store.
 #pragma unroll
   for (int u = 0; u < APPLY_UNROLL; ++u) {
     const long long i = base + (static_cast<long long>(u) * APPLY_THREADS + threadIdx.x) * APPLY_VEC;
     if (i >= it.n) continue;
     if (vec_ok && i + APPLY_VEC <= it.n) {
-      const float4 g4 = *reinterpret_cast<const float4*>(it.grad + i);
+      const float4 g4 = ldg_[u];
       float g[4] = {g4.x * a.h.grad_scale, g4.y * a.h.grad_scale, g4.z * a.h.grad_scale,
                     g4.w * a.h.grad_scale};
-      if (OPT == DTF_OPT_SGD && a.h.atomic_sgd) {
+      if (!rmw) {
         // write-only push: var += -lr * g via reduction atomics at the owner's L2
 #pragma unroll
         for (int j = 0; j < 4; ++j) red_add_f32_sys(it.var + i + j, -a.h.lr * g[j]);
         continue;  // shadow is refreshed by the owner in this mode
       }
-      float4 v4 = *reinterpret_cast<float4*>(it.var + i);
+      const float4 v4 = ldv_[u];
       float v[4] = {v4.x, v4.y, v4.z, v4.w};
-      float s0[4] = {0, 0, 0, 0}, s1[4] = {0, 0, 0, 0};
-      if (OPT != DTF_OPT_SGD) {
-        const float4 t = *reinterpret_cast<float4*>(it.slot0 + i);
-        s0[0] = t.x; s0[1] = t.y; s0[2] = t.z; s0[3] = t.w;
-      }
-      if (OPT == DTF_OPT_ADAM) {
-        const float4 t = *reinterpret_cast<float4*>(it.slot1 + i);
-        s1[0] = t.x; s1[1] = t.y; s1[2] = t.z; s1[3] = t.w;
-      }
+      float s0[4] = {ld0_[u].x, ld0_[u].y, ld0_[u].z, ld0_[u].w};
+      float s1[4] = {ld1_[u].x, ld1_[u].y, ld1_[u].z, ld1_[u].w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) update_one<OPT>(g[j], v[j], s0[j], s1[j], a.h, lr_t);
       *reinterpret_cast<float4*>(it.var + i) = make_float4(v[0], v[1], v[2], v[3]);
@@ -239,10 +252,10 @@ extern "C" int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
   a.step_out = step_out;
   a.block_counter = block_counter;
   switch (opt) {
-    case DTF_OPT_SGD: push_apply_kernel<DTF_OPT_SGD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
-    case DTF_OPT_MOMENTUM: push_apply_kernel<DTF_OPT_MOMENTUM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
-    case DTF_OPT_ADAGRAD: push_apply_kernel<DTF_OPT_ADAGRAD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
-    case DTF_OPT_ADAM: push_apply_kernel<DTF_OPT_ADAM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_SGD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_SGD>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_MOMENTUM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_MOMENTUM>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAGRAD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAGRAD>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAM>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
     default: DTF_REQUIRE(false, "push_apply: unknown optimizer %d", opt);
   }
   DTF_LAUNCH_CHECK();
@@ -363,10 +376,10 @@ extern "C" int dtf_push_apply_static(int opt, const dtf_apply_item* items, int n
   // the array keeps the previous call's contents: the election counter must start at zero
   DTF_CHECK_CUDA(cudaMemsetAsync(scratch, 0, sizeof(unsigned int), stream));
   switch (opt) {
-    case DTF_OPT_SGD: push_apply_kernel<DTF_OPT_SGD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
-    case DTF_OPT_MOMENTUM: push_apply_kernel<DTF_OPT_MOMENTUM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
-    case DTF_OPT_ADAGRAD: push_apply_kernel<DTF_OPT_ADAGRAD><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
-    case DTF_OPT_ADAM: push_apply_kernel<DTF_OPT_ADAM><<<blocks, APPLY_THREADS, 0, stream>>>(a); break;
+    case DTF_OPT_SGD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_SGD>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_MOMENTUM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_MOMENTUM>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAGRAD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAGRAD>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAM>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
     default: DTF_REQUIRE(false, "push_apply_static: unknown optimizer %d", opt);
   }
   DTF_LAUNCH_CHECK();

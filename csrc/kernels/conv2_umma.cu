@@ -77,6 +77,9 @@ __device__ __forceinline__ uint32_t conv_setup(const ConvSmem& s, int warp, uint
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  // PDL: the prologue above overlapped the previous kernel; its outputs are needed from here on
+  griddep_wait();
+  griddep_launch();
   return *s.tmem_slot;
 }
 
@@ -92,14 +95,14 @@ __device__ __forceinline__ void conv_teardown(int warp, uint32_t tmem_base, uint
 // ---------------------------------------------------------------------------------------------
 // forward: conv + bias + ReLU + 2x2 max-pool
 // ---------------------------------------------------------------------------------------------
-constexpr int FW_STAGES = 3;
+constexpr int FW_STAGES = 8;
 constexpr int FW_A_TAP = 128 * CV_C1 * 2;        // 8 KB per tap
-constexpr int FW_A_BYTES = 5 * FW_A_TAP;         // one filter row: 40 KB
-constexpr int FW_B_BYTES = 160 * CV_C2 * 2;      // 5 taps x 32 cin rows x 128 B = 20 KB
+constexpr int FW_A_BYTES = FW_A_TAP;             // one filter tap: 8 KB
+constexpr int FW_B_BYTES = 32 * CV_C2 * 2;       // 32 cin rows x 128 B = 4 KB
 constexpr int FW_STAGE = FW_A_BYTES + FW_B_BYTES;
 constexpr int FW_SMEM = FW_STAGES * FW_STAGE + 1024 + 256;
 
-__global__ void __launch_bounds__(CV_THREADS, 1)
+__global__ void __launch_bounds__(CV_THREADS, 2)
 conv2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x,   // pool1p [B,18,18,32]
                  const __grid_constant__ CUtensorMap tmap_w,   // w2 [800,64]
                  const ConvParams p) {
@@ -110,42 +113,38 @@ conv2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x,   // pool1p [B,18,1
   const int n0 = (blockIdx.x / CV_YT) * 4;
   const int y0 = (blockIdx.x % CV_YT) * 2;
 
+  // One ring slot per filter tap (A 8 KB + B 4 KB): 8 slots = 96 KB, so two CTAs share an SM and
+  // one CTA's prologue / epilogue overlaps the other's MMAs.
   if (warp == 0) {
     if (elect_one()) {
-      for (int r = 0; r < 5; ++r) {
-        const int s = r % FW_STAGES;
-        const uint32_t ph = (r / FW_STAGES) & 1;
+      for (int t = 0; t < 25; ++t) {
+        const int s = t % FW_STAGES;
+        const uint32_t ph = (t / FW_STAGES) & 1;
         mbar_wait(&sm.empty_bar[s], ph ^ 1);
         uint8_t* a_dst = sm.tiles + s * FW_STAGE;
         uint8_t* b_dst = a_dst + FW_A_BYTES;
         mbar_arrive_expect_tx(&sm.full_bar[s], FW_STAGE);
-#pragma unroll
-        for (int t = 0; t < 5; ++t)
-          tma_load_4d(a_dst + t * FW_A_TAP, &tmap_x, &sm.full_bar[s], 0, t, y0 + r, n0);
-        tma_load_2d(b_dst, &tmap_w, &sm.full_bar[s], 0, r * 160);
+        tma_load_4d(a_dst, &tmap_x, &sm.full_bar[s], 0, t % 5, y0 + t / 5, n0);
+        tma_load_2d(b_dst, &tmap_w, &sm.full_bar[s], 0, t * 32);
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, 64, /*a_mn=*/false, /*b_mn=*/true);
-      for (int r = 0; r < 5; ++r) {
-        const int s = r % FW_STAGES;
-        const uint32_t ph = (r / FW_STAGES) & 1;
+      for (int t = 0; t < 25; ++t) {
+        const int s = t % FW_STAGES;
+        const uint32_t ph = (t / FW_STAGES) & 1;
         mbar_wait(&sm.full_bar[s], ph);
         tc_fence_after();
         const uint32_t a_base = smem_u32(sm.tiles + s * FW_STAGE);
         const uint32_t b_base = a_base + FW_A_BYTES;
 #pragma unroll
-        for (int t = 0; t < 5; ++t) {
-#pragma unroll
-          for (int kk = 0; kk < 2; ++kk) {
-            // A: K-major, 64 B rows, 64B swizzle: 8-row groups 512 B apart.
-            const uint64_t adesc = umma_smem_desc(a_base + t * FW_A_TAP + kk * 32, 16, 512, 4);
-            // B: MN-major (cout contiguous), 128B swizzle, K rows of 128 B.
-            const uint64_t bdesc =
-                umma_smem_desc(b_base + (t * 32 + kk * 16) * 128, 8192, 1024, 2);
-            umma_bf16(tmem_base, adesc, bdesc, idesc, (r > 0 || t > 0 || kk > 0) ? 1u : 0u);
-          }
+        for (int kk = 0; kk < 2; ++kk) {
+          // A: K-major, 64 B rows, 64B swizzle: 8-row groups 512 B apart.
+          const uint64_t adesc = umma_smem_desc(a_base + kk * 32, 16, 512, 4);
+          // B: MN-major (cout contiguous), 128B swizzle, K rows of 128 B, 16 rows per K-slice.
+          const uint64_t bdesc = umma_smem_desc(b_base + kk * 2048, 8192, 1024, 2);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (t > 0 || kk > 0) ? 1u : 0u);
         }
         umma_commit(&sm.empty_bar[s]);
       }
@@ -204,13 +203,13 @@ conv2_fwd_kernel(const __grid_constant__ CUtensorMap tmap_x,   // pool1p [B,18,1
 // ---------------------------------------------------------------------------------------------
 // dgrad: dpool1[pixels, 32] = sum over taps of dconv2p box * W2[flipped tap]^T
 // ---------------------------------------------------------------------------------------------
-constexpr int DG_STAGES = 6;
+constexpr int DG_STAGES = 5;
 constexpr int DG_A_BYTES = 128 * CV_C2 * 2;  // 16 KB
 constexpr int DG_B_BYTES = 32 * CV_C2 * 2;   // 4 KB
 constexpr int DG_STAGE = DG_A_BYTES + DG_B_BYTES;
 constexpr int DG_SMEM = DG_STAGES * DG_STAGE + 1024 + 256;
 
-__global__ void __launch_bounds__(CV_THREADS, 1)
+__global__ void __launch_bounds__(CV_THREADS, 2)
 conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy,  // dconv2p [B,18,18,64]
                    const __grid_constant__ CUtensorMap tmap_w,   // w2 [800,64], box {64,32}
                    const ConvParams p) {
@@ -401,7 +400,7 @@ extern "C" int dtf_conv2_fwd(const void* pool1p, const void* w2, const float* b2
                              unsigned char* amax2, int B, void* stream) {
   CUtensorMap tx, tw;
   if (make_act_tmap(&tx, pool1p, B, CV_C1, 64) != 0) return -1;
-  if (make_w2_tmap(&tw, w2, 160) != 0) return -1;
+  if (make_w2_tmap(&tw, w2, 32) != 0) return -1;
   ConvParams p;
   memset(&p, 0, sizeof(p));
   p.B = B;
@@ -410,8 +409,8 @@ extern "C" int dtf_conv2_fwd(const void* pool1p, const void* w2, const float* b2
   p.out = reinterpret_cast<__nv_bfloat16*>(pool2);
   p.amax = amax2;
   if (set_smem(conv2_fwd_kernel, FW_SMEM) != 0) return -1;
-  conv2_fwd_kernel<<<p.tiles, CV_THREADS, FW_SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(tx, tw, p);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(conv2_fwd_kernel, dim3(p.tiles), dim3(CV_THREADS), FW_SMEM,
+                               reinterpret_cast<cudaStream_t>(stream), tx, tw, p));
   return 0;
 }
 
@@ -426,8 +425,8 @@ extern "C" int dtf_conv2_dgrad(const void* dconv2p, const void* w2, void* dpool1
   p.tiles = ceil_div(B, 4) * CV_YT;
   p.out = reinterpret_cast<__nv_bfloat16*>(dpool1);
   if (set_smem(conv2_dgrad_kernel, DG_SMEM) != 0) return -1;
-  conv2_dgrad_kernel<<<p.tiles, CV_THREADS, DG_SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(ty, tw, p);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(conv2_dgrad_kernel, dim3(p.tiles), dim3(CV_THREADS), DG_SMEM,
+                               reinterpret_cast<cudaStream_t>(stream), ty, tw, p));
   return 0;
 }
 
@@ -447,7 +446,7 @@ extern "C" int dtf_conv2_wgrad(const void* pool1p, const void* dconv2p, float* d
   p.dw_accum = dw2_accum;
   if (set_smem(conv2_wgrad_kernel, WG_SMEM) != 0) return -1;
   dim3 grid(7, splits);
-  conv2_wgrad_kernel<<<grid, CV_THREADS, WG_SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(tx, ty, p);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(conv2_wgrad_kernel, grid, dim3(CV_THREADS), WG_SMEM,
+                               reinterpret_cast<cudaStream_t>(stream), tx, ty, p));
   return 0;
 }

@@ -34,6 +34,8 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   __shared__ float w[25][C1_CH];
   __shared__ float bias[C1_CH];
   const int n = blockIdx.x;
+  griddep_wait();
+  griddep_launch();
   load_image_padded(img, x_u8, x_f32, scale, n);
   for (int i = threadIdx.x; i < 25 * C1_CH; i += blockDim.x) w[i / C1_CH][i % C1_CH] = w1[i];
   if (threadIdx.x < C1_CH) bias[threadIdx.x] = b1[threadIdx.x];
@@ -97,30 +99,43 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
                  float* __restrict__ dw1_accum, float* __restrict__ db1_accum) {
   __shared__ float img[C1_PAD][C1_PAD];
   __shared__ float g[C1_OUT * C1_OUT][C1_CH];          // 25 KB
-  __shared__ unsigned char am[C1_OUT * C1_OUT][C1_CH]; // 6 KB
+  __shared__ __align__(16) unsigned char am[C1_OUT * C1_OUT][C1_CH]; // 6 KB
   const int n = blockIdx.x;
+  griddep_wait();
+  griddep_launch();
   load_image_padded(img, x_u8, x_f32, scale, n);
-  for (int i = threadIdx.x; i < C1_OUT * C1_OUT * C1_CH; i += blockDim.x) {
-    const int pp = i / C1_CH, c = i % C1_CH;
+  // stage the ReLU-masked gradient and the argmax map: one (pooled pixel, 8 channels) item per
+  // thread, 16-byte loads, a single pass (784 items <= 800 threads)
+  for (int item = threadIdx.x; item < C1_OUT * C1_OUT * 4; item += blockDim.x) {
+    const int pp = item >> 2, cg = item & 3;
     const int py = pp / C1_OUT, px = pp % C1_OUT;
-    const float act = __bfloat162float(
-        pool1p[((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + c]);
-    const float d = __bfloat162float(dpool1[static_cast<size_t>(n) * (C1_OUT * C1_OUT * C1_CH) + i]);
-    g[pp][c] = (act > 0.f) ? d : 0.f;  // ReLU gradient through the max-pool
-    am[pp][c] = amax1[static_cast<size_t>(n) * (C1_OUT * C1_OUT * C1_CH) + i];
+    const uint4 av = *reinterpret_cast<const uint4*>(
+        pool1p + ((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + cg * 8);
+    const size_t o = (static_cast<size_t>(n) * (C1_OUT * C1_OUT) + pp) * C1_CH + cg * 8;
+    const uint4 dv = *reinterpret_cast<const uint4*>(dpool1 + o);
+    const uint2 mv = *reinterpret_cast<const uint2*>(amax1 + o);
+    const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(&av);
+    const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(&dv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j)  // ReLU gradient through the max-pool
+      g[pp][cg * 8 + j] = (__bfloat162float(a[j]) > 0.f) ? __bfloat162float(d[j]) : 0.f;
+    *reinterpret_cast<uint2*>(&am[pp][cg * 8]) = mv;
   }
   __syncthreads();
   const int tap = threadIdx.x >> 5, c = threadIdx.x & 31;
   const int r = tap / 5, s = tap % 5;
-  float acc = 0.f, accb = 0.f;
-  for (int pp = 0; pp < C1_OUT * C1_OUT; ++pp) {
-    const int py = pp / C1_OUT, px = pp % C1_OUT;
-    const int a = am[pp][c];
-    const float gv = g[pp][c];
-    acc = fmaf(img[2 * py + (a >> 1) + r][2 * px + (a & 1) + s], gv, acc);
-    accb += gv;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f}, accb = 0.f;
+  for (int py = 0; py < C1_OUT; ++py) {
+#pragma unroll
+    for (int px = 0; px < C1_OUT; ++px) {  // 14 independent smem chains per row
+      const int pp = py * C1_OUT + px;
+      const int a = am[pp][c];
+      const float gv = g[pp][c];
+      acc[px & 3] = fmaf(img[2 * py + (a >> 1) + r][2 * px + (a & 1) + s], gv, acc[px & 3]);
+      accb += gv;
+    }
   }
-  atomicAdd(&dw1_accum[tap * C1_CH + c], acc);
+  atomicAdd(&dw1_accum[tap * C1_CH + c], (acc[0] + acc[1]) + (acc[2] + acc[3]));
   if (tap == 0) atomicAdd(&db1_accum[c], accb);
 }
 
@@ -133,9 +148,13 @@ pool2_bwd_kernel(const __nv_bfloat16* __restrict__ dpool2, int ld, const __nv_bf
   __shared__ float s_db[64];
   if (threadIdx.x < 64) s_db[threadIdx.x] = 0.f;
   __syncthreads();
+  griddep_wait();
+  griddep_launch();
   const int total = B * 49 * 8;
-  for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < total; item += gridDim.x * blockDim.x) {
-    const int cg = item & 7;
+  const int stride = gridDim.x * blockDim.x;             // multiple of 8: cg is fixed per thread
+  const int cg = threadIdx.x & 7;
+  float dbs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int item = blockIdx.x * blockDim.x + threadIdx.x; item < total; item += stride) {
     const int pp = (item >> 3) % 49;
     const int n = (item >> 3) / 49;
     const int py = pp / 7, px = pp % 7;
@@ -152,7 +171,7 @@ pool2_bwd_kernel(const __nv_bfloat16* __restrict__ dpool2, int ld, const __nv_bf
       const __nv_bfloat16 gv = on ? d[c] : __float2bfloat16(0.f);
 #pragma unroll
       for (int q = 0; q < 4; ++q) out[q][c] = (m[c] == q) ? gv : __float2bfloat16(0.f);
-      if (on) atomicAdd(&s_db[cg * 8 + c], __bfloat162float(d[c]));
+      if (on) dbs[c] += __bfloat162float(d[c]);
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -160,6 +179,15 @@ pool2_bwd_kernel(const __nv_bfloat16* __restrict__ dpool2, int ld, const __nv_bf
       *reinterpret_cast<uint4*>(dconv2p + ((static_cast<size_t>(n) * 18 + y) * 18 + x) * 64 + cg * 8) =
           *reinterpret_cast<const uint4*>(out[q]);
     }
+  }
+  // bias gradient: the 4 lanes of a warp that share a channel group fold with shuffles, then one
+  // shared-memory atomic per (warp, channel)
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    float v = dbs[c];
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    if ((threadIdx.x & 31) < 8) atomicAdd(&s_db[cg * 8 + c], v);
   }
   __syncthreads();
   if (threadIdx.x < 64) atomicAdd(&db2_accum[threadIdx.x], s_db[threadIdx.x]);
@@ -173,9 +201,9 @@ extern "C" int dtf_conv1_fwd(const unsigned char* x_u8, const float* x_f32, floa
                              const float* w1, const float* b1, void* pool1p,
                              unsigned char* amax1, int B, void* stream) {
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_fwd: pass exactly one of x_u8/x_f32");
-  conv1_fwd_kernel<<<B, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      x_u8, x_f32, scale, w1, b1, reinterpret_cast<__nv_bfloat16*>(pool1p), amax1);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B), dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale, w1, b1,
+                               reinterpret_cast<__nv_bfloat16*>(pool1p), amax1));
   return 0;
 }
 
@@ -183,10 +211,11 @@ extern "C" int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, floa
                              const void* dpool1, const void* pool1p, const unsigned char* amax1,
                              float* dw1_accum, float* db1_accum, int B, void* stream) {
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_bwd: pass exactly one of x_u8/x_f32");
-  conv1_bwd_kernel<<<B, 800, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      x_u8, x_f32, scale, reinterpret_cast<const __nv_bfloat16*>(dpool1),
-      reinterpret_cast<const __nv_bfloat16*>(pool1p), amax1, dw1_accum, db1_accum);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(conv1_bwd_kernel, dim3(B), dim3(800), 0,
+                               reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale,
+                               reinterpret_cast<const __nv_bfloat16*>(dpool1),
+                               reinterpret_cast<const __nv_bfloat16*>(pool1p),
+                               static_cast<const unsigned char*>(amax1), dw1_accum, db1_accum));
   return 0;
 }
 
@@ -197,10 +226,10 @@ extern "C" int dtf_pool2_bwd(const void* dpool2, int ld_dpool2, const void* pool
   const int total = B * 49 * 8;
   int blocks = ceil_div(total, 256);
   if (blocks > 148 * 4) blocks = 148 * 4;
-  pool2_bwd_kernel<<<blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(dpool2), ld_dpool2,
-      reinterpret_cast<const __nv_bfloat16*>(pool2), amax2,
-      reinterpret_cast<__nv_bfloat16*>(dconv2p), db2_accum, B);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(pool2_bwd_kernel, dim3(blocks), dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream),
+                               reinterpret_cast<const __nv_bfloat16*>(dpool2), ld_dpool2,
+                               reinterpret_cast<const __nv_bfloat16*>(pool2), amax2,
+                               reinterpret_cast<__nv_bfloat16*>(dconv2p), db2_accum, B));
   return 0;
 }

@@ -10,6 +10,8 @@ namespace dtf {
 __global__ void u8_to_bf16_kernel(const unsigned char* __restrict__ src,
                                   __nv_bfloat16* __restrict__ dst, int rows, int cols, int ldd,
                                   float scale) {
+  griddep_wait();
+  griddep_launch();
   const long long total = static_cast<long long>(rows) * ldd;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -21,6 +23,8 @@ __global__ void u8_to_bf16_kernel(const unsigned char* __restrict__ src,
 
 __global__ void f32_to_bf16_kernel(const float* __restrict__ src, int lds,
                                    __nv_bfloat16* __restrict__ dst, int ldd, int rows, int cols) {
+  griddep_wait();
+  griddep_launch();
   const long long total = static_cast<long long>(rows) * ldd;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -34,6 +38,8 @@ __global__ void __launch_bounds__(256)
 colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int rows, int cols,
                    float* __restrict__ out_accum, int rows_per_block) {
   __shared__ float s[8][33];
+  griddep_wait();
+  griddep_launch();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + tx;
   const int r0 = blockIdx.y * rows_per_block;
@@ -52,6 +58,8 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int rows, int c
 }
 
 __global__ void fill_u32_kernel(unsigned int* __restrict__ dst, unsigned int v, long long n) {
+  griddep_wait();
+  griddep_launch();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
     dst[i] = v;
@@ -71,37 +79,38 @@ using namespace dtf;
 extern "C" int dtf_u8_to_bf16(const unsigned char* src, void* dst, int rows, int cols, int ldd,
                               float scale, void* stream) {
   const long long total = static_cast<long long>(rows) * ldd;
-  u8_to_bf16_kernel<<<grid_for(total, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      src, reinterpret_cast<__nv_bfloat16*>(dst), rows, cols, ldd, scale);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(u8_to_bf16_kernel, dim3(grid_for(total, 256)), dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream), src,
+                               reinterpret_cast<__nv_bfloat16*>(dst), rows, cols, ldd, scale));
   return 0;
 }
 
 extern "C" int dtf_f32_to_bf16(const float* src, int lds, void* dst, int ldd, int rows, int cols,
                                void* stream) {
   const long long total = static_cast<long long>(rows) * ldd;
-  f32_to_bf16_kernel<<<grid_for(total, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, rows, cols);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(f32_to_bf16_kernel, dim3(grid_for(total, 256)), dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream), src, lds,
+                               reinterpret_cast<__nv_bfloat16*>(dst), ldd, rows, cols));
   return 0;
 }
 
 extern "C" int dtf_colsum_bf16(const void* x, int ldx, int rows, int cols, float* out_accum,
                                void* stream) {
-  int ysplit = ceil_div(rows, 256);
+  int ysplit = ceil_div(rows, 32);  // >= 128 CTAs for the [128, 1024] activations of the CNN
   if (ysplit > 64) ysplit = 64;
   const int rpb = ceil_div(rows, ysplit);
   dim3 grid(ceil_div(cols, 32), ceil_div(rows, rpb));
-  colsum_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), ldx, rows, cols, out_accum, rpb);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(colsum_bf16_kernel, grid, dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream),
+                               reinterpret_cast<const __nv_bfloat16*>(x), ldx, rows, cols, out_accum,
+                               rpb));
   return 0;
 }
 
 extern "C" int dtf_fill_u32(void* dst, unsigned int value, long long n_words, void* stream) {
   if (n_words <= 0) return 0;
-  fill_u32_kernel<<<grid_for(n_words, 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<unsigned int*>(dst), value, n_words);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(fill_u32_kernel, dim3(grid_for(n_words, 256)), dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream),
+                               reinterpret_cast<unsigned int*>(dst), value, n_words));
   return 0;
 }

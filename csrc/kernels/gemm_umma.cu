@@ -9,7 +9,6 @@
 //   warp 2     TMEM allocator tcgen05.alloc / dealloc of BN fp32 columns
 //   warps 4-7  epilogue       tcgen05.ld (thread = accumulator row), fused bias / ReLU /
 //                             ReLU-grad mask / scale, bf16 or fp32 store, or red.global.add
-//                             (split-K and gradient accumulation into peer memory)
 //
 // Both operands may be K-major (the reduction dim is contiguous in memory) or MN-major (the
 // M/N dim is contiguous), so forward (X*W), input-gradient (dY*W^T) and weight-gradient (X^T*dY)
@@ -21,6 +20,15 @@
 // serving copy): the TMA descriptor is simply encoded on the peer-mapped address, which fuses the
 // parameter pull into the first GEMM (reference: the _Recv of hid_w feeding MatMul,
 // templates/00_mnist_replica.py:160 / run_mnist_distributed.py:67).
+//
+// The MNIST shapes are skinny (M = batch = 128): a 128 x 1024 x 3136 layer has only 8-16 output
+// tiles for 148 SMs. Two remedies live here:
+//   * the smem ring depth is a launch parameter, so short-K problems take little smem and
+//     several CTAs share an SM;
+//   * split-K with an in-kernel fix-up: every K-slice CTA adds its partial tile into an fp32
+//     workspace with red.global.add.v4.f32, bumps a per-tile counter, and the LAST slice to arrive
+//     re-reads the summed tile from L2 and runs the full epilogue (bias / ReLU / mask / bf16), so
+//     fused epilogues survive splitting and no second kernel is needed.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "../../include/dtf_b200.h"
@@ -30,19 +38,22 @@ namespace dtf {
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int GEMM_THREADS = 256;
+constexpr int GEMM_MAX_STAGES = 6;
 
 template <int BN>
 struct GemmCfg {
   static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;  // 16 KB
   static constexpr int B_BYTES = BN * GEMM_BK * 2;       // 8 / 16 KB
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN <= 64) ? 6 : 5;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int MAX_STAGES = (BN <= 64) ? 6 : 5;
+  static constexpr int smem_bytes(int stages) { return stages * STAGE_BYTES + 1024 + 256; }
 };
 
 struct GemmParams {
   int M, N, K;
   int kb_per_split;  // k-blocks (of 64) handled by one blockIdx.z
+  int num_stages;
+  int splits;
   // epilogue
   void* out;
   int ldo;
@@ -54,21 +65,98 @@ struct GemmParams {
   int ldmask;
   int reduce;  // red.global.add.f32 into out instead of a store
   float alpha;
+  // split-K fix-up (splits > 1 && !reduce)
+  float* ws;                // [M, ldws] fp32, zero on entry
+  int ldws;
+  unsigned int* counters;   // one per output tile, zero on entry (self-resetting)
 };
+
+// Applies the fused epilogue to 32 consecutive accumulator columns of row m and stores them.
+__device__ __forceinline__ void gemm_epilogue_store(const GemmParams& p, int m, int nb, float (&v)[32]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+  if (p.bias != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
+  }
+  if (p.relu) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+  }
+  if (p.mask != nullptr) {
+    const __nv_bfloat16* mrow = p.mask + static_cast<size_t>(m) * p.ldmask + nb;
+    if ((p.ldmask & 7) == 0 && nb + 32 <= p.ldmask) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        uint4 mv = *reinterpret_cast<const uint4*>(mrow + g * 8);
+        const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (!(__bfloat162float(mb[j]) > 0.f)) v[g * 8 + j] = 0.f;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (nb + j < p.ldmask && !(__bfloat162float(mrow[j]) > 0.f)) v[j] = 0.f;
+    }
+  }
+  if (p.out_f32) {
+    float* orow = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
+    if (p.reduce) {
+      if ((p.ldo & 3) == 0 && nb + 32 <= p.n_store) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) red_add_v4_f32_sys(orow + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (nb + j < p.n_store) red_add_f32_sys(orow + j, v[j]);
+      }
+    } else if ((p.ldo & 3) == 0 && nb + 32 <= p.n_store) {
+#pragma unroll
+      for (int g = 0; g < 8; ++g)
+        *reinterpret_cast<float4*>(orow + g * 4) =
+            make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (nb + j < p.n_store) orow[j] = v[j];
+    }
+  } else {
+    __nv_bfloat16* orow =
+        reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
+    if ((p.ldo & 7) == 0 && nb + 32 <= p.n_store) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        uint4 o;
+        o.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
+        o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
+        o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
+        o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
+        *reinterpret_cast<uint4*>(orow + g * 8) = o;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (nb + j < p.n_store) orow[j] = __float2bfloat16(v[j]);
+    }
+  }
+}
 
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
                  const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
-  constexpr int S = Cfg::STAGES;
+  const int S = p.num_stages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S * Cfg::STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + S;
-  uint64_t* tmem_full_bar = empty_bar + S;
+  uint64_t* empty_bar = full_bar + GEMM_MAX_STAGES;
+  uint64_t* tmem_full_bar = empty_bar + GEMM_MAX_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint32_t* last_flag = tmem_slot + 1;
 
   const int warp = threadIdx.x >> 5;
   const int n0 = blockIdx.x * BN;
@@ -99,12 +187,16 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // PDL: everything above overlapped the previous kernel; its outputs are needed from here on.
+  griddep_wait();
+  griddep_launch();
+
   if (warp == 0) {
     // ------------------------------ TMA producer ------------------------------
     if (elect_one()) {
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < num_kb; ++i) {
-        const int s = i % S;
-        const uint32_t ph = (i / S) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
         uint8_t* a_dst = smem + s * Cfg::STAGE_BYTES;
         uint8_t* b_dst = a_dst + Cfg::A_BYTES;
@@ -124,15 +216,16 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
           for (int c = 0; c < BN / 64; ++c)  // box {64 n, 64 k}
             tma_load_2d(b_dst + c * 8192, &tmap_b, &full_bar[s], n0 + c * 64, k0);
         }
+        if (++s == S) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ------------------------------ MMA issuer --------------------------------
     if (elect_one()) {
       constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < num_kb; ++i) {
-        const int s = i % S;
-        const uint32_t ph = (i / S) & 1;
         mbar_wait(&full_bar[s], ph);
         tc_fence_after();
         const uint32_t a_base = smem_u32(smem + s * Cfg::STAGE_BYTES);
@@ -149,6 +242,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
           umma_bf16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(&empty_bar[s]);  // frees the smem slot once these MMAs have read it
+        if (++s == S) { s = 0; ph ^= 1; }
       }
       umma_commit(tmem_full_bar);  // accumulator complete
     }
@@ -162,6 +256,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
       tc_fence_after();
     }
     const bool row_ok = m < p.M;
+    const bool fixup = p.splits > 1 && !p.reduce;
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       uint32_t r[32];
@@ -176,66 +271,44 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (!row_ok || nb >= p.n_store) continue;
       float v[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
-      if (p.bias != nullptr) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (nb + j < p.N) v[j] += __ldg(p.bias + nb + j);
-      }
-      if (p.relu) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-      }
-      if (p.mask != nullptr) {
-        const __nv_bfloat16* mrow = p.mask + static_cast<size_t>(m) * p.ldmask + nb;
-        if ((p.ldmask & 7) == 0 && nb + 32 <= p.ldmask) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            uint4 mv = *reinterpret_cast<const uint4*>(mrow + g * 8);
-            const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mv);
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (!(__bfloat162float(mb[j]) > 0.f)) v[g * 8 + j] = 0.f;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.ldmask && !(__bfloat162float(mrow[j]) > 0.f)) v[j] = 0.f;
-        }
-      }
-      if (p.out_f32) {
-        float* orow = reinterpret_cast<float*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
-        if (p.reduce) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.n_store) red_add_f32_sys(orow + j, v[j]);
-        } else if ((p.ldo & 3) == 0 && nb + 32 <= p.n_store) {
-#pragma unroll
-          for (int g = 0; g < 8; ++g)
-            *reinterpret_cast<float4*>(orow + g * 4) =
-                make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.n_store) orow[j] = v[j];
-        }
+      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+      if (!fixup) {
+        gemm_epilogue_store(p, m, nb, v);
       } else {
-        __nv_bfloat16* orow =
-            reinterpret_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(m) * p.ldo + nb;
-        if ((p.ldo & 7) == 0 && nb + 32 <= p.n_store) {
+        // partial tile -> fp32 workspace (ldws is a multiple of 4, rows are 16-byte aligned)
+        float* wrow = p.ws + static_cast<size_t>(m) * p.ldws + nb;
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            uint4 o;
-            o.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
-            o.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
-            o.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
-            o.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
-            *reinterpret_cast<uint4*>(orow + g * 8) = o;
+        for (int j = 0; j < 32; j += 4)
+          if (nb + j < p.ldws) red_add_v4_f32_gpu(wrow + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+    }
+    if (fixup) {
+      // elect the last K-slice of this tile (threadfence-reduction pattern)
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (threadIdx.x == 128) {
+        const unsigned int tile = blockIdx.y * gridDim.x + blockIdx.x;
+        const unsigned int old = atomicInc(p.counters + tile, static_cast<unsigned int>(p.splits - 1));
+        *last_flag = (old == static_cast<unsigned int>(p.splits - 1)) ? 1u : 0u;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*last_flag) {
+        __threadfence();
+        if (row_ok) {
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            const int nb = n0 + c * 32;
+            if (nb >= p.n_store) continue;
+            const float* wrow = p.ws + static_cast<size_t>(m) * p.ldws + nb;
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (nb + j < p.ldws) t = __ldcg(reinterpret_cast<const float4*>(wrow + j));
+              v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
+            }
+            gemm_epilogue_store(p, m, nb, v);
           }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.n_store) orow[j] = __float2bfloat16(v[j]);
         }
       }
     }
@@ -251,18 +324,14 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
 template <int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
-                       int splits, cudaStream_t stream) {
+                       cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
   auto kern = gemm_umma_kernel<BN, A_MN, B_MN>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DTF_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        Cfg::SMEM_BYTES));
-    attr_set = true;
-  }
-  dim3 grid(ceil_div(p.N, BN), ceil_div(p.M, GEMM_BM), splits);
-  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
-  DTF_LAUNCH_CHECK();
+  const int smem = Cfg::smem_bytes(p.num_stages);
+  DTF_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      Cfg::smem_bytes(Cfg::MAX_STAGES)));
+  dim3 grid(ceil_div(p.N, BN), ceil_div(p.M, GEMM_BM), p.splits);
+  DTF_CHECK_CUDA(launch_kernel(kern, grid, dim3(GEMM_THREADS), smem, stream, ta, tb, p));
   return 0;
 }
 
@@ -282,8 +351,12 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
   const int num_kb = ceil_div(K, GEMM_BK);
   if (splits < 1) splits = 1;
   if (splits > num_kb) splits = num_kb;
-  DTF_REQUIRE(splits == 1 || (epi->reduce && epi->out_f32),
-              "gemm: split-K needs an fp32 reduce epilogue");
+  const bool fixup = splits > 1 && !epi->reduce;
+  DTF_REQUIRE(splits == 1 || (epi->reduce && epi->out_f32) || (epi->splitk_ws && epi->tile_counters),
+              "gemm: split-K needs an fp32 reduce epilogue, or a workspace + tile counters");
+  DTF_REQUIRE(!fixup || (epi->ldws % 4 == 0 && epi->ldws >= N &&
+                         (reinterpret_cast<uintptr_t>(epi->splitk_ws) & 15) == 0),
+              "gemm: split-K workspace needs ldws %% 4 == 0, ldws >= N and a 16-byte aligned base");
 
   CUtensorMap ta, tb;
   {
@@ -306,9 +379,12 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
   }
 
   GemmParams p;
+  memset(&p, 0, sizeof(p));
   p.M = M; p.N = N; p.K = K;
   p.kb_per_split = ceil_div(num_kb, splits);
-  splits = ceil_div(num_kb, p.kb_per_split);
+  p.splits = ceil_div(num_kb, p.kb_per_split);
+  const int max_stages = BN <= 64 ? GemmCfg<64>::MAX_STAGES : GemmCfg<128>::MAX_STAGES;
+  p.num_stages = p.kb_per_split < max_stages ? (p.kb_per_split < 2 ? 2 : p.kb_per_split) : max_stages;
   p.out = epi->out;
   p.ldo = epi->ldo;
   p.out_f32 = epi->out_f32;
@@ -323,8 +399,11 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
   p.ldmask = epi->ldmask;
   p.reduce = epi->reduce;
   p.alpha = epi->alpha;
+  p.ws = epi->splitk_ws;
+  p.ldws = epi->ldws;
+  p.counters = epi->tile_counters;
 
-#define DTF_DISPATCH(BN_, AM_, BM_) return launch_gemm<BN_, AM_, BM_>(ta, tb, p, splits, stream)
+#define DTF_DISPATCH(BN_, AM_, BM_) return launch_gemm<BN_, AM_, BM_>(ta, tb, p, stream)
   if (BN == 64) {
     if (!a_mn && !b_mn) DTF_DISPATCH(64, false, false);
     if (!a_mn && b_mn) DTF_DISPATCH(64, false, true);

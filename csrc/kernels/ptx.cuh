@@ -34,6 +34,19 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// Programmatic dependent launch (PDL): a kernel launched with the programmatic-serialization
+// attribute may start while its predecessor in the stream is still running. Everything before
+// griddep_wait() (smem carve-up, mbarrier init, TMEM alloc, descriptor prefetch) overlaps the
+// predecessor's tail; griddep_wait() returns once the predecessor grid has completed and its
+// memory is visible. griddep_launch() lets the NEXT kernel begin its own prologue. Both are no-ops
+// for a kernel launched without the attribute.
+__device__ __forceinline__ void griddep_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+__device__ __forceinline__ void griddep_launch() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 // Watchdog budget for every in-kernel wait (cycles). A broken pipeline traps (the launch then
 // returns an error to the host) instead of hanging the GPU.
 #ifndef DTF_WAIT_TIMEOUT_CYCLES
@@ -202,6 +215,12 @@ __device__ __forceinline__ void red_add_f32_gpu(float* addr, float v) {
 __device__ __forceinline__ void red_add_v4_f32_gpu(float* addr, float a, float b, float c,
                                                    float d) {
   asm volatile("red.relaxed.gpu.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a),
+               "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_v4_f32_sys(float* addr, float a, float b, float c,
+                                                   float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a),
                "f"(b), "f"(c), "f"(d)
                : "memory");
 }

@@ -24,6 +24,8 @@ struct PullArgs {
 
 __global__ void __launch_bounds__(PULL_THREADS)
 pull_bulk_kernel(const __grid_constant__ PullArgs a) {
+  griddep_wait();
+  griddep_launch();
   int it = 0;
   while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
   const dtf_copy_item& c = a.items[it];
@@ -80,7 +82,7 @@ extern "C" int dtf_pull_bulk(const dtf_copy_item* items, int n_items,
     a.items[0].bytes = 0;
     a.block_start[1] = 1;
   }
-  pull_bulk_kernel<<<blocks, PULL_THREADS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(pull_bulk_kernel, dim3(blocks), dim3(PULL_THREADS), 0,
+                               reinterpret_cast<cudaStream_t>(stream), a));
   return 0;
 }

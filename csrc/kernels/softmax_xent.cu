@@ -34,6 +34,8 @@ softmax_xent_kernel(const float* __restrict__ logits, int ldl, const int* __rest
   __shared__ float s_db[128];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * 8 + warp;
+  griddep_wait();
+  griddep_launch();
   if (dbias_accum != nullptr)
     for (int i = threadIdx.x; i < 128; i += blockDim.x) s_db[i] = 0.f;
   __syncthreads();
@@ -120,10 +122,10 @@ extern "C" int dtf_softmax_xent_sparse(const float* logits, int ldl, const int* 
                                        float* dbias_accum, void* stream) {
   DTF_REQUIRE(C >= 1 && C <= 32 * XENT_MAX_PER_LANE && ldd <= 32 * XENT_MAX_PER_LANE,
               "softmax_xent: C=%d / ldd=%d exceed %d classes", C, ldd, 32 * XENT_MAX_PER_LANE);
-  softmax_xent_kernel<false><<<ceil_div(B, 8), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      logits, ldl, labels, nullptr, 0, B, C, loss_accum,
-      reinterpret_cast<__nv_bfloat16*>(dlogits), ldd, dbias_accum);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(softmax_xent_kernel<false>, dim3(ceil_div(B, 8)), dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream), logits, ldl, labels,
+                               static_cast<const float*>(nullptr), 0, B, C, loss_accum,
+                               reinterpret_cast<__nv_bfloat16*>(dlogits), ldd, dbias_accum));
   return 0;
 }
 
@@ -132,9 +134,9 @@ extern "C" int dtf_softmax_xent_dense(const float* logits, int ldl, const float*
                                       float* dbias_accum, void* stream) {
   DTF_REQUIRE(C >= 1 && C <= 32 * XENT_MAX_PER_LANE && ldd <= 32 * XENT_MAX_PER_LANE,
               "softmax_xent: C=%d / ldd=%d exceed %d classes", C, ldd, 32 * XENT_MAX_PER_LANE);
-  softmax_xent_kernel<true><<<ceil_div(B, 8), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      logits, ldl, nullptr, labels, ldy, B, C, loss_accum,
-      reinterpret_cast<__nv_bfloat16*>(dlogits), ldd, dbias_accum);
-  DTF_LAUNCH_CHECK();
+  DTF_CHECK_CUDA(launch_kernel(softmax_xent_kernel<true>, dim3(ceil_div(B, 8)), dim3(256), 0,
+                               reinterpret_cast<cudaStream_t>(stream), logits, ldl,
+                               static_cast<const int*>(nullptr), labels, ldy, B, C, loss_accum,
+                               reinterpret_cast<__nv_bfloat16*>(dlogits), ldd, dbias_accum));
   return 0;
 }

@@ -7,6 +7,8 @@ namespace dtf {
 
 static thread_local char g_err[1024] = "";
 
+int g_pdl_enabled = 0;
+
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -79,3 +81,9 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
 extern "C" const char* dtf_last_error() { return dtf::g_err; }
 
 extern "C" int dtf_abi_version() { return 1; }
+
+extern "C" int dtf_set_pdl(int enabled) {
+  const int old = dtf::g_pdl_enabled;
+  dtf::g_pdl_enabled = enabled ? 1 : 0;
+  return old;
+}

@@ -174,9 +174,23 @@ class _Zero:
         return out
 
 
+def plan_gemm(M: int, N: int, K: int) -> Tuple[int, int]:
+    """(block_n, splits) for the skinny MNIST GEMMs: prefer more, narrower tiles while the grid is
+    far below 148 SMs, and split K (with the in-kernel fix-up) until the grid roughly fills them."""
+    tiles128 = -(-M // 128) * -(-N // 128)
+    bn = 64 if (N <= 64 or tiles128 < 74) else 128
+    tiles = -(-M // 128) * -(-N // bn)
+    kb = -(-K // 64)
+    splits = 1
+    if tiles < 100 and kb >= 4:
+        splits = max(1, min(kb // 2, 148 // tiles))
+    return bn, splits
+
+
 class StepState:
     def __init__(self, runner: "B200StepRunner", B: int, train: bool, x_dtype, y_dtype):
         self.B, self.train = B, train
+        self.gemm_plans: Dict[str, dict] = {}
         p, dev = runner.plan, runner.device
         bf, f32 = torch.bfloat16, torch.float32
         self.x_pin = torch.zeros((B, p.in_features), dtype=x_dtype).pin_memory()
@@ -214,7 +228,26 @@ class StepState:
                 zero.add("gkb1", 32)
                 zero.add("gk2", 800 * 64)
                 zero.add("gkb2", 64)
+        # split-K workspaces + tile counters of the skinny GEMMs live in the zeroed region too
+        nl_ = len(p.dense)
+        wants = [(f"fwd{i}", B, dims[i + 1], dims[i]) for i in range(nl_)]
+        if train:
+            wants += [(f"dx{i}", B, dims[i], dims[i + 1]) for i in range(1 if p.kind == "mlp" else 0, nl_)]
+        for key, M_, N_, K_ in wants:
+            bn, splits = plan_gemm(M_, N_, K_)
+            plan = dict(bn=bn, splits=splits)
+            if splits > 1:
+                ldws = (N_ + 3) // 4 * 4
+                zero.add("ws_" + key, M_ * ldws)
+                zero.add("ct_" + key, -(-M_ // 128) * -(-N_ // bn))
+                plan["ldws"] = ldws
+            self.gemm_plans[key] = plan
         self.z = zero.build(dev)
+        for key, plan in self.gemm_plans.items():
+            if plan["splits"] > 1:
+                M_ = B
+                plan["ws"] = self.z["ws_" + key][:M_ * plan["ldws"]].view(M_, plan["ldws"])
+                plan["counters"] = self.z["ct_" + key]
         self.zero = zero
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.launches_per_step = 0
@@ -234,6 +267,9 @@ class B200StepRunner:
         self.use_cuda_graph = bool(opts.get("cuda_graph", True))
         self.fused_first_pull = bool(opts.get("fused_first_pull", True))
         self.atomic_sgd = bool(opts.get("atomic_sgd", False))
+        self.split_k = bool(opts.get("split_k", True))
+        self.pdl = bool(opts.get("pdl", True))
+        L.lib().dtf_set_pdl(1 if self.pdl else 0)
         self.device = torch.device(self._pick_device())
         torch.cuda.set_device(self.device)
         self.store: Optional[NvlStore] = None
@@ -243,6 +279,8 @@ class B200StepRunner:
         self.states: Dict[Tuple[int, bool], StepState] = {}
         self.local: Dict[str, torch.Tensor] = {}     # pulled copies of remote tensors
         self.stream = torch.cuda.Stream(device=self.device)
+        self.side_stream = torch.cuda.Stream(device=self.device)
+        self.overlap = bool(opts.get("overlap", True))
 
     def _pick_device(self) -> str:
         if getattr(self.config, "device", None):
@@ -415,7 +453,16 @@ class B200StepRunner:
             out = s.act[i + 1] if i + 1 < nl else s.logits
             bias = _PtrTensor(self.fptr[d.b.name]) if d.b is not None else None
             K.gemm(s.act[i], None, out, s.B, s.dims[i + 1], s.dims[i], b_mn=True, bias=bias,
-                   relu=d.relu, b_ptr=wp, ldb=ld)
+                   relu=d.relu, b_ptr=wp, ldb=ld, **self._plan_kw(s, f"fwd{i}"))
+
+    def _plan_kw(self, s: StepState, key: str) -> dict:
+        plan = s.gemm_plans.get(key)
+        if plan is None or not self.split_k:
+            return {}
+        kw = dict(block_n=plan["bn"])
+        if plan["splits"] > 1:
+            kw.update(splits=plan["splits"], ws=plan["ws"], counters=plan["counters"])
+        return kw
 
     def _loss(self, s: StepState) -> None:
         p = self.plan
@@ -432,29 +479,64 @@ class B200StepRunner:
         return s._dl
 
     def _backward(self, s: StepState) -> None:
+        """Backward pass on two streams. The activation-gradient chain (dX GEMMs, pooling / conv
+        gradients) is the critical path and stays on the main stream; the weight-gradient GEMMs and
+        the push+apply of each dense kernel depend only on already-available tensors, so they run
+        on a side stream and overlap it — the big apply (12.8 MB of Adam state for dense/kernel)
+        hides behind the convolution backward instead of trailing the step. Both streams are part
+        of the same captured CUDA graph (fork / join through events)."""
         p = self.plan
         nl = len(p.dense)
+        main = torch.cuda.current_stream()
+        side = self.side_stream if self.overlap else main
+        applied: List[G.Variable] = []
+
+        def fork():
+            if side is not main:
+                ev = torch.cuda.Event()
+                ev.record(main)
+                side.wait_event(ev)
+
         dz = s.dlogits
+        fork()                                   # dlogits (and every activation) is ready
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
-            # dW_i = act_i^T dZ_i
-            K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
+            with torch.cuda.stream(side):
+                # dW_i = act_i^T dZ_i
+                K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
             wp, ld = self.wptr[d.w.name]
             if i > 0:
                 # dZ_{i-1} = (dZ_i W_i^T) * relu'(act_i);  db_{i-1} = colsum
-                K.gemm(dz, None, s.dact[i], s.B, din, dout, mask=s.act[i], b_ptr=wp, ldb=ld)
+                K.gemm(dz, None, s.dact[i], s.B, din, dout, mask=s.act[i], b_ptr=wp, ldb=ld,
+                       **self._plan_kw(s, f"dx{i}"))
                 K.colsum_bf16(s.dact[i], s.B, din, s.z[f"gb{i - 1}"])
                 dz = s.dact[i]
+                fork()                           # dZ_{i-1} is ready; W_i is no longer being read
             elif p.kind == "cnn":
-                K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld)
+                K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld, **self._plan_kw(s, "dx0"))
+                fork()
+            if self.overlap:
+                # push+apply of W_i as soon as its gradient exists and the dX GEMM above (which
+                # reads W_i, possibly in place in the local shard) has been ordered before it
+                with torch.cuda.stream(side):
+                    self._apply_vars(s, [d.w], finish=False)
+                applied.append(d.w)
         if p.kind == "cnn":
             c1, c2 = p.convs
             scale = 1.0 / 255.0 if s.x_dev.dtype == torch.uint8 else 1.0
             K.pool2_bwd(s.dpool2, s.act[0].view(s.B, 7, 7, 64), s.amax2, s.dconv2p, s.z["gkb2"])
-            K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
+            fork()                               # dconv2p is ready
+            with torch.cuda.stream(side):
+                K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
             K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
+        if side is not main:                     # join
+            ev = torch.cuda.Event()
+            ev.record(side)
+            main.wait_event(ev)
+        rest = [v for v in self.train_op.var_list if v not in applied]
+        self._apply_vars(s, rest, finish=True)
 
     def _grad_ptr(self, s: StepState, var: G.Variable) -> int:
         p = self.plan
@@ -470,10 +552,12 @@ class B200StepRunner:
                 return s.z[f"gb{i}"].data_ptr()
         raise KeyError(var.name)
 
-    def _apply(self, s: StepState) -> None:
+    def _apply_vars(self, s: StepState, variables: Sequence[G.Variable], finish: bool) -> None:
+        """push+apply of ``variables`` on the current stream; ``finish`` adds TF's _finish (beta
+        powers) and the global_step atomic and must be the step's last apply."""
         st, spec = self.store, self.spec
         entries = []
-        for var in self.train_op.var_list:
+        for var in variables:
             gptr = self._grad_ptr(s, var)
             for r in self._regions(var):
                 entries.append(dict(var=st.var_ptr(r), slot0=st.slot_ptr(r, 0), slot1=st.slot_ptr(r, 1),
@@ -482,8 +566,10 @@ class B200StepRunner:
         hyper = K.make_hyper(spec.learning_rate, spec.beta1, spec.beta2, spec.epsilon, spec.momentum,
                              1.0, spec.use_nesterov, self.atomic_sgd and spec.kind == "sgd")
         chunks = [entries[i:i + L.MAX_APPLY_ITEMS] for i in range(0, len(entries), L.MAX_APPLY_ITEMS)]
+        if not chunks and finish:
+            chunks = [[]]
         for ci, ch in enumerate(chunks):
-            last = ci == len(chunks) - 1
+            last = finish and ci == len(chunks) - 1
             items = K.make_apply_items(ch)
             K.push_apply(spec.code, items, len(ch), hyper, st.powers_ctrl, st.step_ctrl, last,
                          self.worker_id, s.step_dev.data_ptr() if last else None,
@@ -503,8 +589,7 @@ class B200StepRunner:
         self._forward(s)
         self._loss(s)
         if s.train:
-            self._backward(s)
-            self._apply(s)
+            self._backward(s)          # includes the push+apply of every variable
         if with_io:
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
             s.step_pin.copy_(s.step_dev, non_blocking=True)

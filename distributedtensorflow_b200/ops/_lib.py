@@ -61,6 +61,9 @@ class GemmEpilogue(C.Structure):
         ("ldmask", C.c_int),
         ("reduce", C.c_int),
         ("alpha", C.c_float),
+        ("splitk_ws", C.c_void_p),
+        ("ldws", C.c_int),
+        ("tile_counters", C.c_void_p),
     ]
 
 
@@ -139,6 +142,7 @@ def _declare(lib):
         "dtf_memcpy_d2h": [vp, vp, C.c_size_t, vp],
         "dtf_memcpy_h2d": [vp, vp, C.c_size_t, vp],
         "dtf_stream_sync": [vp],
+        "dtf_set_pdl": [i],
         "dtf_host_alloc_pinned": [C.POINTER(vp), C.c_size_t],
         "dtf_host_free_pinned": [vp],
     }

@@ -37,7 +37,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
          relu: bool = False, mask: Optional[torch.Tensor] = None, reduce: bool = False,
          alpha: float = 1.0, splits: int = 1, block_n: int = 0,
          a_ptr: Optional[int] = None, b_ptr: Optional[int] = None, lda: Optional[int] = None,
-         ldb: Optional[int] = None) -> None:
+         ldb: Optional[int] = None, ws: Optional[torch.Tensor] = None,
+         counters: Optional[torch.Tensor] = None) -> None:
     """out[M,N] = alpha * A @ B^T with the fused epilogue of ``dtf_gemm_bf16``.
 
     ``a``/``b`` are 2-D bf16 tensors whose row pitch (stride(0)) is a multiple of 8; with
@@ -62,6 +63,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
     epi.ldmask = mask.stride(0) if mask is not None else 0
     epi.reduce = int(reduce)
     epi.alpha = float(alpha)
+    if ws is not None:
+        # split-K with in-kernel fix-up: ws is a zeroed fp32 [M, ldws] view, counters zeroed u32
+        assert ws.dtype == torch.float32 and ws.dim() == 2 and ws.stride(1) == 1
+        epi.splitk_ws, epi.ldws = ws.data_ptr(), ws.stride(0)
+        epi.tile_counters = counters.data_ptr()
     rc = L.lib().dtf_gemm_bf16(a_ptr, lda, int(a_mn), b_ptr, ldb, int(b_mn), M, N, K,
                                C.byref(epi), splits, block_n, L.current_stream())
     L.check(rc, "dtf_gemm_bf16")

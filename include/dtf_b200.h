@@ -58,6 +58,12 @@ typedef struct dtf_gemm_epilogue {
   int ldmask;
   int reduce;         /* 1: red.global.add.f32 into out (split-K / gradient accumulation) */
   float alpha;        /* out = alpha * acc (applied first) */
+  /* split-K with in-kernel fix-up (splits > 1 and reduce = 0): K-slices sum into this fp32
+   * workspace and the last slice of each tile runs the epilogue above. Both must be zero on
+   * entry; the counters reset themselves, the workspace does not. */
+  float* splitk_ws;             /* [M, ldws] fp32, 16-byte aligned, ldws % 4 == 0, ldws >= N */
+  int ldws;
+  unsigned int* tile_counters;  /* ceil(M/128) * ceil(N/block_n) words */
 } dtf_gemm_epilogue;
 
 int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int b_mn, int M,

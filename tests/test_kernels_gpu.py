@@ -104,6 +104,57 @@ def test_gemm_split_k_reduce(K):
     assert _rel_err(out, ref) < 2e-3
 
 
+@pytest.mark.parametrize("M,N,K_,splits,block_n", [(128, 1024, 3136, 9, 64), (128, 10, 1024, 8, 64),
+                                                   (128, 3136, 1024, 3, 64), (100, 200, 784, 4, 128)])
+def test_gemm_split_k_fixup_keeps_fused_epilogue(K, M, N, K_, splits, block_n):
+    """Split-K with the in-kernel fix-up: K-slices sum into an fp32 workspace, the last slice of
+    each tile applies bias + ReLU and writes bf16; the tile counters re-arm themselves."""
+    torch.manual_seed(12)
+    A = torch.randn(M, K_, device="cuda")
+    W = torch.randn(K_, N, device="cuda") * 0.05
+    bias = torch.randn(N, device="cuda")
+    a, w = _padded(M, K_, fill=A), _padded(K_, N, fill=W)
+    ldws = (N + 3) // 4 * 4
+    tiles = ((M + 127) // 128) * ((N + block_n - 1) // block_n)
+    counters = torch.zeros(tiles, dtype=torch.int32, device="cuda")
+    ref = torch.relu(_bf16(A).float() @ _bf16(W).float() + bias)
+    for _ in range(2):                                   # second run: counters must be back at zero
+        ws = torch.zeros(M, ldws, device="cuda")
+        out = torch.full((M, w.shape[1]), 7.0, dtype=torch.bfloat16, device="cuda")
+        K.gemm(a, w, out, M, N, K_, b_mn=True, bias=bias, relu=True, splits=splits, block_n=block_n,
+               ws=ws, counters=counters)
+        torch.cuda.synchronize()
+        assert _rel_err(out[:, :N], ref) < 1e-2
+        assert (out[:, N:] == 0).all()
+        assert (counters == 0).all()
+
+
+def test_pdl_launches_give_identical_results(K):
+    """Programmatic dependent launch only overlaps prologues: results must not change."""
+    from distributedtensorflow_b200.ops import _lib as L
+    torch.manual_seed(13)
+    M, N, K_ = 128, 256, 512
+    a = _padded(M, K_, fill=torch.randn(M, K_, device="cuda"))
+    b = _padded(N, K_, fill=torch.randn(N, K_, device="cuda"))
+    outs = []
+    for pdl in (0, 1):
+        old = L.lib().dtf_set_pdl(pdl)
+        o1 = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+        o2 = torch.zeros(M, M, device="cuda")
+        cs = torch.zeros(N, device="cuda")
+        for _ in range(3):                               # a chain of dependent kernels
+            K.gemm(a, b, o1, M, N, K_)
+            K.gemm(o1, o1, o2, M, M, N)
+            K.fill_u32(cs, 0)
+            K.colsum_bf16(o1, M, N, cs)
+        torch.cuda.synchronize()
+        L.lib().dtf_set_pdl(old)
+        outs.append((o1.clone(), o2.clone(), cs.clone()))
+    (a1, a2, acs), (b1, b2, bcs) = outs
+    assert torch.equal(a1, b1) and torch.equal(a2, b2)
+    assert (acs - bcs).abs().max().item() < 1e-3        # column sums use float atomics
+
+
 # ------------------------------------------------------------------------------------------------
 # loss
 # ------------------------------------------------------------------------------------------------
