@@ -309,11 +309,29 @@ class B200StepRunner:
         return out
 
     # -- variable lifecycle (called by Session) ---------------------------------------------------
+    handles_sync = True   # SyncReplicasOptimizer rounds run in csrc/kernels/sync_step.cu
+
     def create_variables(self, spec, trainable_names: Sequence[str]) -> None:
         self.spec = spec
         self.trainable_names = list(trainable_names)
+        top = next((n for n in self.graph.nodes if type(n).__name__ == "TrainOp"), None)
+        self.sync_opt = top.sync if top is not None else None
+        sync_workers = 0
+        if self.sync_opt is not None:
+            world = self.client.num_shards
+            nw = self.cluster.num_tasks("worker") if (self.cluster is not None and "worker" in self.cluster.jobs) else 1
+            if nw != world or self.sync_opt.total_num_replicas != world or \
+                    self.sync_opt.replicas_to_aggregate != world:
+                raise NotImplementedError(
+                    "B200 synchronous mode needs one worker colocated with every PS shard and "
+                    "replicas_to_aggregate == total_num_replicas == number of shards (got %d workers, "
+                    "%d shards, aggregate %d of %d); use backend='cpu' for backup-worker mode"
+                    % (nw, world, self.sync_opt.replicas_to_aggregate, self.sync_opt.total_num_replicas))
+            sync_workers = world
         self.store = NvlStore(self.client, self.layout, spec, trainable_names, self.device.index or 0,
-                              self._shard_devices())
+                              self._shard_devices(), sync_workers=sync_workers)
+        self.sync_round_no: Optional[int] = None
+        self.mirror_filled = False
 
     def init_variables(self, values: Dict[str, np.ndarray]) -> None:
         st = self.store
@@ -331,6 +349,8 @@ class B200StepRunner:
             st.write_ctrl(s, global_step=step0 if s == st.arena.step_shard else 0, beta1_power=b1,
                           beta2_power=b2, initialized=1)
         self.client.mark_initialized(True)
+        self.mirror_filled = False
+        self.sync_round_no = None
 
     def uninitialized_variables(self) -> List[str]:
         return self.client.uninitialized_variables(self.layout)
@@ -393,6 +413,9 @@ class B200StepRunner:
         self.copies: List[Tuple[int, int, int]] = []
         self.wptr: Dict[str, Tuple[int, int]] = {}    # bf16 serving copy: name -> (ptr, ld)
         self.fptr: Dict[str, int] = {}                # fp32 tensor: name -> ptr
+        if self.sync_opt is not None:
+            self._setup_params_sync()
+            return
 
         def want_shadow(var: G.Variable, allow_in_place: bool) -> None:
             regs = self._regions(var)
@@ -432,6 +455,84 @@ class B200StepRunner:
             want_shadow(d.w, allow_in_place=(p.kind == "mlp" and i == 0))
             if d.b is not None:
                 want_f32(d.b, False)
+
+    def _setup_params_sync(self) -> None:
+        """Synchronous mode: kernels read the worker's MIRROR inside its own arena; the owners'
+        all-gather keeps it current, so there is no per-step pull. ``copies`` fills the mirror once
+        (after init / restore) from the owners' serving copies."""
+        st, p = self.store, self.plan
+        al = st.arena
+        me = st.base[self.worker_id]
+
+        def use_bf16(var):
+            regs = self._regions(var)
+            ld = regs[0].shadow_ld
+            self.wptr[var.name] = (me + al.mirror_bf16[var.name], ld)
+            row = 0
+            for r in regs:
+                self.copies.append((st.shadow_ptr(r), me + al.mirror_bf16[var.name] + row * ld * 2, r.rows * ld * 2))
+                row += r.rows
+
+        def use_f32(var):
+            self.fptr[var.name] = me + al.mirror_f32[var.name]
+            for r in self._regions(var):
+                self.copies.append((st.var_ptr(r), me + al.mirror_f32[var.name] + r.sl.first * 4,
+                                    (r.sl.n * 4 + 15) // 16 * 16))
+
+        if p.kind == "cnn":
+            use_f32(p.convs[0].k)
+            use_f32(p.convs[0].b)
+            use_bf16(p.convs[1].k)
+            use_f32(p.convs[1].b)
+        for d in p.dense:
+            use_bf16(d.w)
+            if d.b is not None:
+                use_f32(d.b)
+
+    def _sync_segments(self, s: StepState):
+        """Device copy of the dtf_sync_segment table for this state's gradient buffers."""
+        if getattr(s, "sync_table", None) is not None:
+            return s.sync_table, s.sync_n
+        import ctypes as C
+        st, al = self.store, self.store.arena
+        segs = []
+        for var in self.train_op.var_list:
+            gptr = self._grad_ptr(s, var)
+            for r in self._regions(var):
+                sg = L.SyncSegment()
+                sg.owner, sg.cols, sg.shadow_ld = r.shard, r.cols, r.shadow_ld
+                sg.n, sg.first, sg.first_row = r.sl.n, r.sl.first, r.sl.first // r.cols
+                sg.grad_local = gptr + r.sl.first * 4
+                sg.mailbox_off = al.mailbox_off[(var.name, r.shard)]
+                sg.mailbox_stride = al.mailbox_stride[r.shard]
+                sg.var_off = r.var_off
+                sg.slot0_off = r.slot_off[0] if len(r.slot_off) > 0 else 0
+                sg.slot1_off = r.slot_off[1] if len(r.slot_off) > 1 else 0
+                sg.shadow_off = r.shadow_off or 0
+                sg.mirror_f32_off = al.mirror_f32[var.name] if var.name in self.fptr else 0
+                sg.mirror_bf16_off = al.mirror_bf16[var.name] if var.name in self.wptr else 0
+                segs.append(sg)
+        arr = (L.SyncSegment * len(segs))(*segs)
+        raw = bytes(memoryview(arr))
+        s.sync_table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
+        s.sync_n = len(segs)
+        return s.sync_table, s.sync_n
+
+    def _sync_round(self, s: StepState) -> None:
+        import ctypes as C
+        st, spec = self.store, self.spec
+        if self.sync_round_no is None:
+            self.sync_round_no = int(st.read_ctrl(self.worker_id)["epoch"])
+        self.sync_round_no += 1
+        table, n = self._sync_segments(s)
+        hyper = K.make_hyper(spec.learning_rate, spec.beta1, spec.beta2, spec.epsilon, spec.momentum,
+                             1.0, spec.use_nesterov, False)
+        bases = (C.c_ulonglong * st.num_shards)(*st.base)
+        rc = L.lib().dtf_sync_round(spec.code, table.data_ptr(), n, self.worker_id, st.num_shards,
+                                    self.sync_round_no, C.byref(hyper), bases, s.counter.data_ptr() + 8,
+                                    s.step_dev.data_ptr(), st.arena.step_shard, L.current_stream())
+        L.check(rc, "dtf_sync_round")
+        K._count()
 
     # -- kernels of one step ------------------------------------------------------------------------
     def _forward(self, s: StepState) -> None:
@@ -488,7 +589,8 @@ class B200StepRunner:
         p = self.plan
         nl = len(p.dense)
         main = torch.cuda.current_stream()
-        side = self.side_stream if self.overlap else main
+        sync = self.sync_opt is not None
+        side = self.side_stream if (self.overlap and not sync) else main
         applied: List[G.Variable] = []
 
         def fork():
@@ -516,7 +618,7 @@ class B200StepRunner:
             elif p.kind == "cnn":
                 K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld, **self._plan_kw(s, "dx0"))
                 fork()
-            if self.overlap:
+            if self.overlap and not sync:
                 # push+apply of W_i as soon as its gradient exists and the dX GEMM above (which
                 # reads W_i, possibly in place in the local shard) has been ordered before it
                 with torch.cuda.stream(side):
@@ -535,6 +637,9 @@ class B200StepRunner:
             ev = torch.cuda.Event()
             ev.record(side)
             main.wait_event(ev)
+        if sync:
+            self._sync_round(s)      # reduce-scatter + mean + apply + all-gather, one kernel
+            return
         rest = [v for v in self.train_op.var_list if v not in applied]
         self._apply_vars(s, rest, finish=True)
 
@@ -576,6 +681,10 @@ class B200StepRunner:
                          s.counter.data_ptr())
 
     def _pull(self, s: StepState) -> None:
+        if self.sync_opt is not None:
+            if self.mirror_filled:
+                return
+            self.mirror_filled = True
         if self.copies:
             K.pull_bulk(self.copies, self.store.step_ctrl, s.step_dev.data_ptr() + 8)
 
@@ -628,7 +737,7 @@ class B200StepRunner:
 
     def _launch(self, s: StepState) -> None:
         with torch.cuda.stream(self.stream):
-            if not self.use_cuda_graph:
+            if not self.use_cuda_graph or self.sync_opt is not None:
                 self._enqueue_step(s)
                 return
             if s.graph is None:
@@ -654,9 +763,6 @@ class B200StepRunner:
             step = self.store.read_global_step()
             return [self._as_step(step) for _ in fetches]
         top = train_ops[0] if train_ops else None
-        if top is not None and top.sync is not None:
-            raise NotImplementedError("sync replicas on the B200 backend goes through "
-                                      "parallel/nvl_sync.py (session option sync_mode='b200')")
         loss_node = top.loss if top is not None else self._find_loss(plain)
         self._ensure_plan(loss_node, top)
         p = self.plan

@@ -94,6 +94,17 @@ class ApplyHyper(C.Structure):
     ]
 
 
+class SyncSegment(C.Structure):
+    """Mirror of ``dtf_sync_segment``."""
+    _fields_ = [
+        ("owner", C.c_int), ("cols", C.c_int), ("shadow_ld", C.c_int), ("reserved", C.c_int),
+        ("n", C.c_longlong), ("first", C.c_longlong), ("first_row", C.c_longlong),
+        ("grad_local", C.c_ulonglong), ("mailbox_off", C.c_ulonglong), ("mailbox_stride", C.c_ulonglong),
+        ("var_off", C.c_ulonglong), ("slot0_off", C.c_ulonglong), ("slot1_off", C.c_ulonglong),
+        ("shadow_off", C.c_ulonglong), ("mirror_f32_off", C.c_ulonglong), ("mirror_bf16_off", C.c_ulonglong),
+    ]
+
+
 class CopyItem(C.Structure):
     _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("bytes", C.c_longlong)]
 
@@ -143,6 +154,7 @@ def _declare(lib):
         "dtf_memcpy_h2d": [vp, vp, C.c_size_t, vp],
         "dtf_stream_sync": [vp],
         "dtf_set_pdl": [i],
+        "dtf_sync_round": [i, vp, i, i, i, C.c_uint, C.POINTER(ApplyHyper), C.POINTER(C.c_ulonglong), vp, vp, i, vp],
         "dtf_host_alloc_pinned": [C.POINTER(vp), C.c_size_t],
         "dtf_host_free_pinned": [vp],
     }

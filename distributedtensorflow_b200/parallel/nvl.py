@@ -76,10 +76,17 @@ class ArenaLayout:
     step_shard: int
     powers_shard: int
     num_slots: int
+    # synchronous mode (csrc/kernels/sync_step.cu): per-shard gradient mailboxes and, at the SAME
+    # offset in every arena, a mirror of all parameters that the owners all-gather into
+    sync_workers: int = 0
+    mailbox_off: Dict[Tuple[str, int], int] = field(default_factory=dict)   # (name, shard) -> slot-0 offset
+    mailbox_stride: List[int] = field(default_factory=list)                 # bytes per worker slot, per shard
+    mirror_f32: Dict[str, int] = field(default_factory=dict)                # name -> offset (all arenas)
+    mirror_bf16: Dict[str, int] = field(default_factory=dict)
 
 
 def build_arena_layout(layout: Dict[str, VarLayout], num_shards: int, spec: Optional[OptimizerSpec],
-                       trainable_names: Sequence[str]) -> ArenaLayout:
+                       trainable_names: Sequence[str], sync_workers: int = 0) -> ArenaLayout:
     num_slots = spec.num_slots if spec is not None else 0
     offs = [L.CTRL_BYTES] * num_shards
     regions: Dict[str, List[SliceRegion]] = {}
@@ -117,8 +124,29 @@ def build_arena_layout(layout: Dict[str, VarLayout], num_shards: int, spec: Opti
             out.append(SliceRegion(vl.name, s, sl, cols, rows, ld, var_off, slot_off, shadow_off))
         regions[vl.name] = out
     pshard = powers_shard(layout, list(trainable_names)) if trainable_names else 0
-    return ArenaLayout(num_shards, [_align(o, 4096) for o in offs], regions, step_var, step_shard,
-                       pshard, num_slots)
+    al = ArenaLayout(num_shards, [], regions, step_var, step_shard, pshard, num_slots)
+    if sync_workers > 0:
+        al.sync_workers = sync_workers
+        al.mailbox_stride = [0] * num_shards
+        slot_base = [_align(o) for o in offs]
+        for name in trainable_names:                       # one packed slot per worker per shard
+            for r in regions.get(name, []):
+                al.mailbox_off[(name, r.shard)] = slot_base[r.shard] + al.mailbox_stride[r.shard]
+                al.mailbox_stride[r.shard] += _align(r.sl.n * 4)
+        ends = [slot_base[s] + sync_workers * al.mailbox_stride[s] for s in range(num_shards)]
+        o = _align(max(ends))                              # mirrors: same offset in EVERY arena
+        for name, regs in regions.items():
+            if not regs:
+                continue
+            vl = layout[name]
+            al.mirror_f32[name] = o
+            o += _align(vl.num_elements * 4)
+            if regs[0].shadow_off is not None:
+                al.mirror_bf16[name] = o
+                o += _align(vl.rows * regs[0].shadow_ld * 2)
+        offs = [o] * num_shards
+    al.shard_bytes = [_align(o, 4096) for o in offs]
+    return al
 
 
 class NvlStore:
@@ -126,13 +154,13 @@ class NvlStore:
 
     def __init__(self, client, layout: Dict[str, VarLayout], spec: Optional[OptimizerSpec],
                  trainable_names: Sequence[str], local_device: int,
-                 shard_devices: Optional[Sequence[Optional[int]]] = None):
+                 shard_devices: Optional[Sequence[Optional[int]]] = None, sync_workers: int = 0):
         self.client = client
         self.layout = layout
         self.spec = spec
         self.num_shards = client.num_shards
         self.local_device = local_device
-        self.arena = build_arena_layout(layout, self.num_shards, spec, trainable_names)
+        self.arena = build_arena_layout(layout, self.num_shards, spec, trainable_names, sync_workers)
         self.base: List[int] = [0] * self.num_shards
         self.is_local: List[bool] = [False] * self.num_shards
         self.shard_device: List[int] = [local_device] * self.num_shards

@@ -324,12 +324,14 @@ class Session:
                 f.iterator._bind(f.dataset)
             elif op == "InitTokens":
                 self.ensure_created()
-                f.opt.setup(self.ps_client, self.layout)
-                f.opt.init_tokens(self.ps_client, self.layout, f.num_tokens)
+                if not getattr(self._runner, "handles_sync", False):
+                    f.opt.setup(self.ps_client, self.layout)
+                    f.opt.init_tokens(self.ps_client, self.layout, f.num_tokens)
             elif op == "LocalStepInit":
                 self.ensure_created()
-                f.opt.setup(self.ps_client, self.layout)
-                f.opt.init_local_step(self.ps_client, self.layout)
+                if not getattr(self._runner, "handles_sync", False):
+                    f.opt.setup(self.ps_client, self.layout)
+                    f.opt.init_local_step(self.ps_client, self.layout)
             elif op == "ReadyForLocalInit":
                 results[i] = np.asarray(self.uninitialized_variables(), dtype=object)
             elif op == "NoOp" or f is None:

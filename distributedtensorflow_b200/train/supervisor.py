@@ -134,6 +134,8 @@ class Supervisor:
         threads = []
         for qr in (queue_runners or []):
             sess.ensure_created()
+            if getattr(sess._runner, "handles_sync", False):
+                continue   # B200 backend: no chief-side aggregation thread is needed
             if hasattr(qr.opt, "setup"):
                 qr.opt.setup(sess.ps_client, sess.layout)
             t = qr.start(sess.ps_client, sess.layout)

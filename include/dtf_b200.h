@@ -205,7 +205,31 @@ int dtf_conv2_dgrad(const void* dconv2p, const void* w2, void* dpool1, int B, vo
  * shard, followed by an all-gather of the updated bf16 serving copy into every worker, all in
  * ONE cooperative kernel per rank over NVLink peer memory (no NCCL).
  * ------------------------------------------------------------------------------------------ */
-typedef struct dtf_sync_plan dtf_sync_plan; /* opaque, see csrc/kernels/sync_step.cu */
+/* One variable slice as seen by the sync kernel. Offsets are bytes from the base of an arena
+ * (0 = absent); every rank's arena has the same layout, so one table serves all ranks.
+ * All ranks pass the same table; `grad_local` is the only per-rank field. */
+typedef struct dtf_sync_segment {
+  int owner;                          /* shard that owns (reduces + applies) this slice */
+  int cols;                           /* innermost dim of the variable */
+  int shadow_ld;                      /* row pitch of the bf16 copies, elements */
+  int reserved;
+  long long n;                        /* elements in the slice */
+  long long first;                    /* flat index of the slice's first element in the variable */
+  long long first_row;                /* first / cols */
+  unsigned long long grad_local;      /* device pointer: this rank's fp32 gradient slice */
+  unsigned long long mailbox_off;     /* owner arena: slot 0 of this slice's mailbox */
+  unsigned long long mailbox_stride;  /* bytes between consecutive workers' slots */
+  unsigned long long var_off, slot0_off, slot1_off, shadow_off;   /* owner arena */
+  unsigned long long mirror_f32_off;  /* every arena: fp32 mirror of the WHOLE variable */
+  unsigned long long mirror_bf16_off; /* every arena: bf16 row-padded mirror of the WHOLE variable */
+} dtf_sync_segment;
+/* Runs round `round` (1, 2, 3, ... identical on all ranks) on this rank; see sync_step.cu.
+ * segs_dev: device copy of the table; arena_bases[world]: every rank's arena as mapped in this
+ * process; grid_bar: 2 zero-initialised local words; step_out: local u64 receiving global_step. */
+int dtf_sync_round(int opt, const dtf_sync_segment* segs_dev, int n_segs, int rank, int world,
+                   unsigned int round, const dtf_apply_hyper* hyper,
+                   const unsigned long long* arena_bases, unsigned int* grid_bar,
+                   unsigned long long* step_out, int step_shard, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Peer-memory runtime (replaces tf.train.Server's gRPC data plane, run_mnist_distributed.py:96).

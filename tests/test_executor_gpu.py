@@ -124,6 +124,27 @@ def test_eager_mode_equals_cuda_graph_mode():
         assert abs(x - y) <= 0.02 * abs(x) + 0.01
 
 
+def test_sync_round_kernel_single_replica_equals_async_adam():
+    """With one replica a synchronous round (mailbox -> mean -> apply -> all-gather into the
+    mirror, csrc/kernels/sync_step.cu) must train exactly like the asynchronous push+apply."""
+    def build_sync(tf):
+        from distributedtensorflow_b200.models import mnist_mlp
+        x = tf.placeholder(tf.float32, [None, 784])
+        y_ = tf.placeholder(tf.float32, [None, 10])
+        gs, xent, _ = mnist_mlp.build_model(x, y_, hidden_units=100)
+        opt = tf.train.SyncReplicasOptimizer(tf.train.AdamOptimizer(0.01), replicas_to_aggregate=1,
+                                             total_num_replicas=1)
+        return x, y_, xent, gs, opt.minimize(xent, global_step=gs)
+    batches = _batches(4, 100, one_hot=True)
+    a_l, a_g, a_v, _ = _run("b200", _build_mlp("adam"), 10, batches)
+    s_l, s_g, s_v, s_sh = _run("b200", build_sync, 10, batches)
+    assert s_g == a_g == list(range(1, 11))
+    for x, y in zip(a_l, s_l):
+        assert abs(x - y) <= 0.02 * abs(x) + 0.05, (a_l, s_l)
+    for n in a_v:
+        assert float(np.abs(a_v[n] - s_v[n]).mean()) < 2e-3, n
+
+
 def test_eval_fetch_and_validation_batch():
     """Fetching only the loss runs a forward pass at any batch size (the MLP template's
     validation cross-entropy, templates/00_mnist_replica.py:267-271)."""

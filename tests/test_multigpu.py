@@ -1,0 +1,109 @@
+"""Two-GPU checks (one process per GPU, CUDA IPC + NVLink peer memory): asynchronous PS training
+with exact global_step accounting, and the synchronous round kernel (reduce-scatter + mean + apply
++ all-gather) against the CPU SyncReplicasOptimizer path."""
+import json
+import os
+import subprocess
+import sys
+import threading
+
+import numpy as np
+import pytest
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _torchrun(nproc, script, args, port, timeout=300):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
+           "--master-addr", "127.0.0.1", "--master-port", str(port), script, *args]
+    p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
+    line = [l for l in p.stdout.splitlines() if l.startswith("{")][-1]
+    return json.loads(line)
+
+
+def test_async_two_gpus_counts_every_apply():
+    out = _torchrun(2, "bench.py", ["--gpus", "2", "--steps", "20", "--warmup", "3"], 29611)
+    assert out["n_gpus"] == 2 and out["value"] > 0
+    # 2 workers x (3 warm-up + 20 timed + 20 back-to-back + 20 e2e) applies, one atomic each
+    assert out["final_global_step"] == 2 * (3 + 20 + 20 + 20)
+
+
+def test_async_one_ps_shard_plus_worker():
+    out = _torchrun(2, "bench/ps_bench.py", ["--model", "mlp", "--topology", "ps1", "--steps", "30", "--warmup", "3"], 29621)
+    assert out["config"]["workers"] == 1 and out["config"]["ps_shards"] == 1
+    assert out["final_step"] == 33 and np.isfinite(out["final_loss"])
+
+
+def _cpu_sync_oracle(steps, batch, hidden, lr, world):
+    """The same sync-replicas run on the CPU transport (threads as workers, no initial tokens so
+    every round holds exactly one gradient per replica)."""
+    import distributedtensorflow_b200 as tf
+    from distributedtensorflow_b200.models import mnist_mlp
+    sys.path.insert(0, os.path.join(ROOT, "bench"))
+    import ps_bench
+
+    class A:
+        pass
+    args = A()
+    args.batch, args.model = batch, "mlp"
+    tf.reset_default_graph()
+    tf.set_random_seed(0)
+    cluster = tf.train.ClusterSpec({"ps": ["h:%d" % i for i in range(world)], "worker": ["w:%d" % i for i in range(world)]})
+    with tf.device(tf.train.replica_device_setter(worker_device="/job:worker/task:0", cluster=cluster,
+                                                  ps_strategy=tf.train.FlatSlicedStrategy(world))):
+        X = tf.placeholder(tf.float32, [None, 784])
+        Y = tf.placeholder(tf.float32, [None, 10])
+        gs, loss, _ = mnist_mlp.build_model(X, Y, hidden)
+        opt = tf.train.SyncReplicasOptimizer(tf.train.AdamOptimizer(lr), replicas_to_aggregate=world,
+                                             total_num_replicas=world)
+        train_op = opt.minimize(loss, global_step=gs)
+    server = tf.train.Server.create_local_server(num_ps=world)
+    names = [v.name for v in tf.trainable_variables()]
+    out, errs = {}, []
+
+    def worker(i):
+        try:
+            batches = ps_bench.make_batches(args, i)
+            hook = opt.make_session_run_hook(i == 0, num_tokens=0)
+            with tf.train.MonitoredTrainingSession(master=server.target, is_chief=(i == 0), hooks=[hook],
+                                                   config=tf.ConfigProto(backend="cpu"), recovery_wait_secs=0.01) as sess:
+                for k in range(steps):
+                    bx, by = batches[k % len(batches)]
+                    sess.run(train_op, feed_dict={X: bx.astype(np.float32) / 255.0, Y: by})
+                if i == 0:
+                    raw = sess._tf_sess()
+                    out.update(raw.ps_client.pull_all(raw.layout, names))
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+    ts = [threading.Thread(target=worker, args=(i,)) for i in range(world)]
+    [t.start() for t in ts]
+    [t.join(120) for t in ts]
+    assert not errs, errs
+    return out
+
+
+def test_sync_round_kernel_matches_cpu_sync_replicas():
+    steps, warm = 10, 2
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    res = _torchrun(2, "bench/ps_bench.py",
+                    ["--model", "mlp", "--mode", "sync", "--placement", "flat", "--steps", str(steps), "--warmup",
+                     str(warm), "--check", "--lr", "0.001", "--hidden", "100", "--batch", "100"], 29631)
+    assert res["final_step"] == steps + warm          # ONE global step per aggregated round
+    got0 = np.load(os.path.join(ROOT, "gpurun_out", "sync_params_rank0.npz"))
+    got1 = np.load(os.path.join(ROOT, "gpurun_out", "sync_params_rank1.npz"))
+    ref = _cpu_sync_oracle(steps + warm, 100, 100, 0.001, 2)
+    for name, r in ref.items():
+        a, b = got0[name.replace("/", "__")], got1[name.replace("/", "__")]
+        assert np.array_equal(a, b), name             # both ranks see the same PS state
+        diff = np.abs(a - r)
+        assert float(diff.mean()) < 2e-3 and float(diff.max()) < 0.03, (name, float(diff.mean()), float(diff.max()))
+
+
+def test_sync_checkpoint_sharded_save(tmp_path):
+    res = _torchrun(2, "bench/ps_bench.py",
+                    ["--model", "mlp", "--mode", "sync", "--placement", "round_robin", "--steps", "5", "--warmup", "2",
+                     "--ckpt-dir", str(tmp_path)], 29641)
+    assert res["ckpt_shards"] == 2 and res["ckpt_roundtrip_ok"] is True
+    assert res["ckpt_tensors"] == 4 * 3 + 1 + 2        # vars + Adam slots, global_step, beta powers
