@@ -258,8 +258,10 @@ def main() -> int:
             _, l, g = sess.run([train_op, loss, global_step])
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
-        final_step = int(g)
         final_loss = float(l)
+        if world > 1:
+            dist.barrier()           # every worker has finished: the shared counter is final
+        final_step = int(sess.run(global_step))
 
         times = torch.tensor([dev_ms, b2b_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
         if world > 1:

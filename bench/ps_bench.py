@@ -82,7 +82,10 @@ def main() -> int:
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # gloo on purpose: a PS-only rank must wait on the CPU. Parked inside an NCCL collective it
+        # would occupy its GPU with a spinning kernel while its RPC thread needs cudaMalloc for the
+        # shard arena, which needs the device idle -> deadlock.
+        dist.init_process_group("gloo")
         dist.barrier()
     import distributedtensorflow_b200 as tf
 
@@ -108,7 +111,7 @@ def main() -> int:
     strategy = {"flat": tf.train.FlatSlicedStrategy(nps), "greedy": tf.train.GreedyLoadBalancingStrategy(nps),
                 "round_robin": None}[args.placement]
     result = None
-    times = torch.zeros(2, dtype=torch.float64, device="cuda")
+    times = torch.zeros(2, dtype=torch.float64)
     if is_worker:
         tf.set_random_seed(0)
         with tf.device(tf.train.replica_device_setter(worker_device="/job:worker/task:%d" % wk_index,

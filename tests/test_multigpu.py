@@ -14,7 +14,7 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _torchrun(nproc, script, args, port, timeout=300):
+def _torchrun(nproc, script, args, port, timeout=150):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
            "--master-addr", "127.0.0.1", "--master-port", str(port), script, *args]
     p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
