@@ -115,9 +115,8 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
       float g[4] = {g4.x * a.h.grad_scale, g4.y * a.h.grad_scale, g4.z * a.h.grad_scale,
                     g4.w * a.h.grad_scale};
       if (!rmw) {
-        // write-only push: var += -lr * g via reduction atomics at the owner's L2
-#pragma unroll
-        for (int j = 0; j < 4; ++j) red_add_f32_sys(it.var + i + j, -a.h.lr * g[j]);
+        // write-only push: var += -lr * g, one 16-byte reduction atomic at the owner's L2
+        red_add_v4_f32_sys(it.var + i, -a.h.lr * g[0], -a.h.lr * g[1], -a.h.lr * g[2], -a.h.lr * g[3]);
         continue;  // shadow is refreshed by the owner in this mode
       }
       const float4 v4 = ldv_[u];

@@ -267,6 +267,9 @@ class B200StepRunner:
         self.use_cuda_graph = bool(opts.get("cuda_graph", True))
         self.fused_first_pull = bool(opts.get("fused_first_pull", True))
         self.atomic_sgd = bool(opts.get("atomic_sgd", False))
+        self.health_every = int(opts.get("health_every", 256))   # control-plane ping period (steps)
+        self._runs = 0
+        self._incarnations: Dict[int, int] = {}
         self.split_k = bool(opts.get("split_k", True))
         self.pdl = bool(opts.get("pdl", True))
         L.lib().dtf_set_pdl(1 if self.pdl else 0)
@@ -763,6 +766,9 @@ class B200StepRunner:
             step = self.store.read_global_step()
             return [self._as_step(step) for _ in fetches]
         top = train_ops[0] if train_ops else None
+        self._runs += 1
+        if self.health_every > 0 and self._runs % self.health_every == 0:
+            self.check_health()
         loss_node = top.loss if top is not None else self._find_loss(plain)
         self._ensure_plan(loss_node, top)
         p = self.plan
@@ -826,6 +832,23 @@ class B200StepRunner:
         f2[self.plan.loss_node] = np.float32(s.out_pin[0].item())
         vals = evaluate(list(nodes), f2, {})
         return {id(n): _to_numpy(v) for n, v in zip(nodes, vals)}
+
+    def check_health(self) -> None:
+        """Failure detection for the device data plane: a mapped arena stays readable after its
+        owner died, so liveness is checked over the control plane. A PS that is gone, or that came
+        back as a new incarnation (its arena and state were lost), surfaces as AbortedError — the
+        recoverable session then rebuilds the session and the chief restores / re-initialises
+        (reference: run_mnist_distributed.py:146)."""
+        from ..parallel.ps_core import AbortedError
+        for s in range(self.client.num_shards):
+            info = self.client.call(s, "ping")       # raises AbortedError when unreachable
+            inc = int(info.get("incarnation", 0))
+            if self._incarnations.setdefault(s, inc) != inc:
+                raise AbortedError(f"/job:ps/task:{s} restarted (state lost)")
+
+    def worker_heartbeats(self) -> List[int]:
+        """Last global step each worker published in the step-owning shard's control block."""
+        return self.store.read_ctrl(self.store.arena.step_shard)["heartbeat"]
 
     # -- benchmarking hooks ---------------------------------------------------------------------------
     def train_state(self) -> StepState:

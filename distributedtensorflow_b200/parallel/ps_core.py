@@ -268,6 +268,9 @@ class PsShard:
     def read_scalar(self, name: str) -> int:
         return int(self.vars[name].item())
 
+    def ping(self) -> dict:
+        return {"task": self.task_index, "incarnation": self.incarnation}
+
     def heartbeat(self, worker: int, step: int) -> None:
         self.heartbeats[worker] = (step, time.time())
 
