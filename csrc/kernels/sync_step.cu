@@ -141,7 +141,44 @@ sync_round_kernel(const __grid_constant__ SyncArgs a) {
     float* s0p = sg.slot0_off ? reinterpret_cast<float*>(base + sg.slot0_off) : nullptr;
     float* s1p = sg.slot1_off ? reinterpret_cast<float*>(base + sg.slot1_off) : nullptr;
     __nv_bfloat16* shadow = sg.shadow_off ? reinterpret_cast<__nv_bfloat16*>(base + sg.shadow_off) : nullptr;
-    for (long long i = tid; i < sg.n; i += nthreads) {
+    // 4 elements per thread (16-byte mailbox / state accesses, 8-byte bf16 stores) when the slice
+    // is 4-aligned in every view; scalar otherwise and for the tail
+    const bool vec = (sg.n % 4 == 0) && (sg.cols % 4 == 0) && (sg.first % 4 == 0) && (sg.shadow_ld % 4 == 0);
+    const long long nvec = vec ? sg.n / 4 : 0;
+    for (long long q = tid; q < nvec; q += nthreads) {
+      const long long i = q * 4;
+      float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int w = 0; w < a.world; ++w) {   // fixed order: bitwise reproducible
+        const float4 t = __ldcg(reinterpret_cast<const float4*>(
+            base + sg.mailbox_off + static_cast<unsigned long long>(w) * sg.mailbox_stride) + q);
+        g4.x += t.x; g4.y += t.y; g4.z += t.z; g4.w += t.w;
+      }
+      const float sc = inv_w * a.h.grad_scale;
+      float g[4] = {g4.x * sc, g4.y * sc, g4.z * sc, g4.w * sc};
+      float4 v4 = *reinterpret_cast<float4*>(var + i);
+      float4 m4 = s0p ? *reinterpret_cast<float4*>(s0p + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 u4 = s1p ? *reinterpret_cast<float4*>(s1p + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float v[4] = {v4.x, v4.y, v4.z, v4.w}, s0[4] = {m4.x, m4.y, m4.z, m4.w}, s1[4] = {u4.x, u4.y, u4.z, u4.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sync_update<OPT>(g[j], v[j], s0[j], s1[j], a.h, lr_t);
+      const float4 vo = make_float4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<float4*>(var + i) = vo;
+      if (s0p) *reinterpret_cast<float4*>(s0p + i) = make_float4(s0[0], s0[1], s0[2], s0[3]);
+      if (s1p) *reinterpret_cast<float4*>(s1p + i) = make_float4(s1[0], s1[1], s1[2], s1[3]);
+      const long long row = i / sg.cols, col = i % sg.cols;
+      uint2 vb;
+      vb.x = pack_bf16x2(v[0], v[1]);
+      vb.y = pack_bf16x2(v[2], v[3]);
+      if (shadow) *reinterpret_cast<uint2*>(shadow + row * sg.shadow_ld + col) = vb;
+      for (int w = 0; w < a.world; ++w) {   // all-gather into every worker's mirror
+        if (sg.mirror_f32_off)
+          *reinterpret_cast<float4*>(reinterpret_cast<float*>(a.arena[w] + sg.mirror_f32_off) + sg.first + i) = vo;
+        if (sg.mirror_bf16_off)
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(a.arena[w] + sg.mirror_bf16_off) +
+                                    (sg.first_row + row) * sg.shadow_ld + col) = vb;
+      }
+    }
+    for (long long i = nvec * 4 + tid; i < sg.n; i += nthreads) {
       float g = 0.f;
       for (int w = 0; w < a.world; ++w)   // fixed order: bitwise reproducible
         g += __ldcg(reinterpret_cast<const float*>(base + sg.mailbox_off +

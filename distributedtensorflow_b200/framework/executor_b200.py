@@ -641,8 +641,7 @@ class B200StepRunner:
             ev.record(side)
             main.wait_event(ev)
         if sync:
-            self._sync_round(s)      # reduce-scatter + mean + apply + all-gather, one kernel
-            return
+            return                   # the round kernel is launched after the (captured) compute part
         rest = [v for v in self.train_op.var_list if v not in applied]
         self._apply_vars(s, rest, finish=True)
 
@@ -704,7 +703,14 @@ class B200StepRunner:
             self._backward(s)          # includes the push+apply of every variable
         if with_io:
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
-            s.step_pin.copy_(s.step_dev, non_blocking=True)
+            if self.sync_opt is None or not s.train:
+                s.step_pin.copy_(s.step_dev, non_blocking=True)
+
+    def _enqueue_sync_tail(self, s: StepState) -> None:
+        """Synchronous mode: the cross-GPU round (cooperative kernel, launched outside the captured
+        graph) and the read-back of the new global step."""
+        self._sync_round(s)      # reduce-scatter + mean + apply + all-gather, one kernel
+        s.step_pin.copy_(s.step_dev, non_blocking=True)
 
     # -- state management ---------------------------------------------------------------------------
     def _ensure_plan(self, loss: G.Tensor, train_op=None) -> None:
@@ -740,8 +746,11 @@ class B200StepRunner:
 
     def _launch(self, s: StepState) -> None:
         with torch.cuda.stream(self.stream):
-            if not self.use_cuda_graph or self.sync_opt is not None:
+            sync = self.sync_opt is not None and s.train
+            if not self.use_cuda_graph:
                 self._enqueue_step(s)
+                if sync:
+                    self._enqueue_sync_tail(s)
                 return
             if s.graph is None:
                 # one eager step first (sets kernel attributes, warms the allocator), then capture
@@ -753,8 +762,12 @@ class B200StepRunner:
                 with torch.cuda.graph(g, stream=self.stream):
                     self._enqueue_step(s)
                 s.graph = g
+                if sync:
+                    self._enqueue_sync_tail(s)
                 return  # the eager step already did this run's work
             s.graph.replay()
+            if sync:
+                self._enqueue_sync_tail(s)
 
     # -- Session.run entry ---------------------------------------------------------------------------
     def run(self, fetches: Sequence[G.Tensor], feeds: Dict[G.Tensor, Any]) -> List[Any]:
