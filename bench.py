@@ -127,6 +127,7 @@ def main() -> int:
     ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch")
     ap.add_argument("--no-split-k", action="store_true", help="disable split-K for skinny GEMMs")
     ap.add_argument("--no-overlap", action="store_true", help="single-stream backward (no side stream)")
+    ap.add_argument("--fused-apply", action="store_true", help="dW GEMM epilogue does the push+apply")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -197,7 +198,7 @@ def main() -> int:
 
     cfg = tf.ConfigProto(allow_soft_placement=True, backend="b200", device="cuda:%d" % local_rank,
                          cuda_graph=not args.no_cuda_graph, pdl=not args.no_pdl,
-                         split_k=not args.no_split_k, overlap=not args.no_overlap)
+                         split_k=not args.no_split_k, overlap=not args.no_overlap, fused_apply=args.fused_apply)
     result = {}
     with tf.train.MonitoredTrainingSession(master=wk_server.target, is_chief=(rank == 0), config=cfg,
                                            recovery_wait_secs=0.05) as sess:
@@ -283,7 +284,8 @@ def main() -> int:
                                       % (N, N, placement),
                        "l2": "not flushed" if args.no_l2_flush else "flushed between timed steps (256 MiB write)",
                        "cuda_graph": not args.no_cuda_graph, "pdl": not args.no_pdl,
-                       "split_k": not args.no_split_k, "overlap": not args.no_overlap},
+                       "split_k": not args.no_split_k, "overlap": not args.no_overlap,
+                       "fused_apply": args.fused_apply},
             "time_to_1000_global_steps_s": round(1000.0 / value, 5),
             "back_to_back_ms_per_step": round(b2b_ms / args.steps, 5),
             "e2e": {"value": round(N * args.steps / (e2e_ms / 1e3), 2), "unit": "global steps/s",

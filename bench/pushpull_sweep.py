@@ -159,7 +159,9 @@ def main() -> int:
             per = (size // world) // 16 * 16
 
             def pull_all():
-                K.pull_bulk([(bases[s] + off_var, local.data_ptr() + s * per, per) for s in range(world) if s != rank])
+                # ring order starting at my neighbour: at any moment the N ranks read N different peers
+                K.pull_bulk([(bases[s] + off_var, local.data_ptr() + s * per, per)
+                             for s in [(rank + k) % world for k in range(1, world)]])
             us = timed(pull_all)
             row["pull_all_shards_gbs"] = round(per * (world - 1) / us / 1e3, 2)
             ag_in = pattern[:per // 4].contiguous()

@@ -69,7 +69,97 @@ struct GemmParams {
   float* ws;                // [M, ldws] fp32, zero on entry
   int ldws;
   unsigned int* counters;   // one per output tile, zero on entry (self-resetting)
+  // fused push + optimizer apply (see dtf_gemm_epilogue)
+  int apply_opt;
+  int apply_rows_per_slice;
+  int apply_shadow_ld;
+  dtf_apply_hyper ah;
+  const dtf_ps_ctrl* apply_ctrl_powers;
+  float* avar[8];
+  float* aslot0[8];
+  float* aslot1[8];
+  __nv_bfloat16* ashadow[8];
 };
+
+__device__ __forceinline__ void gemm_apply_one(int opt, const dtf_apply_hyper& h, float lr_t, float g,
+                                               float& var, float& s0, float& s1) {
+  if (opt == DTF_OPT_SGD) {
+    var -= h.lr * g;
+  } else if (opt == DTF_OPT_MOMENTUM) {
+    s0 = s0 * h.momentum + g;
+    var -= h.use_nesterov ? (g * h.lr + s0 * h.momentum * h.lr) : h.lr * s0;
+  } else if (opt == DTF_OPT_ADAGRAD) {
+    s0 += g * g;
+    var -= h.lr * g * rsqrtf(s0);
+  } else {
+    s0 += (g - s0) * (1.f - h.beta1);
+    s1 += (g * g - s1) * (1.f - h.beta2);
+    var -= lr_t * s0 / (sqrtf(s1) + h.epsilon);
+  }
+}
+
+// Fused epilogue of a weight-gradient GEMM: v[0..31] are the gradients of row m, columns
+// nb..nb+31 of a variable [M, N]; read-modify-write var / slots on the owning slice (local or
+// peer memory) and refresh its bf16 serving copy. Unlocked, like every PS apply here.
+__device__ __forceinline__ void gemm_epilogue_apply(const GemmParams& p, int m, int nb, float (&v)[32],
+                                                    float lr_t) {
+  const int slice = m / p.apply_rows_per_slice;
+  const long long r = m - slice * p.apply_rows_per_slice;
+  const long long idx = r * p.N + nb;
+  float* var = p.avar[slice] + idx;
+  float* s0p = p.aslot0[slice] ? p.aslot0[slice] + idx : nullptr;
+  float* s1p = p.aslot1[slice] ? p.aslot1[slice] + idx : nullptr;
+  __nv_bfloat16* sh = p.ashadow[slice] ? p.ashadow[slice] + r * p.apply_shadow_ld + nb : nullptr;
+  const float gs = p.alpha * p.ah.grad_scale;
+  const bool vec = (p.N % 4 == 0) && (nb + 32 <= p.N) && (p.apply_shadow_ld % 4 == 0);
+  if (vec) {
+#pragma unroll
+    for (int g8 = 0; g8 < 4; ++g8) {          // 8 columns at a time keeps the register count flat
+      float4 w0 = *reinterpret_cast<float4*>(var + g8 * 8), w1 = *reinterpret_cast<float4*>(var + g8 * 8 + 4);
+      float4 a0 = make_float4(0, 0, 0, 0), a1 = a0, b0 = a0, b1 = a0;
+      if (s0p) { a0 = *reinterpret_cast<float4*>(s0p + g8 * 8); a1 = *reinterpret_cast<float4*>(s0p + g8 * 8 + 4); }
+      if (s1p) { b0 = *reinterpret_cast<float4*>(s1p + g8 * 8); b1 = *reinterpret_cast<float4*>(s1p + g8 * 8 + 4); }
+      float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+      float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      float b[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) gemm_apply_one(p.apply_opt, p.ah, lr_t, v[g8 * 8 + j] * gs, w[j], a[j], b[j]);
+      *reinterpret_cast<float4*>(var + g8 * 8) = make_float4(w[0], w[1], w[2], w[3]);
+      *reinterpret_cast<float4*>(var + g8 * 8 + 4) = make_float4(w[4], w[5], w[6], w[7]);
+      if (s0p) {
+        *reinterpret_cast<float4*>(s0p + g8 * 8) = make_float4(a[0], a[1], a[2], a[3]);
+        *reinterpret_cast<float4*>(s0p + g8 * 8 + 4) = make_float4(a[4], a[5], a[6], a[7]);
+      }
+      if (s1p) {
+        *reinterpret_cast<float4*>(s1p + g8 * 8) = make_float4(b[0], b[1], b[2], b[3]);
+        *reinterpret_cast<float4*>(s1p + g8 * 8 + 4) = make_float4(b[4], b[5], b[6], b[7]);
+      }
+      if (sh) {
+        uint4 o;
+        o.x = pack_bf16x2(w[0], w[1]); o.y = pack_bf16x2(w[2], w[3]);
+        o.z = pack_bf16x2(w[4], w[5]); o.w = pack_bf16x2(w[6], w[7]);
+        if ((p.apply_shadow_ld & 7) == 0) {
+          *reinterpret_cast<uint4*>(sh + g8 * 8) = o;
+        } else {
+          *reinterpret_cast<uint2*>(sh + g8 * 8) = make_uint2(o.x, o.y);
+          *reinterpret_cast<uint2*>(sh + g8 * 8 + 4) = make_uint2(o.z, o.w);
+        }
+      }
+    }
+  } else {
+#pragma unroll 1
+    for (int j = 0; j < 32; ++j) {
+      if (nb + j >= p.N) break;
+      float w = var[j];
+      float a = s0p ? s0p[j] : 0.f, b = s1p ? s1p[j] : 0.f;
+      gemm_apply_one(p.apply_opt, p.ah, lr_t, v[j] * gs, w, a, b);
+      var[j] = w;
+      if (s0p) s0p[j] = a;
+      if (s1p) s1p[j] = b;
+      if (sh) sh[j] = __float2bfloat16(w);
+    }
+  }
+}
 
 // Applies the fused epilogue to 32 consecutive accumulator columns of row m and stores them.
 __device__ __forceinline__ void gemm_epilogue_store(const GemmParams& p, int m, int nb, float (&v)[32]) {
@@ -257,6 +347,13 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     const bool row_ok = m < p.M;
     const bool fixup = p.splits > 1 && !p.reduce;
+    float lr_t = p.ah.lr;
+    if (p.apply_opt == DTF_OPT_ADAM) {
+      // shared beta powers live on the PS; every thread reads them (two cached 4-byte loads)
+      const float b1p = *reinterpret_cast<const volatile float*>(&p.apply_ctrl_powers->beta1_power);
+      const float b2p = *reinterpret_cast<const volatile float*>(&p.apply_ctrl_powers->beta2_power);
+      lr_t = p.ah.lr * sqrtf(1.f - b2p) / (1.f - b1p);
+    }
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       uint32_t r[32];
@@ -272,7 +369,9 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
       float v[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-      if (!fixup) {
+      if (p.apply_opt >= 0) {
+        gemm_epilogue_apply(p, m, nb, v, lr_t);
+      } else if (!fixup) {
         gemm_epilogue_store(p, m, nb, v);
       } else {
         // partial tile -> fp32 workspace (ldws is a multiple of 4, rows are 16-byte aligned)
@@ -344,7 +443,7 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
                              int block_n, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
-  DTF_REQUIRE(epi != nullptr && epi->out != nullptr, "gemm: epilogue/out is null");
+  DTF_REQUIRE(epi != nullptr && (epi->out != nullptr || epi->apply_enable), "gemm: epilogue/out is null");
   DTF_REQUIRE(lda % 8 == 0 && ldb % 8 == 0,
               "gemm: lda=%d ldb=%d must be multiples of 8 elements (TMA 16 B rule)", lda, ldb);
   const int BN = (block_n == 64 || block_n == 128) ? block_n : (N > 64 ? 128 : 64);
@@ -402,6 +501,32 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
   p.ws = epi->splitk_ws;
   p.ldws = epi->ldws;
   p.counters = epi->tile_counters;
+  p.apply_opt = epi->apply_enable ? epi->apply_opt : -1;
+  if (epi->apply_enable) {
+    DTF_REQUIRE(p.apply_opt >= 0, "gemm: unknown optimizer %d", p.apply_opt);
+    DTF_REQUIRE(p.splits == 1, "gemm: the fused apply epilogue cannot be combined with split-K");
+    DTF_REQUIRE(epi->apply_rows_per_slice > 0 && ceil_div(M, epi->apply_rows_per_slice) <= 8,
+                "gemm: fused apply needs 1..8 row slices (rows_per_slice=%d, M=%d)",
+                epi->apply_rows_per_slice, M);
+    DTF_REQUIRE(p.apply_opt <= DTF_OPT_ADAM, "gemm: unknown optimizer %d", p.apply_opt);
+    DTF_REQUIRE(p.apply_opt != DTF_OPT_ADAM || epi->apply_ctrl_powers != nullptr,
+                "gemm: fused Adam needs the control block with the beta powers");
+    p.apply_rows_per_slice = epi->apply_rows_per_slice;
+    p.apply_shadow_ld = epi->apply_shadow_ld;
+    p.ah.lr = epi->apply_lr; p.ah.beta1 = epi->apply_beta1; p.ah.beta2 = epi->apply_beta2;
+    p.ah.epsilon = epi->apply_epsilon; p.ah.momentum = epi->apply_momentum;
+    p.ah.grad_scale = epi->apply_grad_scale; p.ah.use_nesterov = epi->apply_use_nesterov;
+    p.apply_ctrl_powers = epi->apply_ctrl_powers;
+    for (int i = 0; i < 8; ++i) {
+      p.avar[i] = epi->apply_var[i];
+      p.aslot0[i] = epi->apply_slot0[i];
+      p.aslot1[i] = epi->apply_slot1[i];
+      p.ashadow[i] = reinterpret_cast<__nv_bfloat16*>(epi->apply_shadow[i]);
+    }
+    p.n_store = N;
+    for (int i = 0; i < ceil_div(M, p.apply_rows_per_slice); ++i)
+      DTF_REQUIRE(p.avar[i] != nullptr, "gemm: fused apply slice %d has no variable pointer", i);
+  }
 
 #define DTF_DISPATCH(BN_, AM_, BM_) return launch_gemm<BN_, AM_, BM_>(ta, tb, p, stream)
   if (BN == 64) {

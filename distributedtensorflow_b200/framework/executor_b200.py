@@ -270,6 +270,9 @@ class B200StepRunner:
         self.health_every = int(opts.get("health_every", 256))   # control-plane ping period (steps)
         self._runs = 0
         self._incarnations: Dict[int, int] = {}
+        # dW GEMM whose epilogue is the push+apply (no gradient buffer). Measured on the reference CNN it
+        # is slower than GEMM + the coalesced apply kernel (180 vs 158 us/step), so it is opt-in.
+        self.fused_apply = bool(opts.get("fused_apply", False))
         self.split_k = bool(opts.get("split_k", True))
         self.pdl = bool(opts.get("pdl", True))
         L.lib().dtf_set_pdl(1 if self.pdl else 0)
@@ -403,6 +406,13 @@ class B200StepRunner:
     def _regions(self, var: G.Variable) -> List[SliceRegion]:
         return self.store.arena.regions[var.name]
 
+    def _regions_rotated(self, var: G.Variable) -> List[SliceRegion]:
+        """Slices in the order THIS worker should touch them: starting at its own shard and going
+        round the ring, so that N workers sweeping their slice lists in lock-step hit N different
+        shards (and NVLink ports) at any moment instead of all hammering shard 0 first."""
+        n = max(1, self.client.num_shards)
+        return sorted(self._regions(var), key=lambda r: (r.shard - self.worker_id) % n)
+
     def _single_local(self, var: G.Variable) -> Optional[SliceRegion]:
         regs = self._regions(var)
         if len(regs) == 1 and self.store.is_local[regs[0].shard]:
@@ -429,10 +439,9 @@ class B200StepRunner:
             rows = sum(r.rows for r in regs)
             buf = torch.zeros((rows, ld), dtype=torch.bfloat16, device=self.device)
             self.local["w:" + var.name] = buf
-            row = 0
-            for r in regs:
+            for r in self._regions_rotated(var):
+                row = r.sl.first // r.cols
                 self.copies.append((st.shadow_ptr(r), buf.data_ptr() + row * ld * 2, r.rows * ld * 2))
-                row += r.rows
             self.wptr[var.name] = (buf.data_ptr(), ld)
 
         def want_f32(var: G.Variable, allow_in_place: bool) -> None:
@@ -443,7 +452,7 @@ class B200StepRunner:
             n = self.layout[var.name].num_elements
             buf = torch.zeros(((n + 63) // 64 * 64,), dtype=torch.float32, device=self.device)
             self.local["f:" + var.name] = buf
-            for r in regs:
+            for r in self._regions_rotated(var):
                 nbytes = (r.sl.n * 4 + 15) // 16 * 16
                 self.copies.append((st.var_ptr(r), buf.data_ptr() + r.sl.first * 4, nbytes))
             self.fptr[var.name] = buf.data_ptr()
@@ -471,14 +480,13 @@ class B200StepRunner:
             regs = self._regions(var)
             ld = regs[0].shadow_ld
             self.wptr[var.name] = (me + al.mirror_bf16[var.name], ld)
-            row = 0
-            for r in regs:
+            for r in self._regions_rotated(var):
+                row = r.sl.first // r.cols
                 self.copies.append((st.shadow_ptr(r), me + al.mirror_bf16[var.name] + row * ld * 2, r.rows * ld * 2))
-                row += r.rows
 
         def use_f32(var):
             self.fptr[var.name] = me + al.mirror_f32[var.name]
-            for r in self._regions(var):
+            for r in self._regions_rotated(var):
                 self.copies.append((st.var_ptr(r), me + al.mirror_f32[var.name] + r.sl.first * 4,
                                     (r.sl.n * 4 + 15) // 16 * 16))
 
@@ -501,7 +509,7 @@ class B200StepRunner:
         segs = []
         for var in self.train_op.var_list:
             gptr = self._grad_ptr(s, var)
-            for r in self._regions(var):
+            for r in self._regions_rotated(var):
                 sg = L.SyncSegment()
                 sg.owner, sg.cols, sg.shadow_ld = r.shard, r.cols, r.shadow_ld
                 sg.n, sg.first, sg.first_row = r.sl.n, r.sl.first, r.sl.first // r.cols
@@ -607,9 +615,12 @@ class B200StepRunner:
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
-            with torch.cuda.stream(side):
-                # dW_i = act_i^T dZ_i
-                K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
+            fused = self._fused_apply_spec(d.w) if (self.overlap and not sync and self.fused_apply) else None
+            dz_i = dz
+            if fused is None:
+                with torch.cuda.stream(side):
+                    # dW_i = act_i^T dZ_i
+                    K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
             wp, ld = self.wptr[d.w.name]
             if i > 0:
                 # dZ_{i-1} = (dZ_i W_i^T) * relu'(act_i);  db_{i-1} = colsum
@@ -625,7 +636,12 @@ class B200StepRunner:
                 # push+apply of W_i as soon as its gradient exists and the dX GEMM above (which
                 # reads W_i, possibly in place in the local shard) has been ordered before it
                 with torch.cuda.stream(side):
-                    self._apply_vars(s, [d.w], finish=False)
+                    if fused is not None:
+                        # dW_i GEMM whose epilogue IS the push+apply: the gradient never exists in
+                        # memory, the TMEM accumulator goes straight into the owner's var / m / v
+                        K.gemm(s.act[i], dz_i, None, din, dout, s.B, a_mn=True, b_mn=True, apply=fused)
+                    else:
+                        self._apply_vars(s, [d.w], finish=False)
                 applied.append(d.w)
         if p.kind == "cnn":
             c1, c2 = p.convs
@@ -659,6 +675,26 @@ class B200StepRunner:
                 return s.z[f"gb{i}"].data_ptr()
         raise KeyError(var.name)
 
+    def _fused_apply_spec(self, var: G.Variable) -> Optional[dict]:
+        """Arguments of the GEMM's fused push+apply epilogue for a 2-D variable, or None when the
+        variable's slicing cannot be expressed as uniform row slices."""
+        regs = sorted(self._regions(var), key=lambda r: r.sl.first)
+        if len(var.shape) != 2 or not regs or len(regs) > 8:
+            return None
+        M, N = int(var.shape[0]), int(var.shape[1])
+        per = regs[0].rows if len(regs) > 1 else M
+        st, spec = self.store, self.spec
+        slices: List[dict] = []
+        for k, r in enumerate(regs):
+            if r.sl.first != k * per * N or (k + 1 < len(regs) and r.rows != per):
+                return None
+            slices.append(dict(var=st.var_ptr(r), slot0=st.slot_ptr(r, 0), slot1=st.slot_ptr(r, 1),
+                               shadow=st.shadow_ptr(r)))
+        hyper = K.make_hyper(spec.learning_rate, spec.beta1, spec.beta2, spec.epsilon, spec.momentum,
+                             1.0, spec.use_nesterov, False)
+        return dict(opt=spec.code, hyper=hyper, rows_per_slice=per, shadow_ld=regs[0].shadow_ld,
+                    ctrl_powers=st.powers_ctrl, slices=slices)
+
     def _apply_vars(self, s: StepState, variables: Sequence[G.Variable], finish: bool) -> None:
         """push+apply of ``variables`` on the current stream; ``finish`` adds TF's _finish (beta
         powers) and the global_step atomic and must be the step's last apply."""
@@ -666,7 +702,7 @@ class B200StepRunner:
         entries = []
         for var in variables:
             gptr = self._grad_ptr(s, var)
-            for r in self._regions(var):
+            for r in self._regions_rotated(var):
                 entries.append(dict(var=st.var_ptr(r), slot0=st.slot_ptr(r, 0), slot1=st.slot_ptr(r, 1),
                                     shadow=st.shadow_ptr(r), grad=gptr + r.sl.first * 4, n=r.sl.n,
                                     first=0, cols=r.cols, shadow_ld=r.shadow_ld))

@@ -64,6 +64,19 @@ class GemmEpilogue(C.Structure):
         ("splitk_ws", C.c_void_p),
         ("ldws", C.c_int),
         ("tile_counters", C.c_void_p),
+        ("apply_enable", C.c_int),
+        ("apply_opt", C.c_int),
+        ("apply_rows_per_slice", C.c_int),
+        ("apply_shadow_ld", C.c_int),
+        ("apply_lr", C.c_float), ("apply_beta1", C.c_float), ("apply_beta2", C.c_float),
+        ("apply_epsilon", C.c_float), ("apply_momentum", C.c_float), ("apply_grad_scale", C.c_float),
+        ("apply_use_nesterov", C.c_int),
+        ("apply_reserved2", C.c_int),
+        ("apply_ctrl_powers", C.c_void_p),
+        ("apply_var", C.c_void_p * 8),
+        ("apply_slot0", C.c_void_p * 8),
+        ("apply_slot1", C.c_void_p * 8),
+        ("apply_shadow", C.c_void_p * 8),
     ]
 
 

@@ -38,14 +38,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
          alpha: float = 1.0, splits: int = 1, block_n: int = 0,
          a_ptr: Optional[int] = None, b_ptr: Optional[int] = None, lda: Optional[int] = None,
          ldb: Optional[int] = None, ws: Optional[torch.Tensor] = None,
-         counters: Optional[torch.Tensor] = None) -> None:
+         counters: Optional[torch.Tensor] = None, apply: Optional[dict] = None) -> None:
     """out[M,N] = alpha * A @ B^T with the fused epilogue of ``dtf_gemm_bf16``.
 
     ``a``/``b`` are 2-D bf16 tensors whose row pitch (stride(0)) is a multiple of 8; with
     ``a_mn``/``b_mn`` they are stored transposed ([K,M] / [K,N]). ``a_ptr``/``b_ptr`` override
     the base address (peer-mapped PS memory) while ``lda``/``ldb`` give its pitch.
     """
-    assert out.dim() == 2 and out.stride(1) == 1
+    if apply is None:
+        assert out.dim() == 2 and out.stride(1) == 1
     if a_ptr is None:
         assert a.dtype == torch.bfloat16 and a.stride(1) == 1
         a_ptr, lda = a.data_ptr(), a.stride(0)
@@ -53,10 +54,27 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
         assert b.dtype == torch.bfloat16 and b.stride(1) == 1
         b_ptr, ldb = b.data_ptr(), b.stride(0)
     epi = L.GemmEpilogue()
-    epi.out = out.data_ptr()
-    epi.ldo = out.stride(0)
-    epi.out_f32 = 1 if out.dtype == torch.float32 else 0
-    assert out.dtype in (torch.float32, torch.bfloat16)
+    if apply is None:
+        epi.out = out.data_ptr()
+        epi.ldo = out.stride(0)
+        epi.out_f32 = 1 if out.dtype == torch.float32 else 0
+        assert out.dtype in (torch.float32, torch.bfloat16)
+    else:
+        # fused push+apply epilogue: see dtf_gemm_epilogue.apply_* in include/dtf_b200.h
+        epi.out, epi.ldo, epi.out_f32 = None, N, 1
+        h = apply["hyper"]
+        epi.apply_enable, epi.apply_opt = 1, apply["opt"]
+        epi.apply_rows_per_slice = apply["rows_per_slice"]
+        epi.apply_shadow_ld = apply.get("shadow_ld", N)
+        epi.apply_lr, epi.apply_beta1, epi.apply_beta2 = h.lr, h.beta1, h.beta2
+        epi.apply_epsilon, epi.apply_momentum, epi.apply_grad_scale = h.epsilon, h.momentum, h.grad_scale
+        epi.apply_use_nesterov = h.use_nesterov
+        epi.apply_ctrl_powers = apply.get("ctrl_powers")
+        for i, sl in enumerate(apply["slices"]):
+            epi.apply_var[i] = sl["var"]
+            epi.apply_slot0[i] = sl.get("slot0")
+            epi.apply_slot1[i] = sl.get("slot1")
+            epi.apply_shadow[i] = sl.get("shadow")
     epi.bias = _ptr(bias)
     epi.relu = int(relu)
     epi.mask = _ptr(mask)

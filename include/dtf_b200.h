@@ -64,6 +64,24 @@ typedef struct dtf_gemm_epilogue {
   float* splitk_ws;             /* [M, ldws] fp32, 16-byte aligned, ldws % 4 == 0, ldws >= N */
   int ldws;
   unsigned int* tile_counters;  /* ceil(M/128) * ceil(N/block_n) words */
+  /* Fused gradient push + optimizer apply (weight-gradient GEMMs, K2 + K9 in one kernel): when
+   * apply_enable != 0 the accumulator element (m, n) is the gradient of element m*N + n of a
+   * variable [M, N] and the epilogue applies the TF1 update rule to it in place on the owning
+   * shard(s) - local or NVLink peer pointers - instead of storing `out` (which is ignored).
+   * The variable may be cut into row slices of apply_rows_per_slice rows, slice i living at
+   * apply_var[i] etc. (slice-local indexing). Not combinable with split-K. */
+  int apply_enable;             /* 0 = off (a zero-initialised struct is a plain GEMM) */
+  int apply_opt;                /* DTF_OPT_* */
+  int apply_rows_per_slice;
+  int apply_shadow_ld;          /* row pitch of the bf16 serving copy, elements */
+  float apply_lr, apply_beta1, apply_beta2, apply_epsilon, apply_momentum, apply_grad_scale;
+  int apply_use_nesterov;
+  int apply_reserved2;
+  const struct dtf_ps_ctrl* apply_ctrl_powers;   /* Adam: control block with the beta powers */
+  float* apply_var[8];
+  float* apply_slot0[8];
+  float* apply_slot1[8];
+  void* apply_shadow[8];        /* bf16 serving copy per slice, or NULL */
 } dtf_gemm_epilogue;
 
 int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int b_mn, int M,

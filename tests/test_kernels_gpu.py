@@ -129,6 +129,58 @@ def test_gemm_split_k_fixup_keeps_fused_epilogue(K, M, N, K_, splits, block_n):
         assert (counters == 0).all()
 
 
+@pytest.mark.parametrize("opt", ["adam", "sgd", "momentum", "adagrad"])
+@pytest.mark.parametrize("M,N,B,slices", [(3136, 1024, 128, 1), (1024, 10, 128, 1), (784, 104, 100, 3)])
+def test_gemm_fused_push_apply_matches_gemm_then_apply(K, opt, M, N, B, slices):
+    """dW = X^T dY with the optimizer applied in the epilogue (no gradient buffer) == the same GEMM
+    writing fp32 gradients followed by dtf_push_apply; the variable may be cut into row slices."""
+    from distributedtensorflow_b200.ops import _lib as L
+    torch.manual_seed(14)
+    code = {"sgd": L.OPT_SGD, "momentum": L.OPT_MOMENTUM, "adagrad": L.OPT_ADAGRAD, "adam": L.OPT_ADAM}[opt]
+    X = _padded(B, M, fill=torch.randn(B, M, device="cuda"))          # [K=B, M]  (MN-major A)
+    dY = _padded(B, N, fill=torch.randn(B, N, device="cuda") * 0.1)   # [K=B, N]  (MN-major B)
+    ld = K.pad8(N)
+    var0 = torch.randn(M * N, device="cuda")
+    m0 = torch.rand(M * N, device="cuda") * 0.1 + 0.1
+    v0 = torch.rand(M * N, device="cuda") * 0.01
+    ctrl = torch.zeros(64, dtype=torch.int32, device="cuda")
+    ctrl.view(torch.float32)[2], ctrl.view(torch.float32)[3] = 0.9 ** 2, 0.999 ** 2
+    hyper = K.make_hyper(0.01, momentum=0.9)
+    # reference: GEMM -> gradient buffer -> push_apply
+    grad = torch.zeros(M, N, device="cuda")
+    K.gemm(X, dY, grad, M, N, B, a_mn=True, b_mn=True)
+    rv, rm, rvv = var0.clone(), m0.clone(), v0.clone()
+    rsh = torch.zeros(M, ld, dtype=torch.bfloat16, device="cuda")
+    counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+    items = K.make_apply_items([dict(var=rv.data_ptr(), slot0=rm.data_ptr(), slot1=rvv.data_ptr(), shadow=rsh.data_ptr(),
+                                     grad=grad.data_ptr(), n=M * N, cols=N, shadow_ld=ld)])
+    K.push_apply(code, items, 1, hyper, ctrl.data_ptr(), ctrl.data_ptr(), False, 0, None, counter.data_ptr())
+    # fused: separate allocations per row slice, as on a flat-sliced cluster
+    rows = -(-M // slices)
+    rows = -(-rows // 64) * 64 if slices > 1 else M
+    sl = []
+    keep = []
+    for i in range(slices):
+        b, e = min(M, i * rows), min(M, (i + 1) * rows)
+        fv, fm, fvv = var0[b * N:e * N].clone(), m0[b * N:e * N].clone(), v0[b * N:e * N].clone()
+        fsh = torch.zeros(max(e - b, 1), ld, dtype=torch.bfloat16, device="cuda")
+        keep.append((b, e, fv, fm, fvv, fsh))
+        sl.append(dict(var=fv.data_ptr(), slot0=fm.data_ptr() if opt != "sgd" else None,
+                       slot1=fvv.data_ptr() if opt == "adam" else None, shadow=fsh.data_ptr()))
+    K.gemm(X, dY, None, M, N, B, a_mn=True, b_mn=True,
+           apply=dict(opt=code, hyper=hyper, rows_per_slice=rows, shadow_ld=ld, ctrl_powers=ctrl.data_ptr(), slices=sl))
+    torch.cuda.synchronize()
+    for b, e, fv, fm, fvv, fsh in keep:
+        assert (fv - rv[b * N:e * N]).abs().max().item() < 1e-6
+        if opt != "sgd":
+            assert (fm - rm[b * N:e * N]).abs().max().item() < 1e-6
+        if opt == "adam":
+            assert (fvv - rvv[b * N:e * N]).abs().max().item() < 1e-6
+        # serving copies agree to one bf16 ulp (the two kernels contract FMAs differently)
+        assert (fsh[:e - b, :N].float() - rsh[b:e, :N].float()).abs().max().item() <= 0.01 * rv.abs().max().item()
+    assert (rv - var0).abs().max().item() > 0
+
+
 def test_pdl_launches_give_identical_results(K):
     """Programmatic dependent launch only overlaps prologues: results must not change."""
     from distributedtensorflow_b200.ops import _lib as L
