@@ -25,7 +25,7 @@ __device__ __forceinline__ void load_image_padded(float (*img)[C1_PAD], const un
   }
 }
 
-// One CTA per image. Work item = (pooled pixel, group of 8 output channels).
+// Two CTAs per image (grid B x 2). Work item = (pooled pixel, group of 8 output channels).
 __global__ void __launch_bounds__(256)
 conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
                  float scale, const float* __restrict__ w1, const float* __restrict__ b1,
@@ -41,8 +41,10 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   if (threadIdx.x < C1_CH) bias[threadIdx.x] = b1[threadIdx.x];
   __syncthreads();
 
-  for (int item = threadIdx.x; item < C1_OUT * C1_OUT * 4; item += blockDim.x) {
-    const int pp = item >> 2, cg = item & 3;
+  // two CTAs per image (blockIdx.y = upper / lower 7 pooled rows): 2 CTAs per SM, twice the warps
+  constexpr int HALF = C1_OUT * C1_OUT / 2;
+  for (int item = threadIdx.x; item < HALF * 4; item += blockDim.x) {
+    const int pp = blockIdx.y * HALF + (item >> 2), cg = item & 3;
     const int py = pp / C1_OUT, px = pp % C1_OUT;
     float patch[6][6];
 #pragma unroll
@@ -90,8 +92,8 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   }
 }
 
-// One CTA (800 threads = 25 taps x 32 channels) per image: thread (tap, c) accumulates
-// dW1[tap, c] over the image's 196 pooled pixels; warp 0 also accumulates db1.
+// Two CTAs (800 threads = 25 taps x 32 channels) per image: thread (tap, c) accumulates
+// dW1[tap, c] over its half of the image's 196 pooled pixels; warp 0 also accumulates db1.
 __global__ void __launch_bounds__(800)
 conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
                  float scale, const __nv_bfloat16* __restrict__ dpool1,
@@ -106,8 +108,10 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   load_image_padded(img, x_u8, x_f32, scale, n);
   // stage the ReLU-masked gradient and the argmax map: one (pooled pixel, 8 channels) item per
   // thread, 16-byte loads, a single pass (784 items <= 800 threads)
-  for (int item = threadIdx.x; item < C1_OUT * C1_OUT * 4; item += blockDim.x) {
-    const int pp = item >> 2, cg = item & 3;
+  constexpr int HALF = C1_OUT * C1_OUT / 2;       // blockIdx.y picks the upper / lower 7 pooled rows
+  const int pp0 = blockIdx.y * HALF;
+  for (int item = threadIdx.x; item < HALF * 4; item += blockDim.x) {
+    const int pp = pp0 + (item >> 2), cg = item & 3;
     const int py = pp / C1_OUT, px = pp % C1_OUT;
     const uint4 av = *reinterpret_cast<const uint4*>(
         pool1p + ((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + cg * 8);
@@ -125,7 +129,7 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   const int tap = threadIdx.x >> 5, c = threadIdx.x & 31;
   const int r = tap / 5, s = tap % 5;
   float acc[4] = {0.f, 0.f, 0.f, 0.f}, accb = 0.f;
-  for (int py = 0; py < C1_OUT; ++py) {
+  for (int py = blockIdx.y * (C1_OUT / 2); py < (blockIdx.y + 1) * (C1_OUT / 2); ++py) {
 #pragma unroll
     for (int px = 0; px < C1_OUT; ++px) {  // 14 independent smem chains per row
       const int pp = py * C1_OUT + px;
@@ -201,7 +205,7 @@ extern "C" int dtf_conv1_fwd(const unsigned char* x_u8, const float* x_f32, floa
                              const float* w1, const float* b1, void* pool1p,
                              unsigned char* amax1, int B, void* stream) {
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_fwd: pass exactly one of x_u8/x_f32");
-  DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B), dim3(256), 0,
+  DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B, 2), dim3(196), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale, w1, b1,
                                reinterpret_cast<__nv_bfloat16*>(pool1p), amax1));
   return 0;
@@ -211,7 +215,7 @@ extern "C" int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, floa
                              const void* dpool1, const void* pool1p, const unsigned char* amax1,
                              float* dw1_accum, float* db1_accum, int B, void* stream) {
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_bwd: pass exactly one of x_u8/x_f32");
-  DTF_CHECK_CUDA(launch_kernel(conv1_bwd_kernel, dim3(B), dim3(800), 0,
+  DTF_CHECK_CUDA(launch_kernel(conv1_bwd_kernel, dim3(B, 2), dim3(800), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale,
                                reinterpret_cast<const __nv_bfloat16*>(dpool1),
                                reinterpret_cast<const __nv_bfloat16*>(pool1p),

@@ -273,6 +273,7 @@ class B200StepRunner:
         # dW GEMM whose epilogue is the push+apply (no gradient buffer). Measured on the reference CNN it
         # is slower than GEMM + the coalesced apply kernel (180 vs 158 us/step), so it is opt-in.
         self.fused_apply = bool(opts.get("fused_apply", False))
+        self.clear_at_end = bool(opts.get("clear_at_end", True))
         self.split_k = bool(opts.get("split_k", True))
         self.pdl = bool(opts.get("pdl", True))
         L.lib().dtf_set_pdl(1 if self.pdl else 0)
@@ -284,8 +285,10 @@ class B200StepRunner:
         self.train_op = None
         self.states: Dict[Tuple[int, bool], StepState] = {}
         self.local: Dict[str, torch.Tensor] = {}     # pulled copies of remote tensors
-        self.stream = torch.cuda.Stream(device=self.device)
-        self.side_stream = torch.cuda.Stream(device=self.device)
+        # the activation-gradient chain is the critical path: its stream outranks the side stream
+        # that carries weight-gradient GEMMs and the bandwidth-heavy applies
+        self.stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self.side_stream = torch.cuda.Stream(device=self.device, priority=0)
         self.overlap = bool(opts.get("overlap", True))
 
     def _pick_device(self) -> str:
@@ -731,7 +734,9 @@ class B200StepRunner:
         if with_io:
             s.x_dev.copy_(s.x_pin, non_blocking=True)
             s.y_dev.copy_(s.y_pin, non_blocking=True)
-        K.fill_u32(s.zero.buf, 0)
+        clear_end = s.train and self.clear_at_end and self.sync_opt is None
+        if not clear_end:
+            K.fill_u32(s.zero.buf, 0)
         self._pull(s)
         self._forward(s)
         self._loss(s)
@@ -741,6 +746,10 @@ class B200StepRunner:
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
             if self.sync_opt is None or not s.train:
                 s.step_pin.copy_(s.step_dev, non_blocking=True)
+        if clear_end:
+            # the accumulators were consumed by the applies above: clearing them now (instead of at
+            # the start of the next step) takes the fill kernel off the next step's critical path
+            K.fill_u32(s.zero.buf, 0)
 
     def _enqueue_sync_tail(self, s: StepState) -> None:
         """Synchronous mode: the cross-GPU round (cooperative kernel, launched outside the captured
