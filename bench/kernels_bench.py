@@ -70,7 +70,7 @@ def bench_gemm(results, hbm, tf):
         A = torch.randn((Kd, M) if a_mn else (M, Kd), device="cuda").to(bf)
         B = torch.randn((Kd, N) if b_mn else (N, Kd), device="cuda").to(bf)
         out = torch.empty(M, N, dtype=bf, device="cuda")
-        for bn in (128,):
+        for bn in ((128, 256) if M >= 1024 else (128,)):
             us = timeit(lambda: K.gemm(A, B, out, M, N, Kd, a_mn=a_mn, b_mn=b_mn, block_n=bn))
             a_t = A.t() if a_mn else A
             b_t = B if b_mn else B.t()

@@ -434,6 +434,208 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   return 0;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Large-GEMM variant (SURVEY K1-K3 at the wide-MLP sizes): persistent CTA PAIRS.
+//
+// A 128 x 128 single-CTA tile moves 32 KB of operands through L2 and shared memory for every
+// 2.1 MFLOP; at tensor peak that is ~128 B/clk per SM in each direction, more than either path
+// sustains, and the single-CTA kernel above stops near 60% of the cuBLAS rate. Here two CTAs of a
+// cluster (the two SMs of one TPC) issue ONE tcgen05.mma.cta_group::2 of M = 256, N = 256: each
+// CTA stages only its own 128 rows of A and its own 128-column half of B (32 KB per k-block for
+// 2 x the math), holds its 128 x 256 accumulator half in its own TMEM, and runs its own epilogue.
+//   * persistent: grid = one pair per TPC, tiles assigned round-robin in an L2-friendly raster
+//     (8 M-tiles wide), so barrier init / TMEM alloc / descriptor prefetch happen once;
+//   * TMEM holds TWO accumulator tiles (2 x 256 columns): the epilogue of tile i drains one while
+//     the MMAs of tile i+1 fill the other;
+//   * every TMA load (from either CTA) credits the LEADER's full barrier; the leader's
+//     tcgen05.commit multicasts "slot free" / "accumulator ready" to both CTAs; the peer's
+//     epilogue warps release the accumulator with a remote mbarrier arrive.
+// ------------------------------------------------------------------------------------------------
+constexpr int PAIR_STAGES = 6;
+constexpr int PAIR_STAGE_BYTES = 32768;  // per CTA: A 128 x 64 + its half of B 128 x 64, bf16
+constexpr int PAIR_TILE = 256;
+constexpr int PAIR_RASTER = 8;           // M-tiles per raster group
+constexpr int pair_smem_bytes() { return PAIR_STAGES * PAIR_STAGE_BYTES + 1024 + 256; }
+
+__device__ __forceinline__ void pair_tile_origin(int t, int tiles_m, int tiles_n, int& m0, int& n0) {
+  const int per_group = PAIR_RASTER * tiles_n;
+  const int g = t / per_group, r = t - g * per_group;
+  const int gm = min(PAIR_RASTER, tiles_m - g * PAIR_RASTER);
+  m0 = (g * PAIR_RASTER + r % gm) * PAIR_TILE;
+  n0 = (r / gm) * PAIR_TILE;
+}
+
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_umma_pair_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                      const __grid_constant__ CUtensorMap tmap_b, const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + PAIR_STAGES * PAIR_STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + PAIR_STAGES;
+  uint64_t* tmem_full_bar = empty_bar + PAIR_STAGES;  // [2] accumulator ready   (per CTA)
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;       // [2] accumulator drained (leader's is used)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const uint32_t rank = cluster_ctarank();            // 0 = leader (issues the MMAs)
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int tiles_m = (p.M + PAIR_TILE - 1) / PAIR_TILE, tiles_n = (p.N + PAIR_TILE - 1) / PAIR_TILE;
+  const int num_tiles = tiles_m * tiles_n;
+  const int num_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && elect_one()) {
+    for (int i = 0; i < PAIR_STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);   // the leader producer's arrive.expect_tx (bytes of BOTH CTAs)
+      mbar_init(&empty_bar[i], 1);  // the leader's multicast tcgen05.commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full_bar[a], 1);
+      mbar_init(&tmem_empty_bar[a], 8);  // 4 epilogue warps x 2 CTAs
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc_pair(tmem_slot, 512);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // barriers of BOTH CTAs are initialised before any remote arrive / TMA credit
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  griddep_wait();
+  griddep_launch();
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------------------
+    if (elect_one()) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs) {
+        int m0, n0;
+        pair_tile_origin(t, tiles_m, tiles_n, m0, n0);
+        m0 += rank * GEMM_BM;  // my rows of A
+        n0 += rank * 128;      // my half of B
+        for (int i = 0; i < num_kb; ++i) {
+          mbar_wait(&empty_bar[s], ph ^ 1);
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[s], 2 * PAIR_STAGE_BYTES);
+          uint8_t* a_dst = smem + s * PAIR_STAGE_BYTES;
+          uint8_t* b_dst = a_dst + 16384;
+          const int k0 = i * GEMM_BK;
+          if constexpr (!A_MN) {
+            tma_load_2d_pair(a_dst, &tmap_a, &full_bar[s], k0, m0);
+          } else {
+            tma_load_2d_pair(a_dst, &tmap_a, &full_bar[s], m0, k0);
+            tma_load_2d_pair(a_dst + 8192, &tmap_a, &full_bar[s], m0 + 64, k0);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d_pair(b_dst, &tmap_b, &full_bar[s], k0, n0);
+          } else {
+            tma_load_2d_pair(b_dst, &tmap_b, &full_bar[s], n0, k0);
+            tma_load_2d_pair(b_dst + 8192, &tmap_b, &full_bar[s], n0 + 64, k0);
+          }
+          if (++s == PAIR_STAGES) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader only) ------------------------------
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = umma_idesc_bf16(256, 256, A_MN, B_MN);
+      int s = 0, it = 0;
+      uint32_t ph = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_ph = (it >> 1) & 1;
+        mbar_wait(&tmem_empty_bar[acc], acc_ph ^ 1);  // both epilogues drained this accumulator
+        tc_fence_after();
+        const uint32_t d = tmem_base + acc * 256;
+        for (int i = 0; i < num_kb; ++i) {
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(smem + s * PAIR_STAGE_BYTES);
+          const uint32_t b_base = a_base + 16384;
+#pragma unroll
+          for (int k = 0; k < GEMM_BK / 16; ++k) {
+            const uint64_t adesc = A_MN ? umma_smem_desc(a_base + k * 2048, 8192, 1024, 2)
+                                        : umma_smem_desc(a_base + k * 32, 16, 1024, 2);
+            const uint64_t bdesc = B_MN ? umma_smem_desc(b_base + k * 2048, 8192, 1024, 2)
+                                        : umma_smem_desc(b_base + k * 32, 16, 1024, 2);
+            umma_bf16_pair(d, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[s], 3);  // slot free in both CTAs
+          if (++s == PAIR_STAGES) { s = 0; ph ^= 1; }
+        }
+        umma_commit_pair(&tmem_full_bar[acc], 3);  // accumulator complete in both CTAs
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ epilogue (both CTAs) ----------------------------------
+    const int q = warp - 4;
+    const int lane = threadIdx.x & 31;
+    const uint32_t leader_empty[2] = {mapa_u32(&tmem_empty_bar[0], 0), mapa_u32(&tmem_empty_bar[1], 0)};
+    int it = 0;
+    for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_ph = (it >> 1) & 1;
+      int m0, n0;
+      pair_tile_origin(t, tiles_m, tiles_n, m0, n0);
+      const int m = m0 + rank * GEMM_BM + q * 32 + lane;
+      const bool row_ok = m < p.M;
+      mbar_wait(&tmem_full_bar[acc], acc_ph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < PAIR_TILE / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * 256 + c * 32, r);
+        tmem_ld_wait();
+        const int nb = n0 + c * 32;
+        if (!row_ok || nb >= p.n_store) continue;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        gemm_epilogue_store(p, m, nb, v);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(leader_empty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // the peer's smem / TMEM stay alive until the leader's MMAs have finished
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 512);
+  }
+}
+
+template <bool A_MN, bool B_MN>
+static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p,
+                            cudaStream_t stream) {
+  auto kern = gemm_umma_pair_kernel<A_MN, B_MN>;
+  DTF_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      pair_smem_bytes()));
+  static int sm_count = 0;
+  if (sm_count == 0) {
+    int dev = 0;
+    DTF_CHECK_CUDA(cudaGetDevice(&dev));
+    DTF_CHECK_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int tiles = ceil_div(p.M, PAIR_TILE) * ceil_div(p.N, PAIR_TILE);
+  const int pairs = tiles < sm_count / 2 ? tiles : sm_count / 2;
+  DTF_CHECK_CUDA(launch_kernel(kern, dim3(2 * pairs), dim3(GEMM_THREADS), pair_smem_bytes(), stream,
+                               ta, tb, p));
+  return 0;
+}
+
 }  // namespace dtf
 
 using namespace dtf;
@@ -446,10 +648,16 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
   DTF_REQUIRE(epi != nullptr && (epi->out != nullptr || epi->apply_enable), "gemm: epilogue/out is null");
   DTF_REQUIRE(lda % 8 == 0 && ldb % 8 == 0,
               "gemm: lda=%d ldb=%d must be multiples of 8 elements (TMA 16 B rule)", lda, ldb);
-  const int BN = (block_n == 64 || block_n == 128) ? block_n : (N > 64 ? 128 : 64);
   const int num_kb = ceil_div(K, GEMM_BK);
   if (splits < 1) splits = 1;
   if (splits > num_kb) splits = num_kb;
+  // block_n = 256 asks for the persistent CTA-pair kernel; it is also the default for GEMMs with
+  // at least one 256 x 256 tile per TPC (it has no split-K and no fused-apply epilogue)
+  const bool pair_ok = splits == 1 && !epi->apply_enable;
+  DTF_REQUIRE(block_n != 256 || pair_ok, "gemm: block_n = 256 cannot be combined with split-K or fused apply");
+  const bool use_pair = pair_ok && (block_n == 256 || (block_n == 0 && static_cast<long long>(ceil_div(M, 256)) *
+                                                                           ceil_div(N, 256) >= 74 && K >= 256));
+  const int BN = use_pair ? 128 : ((block_n == 64 || block_n == 128) ? block_n : (N > 64 ? 128 : 64));
   const bool fixup = splits > 1 && !epi->reduce;
   DTF_REQUIRE(splits == 1 || (epi->reduce && epi->out_f32) || (epi->splitk_ws && epi->tile_counters),
               "gemm: split-K needs an fp32 reduce epilogue, or a workspace + tile counters");
@@ -528,6 +736,12 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
       DTF_REQUIRE(p.avar[i] != nullptr, "gemm: fused apply slice %d has no variable pointer", i);
   }
 
+  if (use_pair) {
+    if (!a_mn && !b_mn) return launch_gemm_pair<false, false>(ta, tb, p, stream);
+    if (!a_mn && b_mn) return launch_gemm_pair<false, true>(ta, tb, p, stream);
+    if (a_mn && !b_mn) return launch_gemm_pair<true, false>(ta, tb, p, stream);
+    return launch_gemm_pair<true, true>(ta, tb, p, stream);
+  }
 #define DTF_DISPATCH(BN_, AM_, BM_) return launch_gemm<BN_, AM_, BM_>(ta, tb, p, stream)
   if (BN == 64) {
     if (!a_mn && !b_mn) DTF_DISPATCH(64, false, false);

@@ -18,6 +18,7 @@ else raises and can run with ``ConfigProto(backend="cpu")``.
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass, field
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
@@ -177,6 +178,8 @@ class _Zero:
 def plan_gemm(M: int, N: int, K: int) -> Tuple[int, int]:
     """(block_n, splits) for the skinny MNIST GEMMs: prefer more, narrower tiles while the grid is
     far below 148 SMs, and split K (with the in-kernel fix-up) until the grid roughly fills them."""
+    if -(-M // 256) * -(-N // 256) >= 74 and K >= 256 and os.environ.get("DTF_B200_NO_PAIR_GEMM") != "1":
+        return 256, 1   # large GEMM: persistent CTA-pair kernel (256 x 256 tiles, cta_group::2)
     tiles128 = -(-M // 128) * -(-N // 128)
     bn = 64 if (N <= 64 or tiles128 < 74) else 128
     tiles = -(-M // 128) * -(-N // bn)

@@ -75,6 +75,56 @@ def test_gemm_bias_relu_bf16_out(K, block_n):
     assert (out[:, N:] == 0).all(), "row padding must be written as zeros"
 
 
+# persistent CTA-pair kernel (tcgen05.mma.cta_group::2, 256 x 256 tiles, two TMEM accumulators)
+PAIR_SHAPES = [(512, 512, 256), (256, 256, 64), (300, 520, 200), (1024, 2048, 1000),
+               (4096, 6144, 128)]   # last: 384 tiles on 74 pairs -> both accumulator phases wrap
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K_", PAIR_SHAPES)
+def test_gemm_pair_layouts(K, M, N, K_, a_mn, b_mn):
+    torch.manual_seed(M + N * 3 + K_)
+    A = torch.randn(M, K_, device="cuda")
+    Bm = torch.randn(N, K_, device="cuda")
+    a_store = _padded(K_, M, fill=A.t()) if a_mn else _padded(M, K_, fill=A)
+    b_store = _padded(K_, N, fill=Bm.t()) if b_mn else _padded(N, K_, fill=Bm)
+    out = torch.full((M, N), float("nan"), device="cuda")
+    K.gemm(a_store, b_store, out, M, N, K_, a_mn=a_mn, b_mn=b_mn, block_n=256)
+    torch.cuda.synchronize()
+    ref = _bf16(A).float() @ _bf16(Bm).float().t()
+    err = _rel_err(out, ref)
+    assert err < 2e-3, f"rel err {err}"
+    # element-wise too: a swapped B half or accumulator stage would keep the norm but move values
+    assert torch.allclose(out, ref, rtol=2e-2, atol=2e-2 * ref.abs().max().item())
+
+
+def test_gemm_pair_fused_epilogues(K):
+    torch.manual_seed(5)
+    M, N, K_ = 520, 776, 328
+    A = torch.randn(M, K_, device="cuda")
+    W = torch.randn(K_, N, device="cuda") * 0.1
+    bias = torch.randn(N, device="cuda")
+    a, w = _padded(M, K_, fill=A), _padded(K_, N, fill=W)
+    out = torch.full((M, w.shape[1]), 7.0, dtype=torch.bfloat16, device="cuda")
+    K.gemm(a, w, out, M, N, K_, b_mn=True, bias=bias, relu=True, block_n=256)
+    torch.cuda.synchronize()
+    ref = torch.relu(_bf16(A).float() @ _bf16(W).float() + bias)
+    assert _rel_err(out[:, :N], ref) < 1e-2
+    # ReLU-gradient mask + fp32 accumulate-into (red.add) epilogues
+    dY = torch.randn(M, K_, device="cuda")
+    Wt = torch.randn(N, K_, device="cuda")
+    act = torch.randn(M, N, device="cuda")
+    mask = _padded(M, N, fill=torch.relu(act))
+    out2 = torch.zeros(M, mask.shape[1], dtype=torch.bfloat16, device="cuda")
+    K.gemm(_padded(M, K_, fill=dY), _padded(N, K_, fill=Wt), out2, M, N, K_, mask=mask, block_n=256)
+    acc = torch.ones(M, N, device="cuda")
+    K.gemm(_padded(M, K_, fill=dY), _padded(N, K_, fill=Wt), acc, M, N, K_, reduce=True, alpha=0.5, block_n=256)
+    torch.cuda.synchronize()
+    ref2 = _bf16(dY).float() @ _bf16(Wt).float().t()
+    assert _rel_err(out2[:, :N], ref2 * (act > 0)) < 1e-2
+    assert _rel_err(acc, 1.0 + 0.5 * ref2) < 2e-3
+
+
 def test_gemm_relu_grad_mask(K):
     torch.manual_seed(1)
     M, N, K_ = 128, 104, 16
