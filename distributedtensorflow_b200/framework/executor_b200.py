@@ -28,6 +28,7 @@ import torch
 from ..ops import _lib as L
 from ..ops import kernels as K
 from ..parallel.nvl import NvlStore, SliceRegion, pad8
+from ..utils.tracing import nvtx_range
 from . import graph as G
 
 
@@ -740,11 +741,14 @@ class B200StepRunner:
         clear_end = s.train and self.clear_at_end and self.sync_opt is None
         if not clear_end:
             K.fill_u32(s.zero.buf, 0)
-        self._pull(s)
-        self._forward(s)
-        self._loss(s)
+        with nvtx_range("dtf/pull"):
+            self._pull(s)
+        with nvtx_range("dtf/forward"):
+            self._forward(s)
+            self._loss(s)
         if s.train:
-            self._backward(s)          # includes the push+apply of every variable
+            with nvtx_range("dtf/backward_push_apply"):
+                self._backward(s)      # includes the push+apply of every variable
         if with_io:
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
             if self.sync_opt is None or not s.train:
@@ -840,13 +844,16 @@ class B200StepRunner:
         if x.dtype not in (np.uint8, np.float32):
             x = x.astype(np.float32)
         s = self._state(B, top is not None, x.reshape(B, -1), y)
-        self._stage(s, x.reshape(B, -1), y)
-        if top is not None:
-            self._launch(s)
-        else:
-            with torch.cuda.stream(self.stream):
-                self._enqueue_step(s)
-        self.stream.synchronize()
+        with nvtx_range("dtf/stage_inputs"):
+            self._stage(s, x.reshape(B, -1), y)
+        with nvtx_range("dtf/launch_step"):
+            if top is not None:
+                self._launch(s)
+            else:
+                with torch.cuda.stream(self.stream):
+                    self._enqueue_step(s)
+        with nvtx_range("dtf/wait_step"):
+            self.stream.synchronize()
         loss_val = np.float32(s.out_pin[0].item())
         step_val = int(s.step_pin[0].item()) if top is not None else None
         out: List[Any] = []

@@ -209,3 +209,12 @@ def test_coordinator_propagates_thread_exception():
     with pytest.raises(ValueError, match="boom"):
         coord.join()
     assert coord.should_stop()
+
+
+def test_tracing_helpers_are_noops_without_nvtx():
+    from distributedtensorflow_b200.utils import tracing
+    assert not tracing.nvtx_enabled() or True
+    tracing.enable_nvtx(False)
+    with tracing.nvtx_range("dtf/test"):
+        pass
+    assert tracing.nvtx_range("a") is tracing.nvtx_range("b")      # shared null context when off
