@@ -128,6 +128,9 @@ def main() -> int:
     ap.add_argument("--no-split-k", action="store_true", help="disable split-K for skinny GEMMs")
     ap.add_argument("--no-overlap", action="store_true", help="single-stream backward (no side stream)")
     ap.add_argument("--fused-apply", action="store_true", help="dW GEMM epilogue does the push+apply")
+    ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"],
+                    help="gradient push: worker-side remote read-modify-write, or posted stores + the "
+                         "owner's apply daemon (auto = mailbox when there is more than one worker)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -198,7 +201,8 @@ def main() -> int:
 
     cfg = tf.ConfigProto(allow_soft_placement=True, backend="b200", device="cuda:%d" % local_rank,
                          cuda_graph=not args.no_cuda_graph, pdl=not args.no_pdl,
-                         split_k=not args.no_split_k, overlap=not args.no_overlap, fused_apply=args.fused_apply)
+                         split_k=not args.no_split_k, overlap=not args.no_overlap, fused_apply=args.fused_apply,
+                         push_mode=args.push_mode)
     result = {}
     with tf.train.MonitoredTrainingSession(master=wk_server.target, is_chief=(rank == 0), config=cfg,
                                            recovery_wait_secs=0.05) as sess:
@@ -260,6 +264,7 @@ def main() -> int:
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
         final_loss = float(l)
+        runner.flush_pushes()        # "owner applies" mode: my last gradients have been applied
         if world > 1:
             dist.barrier()           # every worker has finished: the shared counter is final
         final_step = int(sess.run(global_step))
@@ -285,7 +290,10 @@ def main() -> int:
                        "l2": "not flushed" if args.no_l2_flush else "flushed between timed steps (256 MiB write)",
                        "cuda_graph": not args.no_cuda_graph, "pdl": not args.no_pdl,
                        "split_k": not args.no_split_k, "overlap": not args.no_overlap,
-                       "fused_apply": args.fused_apply},
+                       "fused_apply": args.fused_apply,
+                       "push": ("mailbox: posted gradient stores + owner-side apply daemon, depth %d"
+                                % runner.store.arena.mailbox_depth) if runner.use_mailbox
+                               else "rmw: worker-side fused push+apply"},
             "time_to_1000_global_steps_s": round(1000.0 / value, 5),
             "back_to_back_ms_per_step": round(b2b_ms / args.steps, 5),
             "e2e": {"value": round(N * args.steps / (e2e_ms / 1e3), 2), "unit": "global steps/s",

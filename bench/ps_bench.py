@@ -72,6 +72,7 @@ def main() -> int:
     ap.add_argument("--check", action="store_true")
     ap.add_argument("--ckpt-dir", default="")
     ap.add_argument("--no-l2-flush", action="store_true")
+    ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"])
     args = ap.parse_args()
 
     import numpy as np
@@ -125,7 +126,7 @@ def main() -> int:
                 opt = tf.train.SyncReplicasOptimizer(opt, replicas_to_aggregate=nw, total_num_replicas=nw)
             train_op = opt.minimize(loss, global_step=gs)
         hooks = [opt.make_session_run_hook(wk_index == 0)] if args.mode == "sync" else []
-        cfg = tf.ConfigProto(backend="b200", device="cuda:%d" % local_rank)
+        cfg = tf.ConfigProto(backend="b200", device="cuda:%d" % local_rank, push_mode=args.push_mode)
         batches = make_batches(args, wk_index)
         with tf.train.MonitoredTrainingSession(master=servers[-1].target, is_chief=(wk_index == 0), config=cfg,
                                                hooks=hooks, recovery_wait_secs=0.05,
@@ -154,6 +155,9 @@ def main() -> int:
             times[0], times[1] = dev_ms, wall * 1e3
             final_step, final_loss = int(g), float(l)
             extra = {}
+            if runner.use_mailbox:
+                runner.flush_pushes()        # my last gradients have been applied by their owners
+                extra["push"] = "mailbox"
             if args.check and args.mode == "sync":
                 names = [v.name for v in tf.trainable_variables()]
                 got = {n: runner.store.read_variable(n) for n in names}
@@ -175,6 +179,8 @@ def main() -> int:
                                                                      runner.store.read_variable(name0)))
             if world > 1:
                 dist.barrier()       # nobody tears its arena down while a peer may still touch it
+            if runner.use_mailbox:   # every worker has flushed: the shared counter is final
+                final_step = int(runner.store.read_global_step())
             result = dict(final_step=final_step, final_loss=final_loss, launches_per_step=runner.train_state().launches_per_step,
                           **extra)
     else:
@@ -195,7 +201,7 @@ def main() -> int:
             ms_per_step=round(dev_ms / args.steps, 5), e2e_value=round(steps_total / (wall_ms / 1e3), 2),
             config=dict(model=args.model, mode=args.mode, topology=args.topology, placement=args.placement,
                         optimizer=args.optimizer, batch_per_worker=args.batch, hidden=args.hidden,
-                        workers=nw, ps_shards=nps, l2="not flushed" if args.no_l2_flush else "flushed per step"),
+                        workers=nw, ps_shards=nps, push_mode=args.push_mode, l2="not flushed" if args.no_l2_flush else "flushed per step"),
             **(result or {}))))
     if world > 1:
         dist.destroy_process_group()

@@ -11,6 +11,7 @@
 // AdamOptimizer(...).minimize (run_mnist_distributed.py:116).
 #include "common.cuh"
 #include "ptx.cuh"
+#include "apply_rules.cuh"
 #include "../../include/dtf_b200.h"
 
 namespace dtf {
@@ -33,27 +34,6 @@ struct ApplyArgs {
   unsigned long long* step_out;
   unsigned int* block_counter;
 };
-
-template <int OPT>
-__device__ __forceinline__ void update_one(float g, float& var, float& s0, float& s1,
-                                           const dtf_apply_hyper& h, float lr_t) {
-  if (OPT == DTF_OPT_SGD) {
-    var -= h.lr * g;
-  } else if (OPT == DTF_OPT_MOMENTUM) {
-    s0 = s0 * h.momentum + g;
-    if (h.use_nesterov)
-      var -= g * h.lr + s0 * h.momentum * h.lr;
-    else
-      var -= h.lr * s0;
-  } else if (OPT == DTF_OPT_ADAGRAD) {
-    s0 += g * g;
-    var -= h.lr * g * rsqrtf(s0);
-  } else {  // Adam, TF1 "epsilon hat" form
-    s0 += (g - s0) * (1.f - h.beta1);
-    s1 += (g * g - s1) * (1.f - h.beta2);
-    var -= lr_t * s0 / (sqrtf(s1) + h.epsilon);
-  }
-}
 
 template <int OPT>
 __global__ void __launch_bounds__(APPLY_THREADS)

@@ -1,0 +1,422 @@
+// Asynchronous "owner applies" gradient push (SURVEY 5.9 option (b); K9 + K11).
+//
+// dtf_push_apply lets the WORKER's SMs read-modify-write the owner's var / m / v over NVLink:
+// 12 bytes of round-trip reads and 14 bytes of writes per Adam parameter. At 8 GPUs that traffic
+// (74 MB per CNN step per worker) is what limits scaling. The reference's PS applies the gradient
+// itself after receiving it (the ApplyAdam op is placed on /job:ps, run_mnist_distributed.py:107,
+// 116) — this file is that protocol over peer memory:
+//
+//   worker   mailbox_push_kernel   posted 16-byte stores of the fp32 gradient into its own mailbox
+//                                  on every owning shard (4 bytes per parameter, no reads), then
+//                                  ONE st.release.sys of a sequence number per owner;
+//   owner    mailbox_drain_kernel  part of the owner's own step (side stream): reads var / slots
+//                                  once from LOCAL HBM, applies every pending worker's gradient in
+//                                  turn, writes var / slots / bf16 serving copy once, publishes
+//                                  consumed[w] and bumps global_step by the number applied.
+//
+// Flow control is a counter pair per (owner, worker): the worker never runs more than `depth`
+// pushes ahead of the owner's applies, which bounds staleness (TF1's async mode is unbounded).
+#include "common.cuh"
+#include "ptx.cuh"
+#include "apply_rules.cuh"
+#include "../../include/dtf_b200.h"
+
+namespace dtf {
+
+constexpr int MBOX_THREADS = 256;
+constexpr int MBOX_UNROLL = 8;
+constexpr long long MBOX_CHUNK = static_cast<long long>(MBOX_THREADS) * MBOX_UNROLL * 16;  // 32 KB
+
+struct MboxPushArgs {
+  dtf_mbox_push_item items[DTF_MAX_MBOX_ITEMS];
+  int block_start[DTF_MAX_MBOX_ITEMS + 1];
+  int n_items;
+  int total_blocks;
+  int depth;
+  int worker_id;
+  dtf_mbox_flags* owner_flags[DTF_MAX_WORKERS];
+  int n_owners;
+  int publish;
+  unsigned int* seq;
+  unsigned int* block_counter;
+  unsigned int* min_consumed_out;
+  const dtf_ps_ctrl* ctrl_step;
+  unsigned long long* step_out;
+};
+
+__global__ void __launch_bounds__(MBOX_THREADS)
+mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
+  __shared__ unsigned int s_last;
+  __shared__ unsigned int s_min;
+  griddep_wait();
+  griddep_launch();
+  // every CTA reads the sequence number before any CTA can reach the election below, and only the
+  // elected (last) CTA changes it
+  const unsigned int seq = *reinterpret_cast<volatile unsigned int*>(a.seq);
+  const long long buf = seq % static_cast<unsigned int>(a.depth);
+  {
+    int it = 0;
+    while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
+    const dtf_mbox_push_item& c = a.items[it];
+    const long long base = static_cast<long long>(blockIdx.x - a.block_start[it]) * MBOX_CHUNK;
+    if (base < c.bytes) {
+      const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(c.src) + base);
+      uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(c.dst0) + buf * c.buf_stride + base);
+      const long long nvec = min(MBOX_CHUNK, c.bytes - base) / 16;
+      uint4 v[MBOX_UNROLL];
+#pragma unroll
+      for (int u = 0; u < MBOX_UNROLL; ++u) {
+        const long long i = static_cast<long long>(u) * MBOX_THREADS + threadIdx.x;
+        if (i < nvec) v[u] = src[i];
+      }
+#pragma unroll
+      for (int u = 0; u < MBOX_UNROLL; ++u) {
+        const long long i = static_cast<long long>(u) * MBOX_THREADS + threadIdx.x;
+        if (i < nvec) dst[i] = v[u];
+      }
+    }
+  }
+  if (!a.publish) return;
+  // ---- the last CTA publishes the push to every owner ----
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int old = atomicInc(a.block_counter, static_cast<unsigned int>(a.total_blocks - 1));
+    s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
+    s_min = 0xffffffffu;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence_system();  // acquire side of the election: every CTA's stores precede the flags
+  if (static_cast<int>(threadIdx.x) < a.n_owners) {
+    dtf_mbox_flags* f = a.owner_flags[threadIdx.x];
+    st_release_sys_u32(&f->produced[a.worker_id], seq + 1u);
+    // how far has this owner got with MY gradients (flow control for the next pushes)
+    const unsigned int c = ld_acquire_sys_u32(&f->consumed[a.worker_id]);
+    atomicMin(&s_min, c);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *reinterpret_cast<volatile unsigned int*>(a.seq) = seq + 1u;
+    if (a.min_consumed_out != nullptr) *a.min_consumed_out = s_min;
+    // what sess.run([train_op, global_step]) reports: the shared counter as this step ends
+    if (a.step_out != nullptr && a.ctrl_step != nullptr)
+      *a.step_out = ld_acquire_sys_u64(&a.ctrl_step->global_step);
+  }
+}
+
+__global__ void mailbox_snapshot_kernel(dtf_mbox_flags* flags, unsigned int* todo, int n_workers,
+                                        int depth) {
+  griddep_wait();
+  griddep_launch();
+  const int w = threadIdx.x;
+  if (w >= DTF_MAX_WORKERS) return;
+  unsigned int t = 0;
+  if (w < n_workers) {
+    const unsigned int p = ld_acquire_sys_u32(&flags->produced[w]);
+    const unsigned int c = *reinterpret_cast<volatile unsigned int*>(&flags->consumed[w]);
+    if (static_cast<int>(p - c) > 0) t = c % static_cast<unsigned int>(depth) + 1u;  // oldest first
+  }
+  todo[w] = t;
+}
+
+constexpr int DRAIN_THREADS = 256;
+constexpr int DRAIN_VEC = 4;
+constexpr int DRAIN_UNROLL = 2;
+constexpr int DRAIN_CHUNK = DRAIN_THREADS * DRAIN_VEC * DRAIN_UNROLL;  // 2048 elements / CTA
+
+struct DrainArgs {
+  dtf_apply_item items[DTF_MAX_APPLY_ITEMS];
+  int block_start[DTF_MAX_APPLY_ITEMS + 1];
+  int n_items;
+  int total_blocks;
+  dtf_apply_hyper h;
+  dtf_ps_ctrl* ctrl_powers;
+  dtf_ps_ctrl* ctrl_step;
+  dtf_mbox_flags* flags;
+  const unsigned int* todo;
+  long long slot_stride;  // bytes
+  int depth;
+  int n_workers;
+  unsigned long long* step_out;
+  unsigned int* block_counter;
+};
+
+template <int OPT>
+__global__ void __launch_bounds__(DRAIN_THREADS)
+mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
+  __shared__ int s_item;
+  __shared__ int s_n;
+  __shared__ long long s_off[DTF_MAX_WORKERS];  // element offset of pending gradient k from item.grad
+  __shared__ float s_lr[DTF_MAX_WORKERS];
+  __shared__ unsigned int s_last;
+  griddep_wait();
+  griddep_launch();
+  if (threadIdx.x == 0) {
+    int it = 0;
+    while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
+    s_item = it;
+    float b1p = 0.f, b2p = 0.f;
+    if (OPT == DTF_OPT_ADAM) {
+      b1p = *reinterpret_cast<volatile float*>(&a.ctrl_powers->beta1_power);
+      b2p = *reinterpret_cast<volatile float*>(&a.ctrl_powers->beta2_power);
+    }
+    int n = 0;
+    for (int w = 0; w < a.n_workers; ++w) {
+      const unsigned int t = a.todo[w];
+      if (t == 0) continue;
+      s_off[n] = (static_cast<long long>(w) * a.depth + (t - 1)) * (a.slot_stride / 4);
+      // the k-th apply of this drain sees the powers the k-1 applies before it left behind
+      s_lr[n] = (OPT == DTF_OPT_ADAM) ? a.h.lr * sqrtf(1.f - b2p) / (1.f - b1p) : a.h.lr;
+      b1p *= a.h.beta1;
+      b2p *= a.h.beta2;
+      ++n;
+    }
+    s_n = n;
+  }
+  __syncthreads();
+  const int n_pending = s_n;
+  const dtf_apply_item& it = a.items[s_item];
+  if (n_pending > 0 && it.n > 0) {
+    const long long base = static_cast<long long>(blockIdx.x - a.block_start[s_item]) * DRAIN_CHUNK;
+    const bool vec_ok =
+        ((reinterpret_cast<uintptr_t>(it.var) | reinterpret_cast<uintptr_t>(it.grad) |
+          reinterpret_cast<uintptr_t>(it.slot0) | reinterpret_cast<uintptr_t>(it.slot1)) & 15) == 0 &&
+        (a.slot_stride % 16 == 0);
+    __nv_bfloat16* shadow = reinterpret_cast<__nv_bfloat16*>(it.shadow);
+    const bool shadow_vec = shadow != nullptr && (it.cols % 4 == 0) && (it.shadow_ld % 4 == 0) &&
+                            (it.first % 4 == 0) && ((reinterpret_cast<uintptr_t>(shadow) & 7) == 0);
+    float4 v4[DRAIN_UNROLL], m4[DRAIN_UNROLL], u4[DRAIN_UNROLL];
+    bool full[DRAIN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < DRAIN_UNROLL; ++u) {
+      const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
+      full[u] = vec_ok && i + DRAIN_VEC <= it.n;
+      v4[u] = m4[u] = u4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (full[u]) {
+        v4[u] = *reinterpret_cast<const float4*>(it.var + i);
+        if (OPT != DTF_OPT_SGD) m4[u] = *reinterpret_cast<const float4*>(it.slot0 + i);
+        if (OPT == DTF_OPT_ADAM) u4[u] = *reinterpret_cast<const float4*>(it.slot1 + i);
+      }
+    }
+#pragma unroll 1
+    for (int k = 0; k < n_pending; ++k) {
+      const float* g = it.grad + s_off[k];
+      const float lr_t = s_lr[k];
+      float4 g4[DRAIN_UNROLL];
+#pragma unroll
+      for (int u = 0; u < DRAIN_UNROLL; ++u) {
+        const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
+        if (full[u]) {  // written by a peer GPU since the last drain: read at L2, not through .nc
+          const uint4 r = ld_relaxed_u4(reinterpret_cast<const uint4*>(g + i));
+          g4[u] = make_float4(__uint_as_float(r.x), __uint_as_float(r.y), __uint_as_float(r.z),
+                              __uint_as_float(r.w));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < DRAIN_UNROLL; ++u) {
+        if (!full[u]) continue;
+        const float s = a.h.grad_scale;
+        update_one<OPT>(g4[u].x * s, v4[u].x, m4[u].x, u4[u].x, a.h, lr_t);
+        update_one<OPT>(g4[u].y * s, v4[u].y, m4[u].y, u4[u].y, a.h, lr_t);
+        update_one<OPT>(g4[u].z * s, v4[u].z, m4[u].z, u4[u].z, a.h, lr_t);
+        update_one<OPT>(g4[u].w * s, v4[u].w, m4[u].w, u4[u].w, a.h, lr_t);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < DRAIN_UNROLL; ++u) {
+      const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
+      if (i >= it.n) continue;
+      if (full[u]) {
+        *reinterpret_cast<float4*>(it.var + i) = v4[u];
+        if (OPT != DTF_OPT_SGD) *reinterpret_cast<float4*>(it.slot0 + i) = m4[u];
+        if (OPT == DTF_OPT_ADAM) *reinterpret_cast<float4*>(it.slot1 + i) = u4[u];
+        if (shadow != nullptr) {
+          const long long f = it.first + i;
+          const float v[4] = {v4[u].x, v4[u].y, v4[u].z, v4[u].w};
+          if (shadow_vec) {
+            const long long r = f / it.cols, c = f % it.cols;
+            *reinterpret_cast<uint2*>(shadow + r * it.shadow_ld + c) =
+                make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const long long r = (f + j) / it.cols, c = (f + j) % it.cols;
+              shadow[r * it.shadow_ld + c] = __float2bfloat16(v[j]);
+            }
+          }
+        }
+      } else {
+        // ragged tail / unaligned slice: element by element
+        for (int j = 0; j < DRAIN_VEC && i + j < it.n; ++j) {
+          float v = it.var[i + j];
+          float s0 = (OPT != DTF_OPT_SGD) ? it.slot0[i + j] : 0.f;
+          float s1 = (OPT == DTF_OPT_ADAM) ? it.slot1[i + j] : 0.f;
+          for (int k = 0; k < n_pending; ++k)
+            update_one<OPT>(it.grad[s_off[k] + i + j] * a.h.grad_scale, v, s0, s1, a.h, s_lr[k]);
+          it.var[i + j] = v;
+          if (OPT != DTF_OPT_SGD) it.slot0[i + j] = s0;
+          if (OPT == DTF_OPT_ADAM) it.slot1[i + j] = s1;
+          if (shadow != nullptr) {
+            const long long f = it.first + i + j;
+            shadow[(f / it.cols) * it.shadow_ld + (f % it.cols)] = __float2bfloat16(v);
+          }
+        }
+      }
+    }
+  }
+
+  // ---- the last CTA retires the drained gradients ----
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int old = atomicInc(a.block_counter, static_cast<unsigned int>(a.total_blocks - 1));
+    s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
+  }
+  __syncthreads();
+  if (!s_last || threadIdx.x != 0) return;
+  __threadfence_system();
+  unsigned long long step = 0;
+  if (n_pending > 0) {
+    if (OPT == DTF_OPT_ADAM) {
+      volatile float* b1 = &a.ctrl_powers->beta1_power;
+      volatile float* b2 = &a.ctrl_powers->beta2_power;
+      float p1 = *b1, p2 = *b2;
+      for (int k = 0; k < n_pending; ++k) { p1 *= a.h.beta1; p2 *= a.h.beta2; }
+      *b1 = p1;
+      *b2 = p2;
+    }
+    if (a.ctrl_step != nullptr) {
+      step = atom_add_u64_sys(&a.ctrl_step->global_step, static_cast<unsigned long long>(n_pending)) +
+             static_cast<unsigned long long>(n_pending);
+      atomicAdd(&a.ctrl_step->apply_count, static_cast<unsigned int>(n_pending));
+    }
+    for (int w = 0; w < a.n_workers; ++w) {
+      if (a.todo[w] == 0) continue;
+      if (a.ctrl_step != nullptr)
+        *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[w]) = step;
+      // the mailbox buffer may be overwritten by worker w from here on
+      const unsigned int c = *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
+      st_release_sys_u32(&a.flags->consumed[w], c + 1u);
+    }
+  }
+  if (a.step_out != nullptr) {
+    *a.step_out = (a.ctrl_step != nullptr && n_pending == 0)
+                      ? ld_acquire_sys_u64(&a.ctrl_step->global_step)
+                      : step;
+  }
+}
+
+}  // namespace dtf
+
+using namespace dtf;
+
+extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, int depth,
+                                int worker_id, dtf_mbox_flags* const* owner_flags, int n_owners,
+                                int publish, unsigned int* seq, unsigned int* block_counter,
+                                unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
+                                unsigned long long* step_out, void* stream) {
+  DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_MBOX_ITEMS, "mailbox_push: %d items (max %d)",
+              n_items, DTF_MAX_MBOX_ITEMS);
+  DTF_REQUIRE(depth >= 1 && seq != nullptr, "mailbox_push: depth %d / seq", depth);
+  DTF_REQUIRE(worker_id >= 0 && worker_id < DTF_MAX_WORKERS, "mailbox_push: worker %d", worker_id);
+  DTF_REQUIRE(!publish || (n_owners >= 1 && n_owners <= DTF_MAX_WORKERS && owner_flags != nullptr &&
+                           block_counter != nullptr),
+              "mailbox_push: publish needs 1..%d owners and a block counter", DTF_MAX_WORKERS);
+  MboxPushArgs a;
+  memset(&a, 0, sizeof(a));
+  int blocks = 0;
+  for (int i = 0; i < n_items; ++i) {
+    DTF_REQUIRE(items[i].bytes >= 0 && items[i].bytes % 16 == 0 && items[i].buf_stride % 16 == 0,
+                "mailbox_push: item %d: bytes %lld / stride %lld not multiples of 16", i,
+                items[i].bytes, items[i].buf_stride);
+    DTF_REQUIRE(((reinterpret_cast<uintptr_t>(items[i].src) |
+                  reinterpret_cast<uintptr_t>(items[i].dst0)) & 15) == 0,
+                "mailbox_push: item %d is not 16-byte aligned", i);
+    a.items[i] = items[i];
+    a.block_start[i] = blocks;
+    blocks += static_cast<int>((items[i].bytes + MBOX_CHUNK - 1) / MBOX_CHUNK);
+  }
+  a.block_start[n_items] = blocks;
+  if (blocks == 0) {
+    if (!publish) return 0;
+    blocks = 1;
+    a.block_start[n_items > 0 ? n_items : 1] = 1;
+  }
+  a.n_items = n_items > 0 ? n_items : 1;
+  a.total_blocks = blocks;
+  a.depth = depth;
+  a.worker_id = worker_id;
+  a.n_owners = publish ? n_owners : 0;
+  for (int i = 0; i < a.n_owners; ++i) {
+    DTF_REQUIRE(owner_flags[i] != nullptr, "mailbox_push: owner %d has no flag block", i);
+    a.owner_flags[i] = owner_flags[i];
+  }
+  a.publish = publish;
+  a.seq = seq;
+  a.block_counter = block_counter;
+  a.min_consumed_out = min_consumed_out;
+  a.ctrl_step = ctrl_step;
+  a.step_out = step_out;
+  DTF_CHECK_CUDA(launch_kernel(mailbox_push_kernel, dim3(blocks), dim3(MBOX_THREADS), 0,
+                               reinterpret_cast<cudaStream_t>(stream), a));
+  return 0;
+}
+
+extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_items,
+                                 long long slot_stride, int depth, int n_workers,
+                                 const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
+                                 dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, unsigned int* todo,
+                                 unsigned int* block_counter, unsigned long long* step_out,
+                                 void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "mailbox_drain: %d items (max %d)",
+              n_items, DTF_MAX_APPLY_ITEMS);
+  DTF_REQUIRE(depth >= 1 && n_workers >= 1 && n_workers <= DTF_MAX_WORKERS,
+              "mailbox_drain: depth %d, %d workers", depth, n_workers);
+  DTF_REQUIRE(hyper && flags && todo && block_counter, "mailbox_drain: null argument");
+  DTF_REQUIRE(opt != DTF_OPT_ADAM || ctrl_powers != nullptr, "mailbox_drain: Adam needs the beta powers");
+  DTF_REQUIRE(slot_stride % 4 == 0, "mailbox_drain: slot stride %lld", slot_stride);
+  DrainArgs a;
+  memset(&a, 0, sizeof(a));
+  int blocks = 0;
+  for (int i = 0; i < n_items; ++i) {
+    DTF_REQUIRE(items[i].n >= 0 && items[i].var && items[i].grad, "mailbox_drain: item %d invalid", i);
+    DTF_REQUIRE(opt == DTF_OPT_SGD || items[i].slot0, "mailbox_drain: item %d lacks slot0", i);
+    DTF_REQUIRE(opt != DTF_OPT_ADAM || items[i].slot1, "mailbox_drain: item %d lacks slot1", i);
+    a.items[i] = items[i];
+    a.block_start[i] = blocks;
+    blocks += static_cast<int>((items[i].n + DRAIN_CHUNK - 1) / DRAIN_CHUNK);
+  }
+  a.block_start[n_items] = blocks;
+  if (blocks == 0) {  // a shard that only owns global_step still counts the pushes
+    blocks = 1;
+    if (n_items == 0) {
+      n_items = 1;
+      a.block_start[1] = 1;
+    }
+  }
+  a.n_items = n_items;
+  a.total_blocks = blocks;
+  a.h = *hyper;
+  a.ctrl_powers = ctrl_powers;
+  a.ctrl_step = ctrl_step;
+  a.flags = flags;
+  a.todo = todo;
+  a.slot_stride = slot_stride;
+  a.depth = depth;
+  a.n_workers = n_workers;
+  a.step_out = step_out;
+  a.block_counter = block_counter;
+  DTF_CHECK_CUDA(launch_kernel(mailbox_snapshot_kernel, dim3(1), dim3(32), 0, stream, flags, todo,
+                               n_workers, depth));
+  switch (opt) {
+    case DTF_OPT_SGD: DTF_CHECK_CUDA(launch_kernel(mailbox_drain_kernel<DTF_OPT_SGD>, dim3(blocks), dim3(DRAIN_THREADS), 0, stream, a)); break;
+    case DTF_OPT_MOMENTUM: DTF_CHECK_CUDA(launch_kernel(mailbox_drain_kernel<DTF_OPT_MOMENTUM>, dim3(blocks), dim3(DRAIN_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAGRAD: DTF_CHECK_CUDA(launch_kernel(mailbox_drain_kernel<DTF_OPT_ADAGRAD>, dim3(blocks), dim3(DRAIN_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAM: DTF_CHECK_CUDA(launch_kernel(mailbox_drain_kernel<DTF_OPT_ADAM>, dim3(blocks), dim3(DRAIN_THREADS), 0, stream, a)); break;
+    default: DTF_REQUIRE(false, "mailbox_drain: unknown optimizer %d", opt);
+  }
+  DTF_LAUNCH_CHECK();
+  return 0;
+}

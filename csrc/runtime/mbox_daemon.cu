@@ -1,0 +1,205 @@
+// The parameter server's apply daemon ("PS process ... parks, optionally running a
+// persistent apply-server"). In the reference the PS task's CPU executes the ApplyAdam ops that
+// replica_device_setter placed on /job:ps whenever a worker's gradient arrives
+// (run_mnist_distributed.py:107,116; the PS itself just sits in server.join(), :96-98). Here the
+// task that owns a shard arena runs ONE native host thread per shard that
+//   1. polls the shard's mailbox flags (a 512-byte D2H copy on its own stream — copy engine only,
+//      no SM is occupied while nothing is pending),
+//   2. when some worker has published a gradient, launches dtf_mailbox_drain (snapshot + apply
+//      from local HBM) on that stream, concurrently with whatever the colocated worker computes.
+// No Python and no GIL on this path; kernels never wait on other kernels (the drain only touches
+// gradients whose sequence number was already published), so nothing can deadlock on the device.
+#include <atomic>
+#include <chrono>
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+#include <thread>
+
+#include "../kernels/common.cuh"
+#include "../../include/dtf_b200.h"
+
+using namespace dtf;
+
+struct dtf_mbox_daemon {
+  int device = 0;
+  int opt = 0;
+  dtf_apply_item items[DTF_MAX_APPLY_ITEMS];
+  int n_items = 0;
+  long long slot_stride = 0;
+  int depth = 1;
+  int n_workers = 1;
+  dtf_apply_hyper hyper;
+  dtf_ps_ctrl* ctrl_powers = nullptr;
+  dtf_ps_ctrl* ctrl_step = nullptr;
+  dtf_mbox_flags* flags = nullptr;
+  int poll_us = 20;
+
+  cudaStream_t stream = nullptr;
+  dtf_mbox_flags* host_flags = nullptr;  // pinned
+  unsigned int* scratch = nullptr;       // device: todo[16] | block counter
+  std::thread thread;
+  std::atomic<int> stop{0};
+  std::atomic<int> paused{0};
+  std::atomic<int> idle{0};
+  std::atomic<int> failed{0};
+  std::atomic<unsigned long long> polls{0}, drains{0}, applied{0};
+  std::mutex err_mu;
+  char err[512] = {0};
+
+  void fail(const char* fmt, ...) {
+    std::lock_guard<std::mutex> g(err_mu);
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(err, sizeof err, fmt, ap);
+    va_end(ap);
+    failed.store(1);
+  }
+};
+
+namespace {
+
+int pending_count(const dtf_mbox_flags* f, int n_workers) {
+  int n = 0;
+  for (int w = 0; w < n_workers; ++w)
+    if (static_cast<int>(f->produced[w] - f->consumed[w]) > 0) ++n;
+  return n;
+}
+
+void daemon_main(dtf_mbox_daemon* d) {
+  if (cudaSetDevice(d->device) != cudaSuccess) {
+    d->fail("apply daemon: cudaSetDevice(%d) failed", d->device);
+    return;
+  }
+  while (!d->stop.load(std::memory_order_acquire)) {
+    if (d->paused.load(std::memory_order_acquire)) {
+      d->idle.store(1, std::memory_order_release);
+      std::this_thread::sleep_for(std::chrono::microseconds(50));
+      continue;
+    }
+    d->idle.store(0, std::memory_order_release);
+    cudaError_t e = cudaMemcpyAsync(d->host_flags, d->flags, sizeof(dtf_mbox_flags),
+                                    cudaMemcpyDeviceToHost, d->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
+    if (e != cudaSuccess) {
+      d->fail("apply daemon: polling the mailbox flags failed: %s", cudaGetErrorString(e));
+      return;
+    }
+    d->polls.fetch_add(1, std::memory_order_relaxed);
+    const int n = pending_count(d->host_flags, d->n_workers);
+    if (n == 0) {
+      if (d->poll_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(d->poll_us));
+      continue;
+    }
+    if (dtf_mailbox_drain(d->opt, d->items, d->n_items, d->slot_stride, d->depth, d->n_workers,
+                          &d->hyper, d->ctrl_powers, d->ctrl_step, d->flags, d->scratch,
+                          d->scratch + DTF_MAX_WORKERS, nullptr, d->stream) != 0) {
+      d->fail("apply daemon: %s", dtf_last_error());
+      return;
+    }
+    e = cudaStreamSynchronize(d->stream);
+    if (e != cudaSuccess) {
+      d->fail("apply daemon: drain kernel failed: %s", cudaGetErrorString(e));
+      return;
+    }
+    d->drains.fetch_add(1, std::memory_order_relaxed);
+    d->applied.fetch_add(static_cast<unsigned long long>(n), std::memory_order_relaxed);
+  }
+}
+
+}  // namespace
+
+extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
+                                     const dtf_apply_item* items, int n_items, long long slot_stride,
+                                     int depth, int n_workers, const dtf_apply_hyper* hyper,
+                                     dtf_ps_ctrl* ctrl_powers, dtf_ps_ctrl* ctrl_step,
+                                     dtf_mbox_flags* flags, int poll_us) {
+  DTF_REQUIRE(out != nullptr && hyper != nullptr && flags != nullptr, "mbox_daemon_start: null argument");
+  DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "mbox_daemon_start: %d items (max %d)",
+              n_items, DTF_MAX_APPLY_ITEMS);
+  DTF_REQUIRE(depth >= 1 && n_workers >= 1 && n_workers <= DTF_MAX_WORKERS,
+              "mbox_daemon_start: depth %d, %d workers", depth, n_workers);
+  int prev = -1;
+  DTF_CHECK_CUDA(cudaGetDevice(&prev));
+  DTF_CHECK_CUDA(cudaSetDevice(device));
+  dtf_mbox_daemon* d = new dtf_mbox_daemon();
+  d->device = device;
+  d->opt = opt;
+  for (int i = 0; i < n_items; ++i) d->items[i] = items[i];
+  d->n_items = n_items;
+  d->slot_stride = slot_stride;
+  d->depth = depth;
+  d->n_workers = n_workers;
+  d->hyper = *hyper;
+  d->ctrl_powers = ctrl_powers;
+  d->ctrl_step = ctrl_step;
+  d->flags = flags;
+  d->poll_us = poll_us;
+  int lo = 0, hi = 0;
+  cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&d->stream, cudaStreamNonBlocking, lo);
+  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&d->host_flags), sizeof(dtf_mbox_flags));
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&d->scratch), (DTF_MAX_WORKERS + 16) * 4);
+  if (e == cudaSuccess) e = cudaMemset(d->scratch, 0, (DTF_MAX_WORKERS + 16) * 4);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    set_error("mbox_daemon_start: %s", cudaGetErrorString(e));
+    if (d->scratch) cudaFree(d->scratch);
+    if (d->host_flags) cudaFreeHost(d->host_flags);
+    if (d->stream) cudaStreamDestroy(d->stream);
+    delete d;
+    cudaSetDevice(prev);
+    return -1;
+  }
+  d->thread = std::thread(daemon_main, d);
+  cudaSetDevice(prev);
+  *out = d;
+  return 0;
+}
+
+/* pause = 1 returns once the daemon is parked between drains (checkpoint / restore want a quiet
+ * shard); pause = 0 resumes. */
+extern "C" int dtf_mbox_daemon_pause(dtf_mbox_daemon* d, int pause) {
+  DTF_REQUIRE(d != nullptr, "mbox_daemon_pause: null daemon");
+  d->paused.store(pause ? 1 : 0, std::memory_order_release);
+  if (pause) {
+    for (int i = 0; i < 200000 && !d->idle.load(std::memory_order_acquire) && !d->failed.load(); ++i)
+      std::this_thread::sleep_for(std::chrono::microseconds(10));
+    DTF_REQUIRE(d->idle.load() || d->failed.load(), "mbox_daemon_pause: the daemon did not park");
+  }
+  return 0;
+}
+
+extern "C" int dtf_mbox_daemon_stats(dtf_mbox_daemon* d, unsigned long long* polls,
+                                     unsigned long long* drains, unsigned long long* applied) {
+  DTF_REQUIRE(d != nullptr, "mbox_daemon_stats: null daemon");
+  if (polls) *polls = d->polls.load();
+  if (drains) *drains = d->drains.load();
+  if (applied) *applied = d->applied.load();
+  if (d->failed.load()) {
+    std::lock_guard<std::mutex> g(d->err_mu);
+    set_error("%s", d->err);
+    return -1;
+  }
+  return 0;
+}
+
+extern "C" int dtf_mbox_daemon_stop(dtf_mbox_daemon* d) {
+  if (d == nullptr) return 0;
+  d->stop.store(1, std::memory_order_release);
+  if (d->thread.joinable()) d->thread.join();
+  int prev = -1;
+  cudaGetDevice(&prev);
+  cudaSetDevice(d->device);
+  int rc = 0;
+  if (d->failed.load()) {
+    set_error("%s", d->err);
+    rc = -1;
+  }
+  cudaStreamDestroy(d->stream);
+  cudaFreeHost(d->host_flags);
+  cudaFree(d->scratch);
+  if (prev >= 0) cudaSetDevice(prev);
+  delete d;
+  return rc;
+}

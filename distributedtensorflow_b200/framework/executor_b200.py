@@ -19,6 +19,7 @@ from __future__ import annotations
 
 import math
 import os
+import time
 from dataclasses import dataclass, field
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
@@ -203,8 +204,8 @@ class StepState:
         self.x_dev = torch.zeros((B, p.in_features), dtype=x_dtype, device=dev)
         self.y_dev = torch.zeros(ysh, dtype=y_dtype, device=dev)
         self.out_pin = torch.zeros(4, dtype=torch.float32).pin_memory()      # loss
-        self.step_pin = torch.zeros(2, dtype=torch.int64).pin_memory()       # global_step, pulled
-        self.step_dev = torch.zeros(2, dtype=torch.int64, device=dev)
+        self.step_pin = torch.zeros(4, dtype=torch.int64).pin_memory()       # global_step, pulled, min consumed
+        self.step_dev = torch.zeros(4, dtype=torch.int64, device=dev)
         self.counter = torch.zeros(4, dtype=torch.int32, device=dev)
         dims = [int(d.w.shape[0]) for d in p.dense] + [p.num_classes]
         self.dims = dims
@@ -278,6 +279,17 @@ class B200StepRunner:
         # is slower than GEMM + the coalesced apply kernel (180 vs 158 us/step), so it is opt-in.
         self.fused_apply = bool(opts.get("fused_apply", False))
         self.clear_at_end = bool(opts.get("clear_at_end", True))
+        # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
+        # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
+        # daemon (csrc/kernels/mailbox.cu, csrc/runtime/mbox_daemon.cu); "auto" = mailbox whenever
+        # there is more than one worker (a lone worker keeps the exact in-order apply)
+        self.push_mode = str(opts.get("push_mode", os.environ.get("DTF_B200_PUSH_MODE", "auto")))
+        self.mailbox_depth = int(opts.get("mailbox_depth", 4))      # = max pushes in flight per worker
+        self.mailbox_timeout = float(opts.get("mailbox_timeout", 60.0))
+        self.mailbox_poll_us = int(opts.get("mailbox_poll_us", 20))
+        self.use_mailbox = False
+        self._pushes = 0
+        self._min_consumed = 0
         self.split_k = bool(opts.get("split_k", True))
         self.pdl = bool(opts.get("pdl", True))
         L.lib().dtf_set_pdl(1 if self.pdl else 0)
@@ -341,10 +353,27 @@ class B200StepRunner:
                     "%d shards, aggregate %d of %d); use backend='cpu' for backup-worker mode"
                     % (nw, world, self.sync_opt.replicas_to_aggregate, self.sync_opt.total_num_replicas))
             sync_workers = world
+        depth, mirrors = 1, True
+        self.use_mailbox = False
+        if self.sync_opt is None and spec is not None and self.trainable_names and self.push_mode != "rmw":
+            if self.push_mode not in ("auto", "mailbox"):
+                raise ValueError("push_mode must be 'auto', 'rmw' or 'mailbox' (got %r)" % self.push_mode)
+            nw = self.cluster.num_tasks("worker") if (self.cluster is not None and "worker" in self.cluster.jobs) else 1
+            fits = nw <= L.MAX_WORKERS and self.worker_id < nw
+            if self.push_mode == "mailbox" and not fits:
+                raise NotImplementedError("push_mode='mailbox' supports at most %d workers" % L.MAX_WORKERS)
+            # a lone worker keeps the exact in-order apply; with several workers the applies are
+            # interleaved anyway and the write-only push is what scales
+            self.use_mailbox = fits and (self.push_mode == "mailbox" or nw > 1)
+            if self.use_mailbox:
+                sync_workers, depth, mirrors = nw, max(1, self.mailbox_depth), False
         self.store = NvlStore(self.client, self.layout, spec, trainable_names, self.device.index or 0,
-                              self._shard_devices(), sync_workers=sync_workers)
+                              self._shard_devices(), sync_workers=sync_workers, mailbox_depth=depth,
+                              mirrors=mirrors)
         self.sync_round_no: Optional[int] = None
         self.mirror_filled = False
+        if self.use_mailbox:
+            self._mbox_setup()
 
     def init_variables(self, values: Dict[str, np.ndarray]) -> None:
         st = self.store
@@ -622,7 +651,8 @@ class B200StepRunner:
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
-            fused = self._fused_apply_spec(d.w) if (self.overlap and not sync and self.fused_apply) else None
+            fused = self._fused_apply_spec(d.w) if (self.overlap and not sync and self.fused_apply
+                                                    and not self.use_mailbox) else None
             dz_i = dz
             if fused is None:
                 with torch.cuda.stream(side):
@@ -702,9 +732,111 @@ class B200StepRunner:
         return dict(opt=spec.code, hyper=hyper, rows_per_slice=per, shadow_ld=regs[0].shadow_ld,
                     ctrl_powers=st.powers_ctrl, slices=slices)
 
+    # -- "owner applies" push (mailboxes + the PS tasks' apply daemons) --------------------------------
+    def _mbox_setup(self) -> None:
+        """Start every shard's apply daemon (idempotent: the first worker to ask wins) and reset
+        this worker's sequence numbers on every owner."""
+        st, al, me, spec = self.store, self.store.arena, self.worker_id, self.spec
+        hyper = dict(lr=float(spec.learning_rate), beta1=float(spec.beta1), beta2=float(spec.beta2),
+                     epsilon=float(spec.epsilon), momentum=float(spec.momentum),
+                     use_nesterov=bool(spec.use_nesterov))
+        for sh in range(st.num_shards):
+            items = []
+            for name in self.trainable_names:
+                for r in al.regions.get(name, []):
+                    if r.shard != sh:
+                        continue
+                    items.append(dict(var_off=r.var_off,
+                                      slot0_off=r.slot_off[0] if len(r.slot_off) > 0 else -1,
+                                      slot1_off=r.slot_off[1] if len(r.slot_off) > 1 else -1,
+                                      shadow_off=r.shadow_off if r.shadow_off is not None else -1,
+                                      grad_off=al.mailbox_off[(name, sh)], n=int(r.sl.n), cols=int(r.cols),
+                                      shadow_ld=int(r.shadow_ld)))
+            desc = dict(opt=int(spec.code), items=items, slot_stride=int(al.mailbox_stride[sh]),
+                        depth=int(al.mailbox_depth), n_workers=int(al.sync_workers), hyper=hyper,
+                        owns_step=bool(al.step_shard == sh), flags_off=int(al.mbox_flags_off[sh]),
+                        poll_us=int(self.mailbox_poll_us))
+            self.client.call(sh, "mbox_start", desc)
+        zero = np.zeros(1, np.uint32)
+        for sh in range(st.num_shards):
+            f = st.mbox_flags_ptr(sh)
+            # produced first: "nothing pending" holds at every instant of the reset
+            st._h2d(f + L.MBOX_OFF_PRODUCED + 4 * me, zero)
+            st._h2d(f + L.MBOX_OFF_CONSUMED + 4 * me, zero)
+            st._h2d(f + L.MBOX_OFF_DONE + 4 * me, zero)
+        self._pushes = 0
+        self._min_consumed = 0
+        self.mbox_seq = torch.zeros(4, dtype=torch.int32, device=self.device)
+        # the push kernel's last CTA stores "how many of my pushes every owner has applied" straight
+        # into this pinned host word (UVA: pinned memory is device-addressable), so admitting the
+        # next step costs the host one memory read, not a stream sync or a copy
+        self.mbox_host = torch.zeros(16, dtype=torch.int32).pin_memory()
+        self._mbox_host_np = self.mbox_host.numpy()
+        torch.cuda.synchronize(self.device)
+
+    def _push_vars(self, s: StepState, variables: Sequence[G.Variable], publish: bool) -> None:
+        """Posted stores of the gradients into this worker's mailbox on every owning shard;
+        ``publish`` releases the push (one sequence number per owner) and must be the step's last."""
+        st, al, me = self.store, self.store.arena, self.worker_id
+        items = []
+        for var in variables:
+            gptr = self._grad_ptr(s, var)
+            for r in self._regions_rotated(var):
+                dst0 = st.mbox_slot_ptr(r.shard, me, 0) + st.mbox_slice_off(var.name, r.shard)
+                items.append((gptr + r.sl.first * 4, dst0, (r.sl.n * 4 + 15) // 16 * 16,
+                              al.mailbox_stride[r.shard]))
+        flags = [st.mbox_flags_ptr(sh) for sh in range(st.num_shards)]
+        K.mailbox_push(items, al.mailbox_depth, me, flags, publish, self.mbox_seq.data_ptr(),
+                       s.counter.data_ptr(), self.mbox_host.data_ptr() if publish else None,
+                       st.step_ctrl if publish else None, s.step_dev.data_ptr() if publish else None)
+
+    def _mbox_consumed(self) -> int:
+        """min over owners of how many of MY gradients they have applied (host-side read)."""
+        st, me = self.store, self.worker_id
+        return min(int(st._d2h(st.mbox_flags_ptr(sh) + L.MBOX_OFF_CONSUMED + 4 * me, 4, np.uint32)[0])
+                   for sh in range(st.num_shards))
+
+    def _mbox_wait(self, needed: int) -> None:
+        """Flow control / flush: block until every owner has applied ``needed`` of my pushes.
+        Fast path: the host word the push kernels keep fresh. Slow path (nothing of mine is in
+        flight, so nothing will refresh that word): read the owners' counters over the mapping."""
+        if self._min_consumed >= needed:
+            return
+        from ..parallel.ps_core import AbortedError
+        t0 = time.monotonic()
+        while True:
+            v = int(self._mbox_host_np[0])
+            if v > self._min_consumed:
+                self._min_consumed = v
+            if self._min_consumed >= needed:
+                return
+            if self.stream.query():
+                self._min_consumed = max(self._min_consumed, self._mbox_consumed())
+                if self._min_consumed >= needed:
+                    return
+                time.sleep(20e-6)
+            if time.monotonic() - t0 > self.mailbox_timeout:
+                raise AbortedError("a parameter server stopped applying gradients: %d of %d pushes of "
+                                   "worker %d consumed after %.0f s" % (self._min_consumed, needed,
+                                                                         self.worker_id, self.mailbox_timeout))
+
+    def _mbox_admit(self) -> None:
+        """Called right before a training step is enqueued: push k reuses the mailbox buffer of
+        push k - depth, which the owners must have applied. Bounds staleness to ``depth`` pushes."""
+        self._mbox_wait(self._pushes + 1 - self.store.arena.mailbox_depth)
+        self._pushes += 1
+
+    def flush_pushes(self) -> None:
+        """Wait until every gradient this worker has pushed is applied (exact global_step reads)."""
+        if self.use_mailbox:
+            self._mbox_wait(self._pushes)
+
     def _apply_vars(self, s: StepState, variables: Sequence[G.Variable], finish: bool) -> None:
         """push+apply of ``variables`` on the current stream; ``finish`` adds TF's _finish (beta
         powers) and the global_step atomic and must be the step's last apply."""
+        if self.use_mailbox:
+            self._push_vars(s, variables, publish=finish)
+            return
         st, spec = self.store, self.spec
         entries = []
         for var in variables:
@@ -811,7 +943,9 @@ class B200StepRunner:
                 s.launches_per_step = K.LAUNCHES - before
                 self.stream.synchronize()
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=self.stream):
+                # thread-local capture mode: the PS apply daemon (a native host thread of this
+                # process) keeps polling and launching on its own stream while we capture
+                with torch.cuda.graph(g, stream=self.stream, capture_error_mode="thread_local"):
                     self._enqueue_step(s)
                 s.graph = g
                 if sync:
@@ -828,6 +962,7 @@ class B200StepRunner:
         plain = [f for f in fetches if not isinstance(f, TrainOp)]
         gs_var = G.get_global_step(self.graph)
         if not train_ops and all(f is gs_var for f in plain):
+            self.flush_pushes()
             step = self.store.read_global_step()
             return [self._as_step(step) for _ in fetches]
         top = train_ops[0] if train_ops else None
@@ -848,6 +983,8 @@ class B200StepRunner:
             self._stage(s, x.reshape(B, -1), y)
         with nvtx_range("dtf/launch_step"):
             if top is not None:
+                if self.use_mailbox:
+                    self._mbox_admit()
                 self._launch(s)
             else:
                 with torch.cuda.stream(self.stream):
@@ -856,6 +993,7 @@ class B200StepRunner:
             self.stream.synchronize()
         loss_val = np.float32(s.out_pin[0].item())
         step_val = int(s.step_pin[0].item()) if top is not None else None
+
         out: List[Any] = []
         extra: Optional[Dict[int, Any]] = None
         for f in fetches:
@@ -930,6 +1068,8 @@ class B200StepRunner:
         s = self.train_state()
         with torch.cuda.stream(self.stream):
             for _ in range(n):
+                if self.use_mailbox:
+                    self._mbox_admit()
                 if s.graph is not None:
                     s.graph.replay()
                 else:
@@ -940,6 +1080,14 @@ class B200StepRunner:
             self.stream.synchronize()
         except Exception:
             pass
+        if self.use_mailbox and self.store is not None:
+            try:
+                self.flush_pushes()
+                one = np.ones(1, np.uint32)
+                for sh in range(self.store.num_shards):
+                    self.store._h2d(self.store.mbox_flags_ptr(sh) + L.MBOX_OFF_DONE + 4 * self.worker_id, one)
+            except Exception:
+                pass
         self.states.clear()
         if self.store is not None:
             self.store.close()

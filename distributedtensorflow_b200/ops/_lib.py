@@ -122,6 +122,17 @@ class CopyItem(C.Structure):
     _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("bytes", C.c_longlong)]
 
 
+class MboxPushItem(C.Structure):
+    """Mirror of ``dtf_mbox_push_item``."""
+    _fields_ = [("src", C.c_void_p), ("dst0", C.c_void_p), ("bytes", C.c_longlong),
+                ("buf_stride", C.c_longlong)]
+
+
+MAX_MBOX_ITEMS = 64
+MBOX_FLAGS_BYTES = 512
+MBOX_OFF_PRODUCED, MBOX_OFF_CONSUMED, MBOX_OFF_DONE = 0, 128, 256
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -168,6 +179,14 @@ def _declare(lib):
         "dtf_stream_sync": [vp],
         "dtf_set_pdl": [i],
         "dtf_sync_round": [i, vp, i, i, i, C.c_uint, C.POINTER(ApplyHyper), C.POINTER(C.c_ulonglong), vp, vp, i, vp],
+        "dtf_mailbox_push": [C.POINTER(MboxPushItem), i, i, i, C.POINTER(vp), i, i, vp, vp, vp, vp, vp, vp],
+        "dtf_mailbox_drain": [i, C.POINTER(ApplyItem), i, C.c_longlong, i, i, C.POINTER(ApplyHyper), vp, vp,
+                              vp, vp, vp, vp, vp],
+        "dtf_mbox_daemon_start": [C.POINTER(vp), i, i, C.POINTER(ApplyItem), i, C.c_longlong, i, i,
+                                  C.POINTER(ApplyHyper), vp, vp, vp, i],
+        "dtf_mbox_daemon_pause": [vp, i],
+        "dtf_mbox_daemon_stats": [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)],
+        "dtf_mbox_daemon_stop": [vp],
         "dtf_host_alloc_pinned": [C.POINTER(vp), C.c_size_t],
         "dtf_host_free_pinned": [vp],
     }

@@ -162,6 +162,44 @@ def push_apply(opt: int, items, n_items: int, hyper: L.ApplyHyper, ctrl_powers: 
     _count()
 
 
+def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags: Sequence[int],
+                 publish: bool, seq: int, block_counter: Optional[int],
+                 min_consumed_out: Optional[int], ctrl_step: Optional[int] = None,
+                 step_out: Optional[int] = None) -> None:
+    """Worker side of the "owner applies" push (csrc/kernels/mailbox.cu).
+
+    items: (src_ptr, dst0_ptr, nbytes, buf_stride) — gradient slice -> its place in MY buffer 0 on
+    the owning shard. ``publish`` makes the last CTA release the sequence number to every owner in
+    ``owner_flags`` (pointers to their ``dtf_mbox_flags``)."""
+    n = len(items)
+    chunks = [items[i:i + L.MAX_MBOX_ITEMS] for i in range(0, n, L.MAX_MBOX_ITEMS)] or [[]]
+    flags = (C.c_void_p * max(1, len(owner_flags)))(*owner_flags)
+    for ci, chunk in enumerate(chunks):
+        arr = (L.MboxPushItem * max(1, len(chunk)))()
+        for i, (s, d, b, st) in enumerate(chunk):
+            arr[i].src, arr[i].dst0, arr[i].bytes, arr[i].buf_stride = s, d, b, st
+        last = publish and ci == len(chunks) - 1
+        if not chunk and not last:
+            continue
+        rc = L.lib().dtf_mailbox_push(arr, len(chunk), depth, worker_id, flags, len(owner_flags),
+                                      int(last), seq, block_counter, min_consumed_out if last else None,
+                                      ctrl_step if last else None, step_out if last else None,
+                                      L.current_stream())
+        L.check(rc, "dtf_mailbox_push")
+        _count()
+
+
+def mailbox_drain(opt: int, items, n_items: int, slot_stride: int, depth: int, n_workers: int,
+                  hyper: L.ApplyHyper, ctrl_powers: Optional[int], ctrl_step: Optional[int],
+                  flags: int, todo: int, block_counter: int, step_out: Optional[int]) -> None:
+    """Owner side: snapshot pending mailboxes + apply them from local HBM (two launches)."""
+    rc = L.lib().dtf_mailbox_drain(opt, items, n_items, slot_stride, depth, n_workers, C.byref(hyper),
+                                   ctrl_powers, ctrl_step, flags, todo, block_counter, step_out,
+                                   L.current_stream())
+    L.check(rc, "dtf_mailbox_drain")
+    _count(2)
+
+
 def pull_bulk(copies: Sequence[tuple], ctrl_step: Optional[int] = None,
               pulled_step_out: Optional[int] = None) -> None:
     """copies: (src_ptr, dst_ptr, nbytes) triples, nbytes % 16 == 0."""

@@ -83,10 +83,16 @@ class ArenaLayout:
     mailbox_stride: List[int] = field(default_factory=list)                 # bytes per worker slot, per shard
     mirror_f32: Dict[str, int] = field(default_factory=dict)                # name -> offset (all arenas)
     mirror_bf16: Dict[str, int] = field(default_factory=dict)
+    # asynchronous "owner applies" push (csrc/kernels/mailbox.cu): the same per-worker mailboxes,
+    # `mailbox_depth` buffers deep, plus one dtf_mbox_flags block per shard; no mirrors
+    mailbox_depth: int = 1
+    mbox_flags_off: List[int] = field(default_factory=list)
+    mbox_slot_base: List[int] = field(default_factory=list)
 
 
 def build_arena_layout(layout: Dict[str, VarLayout], num_shards: int, spec: Optional[OptimizerSpec],
-                       trainable_names: Sequence[str], sync_workers: int = 0) -> ArenaLayout:
+                       trainable_names: Sequence[str], sync_workers: int = 0, mailbox_depth: int = 1,
+                       mirrors: bool = True) -> ArenaLayout:
     num_slots = spec.num_slots if spec is not None else 0
     offs = [L.CTRL_BYTES] * num_shards
     regions: Dict[str, List[SliceRegion]] = {}
@@ -127,15 +133,18 @@ def build_arena_layout(layout: Dict[str, VarLayout], num_shards: int, spec: Opti
     al = ArenaLayout(num_shards, [], regions, step_var, step_shard, pshard, num_slots)
     if sync_workers > 0:
         al.sync_workers = sync_workers
+        al.mailbox_depth = mailbox_depth
         al.mailbox_stride = [0] * num_shards
-        slot_base = [_align(o) for o in offs]
+        al.mbox_flags_off = [_align(o) for o in offs]
+        slot_base = [o + L.MBOX_FLAGS_BYTES for o in al.mbox_flags_off]
+        al.mbox_slot_base = slot_base
         for name in trainable_names:                       # one packed slot per worker per shard
             for r in regions.get(name, []):
                 al.mailbox_off[(name, r.shard)] = slot_base[r.shard] + al.mailbox_stride[r.shard]
                 al.mailbox_stride[r.shard] += _align(r.sl.n * 4)
-        ends = [slot_base[s] + sync_workers * al.mailbox_stride[s] for s in range(num_shards)]
+        ends = [slot_base[s] + sync_workers * mailbox_depth * al.mailbox_stride[s] for s in range(num_shards)]
         o = _align(max(ends))                              # mirrors: same offset in EVERY arena
-        for name, regs in regions.items():
+        for name, regs in (regions.items() if mirrors else ()):
             if not regs:
                 continue
             vl = layout[name]
@@ -154,13 +163,15 @@ class NvlStore:
 
     def __init__(self, client, layout: Dict[str, VarLayout], spec: Optional[OptimizerSpec],
                  trainable_names: Sequence[str], local_device: int,
-                 shard_devices: Optional[Sequence[Optional[int]]] = None, sync_workers: int = 0):
+                 shard_devices: Optional[Sequence[Optional[int]]] = None, sync_workers: int = 0,
+                 mailbox_depth: int = 1, mirrors: bool = True):
         self.client = client
         self.layout = layout
         self.spec = spec
         self.num_shards = client.num_shards
         self.local_device = local_device
-        self.arena = build_arena_layout(layout, self.num_shards, spec, trainable_names, sync_workers)
+        self.arena = build_arena_layout(layout, self.num_shards, spec, trainable_names, sync_workers,
+                                        mailbox_depth, mirrors)
         self.base: List[int] = [0] * self.num_shards
         self.is_local: List[bool] = [False] * self.num_shards
         self.shard_device: List[int] = [local_device] * self.num_shards
@@ -206,6 +217,20 @@ class NvlStore:
 
     def shadow_ptr(self, r: SliceRegion) -> Optional[int]:
         return None if r.shadow_off is None else self.base[r.shard] + r.shadow_off
+
+    def mbox_flags_ptr(self, shard: int) -> int:
+        return self.base[shard] + self.arena.mbox_flags_off[shard]
+
+    def mbox_slot_ptr(self, shard: int, worker: int, buf: int = 0) -> int:
+        """Start of mailbox slot (worker, buffer) inside ``shard``'s arena."""
+        al = self.arena
+        return self.base[shard] + al.mbox_slot_base[shard] + \
+            (worker * al.mailbox_depth + buf) * al.mailbox_stride[shard]
+
+    def mbox_slice_off(self, name: str, shard: int) -> int:
+        """Byte offset of a variable's slice inside every mailbox slot of ``shard``."""
+        al = self.arena
+        return al.mailbox_off[(name, shard)] - al.mbox_slot_base[shard]
 
     @property
     def step_ctrl(self) -> int:

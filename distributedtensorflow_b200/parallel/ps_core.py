@@ -233,6 +233,76 @@ class PsShard:
     def nvl_info(self) -> Optional[dict]:
         return self._arena
 
+    # -- apply daemon ("owner applies" push, csrc/runtime/mbox_daemon.cu) ---------------------------
+    def mbox_start(self, desc: dict) -> dict:
+        """Start (once) the native apply daemon on this shard's arena. ``desc`` describes the
+        shard's trainable slices with byte offsets from the arena base — every task derives the
+        same layout, so whichever worker calls first wins and later calls are checked no-ops.
+        This is the PS doing what the reference's PS does: execute the optimizer's apply ops that
+        replica_device_setter placed on /job:ps (run_mnist_distributed.py:107,116)."""
+        import atexit
+        import ctypes as C
+        from ..ops import _lib as L
+        from ..ops import kernels as K
+        sig = repr(sorted((k, repr(v)) for k, v in desc.items()))
+        with self._lock:
+            if self._arena is None:
+                raise RuntimeError("mbox_start before nvl_alloc")
+            if getattr(self, "_mbox_daemon", None) is not None:
+                if sig != self._mbox_sig:
+                    raise ValueError("apply daemon already running with a different layout / optimizer")
+                return {"started": False}
+            base = self._arena["ptr"]
+
+            def at(off):
+                return None if off is None or off < 0 else base + int(off)
+
+            entries = [dict(var=at(it["var_off"]), slot0=at(it["slot0_off"]), slot1=at(it["slot1_off"]),
+                            shadow=at(it["shadow_off"]), grad=at(it["grad_off"]), n=int(it["n"]),
+                            first=0, cols=int(it["cols"]), shadow_ld=int(it["shadow_ld"]))
+                       for it in desc["items"]]
+            items = K.make_apply_items(entries)
+            h = desc["hyper"]
+            hyper = K.make_hyper(h["lr"], h["beta1"], h["beta2"], h["epsilon"], h["momentum"], 1.0,
+                                 bool(h["use_nesterov"]), False)
+            handle = C.c_void_p()
+            lib = L.lib()
+            rc = lib.dtf_mbox_daemon_start(C.byref(handle), self._arena["device"], int(desc["opt"]), items,
+                                           len(entries), int(desc["slot_stride"]), int(desc["depth"]),
+                                           int(desc["n_workers"]), C.byref(hyper), base,
+                                           base if desc["owns_step"] else None,
+                                           base + int(desc["flags_off"]), int(desc.get("poll_us", 20)))
+            L.check(rc, "dtf_mbox_daemon_start")
+            self._mbox_daemon = handle
+            self._mbox_sig = sig
+            atexit.register(self.mbox_stop)
+            return {"started": True}
+
+    def mbox_stats(self) -> dict:
+        import ctypes as C
+        from ..ops import _lib as L
+        d = getattr(self, "_mbox_daemon", None)
+        if d is None:
+            return {"running": False}
+        polls, drains, applied = C.c_ulonglong(), C.c_ulonglong(), C.c_ulonglong()
+        rc = L.lib().dtf_mbox_daemon_stats(d, C.byref(polls), C.byref(drains), C.byref(applied))
+        L.check(rc, "apply daemon")
+        return {"running": True, "polls": polls.value, "drains": drains.value, "applied": applied.value}
+
+    def mbox_pause(self, pause: bool) -> None:
+        from ..ops import _lib as L
+        d = getattr(self, "_mbox_daemon", None)
+        if d is not None:
+            L.check(L.lib().dtf_mbox_daemon_pause(d, 1 if pause else 0), "dtf_mbox_daemon_pause")
+
+    def mbox_stop(self) -> None:
+        from ..ops import _lib as L
+        with self._lock:
+            d = getattr(self, "_mbox_daemon", None)
+            self._mbox_daemon = None
+        if d is not None:
+            L.lib().dtf_mbox_daemon_stop(d)
+
     # -- data plane ---------------------------------------------------------------------------------
     def pull(self, names: Sequence[str]) -> List[np.ndarray]:
         # Unlocked reads: a pull can observe a half-applied update, exactly like TF's PS.
@@ -337,6 +407,8 @@ class PsShard:
         return out
 
     def request_shutdown(self) -> None:
+        # the apply daemon keeps running while the server drains (workers may be mid-step); it is
+        # stopped by PsRpcServer.stop() / LocalCluster.close() / atexit
         self.shutdown_requested.set()
         for q in self.queues.values():
             q.close()

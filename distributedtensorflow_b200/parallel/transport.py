@@ -189,6 +189,9 @@ class LocalCluster:
 
     def close(self) -> None:
         LocalCluster._registry.pop(self.name, None)
+        for sh in self.shards:
+            if hasattr(sh, "mbox_stop"):
+                sh.mbox_stop()
 
 
 class LocalClient(PsClient):

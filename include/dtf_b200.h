@@ -161,6 +161,73 @@ int dtf_push_apply_static(int opt, const dtf_apply_item* items, int n_items,
                           unsigned long long* step_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * K9/K11, asynchronous "owner applies" push (option (b)). The remote read-modify-write
+ * of dtf_push_apply moves 26 bytes per Adam parameter over NVLink, half of them as round-trip
+ * reads. Here the worker only WRITES its fp32 gradient into a per-worker mailbox inside the
+ * owning shard's arena (4 bytes per parameter, posted stores) and publishes a sequence number;
+ * the owner's own step stream drains its mailboxes with local HBM traffic, applying each pending
+ * gradient separately and in order (worker 0..W-1), exactly as the reference's PS applies each
+ * worker's ApplyAdam when it arrives (run_mnist_distributed.py:116,143-150). Mailboxes are
+ * `depth` buffers deep per worker: a worker may run at most `depth` pushes ahead of the owner,
+ * which is the bounded-staleness knob TF1 lacks.
+ *   arena:  flags (dtf_mbox_flags) ... slot(w, b) = slots + (w * depth + b) * slot_stride
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dtf_mbox_flags {               /* 512 bytes, zero = idle */
+  unsigned int produced[DTF_MAX_WORKERS];     /* +0   worker w: gradients published so far (st.release.sys) */
+  unsigned int pad0[16];
+  unsigned int consumed[DTF_MAX_WORKERS];     /* +128 owner: gradients of worker w applied so far */
+  unsigned int pad1[16];
+  unsigned int done[DTF_MAX_WORKERS];         /* +256 worker w has finished training */
+  unsigned int pad2[48];
+} dtf_mbox_flags;
+#define DTF_MAX_MBOX_ITEMS 64
+typedef struct dtf_mbox_push_item {
+  const void* src;        /* local fp32 gradient slice */
+  void* dst0;             /* the slice's place inside MY buffer 0 on the owning shard (peer pointer) */
+  long long bytes;        /* multiple of 16 */
+  long long buf_stride;   /* bytes from buffer b to buffer b + 1 of the same worker on that shard */
+} dtf_mbox_push_item;
+/* Copies every item into buffer (*seq % depth) of the caller's mailboxes. With publish = 1 the
+ * last CTA then stores produced[worker_id] = *seq + 1 on EVERY owner (owner_flags[0..n_owners)),
+ * advances *seq, and writes min over owners of consumed[worker_id] to *min_consumed_out — the
+ * host's flow control: push k may only be issued once every owner has consumed push k - depth.
+ * With ctrl_step / step_out it also reads the shared global_step into *step_out (local u64).
+ * Several non-publishing calls followed by one publishing call form one push. */
+int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, int depth, int worker_id,
+                     dtf_mbox_flags* const* owner_flags, int n_owners, int publish,
+                     unsigned int* seq, unsigned int* block_counter,
+                     unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
+                     unsigned long long* step_out, void* stream);
+/* Owner side, two launches: (1) snapshot which workers have an unconsumed gradient (at most one
+ * per worker per call, the oldest) into `todo` (local scratch, DTF_MAX_WORKERS words);
+ * (2) for every item read var / slots once, apply the pending gradients one after another with
+ * the beta powers each apply would have seen, write var / slots / bf16 serving copy once. Items
+ * are dtf_apply_item whose `grad` points at the slice inside slot (worker 0, buffer 0). The last
+ * CTA publishes consumed[w] += 1, multiplies the shard's beta powers, and — when ctrl_step is not
+ * NULL (this shard owns global_step) — adds the number of applied gradients to global_step and
+ * refreshes the workers' heartbeats. step_out (optional, local u64) receives global_step. */
+int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_items, long long slot_stride,
+                      int depth, int n_workers, const dtf_apply_hyper* hyper,
+                      dtf_ps_ctrl* ctrl_powers, dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags,
+                      unsigned int* todo, unsigned int* block_counter,
+                      unsigned long long* step_out, void* stream);
+
+/* The shard owner's apply daemon: one native host thread per shard that polls the mailbox flags
+ * (D2H copy, no SM use while idle) and launches dtf_mailbox_drain on its own low-priority stream
+ * whenever a worker has published a gradient — the B200 stand-in for the PS task's CPU executing
+ * the ApplyAdam ops placed on /job:ps (run_mnist_distributed.py:96-98,107,116). Pointers are
+ * device addresses in the OWNER's address space. */
+typedef struct dtf_mbox_daemon dtf_mbox_daemon;
+int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt, const dtf_apply_item* items,
+                          int n_items, long long slot_stride, int depth, int n_workers,
+                          const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
+                          dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, int poll_us);
+int dtf_mbox_daemon_pause(dtf_mbox_daemon* d, int pause);   /* 1: returns once parked; 0: resume */
+int dtf_mbox_daemon_stats(dtf_mbox_daemon* d, unsigned long long* polls,
+                          unsigned long long* drains, unsigned long long* applied); /* -1: daemon died */
+int dtf_mbox_daemon_stop(dtf_mbox_daemon* d);               /* joins the thread, frees d */
+
+/* ------------------------------------------------------------------------------------------
  * K11: bulk parameter pull, peer -> local (one launch for a list of tensors). Reference: the
  * per-tensor RecvTensor RPCs of every mon_sess.run (run_mnist_distributed.py:150,161).
  * ------------------------------------------------------------------------------------------ */

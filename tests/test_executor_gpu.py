@@ -166,3 +166,51 @@ def test_eval_fetch_and_validation_batch():
         v1 = float(sess.run(xent, feed_dict={x: vx, y_: vy}))
         assert int(sess.run(gs)) == 30
     assert v1 < v0
+
+
+@pytest.mark.parametrize("num_ps,depth", [(1, 2), (2, 4)])
+def test_mailbox_push_mode_owner_applies_every_gradient(num_ps, depth):
+    """push_mode='mailbox': the worker only stores gradients into its mailboxes; the PS shards'
+    native apply daemons apply them. Every push must be applied exactly once (global_step and the
+    daemons' counters), the loss must fall, and staleness is bounded by the mailbox depth."""
+    import distributedtensorflow_b200 as tf
+    tf.reset_default_graph()
+    tf.set_random_seed(7)
+    server = tf.train.Server.create_local_server(num_ps=num_ps)
+    cluster = tf.train.ClusterSpec({"ps": ["localhost:%d" % (1000 + i) for i in range(num_ps)],
+                                    "worker": ["localhost:2000"]})
+    strategy = tf.train.FlatSlicedStrategy(num_ps) if num_ps > 1 else None
+    with tf.device(tf.train.replica_device_setter(worker_device="/job:worker/task:0", cluster=cluster,
+                                                  ps_strategy=strategy)):
+        x_ph, y_ph, loss, gs, train_op = _build_mlp("adam")(tf)
+    batches = _batches(4, 100, one_hot=True)
+    cfg = tf.ConfigProto(backend="b200", device="cuda:0", push_mode="mailbox", mailbox_depth=depth)
+    steps = 40
+    losses = []
+    with tf.train.MonitoredTrainingSession(master=server.target, is_chief=True, config=cfg) as sess:
+        raw = sess._tf_sess()
+        for i in range(steps):
+            bx, by = batches[i % len(batches)]
+            _, l, g = sess.run([train_op, loss, gs], feed_dict={x_ph: bx, y_ph: by})
+            losses.append(float(l))
+            assert i + 1 - depth <= int(g) <= i + 1        # bounded staleness: at most `depth` pushes in flight
+        runner = raw._runner
+        assert runner.use_mailbox and runner.store.arena.mailbox_depth == depth
+        assert int(sess.run(gs)) == steps                  # flushes my pushes first
+        runner.replay(25)                                  # pipelined device steps go through the same admission
+        runner.flush_pushes()
+        assert runner.store.read_global_step() == steps + 25
+        for sh in range(num_ps):
+            st = raw.ps_client.call(sh, "mbox_stats")
+            assert st["running"] and st["applied"] == steps + 25
+        w = runner.store.read_variable("hid_w")
+        assert np.isfinite(w).all()
+        np.testing.assert_array_equal(runner.store.read_shadow("hid_w"),
+                                      _bf16_round(w))
+    server.stop()
+    assert np.mean(losses[-5:]) < 0.7 * np.mean(losses[:3])
+
+
+def _bf16_round(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a)).to(torch.bfloat16).float().numpy()

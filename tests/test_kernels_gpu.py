@@ -543,3 +543,100 @@ def test_pool2_bwd(K):
     got = dconv2p[:, 2:16, 2:16, :].float()
     assert (got - ref).abs().max().item() < 1e-2
     assert (db2 - ref.sum((0, 1, 2))).abs().max().item() < 0.05
+
+
+# ---------------------------------------------------------------------------------------------
+# "owner applies" push: mailbox_push (worker) + mailbox_drain (owner), csrc/kernels/mailbox.cu
+# ---------------------------------------------------------------------------------------------
+def _adam_ref(var, m, v, g, lr, b1, b2, eps, b1p, b2p):
+    lr_t = lr * math.sqrt(1.0 - b2p) / (1.0 - b1p)
+    m = m + (g - m) * (1.0 - b1)
+    v = v + (g * g - v) * (1.0 - b2)
+    var = var - lr_t * m / (v.sqrt() + eps)
+    return var, m, v
+
+
+def test_mailbox_push_and_drain_apply_pending_gradients_in_worker_order(K):
+    from distributedtensorflow_b200.ops import _lib as L
+    torch.manual_seed(11)
+    dev = "cuda"
+    W, depth = 3, 2
+    rows, cols = 300, 40
+    n0, n1 = rows * cols, 10                       # a matrix with a serving copy + a ragged bias
+    off1 = (n0 * 4 + 255) // 256 * 256
+    stride = off1 + 256                            # bytes per (worker, buffer) slot
+    slots = torch.zeros(W * depth * stride // 4, device=dev)
+    flags = torch.zeros(128, dtype=torch.int32, device=dev)
+    todo = torch.zeros(16, dtype=torch.int32, device=dev)
+    counter = torch.zeros(4, dtype=torch.int32, device=dev)
+    ctrl = torch.zeros(64, dtype=torch.int32, device=dev)
+    lr, b1, b2, eps = 1e-2, 0.9, 0.999, 1e-8
+    ctrl.view(torch.float32)[2], ctrl.view(torch.float32)[3] = b1, b2
+    step_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    var = [torch.randn(n0, device=dev), torch.randn(n1, device=dev)]
+    m = [torch.zeros(n0, device=dev), torch.zeros(n1, device=dev)]
+    v = [torch.zeros(n0, device=dev), torch.zeros(n1, device=dev)]
+    shadow = torch.zeros(rows, cols, dtype=torch.bfloat16, device=dev)
+    ref = [[x.clone() for x in var], [x.clone() for x in m], [x.clone() for x in v]]
+    b1p, b2p = b1, b2
+    items = K.make_apply_items([
+        dict(var=var[0].data_ptr(), slot0=m[0].data_ptr(), slot1=v[0].data_ptr(), shadow=shadow.data_ptr(),
+             grad=slots.data_ptr(), n=n0, cols=cols, shadow_ld=cols),
+        dict(var=var[1].data_ptr(), slot0=m[1].data_ptr(), slot1=v[1].data_ptr(), shadow=None,
+             grad=slots.data_ptr() + off1, n=n1, cols=n1, shadow_ld=n1)])
+    hyper = K.make_hyper(lr, b1, b2, eps)
+    seq = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(W)]
+    pcount = torch.zeros(4, dtype=torch.int32, device=dev)
+    minc = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def push(w, grads):
+        g1 = torch.zeros(16, device=dev)
+        g1[:n1] = grads[1]
+        base = slots.data_ptr() + w * depth * stride
+        K.mailbox_push([(grads[0].data_ptr(), base, n0 * 4, stride)], depth, w, [flags.data_ptr()], False,
+                       seq[w].data_ptr(), None, None)
+        K.mailbox_push([(g1.data_ptr(), base + off1, 16 * 4, stride)], depth, w, [flags.data_ptr()], True,
+                       seq[w].data_ptr(), pcount.data_ptr(), minc.data_ptr())
+        torch.cuda.synchronize()
+
+    def drain():
+        K.mailbox_drain(L.OPT_ADAM, items, 2, stride, depth, W, hyper, ctrl.data_ptr(), ctrl.data_ptr(),
+                        flags.data_ptr(), todo.data_ptr(), counter.data_ptr(), step_out.data_ptr())
+        torch.cuda.synchronize()
+
+    total = 0
+    for rnd, pushers in enumerate([[0, 2], [0, 1, 2], [], [1]]):
+        for w in pushers:
+            g = [torch.randn(n0, device=dev), torch.randn(n1, device=dev)]
+            push(w, g)
+            for t in range(2):
+                ref[0][t], ref[1][t], ref[2][t] = _adam_ref(ref[0][t], ref[1][t], ref[2][t], g[t],
+                                                            lr, b1, b2, eps, b1p, b2p)
+            b1p, b2p = b1p * b1, b2p * b2
+        drain()
+        total += len(pushers)
+        assert int(step_out.item()) == total
+        assert ctrl.view(torch.int64)[0].item() == total
+        for t in range(2):
+            assert torch.allclose(var[t], ref[0][t], rtol=1e-5, atol=1e-6), f"round {rnd} var {t}"
+            assert torch.allclose(m[t], ref[1][t], rtol=1e-5, atol=1e-7)
+            assert torch.allclose(v[t], ref[2][t], rtol=1e-5, atol=1e-7)
+        assert torch.equal(shadow.float().view(-1), var[0].to(torch.bfloat16).float())
+        assert abs(ctrl.view(torch.float32)[2].item() - b1p) < 1e-6
+        produced, consumed = flags[:W].tolist(), flags[32:32 + W].tolist()
+        assert produced == consumed == [int(s.item()) for s in seq]
+    assert [int(s.item()) for s in seq] == [2, 2, 2]
+    # a worker two pushes ahead: the drain retires ONE buffer per call, oldest first
+    ga, gb = [torch.randn(n0, device=dev), torch.randn(n1, device=dev)], \
+             [torch.randn(n0, device=dev), torch.randn(n1, device=dev)]
+    push(1, ga)
+    push(1, gb)
+    assert int(minc.item()) == 2                    # what the owner had consumed when push 4 was published
+    for g in (ga, gb):
+        drain()
+        for t in range(2):
+            ref[0][t], ref[1][t], ref[2][t] = _adam_ref(ref[0][t], ref[1][t], ref[2][t], g[t],
+                                                        lr, b1, b2, eps, b1p, b2p)
+        b1p, b2p = b1p * b1, b2p * b2
+        assert torch.allclose(var[0], ref[0][0], rtol=1e-5, atol=1e-6)
+    assert flags[32 + 1].item() == 4 and ctrl.view(torch.int64)[0].item() == total + 2

@@ -26,8 +26,25 @@ def _torchrun(nproc, script, args, port, timeout=150):
 def test_async_two_gpus_counts_every_apply():
     out = _torchrun(2, "bench.py", ["--gpus", "2", "--steps", "20", "--warmup", "3"], 29611)
     assert out["n_gpus"] == 2 and out["value"] > 0
+    assert out["config"]["push"].startswith("mailbox")     # the default with more than one worker
     # 2 workers x (3 warm-up + 20 timed + 20 back-to-back + 20 e2e) applies, one atomic each
     assert out["final_global_step"] == 2 * (3 + 20 + 20 + 20)
+
+
+def test_async_two_gpus_remote_rmw_push():
+    """The worker-side push (remote read-modify-write over NVLink) stays available and exact."""
+    out = _torchrun(2, "bench.py", ["--gpus", "2", "--steps", "10", "--warmup", "3", "--push-mode", "rmw"], 29631)
+    assert out["config"]["push"].startswith("rmw")
+    assert out["final_global_step"] == 2 * (3 + 10 + 10 + 10)
+
+
+def test_async_mailbox_mode_with_a_ps_only_task():
+    """1 PS task (GPU 0) + 1 worker (GPU 1), push_mode=mailbox: the PS process has no training loop,
+    its apply daemon alone turns the worker's posted gradients into updates."""
+    out = _torchrun(2, "bench/ps_bench.py", ["--model", "mlp", "--topology", "ps1", "--steps", "30", "--warmup", "3",
+                                             "--push-mode", "mailbox"], 29641)
+    assert out["config"]["workers"] == 1 and out["config"]["ps_shards"] == 1 and out.get("push") == "mailbox"
+    assert out["final_step"] == 33 and np.isfinite(out["final_loss"])
 
 
 def test_async_one_ps_shard_plus_worker():
