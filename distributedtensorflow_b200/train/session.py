@@ -349,17 +349,30 @@ class Session:
         return rebuild(results)
 
     def _feed_iterators(self, fetches: Sequence[G.Tensor], feeds: dict) -> None:
-        """One ``get_next`` per run for every iterator the fetches depend on."""
-        seen, stack, iters = set(), list(fetches), {}
-        while stack:
-            t = stack.pop()
-            if id(t) in seen:
-                continue
-            seen.add(id(t))
-            if t.op == "IteratorGetNext" and t not in feeds:
+        """One ``get_next`` per run for every iterator the fetches depend on. The walk over the
+        fetches' ancestors is cached per fetch set (a node's inputs never change), so the hot loop's
+        ``sess.run([train_op, loss, global_step])`` does not re-traverse the graph every step."""
+        key = tuple(id(f) for f in fetches)
+        cache = self.__dict__.setdefault("_iter_cache", {})
+        nodes = cache.get(key)
+        if nodes is None:
+            seen, stack, nodes = set(), list(fetches), []
+            while stack:
+                t = stack.pop()
+                if id(t) in seen:
+                    continue
+                seen.add(id(t))
+                if t.op == "IteratorGetNext":
+                    nodes.append(t)
+                stack.extend(t.inputs)
+            cache[key] = nodes
+        if not nodes:
+            return
+        iters = {}
+        for t in nodes:
+            if t not in feeds:
                 iters.setdefault(id(t.attrs["iterator"]), (t.attrs["iterator"], []))[1].append(t)
-            stack.extend(t.inputs)
-        for it, nodes in iters.values():
+        for it, _ in iters.values():
             elem = it.next_element()
             for out in (it._outputs or ()):
                 feeds[out] = elem[out.attrs["index"]]
