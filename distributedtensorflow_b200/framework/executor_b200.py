@@ -206,6 +206,9 @@ class StepState:
         self.out_pin = torch.zeros(4, dtype=torch.float32).pin_memory()      # loss
         self.step_pin = torch.zeros(4, dtype=torch.int64).pin_memory()       # global_step, pulled, min consumed
         self.step_dev = torch.zeros(4, dtype=torch.int64, device=dev)
+        # numpy views of the pinned buffers: the per-step host path reads / writes them directly
+        self.x_np, self.y_np = self.x_pin.numpy(), self.y_pin.numpy()
+        self.out_np, self.step_np = self.out_pin.numpy(), self.step_pin.numpy()
         self.counter = torch.zeros(4, dtype=torch.int32, device=dev)
         dims = [int(d.w.shape[0]) for d in p.dense] + [p.num_classes]
         self.dims = dims
@@ -911,7 +914,7 @@ class B200StepRunner:
             self.train_op = train_op
 
     def _state(self, B: int, train: bool, x: np.ndarray, y: np.ndarray) -> StepState:
-        key = (B, train, str(x.dtype), str(y.dtype))
+        key = (B, train, x.dtype.char, y.dtype.char)
         s = self.states.get(key)
         if s is None:
             xdt = torch.uint8 if x.dtype == np.uint8 else torch.float32
@@ -923,10 +926,9 @@ class B200StepRunner:
         return s
 
     def _stage(self, s: StepState, x: np.ndarray, y: np.ndarray) -> None:
-        xn = s.x_pin.numpy()
+        xn, yn = s.x_np, s.y_np
         np.copyto(xn, x.reshape(xn.shape), casting="same_kind" if x.dtype != xn.dtype else "no")
-        yn = s.y_pin.numpy()
-        np.copyto(yn, np.asarray(y).reshape(yn.shape), casting="unsafe")
+        np.copyto(yn, y.reshape(yn.shape), casting="unsafe")
 
     def _launch(self, s: StepState) -> None:
         with torch.cuda.stream(self.stream):
@@ -991,8 +993,8 @@ class B200StepRunner:
                     self._enqueue_step(s)
         with nvtx_range("dtf/wait_step"):
             self.stream.synchronize()
-        loss_val = np.float32(s.out_pin[0].item())
-        step_val = int(s.step_pin[0].item()) if top is not None else None
+        loss_val = np.float32(s.out_np[0])
+        step_val = int(s.step_np[0]) if top is not None else None
 
         out: List[Any] = []
         extra: Optional[Dict[int, Any]] = None
