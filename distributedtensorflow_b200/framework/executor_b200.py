@@ -367,7 +367,10 @@ class B200StepRunner:
                 raise NotImplementedError("push_mode='mailbox' supports at most %d workers" % L.MAX_WORKERS)
             # a lone worker keeps the exact in-order apply; with several workers the applies are
             # interleaved anyway and the write-only push is what scales
-            self.use_mailbox = fits and (self.push_mode == "mailbox" or nw > 1)
+            # use_locking=True asks for serialised applies (TF takes the variable's mutex): the owner's
+            # daemon applies one gradient at a time per shard, which is exactly that
+            locked = bool(getattr(spec, "use_locking", False))
+            self.use_mailbox = fits and (self.push_mode == "mailbox" or nw > 1 or locked)
             if self.use_mailbox:
                 sync_workers, depth, mirrors = nw, max(1, self.mailbox_depth), False
         self.store = NvlStore(self.client, self.layout, spec, trainable_names, self.device.index or 0,

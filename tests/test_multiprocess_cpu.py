@@ -121,3 +121,17 @@ def test_ps_clean_shutdown_on_sigint(tmp_path):
     ps.send_signal(signal.SIGINT)
     out = _finish(ps, 20)
     assert ps.returncode == 0 and "Close Parameter Server" in out, out
+
+
+def test_collective_ps_comparator_matches_local_adam_on_gloo():
+    """parallel/nccl_baseline.py (the NCCL/gloo comparator of the PS API): two gloo processes, sync
+    round == Adam on the mean gradient, async-emulated push == W sequential Adam applies."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29877", "-m",
+           "distributedtensorflow_b200.parallel.nccl_baseline"]
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    p = subprocess.run(cmd, cwd=root, capture_output=True, text=True, timeout=240, env=env)
+    assert p.returncode == 0 and "SELFCHECK_OK" in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
