@@ -109,3 +109,13 @@ extern "C" int dtf_host_free_pinned(void* ptr) {
   DTF_CHECK_CUDA(cudaFreeHost(ptr));
   return 0;
 }
+
+// Launch an instantiated CUDA graph (cudaGraphExec_t obtained from the framework that captured it)
+// on an explicit stream: the per-step hot path of the executor, one call, no Python-side stream
+// context juggling.
+extern "C" int dtf_graph_launch(void* graph_exec, void* stream) {
+  DTF_REQUIRE(graph_exec != nullptr, "graph_launch: null graph");
+  DTF_CHECK_CUDA(cudaGraphLaunch(reinterpret_cast<cudaGraphExec_t>(graph_exec),
+                                 reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}

@@ -258,6 +258,7 @@ class StepState:
                 plan["counters"] = self.z["ct_" + key]
         self.zero = zero
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.graph_exec = 0           # raw cudaGraphExec_t of `graph`
         self.launches_per_step = 0
 
 
@@ -309,6 +310,8 @@ class B200StepRunner:
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self.side_stream = torch.cuda.Stream(device=self.device, priority=0)
         self.overlap = bool(opts.get("overlap", True))
+        self._stream_handle = self.stream.cuda_stream
+        self._graph_launch = L.lib().dtf_graph_launch
 
     def _pick_device(self) -> str:
         if getattr(self.config, "device", None):
@@ -934,8 +937,13 @@ class B200StepRunner:
         np.copyto(yn, y.reshape(yn.shape), casting="unsafe")
 
     def _launch(self, s: StepState) -> None:
+        sync = self.sync_opt is not None and s.train
+        if s.graph_exec and not sync:
+            # hot path: one cudaGraphLaunch on our stream, no Python stream-context bookkeeping
+            if self._graph_launch(s.graph_exec, self._stream_handle) != 0:
+                L.check(-1, "dtf_graph_launch")
+            return
         with torch.cuda.stream(self.stream):
-            sync = self.sync_opt is not None and s.train
             if not self.use_cuda_graph:
                 self._enqueue_step(s)
                 if sync:
@@ -953,6 +961,10 @@ class B200StepRunner:
                 with torch.cuda.graph(g, stream=self.stream, capture_error_mode="thread_local"):
                     self._enqueue_step(s)
                 s.graph = g
+                try:
+                    s.graph_exec = int(g.raw_cuda_graph_exec())
+                except Exception:
+                    s.graph_exec = 0          # older torch: fall back to CUDAGraph.replay()
                 if sync:
                     self._enqueue_sync_tail(s)
                 return  # the eager step already did this run's work
@@ -1075,7 +1087,9 @@ class B200StepRunner:
             for _ in range(n):
                 if self.use_mailbox:
                     self._mbox_admit()
-                if s.graph is not None:
+                if s.graph_exec:
+                    L.check(self._graph_launch(s.graph_exec, self._stream_handle), "dtf_graph_launch")
+                elif s.graph is not None:
                     s.graph.replay()
                 else:
                     self._enqueue_step(s)

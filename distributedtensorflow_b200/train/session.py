@@ -88,8 +88,20 @@ def no_op(name=None) -> NoOp:
 # ------------------------------------------------------------------------------------------------
 # Session
 # ------------------------------------------------------------------------------------------------
+def _as_list(vals):
+    return vals if type(vals) is list else list(vals)
+
+
 def _flatten(fetches) -> Tuple[List[Any], Callable[[List[Any]], Any]]:
     """Flattens nested lists / tuples / dicts of fetches; returns (flat, rebuild)."""
+    tf_ = type(fetches)
+    if tf_ is list or tf_ is tuple:
+        # the hot loop's shape, sess.run([train_op, loss, global_step]): no nesting, no recursion
+        for f in fetches:
+            if isinstance(f, (list, tuple, dict)):
+                break
+        else:
+            return list(fetches), (_as_list if tf_ is list else tuple)
     if isinstance(fetches, dict):
         keys = list(fetches.keys())
         parts = [_flatten(fetches[k]) for k in keys]

@@ -212,6 +212,9 @@ int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_items, long lo
                       unsigned int* todo, unsigned int* block_counter,
                       unsigned long long* step_out, void* stream);
 
+/* cudaGraphLaunch of an instantiated graph on an explicit stream (the executor's per-step call). */
+int dtf_graph_launch(void* graph_exec, void* stream);
+
 /* The shard owner's apply daemon: one native host thread per shard that polls the mailbox flags
  * (D2H copy, no SM use while idle) and launches dtf_mailbox_drain on its own low-priority stream
  * whenever a worker has published a gradient — the B200 stand-in for the PS task's CPU executing
