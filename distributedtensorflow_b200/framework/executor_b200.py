@@ -283,6 +283,9 @@ class B200StepRunner:
         # is slower than GEMM + the coalesced apply kernel (180 vs 158 us/step), so it is opt-in.
         self.fused_apply = bool(opts.get("fused_apply", False))
         self.clear_at_end = bool(opts.get("clear_at_end", True))
+        # logits GEMM + softmax-xent + dX GEMM of the last layer + bias column-sum as ONE kernel
+        # (csrc/kernels/head_fused.cu) when the head has <= 16 classes
+        self.fused_head = bool(opts.get("fused_head", True))
         # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
         # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
         # daemon (csrc/kernels/mailbox.cu, csrc/runtime/mbox_daemon.cu); "auto" = mailbox whenever
@@ -605,12 +608,22 @@ class B200StepRunner:
             else:
                 K.f32_to_bf16(s.x_dev, s.act[0])
         nl = len(p.dense)
+        fused_head = self._head_is_fused()
         for i, d in enumerate(p.dense):
+            if fused_head and i == nl - 1:
+                break                      # the logits layer is part of the fused head kernel (_loss)
             wp, ld = self.wptr[d.w.name]
             out = s.act[i + 1] if i + 1 < nl else s.logits
             bias = _PtrTensor(self.fptr[d.b.name]) if d.b is not None else None
             K.gemm(s.act[i], None, out, s.B, s.dims[i + 1], s.dims[i], b_mn=True, bias=bias,
                    relu=d.relu, b_ptr=wp, ldb=ld, **self._plan_kw(s, f"fwd{i}"))
+
+    def _head_is_fused(self) -> bool:
+        p = self.plan
+        nl = len(p.dense)
+        if not self.fused_head or nl < 2 or p.num_classes > 16:
+            return False
+        return self.wptr[p.dense[-1].w.name][1] == 16
 
     def _plan_kw(self, s: StepState, key: str) -> dict:
         plan = s.gemm_plans.get(key)
@@ -623,6 +636,18 @@ class B200StepRunner:
 
     def _loss(self, s: StepState) -> None:
         p = self.plan
+        nl = len(p.dense)
+        if self._head_is_fused():
+            d = p.dense[-1]
+            wp, ld = self.wptr[d.w.name]
+            K.head_fused(s.act[nl - 1], s.dims[nl - 1], wp, ld,
+                         self.fptr[d.b.name] if d.b is not None else None, s.y_dev, s.B, p.num_classes,
+                         s.logits, s.z["loss"],
+                         dlogits=s.dlogits if s.train else None,
+                         dbias_accum=s.z[f"gb{nl - 1}"] if s.train else None,
+                         dact=s.dact[nl - 1] if s.train else None,
+                         dprev_bias_accum=s.z[f"gb{nl - 2}"] if (s.train and p.dense[nl - 2].b is not None) else None)
+            return
         dl = s.dlogits if s.train else self._scratch_dlogits(s)
         gb = s.z[f"gb{len(p.dense) - 1}"] if s.train else None
         if p.loss_kind == "sparse_mean":
@@ -656,6 +681,7 @@ class B200StepRunner:
                 side.wait_event(ev)
 
         dz = s.dlogits
+        head_fused = self._head_is_fused()
         fork()                                   # dlogits (and every activation) is ready
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
@@ -668,7 +694,9 @@ class B200StepRunner:
                     # dW_i = act_i^T dZ_i
                     K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
             wp, ld = self.wptr[d.w.name]
-            if i > 0:
+            if i > 0 and i == nl - 1 and head_fused:
+                dz = s.dact[i]                   # dZ_{i-1} and db_{i-1} came out of the fused head kernel
+            elif i > 0:
                 # dZ_{i-1} = (dZ_i W_i^T) * relu'(act_i);  db_{i-1} = colsum
                 K.gemm(dz, None, s.dact[i], s.B, din, dout, mask=s.act[i], b_ptr=wp, ldb=ld,
                        **self._plan_kw(s, f"dx{i}"))

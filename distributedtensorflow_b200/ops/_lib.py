@@ -188,6 +188,7 @@ def _declare(lib):
         "dtf_mbox_daemon_stats": [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)],
         "dtf_mbox_daemon_stop": [vp],
         "dtf_graph_launch": [vp, vp],
+        "dtf_head_fused": [vp, i, i, vp, i, vp, vp, vp, i, i, i, vp, i, vp, vp, i, vp, vp, i, vp, vp],
         "dtf_host_alloc_pinned": [C.POINTER(vp), C.c_size_t],
         "dtf_host_free_pinned": [vp],
     }

@@ -245,6 +245,24 @@ def f32_to_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
     _count()
 
 
+def head_fused(act: torch.Tensor, H: int, w_ptr: int, ldw: int, bias_ptr: Optional[int],
+               labels: torch.Tensor, B: int, num_classes: int, logits: torch.Tensor, loss_accum: torch.Tensor,
+               dlogits: Optional[torch.Tensor] = None, dbias_accum: Optional[torch.Tensor] = None,
+               dact: Optional[torch.Tensor] = None, dprev_bias_accum: Optional[torch.Tensor] = None) -> None:
+    """Classifier head in one launch (csrc/kernels/head_fused.cu): logits + loss (+ dlogits, bias
+    gradients and the previous layer's masked activation gradient when training)."""
+    sparse = labels.dtype == torch.int32
+    rc = L.lib().dtf_head_fused(act.data_ptr(), act.stride(0), H, w_ptr, ldw, bias_ptr,
+                                labels.data_ptr() if sparse else None,
+                                None if sparse else labels.data_ptr(), 0 if sparse else labels.stride(0),
+                                B, num_classes, logits.data_ptr(), logits.stride(0), loss_accum.data_ptr(),
+                                _ptr(dlogits), dlogits.stride(0) if dlogits is not None else 0,
+                                _ptr(dbias_accum), _ptr(dact), dact.stride(0) if dact is not None else 0,
+                                _ptr(dprev_bias_accum), L.current_stream())
+    L.check(rc, "dtf_head_fused")
+    _count()
+
+
 def colsum_bf16(x: torch.Tensor, rows: int, cols: int, out_accum: torch.Tensor) -> None:
     rc = L.lib().dtf_colsum_bf16(x.data_ptr(), x.stride(0), rows, cols, out_accum.data_ptr(),
                                  L.current_stream())

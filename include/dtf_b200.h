@@ -102,6 +102,17 @@ int dtf_softmax_xent_dense(const float* logits, int ldl, const float* labels, in
                            int C, float* loss_accum, void* dlogits, int ldd, float* dbias_accum,
                            void* stream);
 
+/* Fused classifier head for <= 16 classes (both reference models end in a 10-way layer,
+ * run_mnist_distributed.py:69, templates/00_mnist_replica.py:163): logits = act W + b, the
+ * softmax cross-entropy (sparse/mean or dense/clipped/sum), dlogits, the logits-bias gradient, and
+ * — when dact is given — the previous layer's activation gradient (dlogits W^T masked by act > 0)
+ * plus its bias gradient, in ONE launch instead of GEMM + xent + GEMM + column-sum. w_shadow is
+ * the [H, 16] bf16 serving copy. Pass dlogits = NULL for inference (logits + loss only). */
+int dtf_head_fused(const void* act, int lda, int H, const void* w_shadow, int ldw, const float* bias,
+                   const int* labels_sparse, const float* labels_dense, int ldy, int B, int C,
+                   float* logits, int ldl, float* loss_accum, void* dlogits, int ldd,
+                   float* dbias_accum, void* dact, int lddact, float* dprev_bias_accum, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * K9/K10: gradient push fused with the owning shard's optimizer apply. One launch walks a list
  * of (variable slice, gradient) pairs; var/slots/shadow may be peer (NVLink) pointers. The last

@@ -640,3 +640,54 @@ def test_mailbox_push_and_drain_apply_pending_gradients_in_worker_order(K):
         b1p, b2p = b1p * b1, b2p * b2
         assert torch.allclose(var[0], ref[0][0], rtol=1e-5, atol=1e-6)
     assert flags[32 + 1].item() == 4 and ctrl.view(torch.int64)[0].item() == total + 2
+
+
+@pytest.mark.parametrize("B,H,dense", [(128, 1024, False), (100, 100, True), (37, 300, False)])
+def test_head_fused_matches_separate_ops(K, B, H, dense):
+    """logits + softmax-xent + dlogits + bias grads + masked dX of the last layer in one kernel,
+    against a plain PyTorch fp32 computation on the same bf16-rounded operands."""
+    torch.manual_seed(B + H)
+    C, dev = 10, "cuda"
+    ldh = (H + 7) // 8 * 8
+    act = torch.zeros(B, ldh, dtype=torch.bfloat16, device=dev)
+    act[:, :H] = torch.relu(torch.randn(B, H, device=dev)).to(torch.bfloat16)
+    W = torch.zeros(H, 16, dtype=torch.bfloat16, device=dev)
+    W[:, :C] = (torch.randn(H, C, device=dev) * 0.1).to(torch.bfloat16)
+    bias = torch.randn(C, device=dev) * 0.1
+    if dense:
+        lab = torch.randint(0, C, (B,), device=dev)
+        labels = torch.nn.functional.one_hot(lab, C).float()
+    else:
+        labels = torch.randint(0, C, (B,), device=dev, dtype=torch.int32)
+    logits = torch.zeros(B, C, device=dev)
+    loss = torch.zeros(1, device=dev)
+    dlogits = torch.zeros(B, 16, dtype=torch.bfloat16, device=dev)
+    db = torch.zeros(C, device=dev)
+    dact = torch.zeros(B, ldh, dtype=torch.bfloat16, device=dev)
+    dbp = torch.zeros(H, device=dev)
+    K.head_fused(act, H, W.data_ptr(), 16, bias.data_ptr(), labels, B, C, logits, loss,
+                 dlogits=dlogits, dbias_accum=db, dact=dact, dprev_bias_accum=dbp)
+    torch.cuda.synchronize()
+    a32, w32 = act[:, :H].float(), W[:, :C].float()
+    z = (a32 @ w32 + bias).requires_grad_(True)
+    if dense:
+        p = torch.softmax(z, 1)
+        ref_loss = -(labels * torch.log(torch.clamp(p, 1e-10, 1.0))).sum()
+    else:
+        ref_loss = torch.nn.functional.cross_entropy(z, labels.long())
+    ref_loss.backward()
+    g = z.grad
+    assert torch.allclose(logits, z.detach(), rtol=1e-4, atol=1e-4)
+    assert abs(loss.item() - ref_loss.item()) < 1e-3 * max(1.0, abs(ref_loss.item()))
+    assert torch.allclose(dlogits[:, :C].float(), g, rtol=2e-2, atol=1e-6 + 4e-3 * g.abs().max().item())
+    assert (dlogits[:, C:] == 0).all()
+    assert torch.allclose(db, g.sum(0), rtol=1e-3, atol=1e-5 + 1e-3 * g.abs().max().item())
+    ref_dact = (dlogits[:, :C].float() @ w32.t()) * (a32 > 0)
+    assert _rel_err(dact[:, :H].float(), ref_dact) < 1e-2
+    assert (dact[:, H:] == 0).all()
+    assert torch.allclose(dbp, dact[:, :H].float().sum(0), rtol=1e-3, atol=1e-5 + 1e-3 * ref_dact.abs().max().item())
+    # inference form: logits + loss only
+    logits2, loss2 = torch.zeros_like(logits), torch.zeros(1, device=dev)
+    K.head_fused(act, H, W.data_ptr(), 16, bias.data_ptr(), labels, B, C, logits2, loss2)
+    torch.cuda.synchronize()
+    assert torch.equal(logits2, logits) and abs(loss2.item() - loss.item()) < 1e-5 * max(1.0, abs(loss.item()))
