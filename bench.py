@@ -273,8 +273,8 @@ def main() -> int:
         if world > 1:
             dist.all_reduce(times, op=dist.ReduceOp.MAX)
         dev_ms, b2b_ms, e2e_ms = [float(t) for t in times.tolist()]
-        h2d = BATCH * 784 * 1 + BATCH * 4
-        d2h = 4 + 16
+        h2d = int(state.io_pin.numel())      # images + labels, one pinned staging buffer, one copy
+        d2h = int(state.res_pin.numel() * 4) if runner.host_sink else 4 + 32   # loss + seq + global_step
         value = N * args.steps / (dev_ms / 1e3)
         result = {
             "metric": "global_steps_per_sec", "value": round(value, 2), "unit": "global steps/s",

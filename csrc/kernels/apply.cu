@@ -33,6 +33,7 @@ struct ApplyArgs {
   int worker_id;
   unsigned long long* step_out;
   unsigned int* block_counter;
+  dtf_result_sink sink;
 };
 
 template <int OPT>
@@ -170,6 +171,16 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
       *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[a.worker_id]) =
           old + 1ull;
     atomicAdd(&a.ctrl_step->apply_count, 1u);
+    if (a.sink.host_dst != nullptr) {
+      // report the step straight into pinned host memory (no D2H copy node behind the step)
+      volatile unsigned int* h = a.sink.host_dst;
+      h[0] = __float_as_uint(*reinterpret_cast<const volatile float*>(a.sink.loss_src));
+      *reinterpret_cast<volatile unsigned long long*>(a.sink.host_dst + 2) = old + 1ull;
+      __threadfence_system();
+      const unsigned int q = *a.sink.seq_dev + 1u;
+      *a.sink.seq_dev = q;
+      h[1] = q;
+    }
     __threadfence_system();
   }
 }
@@ -193,6 +204,15 @@ extern "C" int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
                               dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                               unsigned long long* step_out, unsigned int* block_counter,
                               void* stream_) {
+  return dtf_push_apply_ex(opt, items, n_items, hyper, ctrl_for_powers, ctrl_for_step, finish,
+                           worker_id, step_out, block_counter, nullptr, stream_);
+}
+
+extern "C" int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_items,
+                                 const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
+                                 dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
+                                 unsigned long long* step_out, unsigned int* block_counter,
+                                 const dtf_result_sink* sink, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "push_apply: %d items (max %d)",
               n_items, DTF_MAX_APPLY_ITEMS);
@@ -230,6 +250,10 @@ extern "C" int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
   a.worker_id = worker_id;
   a.step_out = step_out;
   a.block_counter = block_counter;
+  if (sink != nullptr && finish) {
+    DTF_REQUIRE(sink->loss_src && sink->host_dst && sink->seq_dev, "push_apply: incomplete result sink");
+    a.sink = *sink;
+  }
   switch (opt) {
     case DTF_OPT_SGD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_SGD>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
     case DTF_OPT_MOMENTUM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_MOMENTUM>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;

@@ -19,6 +19,7 @@ namespace dtf {
 
 constexpr int HEAD_ROWS = 4;
 constexpr int HEAD_THREADS = 256;
+constexpr int HEAD_HPT = 4;     // hidden units per thread per chunk
 constexpr int HEAD_C = 16;  // classes are padded to 16 (the serving copy's row pitch)
 
 struct HeadParams {
@@ -59,32 +60,58 @@ head_fused_kernel(const __grid_constant__ HeadParams p) {
   griddep_launch();
 
   // ---- phase 1: partial logits of HEAD_ROWS rows over this thread's hidden units ----
-  float acc[HEAD_ROWS][HEAD_C];
+  // Chunks of HEAD_THREADS * HEAD_HPT hidden units; every load of a chunk is issued before the first
+  // FMA, so a chunk costs one L2 round trip instead of HEAD_HPT dependent ones.
+  float acc[HEAD_ROWS * HEAD_C];
 #pragma unroll
-  for (int r = 0; r < HEAD_ROWS; ++r)
+  for (int i = 0; i < HEAD_ROWS * HEAD_C; ++i) acc[i] = 0.f;
+  for (int h0 = 0; h0 < p.H; h0 += HEAD_THREADS * HEAD_HPT) {
+    uint4 wa[HEAD_HPT], wb[HEAD_HPT];
+    __nv_bfloat16 av[HEAD_HPT][HEAD_ROWS];
 #pragma unroll
-    for (int c = 0; c < HEAD_C; ++c) acc[r][c] = 0.f;
-  for (int h = threadIdx.x; h < p.H; h += HEAD_THREADS) {
-    const uint4* wr = reinterpret_cast<const uint4*>(p.w + static_cast<size_t>(h) * p.ldw);
-    float w[HEAD_C];
-    unpack16(wr[0], wr[1], w);
+    for (int j = 0; j < HEAD_HPT; ++j) {
+      const int h = h0 + j * HEAD_THREADS + threadIdx.x;
+      wa[j] = wb[j] = make_uint4(0, 0, 0, 0);
+      if (h < p.H) {
+        const uint4* wr = reinterpret_cast<const uint4*>(p.w + static_cast<size_t>(h) * p.ldw);
+        wa[j] = wr[0];
+        wb[j] = wr[1];
+      }
 #pragma unroll
-    for (int r = 0; r < HEAD_ROWS; ++r) {
-      const int row = row0 + r;
-      const float a = (row < p.B) ? __bfloat162float(p.act[static_cast<size_t>(row) * p.lda + h]) : 0.f;
+      for (int r = 0; r < HEAD_ROWS; ++r)
+        av[j][r] = (h < p.H && row0 + r < p.B) ? p.act[static_cast<size_t>(row0 + r) * p.lda + h]
+                                                : __float2bfloat16(0.f);
+    }
 #pragma unroll
-      for (int c = 0; c < HEAD_C; ++c) acc[r][c] = fmaf(a, w[c], acc[r][c]);
+    for (int j = 0; j < HEAD_HPT; ++j) {
+      float w[HEAD_C];
+      unpack16(wa[j], wb[j], w);
+#pragma unroll
+      for (int r = 0; r < HEAD_ROWS; ++r) {
+        const float a = __bfloat162float(av[j][r]);
+#pragma unroll
+        for (int c = 0; c < HEAD_C; ++c) acc[r * HEAD_C + c] = fmaf(a, w[c], acc[r * HEAD_C + c]);
+      }
     }
   }
+  // warp reduction by recursive halving: 62 shuffles for the 64 sums instead of 320; lane L ends
+  // up with the warp totals of entries 2L and 2L + 1
+  {
 #pragma unroll
-  for (int r = 0; r < HEAD_ROWS; ++r)
+    for (int o = 16, n = HEAD_ROWS * HEAD_C; o >= 1; o >>= 1, n >>= 1) {
+      const bool upper = (lane & o) != 0;
 #pragma unroll
-    for (int c = 0; c < HEAD_C; ++c) {
-      float v = acc[r][c];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) s_part[warp][r * HEAD_C + c] = v;
+      for (int i = 0; i < HEAD_ROWS * HEAD_C / 2; ++i) {
+        if (i < n / 2) {
+          const float send = upper ? acc[i] : acc[i + n / 2];
+          const float keep = upper ? acc[i + n / 2] : acc[i];
+          acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+      }
     }
+    s_part[warp][2 * lane] = acc[0];
+    s_part[warp][2 * lane + 1] = acc[1];
+  }
   __syncthreads();
   if (threadIdx.x < HEAD_ROWS * HEAD_C) {
     float t = 0.f;
@@ -158,24 +185,42 @@ head_fused_kernel(const __grid_constant__ HeadParams p) {
   for (int r = 0; r < HEAD_ROWS; ++r)
 #pragma unroll
     for (int c = 0; c < HEAD_C; ++c) dl[r][c] = s_dl[r][c];
-  for (int h = threadIdx.x; h < p.H; h += HEAD_THREADS) {
-    const uint4* wr = reinterpret_cast<const uint4*>(p.w + static_cast<size_t>(h) * p.ldw);
-    float w[HEAD_C];
-    unpack16(wr[0], wr[1], w);
-    float colsum = 0.f;
+  for (int h0 = 0; h0 < p.H; h0 += HEAD_THREADS * HEAD_HPT) {
+    uint4 wa[HEAD_HPT], wb[HEAD_HPT];
+    __nv_bfloat16 av[HEAD_HPT][HEAD_ROWS];
 #pragma unroll
-    for (int r = 0; r < HEAD_ROWS; ++r) {
-      const int row = row0 + r;
-      if (row >= p.B) continue;
-      float d = 0.f;
+    for (int j = 0; j < HEAD_HPT; ++j) {     // L1 / L2 hits: phase 1 just read the same lines
+      const int h = h0 + j * HEAD_THREADS + threadIdx.x;
+      wa[j] = wb[j] = make_uint4(0, 0, 0, 0);
+      if (h < p.H) {
+        const uint4* wr = reinterpret_cast<const uint4*>(p.w + static_cast<size_t>(h) * p.ldw);
+        wa[j] = wr[0];
+        wb[j] = wr[1];
+      }
 #pragma unroll
-      for (int c = 0; c < HEAD_C; ++c) d = fmaf(dl[r][c], w[c], d);
-      const float a = __bfloat162float(p.act[static_cast<size_t>(row) * p.lda + h]);
-      const __nv_bfloat16 o = __float2bfloat16(a > 0.f ? d : 0.f);
-      p.dact[static_cast<size_t>(row) * p.lddact + h] = o;
-      colsum += __bfloat162float(o);
+      for (int r = 0; r < HEAD_ROWS; ++r)
+        av[j][r] = (h < p.H && row0 + r < p.B) ? p.act[static_cast<size_t>(row0 + r) * p.lda + h]
+                                                : __float2bfloat16(0.f);
     }
-    if (p.dprev_bias_accum != nullptr) atomicAdd(&p.dprev_bias_accum[h], colsum);
+#pragma unroll
+    for (int j = 0; j < HEAD_HPT; ++j) {
+      const int h = h0 + j * HEAD_THREADS + threadIdx.x;
+      if (h >= p.H) continue;
+      float w[HEAD_C];
+      unpack16(wa[j], wb[j], w);
+      float colsum = 0.f;
+#pragma unroll
+      for (int r = 0; r < HEAD_ROWS; ++r) {
+        if (row0 + r >= p.B) continue;
+        float d = 0.f;
+#pragma unroll
+        for (int c = 0; c < HEAD_C; ++c) d = fmaf(dl[r][c], w[c], d);
+        const __nv_bfloat16 o = __float2bfloat16(__bfloat162float(av[j][r]) > 0.f ? d : 0.f);
+        p.dact[static_cast<size_t>(row0 + r) * p.lddact + h] = o;
+        colsum += __bfloat162float(o);
+      }
+      if (p.dprev_bias_accum != nullptr) atomicAdd(&p.dprev_bias_accum[h], colsum);
+    }
   }
 }
 

@@ -42,6 +42,7 @@ struct MboxPushArgs {
   unsigned int* min_consumed_out;
   const dtf_ps_ctrl* ctrl_step;
   unsigned long long* step_out;
+  dtf_result_sink sink;
 };
 
 __global__ void __launch_bounds__(MBOX_THREADS)
@@ -100,8 +101,19 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
     *reinterpret_cast<volatile unsigned int*>(a.seq) = seq + 1u;
     if (a.min_consumed_out != nullptr) *a.min_consumed_out = s_min;
     // what sess.run([train_op, global_step]) reports: the shared counter as this step ends
-    if (a.step_out != nullptr && a.ctrl_step != nullptr)
-      *a.step_out = ld_acquire_sys_u64(&a.ctrl_step->global_step);
+    unsigned long long gs = 0;
+    if (a.ctrl_step != nullptr) gs = ld_acquire_sys_u64(&a.ctrl_step->global_step);
+    if (a.step_out != nullptr && a.ctrl_step != nullptr) *a.step_out = gs;
+    if (a.sink.host_dst != nullptr) {
+      volatile unsigned int* h = a.sink.host_dst;
+      h[0] = __float_as_uint(*reinterpret_cast<const volatile float*>(a.sink.loss_src));
+      *reinterpret_cast<volatile unsigned long long*>(a.sink.host_dst + 2) = gs;
+      __threadfence_system();
+      const unsigned int q = *a.sink.seq_dev + 1u;
+      *a.sink.seq_dev = q;
+      h[1] = q;
+      __threadfence_system();
+    }
   }
 }
 
@@ -315,7 +327,8 @@ extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, in
                                 int worker_id, dtf_mbox_flags* const* owner_flags, int n_owners,
                                 int publish, unsigned int* seq, unsigned int* block_counter,
                                 unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
-                                unsigned long long* step_out, void* stream) {
+                                unsigned long long* step_out, const dtf_result_sink* sink,
+                                void* stream) {
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_MBOX_ITEMS, "mailbox_push: %d items (max %d)",
               n_items, DTF_MAX_MBOX_ITEMS);
   DTF_REQUIRE(depth >= 1 && seq != nullptr, "mailbox_push: depth %d / seq", depth);
@@ -358,6 +371,10 @@ extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, in
   a.min_consumed_out = min_consumed_out;
   a.ctrl_step = ctrl_step;
   a.step_out = step_out;
+  if (sink != nullptr && publish) {
+    DTF_REQUIRE(sink->loss_src && sink->host_dst && sink->seq_dev, "mailbox_push: incomplete result sink");
+    a.sink = *sink;
+  }
   DTF_CHECK_CUDA(launch_kernel(mailbox_push_kernel, dim3(blocks), dim3(MBOX_THREADS), 0,
                                reinterpret_cast<cudaStream_t>(stream), a));
   return 0;

@@ -5,6 +5,8 @@
 // inside kernels over NVLink 5 / NVSwitch. Same-process shards (one process driving several
 // GPUs, or PS and worker colocated on one GPU) use the pointer directly after
 // cudaDeviceEnablePeerAccess.
+#include <chrono>
+
 #include "../kernels/common.cuh"
 #include "../../include/dtf_b200.h"
 
@@ -118,4 +120,23 @@ extern "C" int dtf_graph_launch(void* graph_exec, void* stream) {
   DTF_CHECK_CUDA(cudaGraphLaunch(reinterpret_cast<cudaGraphExec_t>(graph_exec),
                                  reinterpret_cast<cudaStream_t>(stream)));
   return 0;
+}
+
+// Spin (on the calling host thread, GIL released by ctypes) until a word of pinned host memory
+// that a kernel writes equals `expected`. Returns 0 when it does, 1 on timeout.
+extern "C" int dtf_host_wait_u32(const unsigned int* word, unsigned int expected, long long timeout_us) {
+  const volatile unsigned int* p = word;
+  if (*p == expected) return 0;
+  const auto t0 = std::chrono::steady_clock::now();
+  for (unsigned long long spins = 0;; ++spins) {
+    if (*p == expected) return 0;
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+    if ((spins & 0xfff) == 0xfff) {
+      const auto dt = std::chrono::duration_cast<std::chrono::microseconds>(
+                          std::chrono::steady_clock::now() - t0).count();
+      if (dt > timeout_us) return 1;
+    }
+  }
 }

@@ -198,17 +198,31 @@ class StepState:
         self.gemm_plans: Dict[str, dict] = {}
         p, dev = runner.plan, runner.device
         bf, f32 = torch.bfloat16, torch.float32
-        self.x_pin = torch.zeros((B, p.in_features), dtype=x_dtype).pin_memory()
         ysh = (B,) if p.loss_kind == "sparse_mean" else (B, p.num_classes)
-        self.y_pin = torch.zeros(ysh, dtype=y_dtype).pin_memory()
-        self.x_dev = torch.zeros((B, p.in_features), dtype=x_dtype, device=dev)
-        self.y_dev = torch.zeros(ysh, dtype=y_dtype, device=dev)
+        # inputs and labels share ONE pinned staging buffer and ONE device buffer: a step's H2D is a
+        # single copy node (two nodes cost an extra ~4 us of graph dependency latency)
+        xb = B * p.in_features * torch.empty((), dtype=x_dtype).element_size()
+        yb = int(np.prod(ysh)) * torch.empty((), dtype=y_dtype).element_size()
+        yoff = (xb + 255) // 256 * 256
+        self.io_pin = torch.zeros(yoff + (yb + 255) // 256 * 256, dtype=torch.uint8).pin_memory()
+        self.io_dev = torch.zeros(self.io_pin.numel(), dtype=torch.uint8, device=dev)
+        self.x_pin = self.io_pin[:xb].view(x_dtype).view(B, p.in_features)
+        self.y_pin = self.io_pin[yoff:yoff + yb].view(y_dtype).view(ysh)
+        self.x_dev = self.io_dev[:xb].view(x_dtype).view(B, p.in_features)
+        self.y_dev = self.io_dev[yoff:yoff + yb].view(y_dtype).view(ysh)
         self.out_pin = torch.zeros(4, dtype=torch.float32).pin_memory()      # loss
         self.step_pin = torch.zeros(4, dtype=torch.int64).pin_memory()       # global_step, pulled, min consumed
         self.step_dev = torch.zeros(4, dtype=torch.int64, device=dev)
         # numpy views of the pinned buffers: the per-step host path reads / writes them directly
         self.x_np, self.y_np = self.x_pin.numpy(), self.y_pin.numpy()
         self.out_np, self.step_np = self.out_pin.numpy(), self.step_pin.numpy()
+        # result sink: the step's last kernel stores {loss, seq, global_step} here (pinned, mapped)
+        self.res_pin = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self.res_u32 = self.res_pin.numpy().view(np.uint32)
+        self.res_f32 = self.res_pin.numpy().view(np.float32)
+        self.res_u64 = self.res_pin.numpy().view(np.uint64)
+        self.res_seq_dev = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.res_expected = 0
         self.counter = torch.zeros(4, dtype=torch.int32, device=dev)
         dims = [int(d.w.shape[0]) for d in p.dense] + [p.num_classes]
         self.dims = dims
@@ -286,6 +300,9 @@ class B200StepRunner:
         # logits GEMM + softmax-xent + dX GEMM of the last layer + bias column-sum as ONE kernel
         # (csrc/kernels/head_fused.cu) when the head has <= 16 classes
         self.fused_head = bool(opts.get("fused_head", True))
+        # the step's last kernel writes loss / global_step into pinned host memory and the host
+        # spins on a sequence word: no D2H copy nodes, no stream synchronise per step
+        self.host_sink = bool(opts.get("host_sink", True))
         # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
         # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
         # daemon (csrc/kernels/mailbox.cu, csrc/runtime/mbox_daemon.cu); "auto" = mailbox whenever
@@ -312,6 +329,7 @@ class B200StepRunner:
         # that carries weight-gradient GEMMs and the bandwidth-heavy applies
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self.side_stream = torch.cuda.Stream(device=self.device, priority=0)
+        self.apply_stream = torch.cuda.Stream(device=self.device, priority=0)
         self.overlap = bool(opts.get("overlap", True))
         self._stream_handle = self.stream.cuda_stream
         self._graph_launch = L.lib().dtf_graph_launch
@@ -661,38 +679,49 @@ class B200StepRunner:
         return s._dl
 
     def _backward(self, s: StepState) -> None:
-        """Backward pass on two streams. The activation-gradient chain (dX GEMMs, pooling / conv
-        gradients) is the critical path and stays on the main stream; the weight-gradient GEMMs and
-        the push+apply of each dense kernel depend only on already-available tensors, so they run
-        on a side stream and overlap it — the big apply (12.8 MB of Adam state for dense/kernel)
-        hides behind the convolution backward instead of trailing the step. Both streams are part
-        of the same captured CUDA graph (fork / join through events)."""
+        """Backward pass on three streams inside the captured graph (fork / join through events):
+
+        * main   — the activation-gradient chain (dX GEMMs, pooling / conv gradients): the critical
+                   path, highest priority;
+        * side   — weight-gradient GEMMs and conv2's filter gradient: they depend only on tensors
+                   that already exist, so they run beside the chain;
+        * apply  — the push(+apply) of each dense kernel as soon as its gradient exists (and the
+                   dX GEMM that reads the same weights has been ordered before it). The big one
+                   (12.8 MB of Adam state for dense/kernel) hides behind the convolution backward
+                   instead of trailing the step, and never delays a weight-gradient GEMM."""
         p = self.plan
         nl = len(p.dense)
         main = torch.cuda.current_stream()
         sync = self.sync_opt is not None
-        side = self.side_stream if (self.overlap and not sync) else main
+        par = self.overlap and not sync
+        side = self.side_stream if par else main
+        apl = self.apply_stream if par else main
         applied: List[G.Variable] = []
 
-        def fork():
-            if side is not main:
-                ev = torch.cuda.Event()
-                ev.record(main)
-                side.wait_event(ev)
+        def after(stream):
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            return ev
+
+        def fork(dst, ev=None):
+            if dst is not main:
+                dst.wait_event(ev if ev is not None else after(main))
 
         dz = s.dlogits
         head_fused = self._head_is_fused()
-        fork()                                   # dlogits (and every activation) is ready
+        fork(side)                               # dlogits (and every activation) is ready
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
-            fused = self._fused_apply_spec(d.w) if (self.overlap and not sync and self.fused_apply
-                                                    and not self.use_mailbox) else None
+            fused = self._fused_apply_spec(d.w) if (par and self.fused_apply and not self.use_mailbox) else None
             dz_i = dz
+            dw_done = None
             if fused is None:
                 with torch.cuda.stream(side):
                     # dW_i = act_i^T dZ_i
                     K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
+                    if par:
+                        dw_done = after(side)
             wp, ld = self.wptr[d.w.name]
             if i > 0 and i == nl - 1 and head_fused:
                 dz = s.dact[i]                   # dZ_{i-1} and db_{i-1} came out of the fused head kernel
@@ -702,14 +731,16 @@ class B200StepRunner:
                        **self._plan_kw(s, f"dx{i}"))
                 K.colsum_bf16(s.dact[i], s.B, din, s.z[f"gb{i - 1}"])
                 dz = s.dact[i]
-                fork()                           # dZ_{i-1} is ready; W_i is no longer being read
+                fork(side)                       # dZ_{i-1} is ready
             elif p.kind == "cnn":
                 K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld, **self._plan_kw(s, "dx0"))
-                fork()
-            if self.overlap and not sync:
-                # push+apply of W_i as soon as its gradient exists and the dX GEMM above (which
-                # reads W_i, possibly in place in the local shard) has been ordered before it
-                with torch.cuda.stream(side):
+            if par:
+                # W_i may be read in place from the local shard by the dX GEMM above: order the
+                # apply after it, and after the gradient it consumes
+                fork(apl)
+                if dw_done is not None:
+                    apl.wait_event(dw_done)
+                with torch.cuda.stream(apl):
                     if fused is not None:
                         # dW_i GEMM whose epilogue IS the push+apply: the gradient never exists in
                         # memory, the TMEM accumulator goes straight into the owner's var / m / v
@@ -721,15 +752,14 @@ class B200StepRunner:
             c1, c2 = p.convs
             scale = 1.0 / 255.0 if s.x_dev.dtype == torch.uint8 else 1.0
             K.pool2_bwd(s.dpool2, s.act[0].view(s.B, 7, 7, 64), s.amax2, s.dconv2p, s.z["gkb2"])
-            fork()                               # dconv2p is ready
+            fork(side)                           # dconv2p is ready
             with torch.cuda.stream(side):
                 K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
             K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
-        if side is not main:                     # join
-            ev = torch.cuda.Event()
-            ev.record(side)
-            main.wait_event(ev)
+        if par:                                  # join
+            main.wait_event(after(side))
+            main.wait_event(after(apl))
         if sync:
             return                   # the round kernel is launched after the (captured) compute part
         rest = [v for v in self.train_op.var_list if v not in applied]
@@ -825,7 +855,8 @@ class B200StepRunner:
         flags = [st.mbox_flags_ptr(sh) for sh in range(st.num_shards)]
         K.mailbox_push(items, al.mailbox_depth, me, flags, publish, self.mbox_seq.data_ptr(),
                        s.counter.data_ptr(), self.mbox_host.data_ptr() if publish else None,
-                       st.step_ctrl if publish else None, s.step_dev.data_ptr() if publish else None)
+                       st.step_ctrl if publish else None, s.step_dev.data_ptr() if publish else None,
+                       sink=self._sink(s) if (publish and self._uses_sink(s)) else None)
 
     def _mbox_consumed(self) -> int:
         """min over owners of how many of MY gradients they have applied (host-side read)."""
@@ -868,6 +899,9 @@ class B200StepRunner:
         if self.use_mailbox:
             self._mbox_wait(self._pushes)
 
+    def _sink(self, s: StepState):
+        return K.make_sink(s.z["loss"].data_ptr(), s.res_pin.data_ptr(), s.res_seq_dev.data_ptr())
+
     def _apply_vars(self, s: StepState, variables: Sequence[G.Variable], finish: bool) -> None:
         """push+apply of ``variables`` on the current stream; ``finish`` adds TF's _finish (beta
         powers) and the global_step atomic and must be the step's last apply."""
@@ -875,6 +909,7 @@ class B200StepRunner:
             self._push_vars(s, variables, publish=finish)
             return
         st, spec = self.store, self.spec
+        sink = self._sink(s) if (finish and self._uses_sink(s)) else None
         entries = []
         for var in variables:
             gptr = self._grad_ptr(s, var)
@@ -892,7 +927,7 @@ class B200StepRunner:
             items = K.make_apply_items(ch)
             K.push_apply(spec.code, items, len(ch), hyper, st.powers_ctrl, st.step_ctrl, last,
                          self.worker_id, s.step_dev.data_ptr() if last else None,
-                         s.counter.data_ptr())
+                         s.counter.data_ptr(), sink=sink if last else None)
 
     def _pull(self, s: StepState) -> None:
         if self.sync_opt is not None:
@@ -902,11 +937,13 @@ class B200StepRunner:
         if self.copies:
             K.pull_bulk(self.copies, self.store.step_ctrl, s.step_dev.data_ptr() + 8)
 
+    def _uses_sink(self, s: StepState) -> bool:
+        return self.host_sink and s.train and self.sync_opt is None
+
     def _enqueue_step(self, s: StepState, with_io: bool = True) -> None:
         """Everything one ``sess.run(train_op)`` does on the device, in stream order."""
         if with_io:
-            s.x_dev.copy_(s.x_pin, non_blocking=True)
-            s.y_dev.copy_(s.y_pin, non_blocking=True)
+            s.io_dev.copy_(s.io_pin, non_blocking=True)
         clear_end = s.train and self.clear_at_end and self.sync_opt is None
         if not clear_end:
             K.fill_u32(s.zero.buf, 0)
@@ -918,7 +955,7 @@ class B200StepRunner:
         if s.train:
             with nvtx_range("dtf/backward_push_apply"):
                 self._backward(s)      # includes the push+apply of every variable
-        if with_io:
+        if with_io and not self._uses_sink(s):
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
             if self.sync_opt is None or not s.train:
                 s.step_pin.copy_(s.step_dev, non_blocking=True)
@@ -1030,14 +1067,24 @@ class B200StepRunner:
             if top is not None:
                 if self.use_mailbox:
                     self._mbox_admit()
+                s.res_expected += 1
                 self._launch(s)
             else:
                 with torch.cuda.stream(self.stream):
                     self._enqueue_step(s)
+        sink = top is not None and self._uses_sink(s)
         with nvtx_range("dtf/wait_step"):
-            self.stream.synchronize()
-        loss_val = np.float32(s.out_np[0])
-        step_val = int(s.step_np[0]) if top is not None else None
+            if sink:
+                self._wait_result(s)
+            else:
+                self.stream.synchronize()
+        if sink:
+            loss_val = np.float32(s.res_f32[0])
+            step_val = int(s.res_u64[1])
+        else:
+            loss_val = np.float32(s.out_np[0])
+            step_val = int(s.step_np[0]) if top is not None else None
+        s.last_loss = loss_val
 
         out: List[Any] = []
         extra: Optional[Dict[int, Any]] = None
@@ -1056,6 +1103,17 @@ class B200StepRunner:
                                             feeds, s)
                 out.append(extra[id(f)])
         return out
+
+    def _wait_result(self, s: StepState) -> None:
+        """Spin (natively, GIL released) on the sequence word the step's last kernel writes."""
+        exp = s.res_expected & 0xffffffff
+        wait = L.lib().dtf_host_wait_u32
+        ptr = s.res_pin.data_ptr() + 4          # word 1 = sequence number
+        while wait(ptr, exp, 200000) != 0:
+            if self.stream.query():                # drained without reporting: surface the error
+                self.stream.synchronize()
+                if int(s.res_u32[1]) != exp:
+                    raise RuntimeError("training step finished without reporting its results")
 
     def _as_step(self, step: int):
         gs = G.get_global_step(self.graph)
@@ -1080,7 +1138,7 @@ class B200StepRunner:
         from .executor_cpu import evaluate, _to_numpy
         f2 = dict(feeds)
         f2[self.plan.logits_node] = s.logits.cpu().numpy()
-        f2[self.plan.loss_node] = np.float32(s.out_pin[0].item())
+        f2[self.plan.loss_node] = np.float32(getattr(s, "last_loss", s.out_np[0]))
         vals = evaluate(list(nodes), f2, {})
         return {id(n): _to_numpy(v) for n, v in zip(nodes, vals)}
 
@@ -1113,6 +1171,7 @@ class B200StepRunner:
         s = self.train_state()
         with torch.cuda.stream(self.stream):
             for _ in range(n):
+                s.res_expected += 1
                 if self.use_mailbox:
                     self._mbox_admit()
                 if s.graph_exec:

@@ -133,6 +133,11 @@ MBOX_FLAGS_BYTES = 512
 MBOX_OFF_PRODUCED, MBOX_OFF_CONSUMED, MBOX_OFF_DONE = 0, 128, 256
 
 
+class ResultSink(C.Structure):
+    """Mirror of ``dtf_result_sink``."""
+    _fields_ = [("loss_src", C.c_void_p), ("host_dst", C.c_void_p), ("seq_dev", C.c_void_p)]
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -153,6 +158,8 @@ def _declare(lib):
         "dtf_softmax_xent_sparse": [vp, i, vp, i, i, vp, vp, i, vp, vp],
         "dtf_softmax_xent_dense": [vp, i, vp, i, i, i, vp, vp, i, vp, vp],
         "dtf_push_apply": [i, C.POINTER(ApplyItem), i, C.POINTER(ApplyHyper), vp, vp, i, i, vp, vp, vp],
+        "dtf_push_apply_ex": [i, C.POINTER(ApplyItem), i, C.POINTER(ApplyHyper), vp, vp, i, i, vp, vp,
+                              C.POINTER(ResultSink), vp],
         "dtf_pull_bulk": [C.POINTER(CopyItem), i, vp, vp, vp],
         "dtf_refresh_shadow": [vp, vp, ll, ll, i, i, vp],
         "dtf_u8_to_bf16": [vp, vp, i, i, i, f, vp],
@@ -179,7 +186,8 @@ def _declare(lib):
         "dtf_stream_sync": [vp],
         "dtf_set_pdl": [i],
         "dtf_sync_round": [i, vp, i, i, i, C.c_uint, C.POINTER(ApplyHyper), C.POINTER(C.c_ulonglong), vp, vp, i, vp],
-        "dtf_mailbox_push": [C.POINTER(MboxPushItem), i, i, i, C.POINTER(vp), i, i, vp, vp, vp, vp, vp, vp],
+        "dtf_mailbox_push": [C.POINTER(MboxPushItem), i, i, i, C.POINTER(vp), i, i, vp, vp, vp, vp, vp,
+                             C.POINTER(ResultSink), vp],
         "dtf_mailbox_drain": [i, C.POINTER(ApplyItem), i, C.c_longlong, i, i, C.POINTER(ApplyHyper), vp, vp,
                               vp, vp, vp, vp, vp],
         "dtf_mbox_daemon_start": [C.POINTER(vp), i, i, C.POINTER(ApplyItem), i, C.c_longlong, i, i,
@@ -188,6 +196,7 @@ def _declare(lib):
         "dtf_mbox_daemon_stats": [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)],
         "dtf_mbox_daemon_stop": [vp],
         "dtf_graph_launch": [vp, vp],
+        "dtf_host_wait_u32": [vp, C.c_uint, C.c_longlong],
         "dtf_head_fused": [vp, i, i, vp, i, vp, vp, vp, i, i, i, vp, i, vp, vp, i, vp, vp, i, vp, vp],
         "dtf_host_alloc_pinned": [C.POINTER(vp), C.c_size_t],
         "dtf_host_free_pinned": [vp],

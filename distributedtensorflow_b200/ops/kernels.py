@@ -152,12 +152,20 @@ def make_hyper(lr: float, beta1: float = 0.9, beta2: float = 0.999, epsilon: flo
     return h
 
 
+def make_sink(loss_ptr: int, host_ptr: int, seq_ptr: int) -> L.ResultSink:
+    sk = L.ResultSink()
+    sk.loss_src, sk.host_dst, sk.seq_dev = loss_ptr, host_ptr, seq_ptr
+    return sk
+
+
 def push_apply(opt: int, items, n_items: int, hyper: L.ApplyHyper, ctrl_powers: Optional[int],
                ctrl_step: Optional[int], finish: bool, worker_id: int,
-               step_out: Optional[int], block_counter: Optional[int]) -> None:
-    rc = L.lib().dtf_push_apply(opt, items, n_items, C.byref(hyper), ctrl_powers, ctrl_step,
-                                int(finish), worker_id, step_out, block_counter,
-                                L.current_stream())
+               step_out: Optional[int], block_counter: Optional[int],
+               sink: Optional[L.ResultSink] = None) -> None:
+    rc = L.lib().dtf_push_apply_ex(opt, items, n_items, C.byref(hyper), ctrl_powers, ctrl_step,
+                                   int(finish), worker_id, step_out, block_counter,
+                                   C.byref(sink) if (sink is not None and finish) else None,
+                                   L.current_stream())
     L.check(rc, "dtf_push_apply")
     _count()
 
@@ -165,7 +173,7 @@ def push_apply(opt: int, items, n_items: int, hyper: L.ApplyHyper, ctrl_powers: 
 def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags: Sequence[int],
                  publish: bool, seq: int, block_counter: Optional[int],
                  min_consumed_out: Optional[int], ctrl_step: Optional[int] = None,
-                 step_out: Optional[int] = None) -> None:
+                 step_out: Optional[int] = None, sink: Optional[L.ResultSink] = None) -> None:
     """Worker side of the "owner applies" push (csrc/kernels/mailbox.cu).
 
     items: (src_ptr, dst0_ptr, nbytes, buf_stride) — gradient slice -> its place in MY buffer 0 on
@@ -184,6 +192,7 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
         rc = L.lib().dtf_mailbox_push(arr, len(chunk), depth, worker_id, flags, len(owner_flags),
                                       int(last), seq, block_counter, min_consumed_out if last else None,
                                       ctrl_step if last else None, step_out if last else None,
+                                      C.byref(sink) if (sink is not None and last) else None,
                                       L.current_stream())
         L.check(rc, "dtf_mailbox_push")
         _count()

@@ -143,10 +143,25 @@ typedef struct dtf_apply_hyper {
  * ctrl_for_step: control block holding global_step. finish: 1 = bump global_step, update beta
  * powers, heartbeat[worker_id]. step_out (device u64, local) receives the new global step.
  * block_counter: a zero-initialised local u32 the kernel uses to elect the last CTA. */
+/* Where the step's LAST kernel reports the step's results, so no D2H copy nodes trail the step:
+ * the finishing thread stores {loss bits, sequence number, global_step} straight into a pinned,
+ * device-mapped host buffer (16-byte aligned): word 0 = *loss_src, words 2..3 = global_step (u64),
+ * then — after a system fence — word 1 = ++(*seq_dev). The host spins on word 1. */
+typedef struct dtf_result_sink {
+  const float* loss_src;     /* device: the step's accumulated loss */
+  unsigned int* host_dst;    /* pinned host memory, 4 words */
+  unsigned int* seq_dev;     /* device counter of steps reported */
+} dtf_result_sink;
 int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
                    const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
                    dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                    unsigned long long* step_out, unsigned int* block_counter, void* stream);
+/* Same, and the finishing thread also fills `sink` (may be NULL). */
+int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_items,
+                      const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
+                      dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
+                      unsigned long long* step_out, unsigned int* block_counter,
+                      const dtf_result_sink* sink, void* stream);
 
 /* dtf_push_apply for callers that cannot allocate device memory (no counterpart in the reference:
  * TensorFlow's ApplyAdam kernels allocate through the TF runtime). Same arguments and result as
@@ -208,7 +223,7 @@ int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, int depth, in
                      dtf_mbox_flags* const* owner_flags, int n_owners, int publish,
                      unsigned int* seq, unsigned int* block_counter,
                      unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
-                     unsigned long long* step_out, void* stream);
+                     unsigned long long* step_out, const dtf_result_sink* sink, void* stream);
 /* Owner side, two launches: (1) snapshot which workers have an unconsumed gradient (at most one
  * per worker per call, the oldest) into `todo` (local scratch, DTF_MAX_WORKERS words);
  * (2) for every item read var / slots once, apply the pending gradients one after another with
@@ -223,6 +238,9 @@ int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_items, long lo
                       unsigned int* todo, unsigned int* block_counter,
                       unsigned long long* step_out, void* stream);
 
+/* Host-side spin on a pinned word written by a kernel (see dtf_result_sink): 0 = reached
+ * `expected`, 1 = timeout. */
+int dtf_host_wait_u32(const unsigned int* word, unsigned int expected, long long timeout_us);
 /* cudaGraphLaunch of an instantiated graph on an explicit stream (the executor's per-step call). */
 int dtf_graph_launch(void* graph_exec, void* stream);
 
