@@ -42,7 +42,7 @@ def main():
         # split into steps at the H2D copies (first event of a step is a memcpy)
         rows = [(e.time_range.start, e.time_range.end - e.time_range.start, e.name[:60]) for e in evs]
         starts = [i for i, r in enumerate(rows) if "Memcpy HtoD" in r[2] or "memcpy" in r[2].lower() and "HtoD" in r[2]]
-        steps = [i for j, i in enumerate(starts) if j % 2 == 0]
+        steps = starts                     # one H2D copy node opens every step
         if len(steps) >= 3:
             a, b = steps[-2], steps[-1]
         else:

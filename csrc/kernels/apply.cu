@@ -151,14 +151,23 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
 
   if (!a.finish) return;
   // ---- elect the last CTA; it performs _finish (K10) ----
-  __threadfence_system();
+  // bar.sync, then ONE thread fences (cumulative: it orders the whole CTA's stores) and takes a
+  // ticket. Device scope is enough: nothing is synchronised on global_step across GPUs (updates are
+  // Hogwild), and the host only reads a shard after the stream or the result word says so.
+  __shared__ float s_loss;
+  __shared__ unsigned int s_seq;
+  __shared__ unsigned long long s_step;
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     const unsigned int old = atomicInc(a.block_counter, static_cast<unsigned int>(a.total_blocks - 1));
     s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
   }
   __syncthreads();
-  if (s_last && threadIdx.x == 0) {
+  if (!s_last) return;
+  // three independent memory round trips, taken by three warps at the same time
+  const bool sink = a.sink.host_dst != nullptr;
+  if (threadIdx.x == 0) {
     if (OPT == DTF_OPT_ADAM) {
       volatile float* b1 = &a.ctrl_powers->beta1_power;
       volatile float* b2 = &a.ctrl_powers->beta2_power;
@@ -166,22 +175,28 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
       *b2 = *b2 * a.h.beta2;
     }
     const unsigned long long old = atom_add_u64_sys(&a.ctrl_step->global_step, 1ull);
+    s_step = old + 1ull;
     if (a.step_out != nullptr) *a.step_out = old + 1ull;
     if (a.worker_id >= 0 && a.worker_id < DTF_MAX_WORKERS)
       *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[a.worker_id]) =
           old + 1ull;
     atomicAdd(&a.ctrl_step->apply_count, 1u);
-    if (a.sink.host_dst != nullptr) {
-      // report the step straight into pinned host memory (no D2H copy node behind the step)
-      volatile unsigned int* h = a.sink.host_dst;
-      h[0] = __float_as_uint(*reinterpret_cast<const volatile float*>(a.sink.loss_src));
-      *reinterpret_cast<volatile unsigned long long*>(a.sink.host_dst + 2) = old + 1ull;
-      __threadfence_system();
-      const unsigned int q = *a.sink.seq_dev + 1u;
-      *a.sink.seq_dev = q;
-      h[1] = q;
-    }
-    __threadfence_system();
+  } else if (threadIdx.x == 32 && sink) {
+    s_loss = *reinterpret_cast<const volatile float*>(a.sink.loss_src);
+  } else if (threadIdx.x == 64 && sink) {
+    const unsigned int q = *reinterpret_cast<volatile unsigned int*>(a.sink.seq_dev) + 1u;
+    *reinterpret_cast<volatile unsigned int*>(a.sink.seq_dev) = q;
+    s_seq = q;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && sink) {
+    // ONE aligned 16-byte store into pinned host memory = one PCIe write: the host, spinning on
+    // the sequence word, can never see it without the loss and the step next to it
+    const unsigned long long st = s_step;
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(a.sink.host_dst),
+                 "r"(__float_as_uint(s_loss)), "r"(s_seq), "r"(static_cast<unsigned int>(st)),
+                 "r"(static_cast<unsigned int>(st >> 32))
+                 : "memory");
   }
 }
 

@@ -105,14 +105,14 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
     if (a.ctrl_step != nullptr) gs = ld_acquire_sys_u64(&a.ctrl_step->global_step);
     if (a.step_out != nullptr && a.ctrl_step != nullptr) *a.step_out = gs;
     if (a.sink.host_dst != nullptr) {
-      volatile unsigned int* h = a.sink.host_dst;
-      h[0] = __float_as_uint(*reinterpret_cast<const volatile float*>(a.sink.loss_src));
-      *reinterpret_cast<volatile unsigned long long*>(a.sink.host_dst + 2) = gs;
-      __threadfence_system();
-      const unsigned int q = *a.sink.seq_dev + 1u;
-      *a.sink.seq_dev = q;
-      h[1] = q;
-      __threadfence_system();
+      const float loss = *reinterpret_cast<const volatile float*>(a.sink.loss_src);
+      const unsigned int q = *reinterpret_cast<volatile unsigned int*>(a.sink.seq_dev) + 1u;
+      *reinterpret_cast<volatile unsigned int*>(a.sink.seq_dev) = q;
+      // one aligned 16-byte store = one PCIe write (see apply.cu)
+      asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(a.sink.host_dst),
+                   "r"(__float_as_uint(loss)), "r"(q), "r"(static_cast<unsigned int>(gs)),
+                   "r"(static_cast<unsigned int>(gs >> 32))
+                   : "memory");
     }
   }
 }

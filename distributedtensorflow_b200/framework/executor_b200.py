@@ -223,6 +223,7 @@ class StepState:
         self.res_u64 = self.res_pin.numpy().view(np.uint64)
         self.res_seq_dev = torch.zeros(4, dtype=torch.int32, device=dev)
         self.res_expected = 0
+        self.zero_copy = False
         self.counter = torch.zeros(4, dtype=torch.int32, device=dev)
         dims = [int(d.w.shape[0]) for d in p.dense] + [p.num_classes]
         self.dims = dims
@@ -303,6 +304,8 @@ class B200StepRunner:
         # the step's last kernel writes loss / global_step into pinned host memory and the host
         # spins on a sequence word: no D2H copy nodes, no stream synchronise per step
         self.host_sink = bool(opts.get("host_sink", True))
+        # the step's first kernel reads the input batch in place from pinned host memory
+        self.zero_copy_input = bool(opts.get("zero_copy_input", True))
         # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
         # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
         # daemon (csrc/kernels/mailbox.cu, csrc/runtime/mbox_daemon.cu); "auto" = mailbox whenever
@@ -327,9 +330,16 @@ class B200StepRunner:
         self.local: Dict[str, torch.Tensor] = {}     # pulled copies of remote tensors
         # the activation-gradient chain is the critical path: its stream outranks the side stream
         # that carries weight-gradient GEMMs and the bandwidth-heavy applies
-        self.stream = torch.cuda.Stream(device=self.device, priority=-1)
-        self.side_stream = torch.cuda.Stream(device=self.device, priority=0)
-        self.apply_stream = torch.cuda.Stream(device=self.device, priority=0)
+        # priorities: activation-gradient chain > weight-gradient GEMMs > bandwidth-heavy applies, so a
+        # pending weight-gradient CTA is dispatched before the apply's hundreds of CTAs
+        def mk(prio):
+            try:
+                return torch.cuda.Stream(device=self.device, priority=prio)
+            except Exception:
+                return torch.cuda.Stream(device=self.device, priority=max(prio, -1))
+        self.stream = mk(-3)
+        self.side_stream = mk(-2)
+        self.apply_stream = mk(0)
         self.overlap = bool(opts.get("overlap", True))
         self._stream_handle = self.stream.cuda_stream
         self._graph_launch = L.lib().dtf_graph_launch
@@ -617,14 +627,21 @@ class B200StepRunner:
         if p.kind == "cnn":
             scale = 1.0 / 255.0 if s.x_dev.dtype == torch.uint8 else 1.0
             c1, c2 = p.convs
-            K_conv1_fwd(s.x_dev, self.fptr[c1.k.name], self.fptr[c1.b.name], s.pool1p, s.amax1, scale)
+            if s.zero_copy:
+                # the first kernel reads the batch straight from pinned host memory (and mirrors it
+                # into x_dev for conv1's backward): no H2D copy node in front of the step
+                K_conv1_fwd(s.x_pin, self.fptr[c1.k.name], self.fptr[c1.b.name], s.pool1p, s.amax1, scale,
+                            x_copy=s.x_dev, ingest=True)
+            else:
+                K_conv1_fwd(s.x_dev, self.fptr[c1.k.name], self.fptr[c1.b.name], s.pool1p, s.amax1, scale)
             K_conv2_fwd(s.pool1p, self.wptr[c2.k.name][0], self.fptr[c2.b.name],
                         s.act[0].view(s.B, 7, 7, 64), s.amax2)
         else:
+            src = s.x_pin if s.zero_copy else s.x_dev     # pinned host memory is device-addressable
             if s.x_dev.dtype == torch.uint8:
-                K.u8_to_bf16(s.x_dev, s.act[0])
+                K.u8_to_bf16(src, s.act[0])
             else:
-                K.f32_to_bf16(s.x_dev, s.act[0])
+                K.f32_to_bf16(src, s.act[0])
         nl = len(p.dense)
         fused_head = self._head_is_fused()
         for i, d in enumerate(p.dense):
@@ -655,6 +672,8 @@ class B200StepRunner:
     def _loss(self, s: StepState) -> None:
         p = self.plan
         nl = len(p.dense)
+        if getattr(s, "y_ready", None) is not None:
+            torch.cuda.current_stream().wait_event(s.y_ready)
         if self._head_is_fused():
             d = p.dense[-1]
             wp, ld = self.wptr[d.w.name]
@@ -709,15 +728,22 @@ class B200StepRunner:
 
         dz = s.dlogits
         head_fused = self._head_is_fused()
+        pre_dw: Dict[int, Any] = {}
         fork(side)                               # dlogits (and every activation) is ready
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
             fused = self._fused_apply_spec(d.w) if (par and self.fused_apply and not self.use_mailbox) else None
             dz_i = dz
-            dw_done = None
-            if fused is None:
+            dw_done = pre_dw.pop(i, None)
+            if fused is None and dw_done is None:
                 with torch.cuda.stream(side):
+                    if head_fused and i == nl - 1 and par and not (self.fused_apply and not self.use_mailbox):
+                        # the fused head already produced dZ_{i-1}: issue the LARGER weight-gradient
+                        # GEMM of the layer below first, so its (big) apply can start earliest
+                        K.gemm(s.act[i - 1], s.dact[i], s.gw[i - 1], s.dims[i - 1], s.dims[i], s.B,
+                               a_mn=True, b_mn=True)
+                        pre_dw[i - 1] = after(side)
                     # dW_i = act_i^T dZ_i
                     K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
                     if par:
@@ -942,7 +968,19 @@ class B200StepRunner:
 
     def _enqueue_step(self, s: StepState, with_io: bool = True) -> None:
         """Everything one ``sess.run(train_op)`` does on the device, in stream order."""
-        if with_io:
+        s.zero_copy = bool(with_io and self.zero_copy_input)
+        s.y_ready = None
+        if s.zero_copy:
+            # labels: a copy node on the side stream, parallel to the first kernel; the loss waits for it
+            main = torch.cuda.current_stream()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            self.side_stream.wait_event(ev)
+            with torch.cuda.stream(self.side_stream):
+                s.y_dev.copy_(s.y_pin, non_blocking=True)
+                s.y_ready = torch.cuda.Event()
+                s.y_ready.record(self.side_stream)
+        elif with_io:
             s.io_dev.copy_(s.io_pin, non_blocking=True)
         clear_end = s.train and self.clear_at_end and self.sync_opt is None
         if not clear_end:
@@ -1209,8 +1247,8 @@ class _PtrTensor:
         return self._ptr
 
 
-def K_conv1_fwd(x, w1_ptr, b1_ptr, pool1p, amax1, scale):
-    K.conv1_fwd(x, _PtrTensor(w1_ptr), _PtrTensor(b1_ptr), pool1p, amax1, scale)
+def K_conv1_fwd(x, w1_ptr, b1_ptr, pool1p, amax1, scale, x_copy=None, ingest=False):
+    K.conv1_fwd(x, _PtrTensor(w1_ptr), _PtrTensor(b1_ptr), pool1p, amax1, scale, x_copy=x_copy, ingest=ingest)
 
 
 def K_conv2_fwd(pool1p, w2_ptr, b2_ptr, pool2, amax2):

@@ -291,9 +291,19 @@ def fill_u32(t: torch.Tensor, value: int = 0) -> None:
 # CNN layers
 # ------------------------------------------------------------------------------------------------
 def conv1_fwd(x: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, pool1p: torch.Tensor,
-              amax1: torch.Tensor, scale: float) -> None:
+              amax1: torch.Tensor, scale: float, x_copy: Optional[torch.Tensor] = None,
+              ingest: bool = False) -> None:
+    """``ingest``: x is pinned host memory read in place by the kernel (and mirrored to x_copy)."""
     B = x.shape[0]
     u8 = x.dtype == torch.uint8
+    if ingest:
+        cp = _ptr(x_copy)
+        rc = L.lib().dtf_conv1_fwd_ingest(x.data_ptr() if u8 else None, None if u8 else x.data_ptr(), scale,
+                                          w1.data_ptr(), b1.data_ptr(), pool1p.data_ptr(), amax1.data_ptr(),
+                                          cp if u8 else None, None if u8 else cp, B, L.current_stream())
+        L.check(rc, "dtf_conv1_fwd_ingest")
+        _count()
+        return
     rc = L.lib().dtf_conv1_fwd(x.data_ptr() if u8 else None, None if u8 else x.data_ptr(), scale,
                                w1.data_ptr(), b1.data_ptr(), pool1p.data_ptr(), amax1.data_ptr(),
                                B, L.current_stream())

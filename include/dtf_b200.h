@@ -296,6 +296,12 @@ int dtf_fill_u32(void* dst, unsigned int value, long long n_words, void* stream)
  * caller), amax1 u8 [B,14,14,32] (argmax position 0..3). w1: fp32 [5,5,1,32], b1: fp32 [32]. */
 int dtf_conv1_fwd(const unsigned char* x_u8, const float* x_f32, float scale, const float* w1,
                   const float* b1, void* pool1p, unsigned char* amax1, int B, void* stream);
+/* Same, but x may be PINNED HOST memory (device-mapped): images are fetched with 16-byte loads and,
+ * when copy_* is given, mirrored into a device buffer (the backward pass reads that). Replaces the
+ * step's H2D copy node. */
+int dtf_conv1_fwd_ingest(const unsigned char* x_u8, const float* x_f32, float scale, const float* w1,
+                         const float* b1, void* pool1p, unsigned char* amax1, unsigned char* copy_u8,
+                         float* copy_f32, int B, void* stream);
 /* dpool1 bf16 [B,14,14,32] + amax1 + pooled output -> dW1 fp32 [25,32], db1 fp32 [32]
  * (accumulated with atomics: zero first). */
 int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, float scale,
