@@ -128,6 +128,8 @@ def main() -> int:
     ap.add_argument("--no-split-k", action="store_true", help="disable split-K for skinny GEMMs")
     ap.add_argument("--no-overlap", action="store_true", help="single-stream backward (no side stream)")
     ap.add_argument("--fused-apply", action="store_true", help="dW GEMM epilogue does the push+apply")
+    ap.add_argument("--opt", action="append", default=[], metavar="KEY=0|1",
+                    help="extra executor option, e.g. --opt zero_copy_input=0 --opt host_sink=0")
     ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"],
                     help="gradient push: worker-side remote read-modify-write, or posted stores + the "
                          "owner's apply daemon (auto = mailbox when there is more than one worker)")
@@ -202,7 +204,8 @@ def main() -> int:
     cfg = tf.ConfigProto(allow_soft_placement=True, backend="b200", device="cuda:%d" % local_rank,
                          cuda_graph=not args.no_cuda_graph, pdl=not args.no_pdl,
                          split_k=not args.no_split_k, overlap=not args.no_overlap, fused_apply=args.fused_apply,
-                         push_mode=args.push_mode)
+                         push_mode=args.push_mode,
+                         **{k: (v == "1") if v in ("0", "1") else v for k, v in (o.split("=", 1) for o in args.opt)})
     result = {}
     with tf.train.MonitoredTrainingSession(master=wk_server.target, is_chief=(rank == 0), config=cfg,
                                            recovery_wait_secs=0.05) as sess:

@@ -306,6 +306,10 @@ class B200StepRunner:
         self.host_sink = bool(opts.get("host_sink", True))
         # the step's first kernel reads the input batch in place from pinned host memory
         self.zero_copy_input = bool(opts.get("zero_copy_input", True))
+        # push(+apply) of each dense kernel as soon as its gradient exists (overlaps NVLink traffic
+        # with the rest of the backward pass). With every shard local the applies are pure HBM work
+        # that only fights the compute kernels for SMs: one apply kernel at the end is faster.
+        self.early_apply = opts.get("early_apply", None)
         # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
         # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
         # daemon (csrc/kernels/mailbox.cu, csrc/runtime/mbox_daemon.cu); "auto" = mailbox whenever
@@ -714,7 +718,10 @@ class B200StepRunner:
         sync = self.sync_opt is not None
         par = self.overlap and not sync
         side = self.side_stream if par else main
-        apl = self.apply_stream if par else main
+        early = self.early_apply
+        if early is None:
+            early = self.use_mailbox or self.fused_apply or not all(self.store.is_local)
+        apl = self.apply_stream if (par and early) else main
         applied: List[G.Variable] = []
 
         def after(stream):
@@ -733,7 +740,8 @@ class B200StepRunner:
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
-            fused = self._fused_apply_spec(d.w) if (par and self.fused_apply and not self.use_mailbox) else None
+            fused = self._fused_apply_spec(d.w) if (par and early and self.fused_apply
+                                                    and not self.use_mailbox) else None
             dz_i = dz
             dw_done = pre_dw.pop(i, None)
             if fused is None and dw_done is None:
@@ -760,7 +768,7 @@ class B200StepRunner:
                 fork(side)                       # dZ_{i-1} is ready
             elif p.kind == "cnn":
                 K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld, **self._plan_kw(s, "dx0"))
-            if par:
+            if par and early:
                 # W_i may be read in place from the local shard by the dX GEMM above: order the
                 # apply after it, and after the gradient it consumes
                 fork(apl)
@@ -785,7 +793,8 @@ class B200StepRunner:
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if par:                                  # join
             main.wait_event(after(side))
-            main.wait_event(after(apl))
+            if apl is not main:
+                main.wait_event(after(apl))
         if sync:
             return                   # the round kernel is launched after the (captured) compute part
         rest = [v for v in self.train_op.var_list if v not in applied]
