@@ -11,8 +11,9 @@
 namespace dtf {
 
 constexpr int C1_IMG = 28, C1_PAD = 32, C1_OUT = 14, C1_CH = 32, C1_HP = 18;
+constexpr int C1_PITCH = C1_PAD + 1;  // odd row pitch: rows y and y+1 fall into different smem banks
 
-__device__ __forceinline__ void load_image_padded(float (*img)[C1_PAD], const unsigned char* x_u8,
+__device__ __forceinline__ void load_image_padded(float (*img)[C1_PITCH], const unsigned char* x_u8,
                                                   const float* x_f32, float scale, int n) {
   for (int i = threadIdx.x; i < C1_PAD * C1_PAD; i += blockDim.x) {
     const int y = i / C1_PAD - 2, x = i % C1_PAD - 2;
@@ -29,7 +30,7 @@ __device__ __forceinline__ void load_image_padded(float (*img)[C1_PAD], const un
 // loads (49 per u8 image: one PCIe read burst instead of 784 byte loads), optionally mirrored into
 // a device buffer for the backward pass, then expanded into the zero-padded float tile. This
 // replaces the step's H2D copy node and the copy-engine -> SM hand-off behind it (~12 us).
-__device__ __forceinline__ void ingest_image_padded(float (*img)[C1_PAD], unsigned char* raw,
+__device__ __forceinline__ void ingest_image_padded(float (*img)[C1_PITCH], unsigned char* raw,
                                                     const unsigned char* x_u8, const float* x_f32,
                                                     unsigned char* copy_u8, float* copy_f32,
                                                     float scale, int n, bool do_copy) {
@@ -61,16 +62,22 @@ __global__ void __launch_bounds__(256)
 conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
                  float scale, const float* __restrict__ w1, const float* __restrict__ b1,
                  __nv_bfloat16* __restrict__ pool1p, unsigned char* __restrict__ amax1,
-                 unsigned char* __restrict__ copy_u8, float* __restrict__ copy_f32, int ingest) {
-  __shared__ float img[C1_PAD][C1_PAD];
+                 unsigned char* __restrict__ copy_u8, float* __restrict__ copy_f32, int ingest,
+                 const uint4* __restrict__ y_src, uint4* __restrict__ y_dst, int y_vecs) {
+  __shared__ float img[C1_PAD][C1_PITCH];
   __shared__ float w[25][C1_CH];
   __shared__ float bias[C1_CH];
   __shared__ __align__(16) unsigned char raw[C1_IMG * C1_IMG * 4];
   const int n = blockIdx.x;
   griddep_wait();
   griddep_launch();
-  if (ingest)
+  if (ingest) {
+    // the labels ride along: the last CTA mirrors them host -> device (16-byte words), so the step
+    // needs no copy node and no cross-stream join in front of the loss
+    if (y_src != nullptr && blockIdx.x == gridDim.x - 1 && blockIdx.y == 1)
+      for (int i = threadIdx.x; i < y_vecs; i += blockDim.x) y_dst[i] = y_src[i];
     ingest_image_padded(img, raw, x_u8, x_f32, copy_u8, copy_f32, scale, n, blockIdx.y == 0);
+  }
   else
     load_image_padded(img, x_u8, x_f32, scale, n);
   for (int i = threadIdx.x; i < 25 * C1_CH; i += blockDim.x) w[i / C1_CH][i % C1_CH] = w1[i];
@@ -135,7 +142,7 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
                  float scale, const __nv_bfloat16* __restrict__ dpool1,
                  const __nv_bfloat16* __restrict__ pool1p, const unsigned char* __restrict__ amax1,
                  float* __restrict__ dw1_accum, float* __restrict__ db1_accum) {
-  __shared__ float img[C1_PAD][C1_PAD];
+  __shared__ float img[C1_PAD][C1_PITCH];
   __shared__ float g[C1_OUT * C1_OUT][C1_CH];          // 25 KB
   __shared__ __align__(16) unsigned char am[C1_OUT * C1_OUT][C1_CH]; // 6 KB
   const int n = blockIdx.x;
@@ -244,20 +251,25 @@ extern "C" int dtf_conv1_fwd(const unsigned char* x_u8, const float* x_f32, floa
   DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B, 2), dim3(196), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale, w1, b1,
                                reinterpret_cast<__nv_bfloat16*>(pool1p), amax1,
-                               static_cast<unsigned char*>(nullptr), static_cast<float*>(nullptr), 0));
+                               static_cast<unsigned char*>(nullptr), static_cast<float*>(nullptr), 0,
+                               static_cast<const uint4*>(nullptr), static_cast<uint4*>(nullptr), 0));
   return 0;
 }
 
 extern "C" int dtf_conv1_fwd_ingest(const unsigned char* x_u8, const float* x_f32, float scale,
                                     const float* w1, const float* b1, void* pool1p,
                                     unsigned char* amax1, unsigned char* copy_u8, float* copy_f32,
-                                    int B, void* stream) {
+                                    const void* y_src, void* y_dst, int y_bytes, int B, void* stream) {
+  DTF_REQUIRE(y_src == nullptr || (y_dst != nullptr && y_bytes % 16 == 0 &&
+                                   ((reinterpret_cast<uintptr_t>(y_src) | reinterpret_cast<uintptr_t>(y_dst)) & 15) == 0),
+              "conv1_fwd_ingest: labels need a destination, 16-byte alignment and a multiple of 16 bytes");
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_fwd_ingest: pass exactly one of x_u8/x_f32");
   const void* x = x_u8 ? static_cast<const void*>(x_u8) : static_cast<const void*>(x_f32);
   DTF_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "conv1_fwd_ingest: x must be 16-byte aligned");
   DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B, 2), dim3(196), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale, w1, b1,
-                               reinterpret_cast<__nv_bfloat16*>(pool1p), amax1, copy_u8, copy_f32, 1));
+                               reinterpret_cast<__nv_bfloat16*>(pool1p), amax1, copy_u8, copy_f32, 1,
+                               static_cast<const uint4*>(y_src), static_cast<uint4*>(y_dst), y_bytes / 16));
   return 0;
 }
 

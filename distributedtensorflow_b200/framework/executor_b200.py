@@ -208,6 +208,7 @@ class StepState:
         self.io_dev = torch.zeros(self.io_pin.numel(), dtype=torch.uint8, device=dev)
         self.x_pin = self.io_pin[:xb].view(x_dtype).view(B, p.in_features)
         self.y_pin = self.io_pin[yoff:yoff + yb].view(y_dtype).view(ysh)
+        self.y_bytes16 = (yb + 15) // 16 * 16
         self.x_dev = self.io_dev[:xb].view(x_dtype).view(B, p.in_features)
         self.y_dev = self.io_dev[yoff:yoff + yb].view(y_dtype).view(ysh)
         self.out_pin = torch.zeros(4, dtype=torch.float32).pin_memory()      # loss
@@ -635,7 +636,8 @@ class B200StepRunner:
                 # the first kernel reads the batch straight from pinned host memory (and mirrors it
                 # into x_dev for conv1's backward): no H2D copy node in front of the step
                 K_conv1_fwd(s.x_pin, self.fptr[c1.k.name], self.fptr[c1.b.name], s.pool1p, s.amax1, scale,
-                            x_copy=s.x_dev, ingest=True)
+                            x_copy=s.x_dev, ingest=True, y_src=s.y_pin.data_ptr(), y_dst=s.y_dev.data_ptr(),
+                            y_bytes=s.y_bytes16)
             else:
                 K_conv1_fwd(s.x_dev, self.fptr[c1.k.name], self.fptr[c1.b.name], s.pool1p, s.amax1, scale)
             K_conv2_fwd(s.pool1p, self.wptr[c2.k.name][0], self.fptr[c2.b.name],
@@ -736,6 +738,7 @@ class B200StepRunner:
         dz = s.dlogits
         head_fused = self._head_is_fused()
         pre_dw: Dict[int, Any] = {}
+        deferred: List[tuple] = []
         fork(side)                               # dlogits (and every activation) is ready
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
@@ -752,10 +755,15 @@ class B200StepRunner:
                         K.gemm(s.act[i - 1], s.dact[i], s.gw[i - 1], s.dims[i - 1], s.dims[i], s.B,
                                a_mn=True, b_mn=True)
                         pre_dw[i - 1] = after(side)
-                    # dW_i = act_i^T dZ_i
-                    K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
-                    if par:
-                        dw_done = after(side)
+                    if i - 1 in pre_dw and p.kind == "cnn" and not early:
+                        # nothing needs the (tiny) logits-layer weight gradient before the final
+                        # apply: let conv2's filter gradient go first on this stream
+                        deferred.append((s.act[i], dz, s.gw[i], din, dout))
+                    else:
+                        # dW_i = act_i^T dZ_i
+                        K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
+                        if par:
+                            dw_done = after(side)
             wp, ld = self.wptr[d.w.name]
             if i > 0 and i == nl - 1 and head_fused:
                 dz = s.dact[i]                   # dZ_{i-1} and db_{i-1} came out of the fused head kernel
@@ -789,6 +797,9 @@ class B200StepRunner:
             fork(side)                           # dconv2p is ready
             with torch.cuda.stream(side):
                 K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
+                for a_, dz_, gw_, din_, dout_ in deferred:
+                    K.gemm(a_, dz_, gw_, din_, dout_, s.B, a_mn=True, b_mn=True)
+                deferred = []
             K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if par:                                  # join
@@ -979,8 +990,9 @@ class B200StepRunner:
         """Everything one ``sess.run(train_op)`` does on the device, in stream order."""
         s.zero_copy = bool(with_io and self.zero_copy_input)
         s.y_ready = None
-        if s.zero_copy:
-            # labels: a copy node on the side stream, parallel to the first kernel; the loss waits for it
+        if s.zero_copy and self.plan.kind != "cnn":
+            # labels: a copy node on the side stream, parallel to the first kernel; the loss waits for
+            # it (the CNN's conv1 kernel mirrors the labels itself)
             main = torch.cuda.current_stream()
             ev = torch.cuda.Event()
             ev.record(main)
@@ -1256,8 +1268,8 @@ class _PtrTensor:
         return self._ptr
 
 
-def K_conv1_fwd(x, w1_ptr, b1_ptr, pool1p, amax1, scale, x_copy=None, ingest=False):
-    K.conv1_fwd(x, _PtrTensor(w1_ptr), _PtrTensor(b1_ptr), pool1p, amax1, scale, x_copy=x_copy, ingest=ingest)
+def K_conv1_fwd(x, w1_ptr, b1_ptr, pool1p, amax1, scale, x_copy=None, ingest=False, **kw):
+    K.conv1_fwd(x, _PtrTensor(w1_ptr), _PtrTensor(b1_ptr), pool1p, amax1, scale, x_copy=x_copy, ingest=ingest, **kw)
 
 
 def K_conv2_fwd(pool1p, w2_ptr, b2_ptr, pool2, amax2):

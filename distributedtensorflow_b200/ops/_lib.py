@@ -167,7 +167,7 @@ def _declare(lib):
         "dtf_colsum_bf16": [vp, i, i, i, vp, vp],
         "dtf_fill_u32": [vp, C.c_uint, ll, vp],
         "dtf_conv1_fwd": [vp, vp, f, vp, vp, vp, vp, i, vp],
-        "dtf_conv1_fwd_ingest": [vp, vp, f, vp, vp, vp, vp, vp, vp, i, vp],
+        "dtf_conv1_fwd_ingest": [vp, vp, f, vp, vp, vp, vp, vp, vp, vp, vp, i, i, vp],
         "dtf_conv1_bwd": [vp, vp, f, vp, vp, vp, vp, vp, i, vp],
         "dtf_conv2_fwd": [vp, vp, vp, vp, vp, i, vp],
         "dtf_pool2_bwd": [vp, i, vp, vp, vp, vp, i, vp],

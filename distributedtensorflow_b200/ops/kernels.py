@@ -292,7 +292,8 @@ def fill_u32(t: torch.Tensor, value: int = 0) -> None:
 # ------------------------------------------------------------------------------------------------
 def conv1_fwd(x: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, pool1p: torch.Tensor,
               amax1: torch.Tensor, scale: float, x_copy: Optional[torch.Tensor] = None,
-              ingest: bool = False) -> None:
+              ingest: bool = False, y_src: Optional[int] = None, y_dst: Optional[int] = None,
+              y_bytes: int = 0) -> None:
     """``ingest``: x is pinned host memory read in place by the kernel (and mirrored to x_copy)."""
     B = x.shape[0]
     u8 = x.dtype == torch.uint8
@@ -300,7 +301,8 @@ def conv1_fwd(x: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, pool1p: torch
         cp = _ptr(x_copy)
         rc = L.lib().dtf_conv1_fwd_ingest(x.data_ptr() if u8 else None, None if u8 else x.data_ptr(), scale,
                                           w1.data_ptr(), b1.data_ptr(), pool1p.data_ptr(), amax1.data_ptr(),
-                                          cp if u8 else None, None if u8 else cp, B, L.current_stream())
+                                          cp if u8 else None, None if u8 else cp, y_src, y_dst, y_bytes, B,
+                                          L.current_stream())
         L.check(rc, "dtf_conv1_fwd_ingest")
         _count()
         return

@@ -301,7 +301,8 @@ int dtf_conv1_fwd(const unsigned char* x_u8, const float* x_f32, float scale, co
  * step's H2D copy node. */
 int dtf_conv1_fwd_ingest(const unsigned char* x_u8, const float* x_f32, float scale, const float* w1,
                          const float* b1, void* pool1p, unsigned char* amax1, unsigned char* copy_u8,
-                         float* copy_f32, int B, void* stream);
+                         float* copy_f32, const void* y_src, void* y_dst, int y_bytes, int B,
+                         void* stream);   /* y_*: labels mirrored host -> device by one CTA (optional) */
 /* dpool1 bf16 [B,14,14,32] + amax1 + pooled output -> dW1 fp32 [25,32], db1 fp32 [32]
  * (accumulated with atomics: zero first). */
 int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, float scale,
