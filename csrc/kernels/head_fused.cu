@@ -34,6 +34,7 @@ struct HeadParams {
   float* dbias_accum;                         // [C] or null
   __nv_bfloat16* dact; int lddact;            // null: no previous layer gradient wanted
   float* dprev_bias_accum;                    // [H] or null
+  float* dw_accum;                            // [H, C] fp32 (zero on entry) or null: dW = act^T dlogits
 };
 
 __device__ __forceinline__ void unpack16(const uint4& a, const uint4& b, float (&w)[HEAD_C]) {
@@ -177,7 +178,7 @@ head_fused_kernel(const __grid_constant__ HeadParams p) {
     for (int r = 0; r < HEAD_ROWS; ++r) t += s_loss[r];
     atomicAdd(p.loss_accum, t);
   }
-  if (!train || p.dact == nullptr) return;
+  if (!train || (p.dact == nullptr && p.dw_accum == nullptr)) return;
 
   // ---- phase 3: dact[r, h] = relu'(act) * sum_c dl[r, c] W[h, c];  db_prev[h] = sum_r dact ----
   float dl[HEAD_ROWS][HEAD_C];
@@ -216,10 +217,22 @@ head_fused_kernel(const __grid_constant__ HeadParams p) {
 #pragma unroll
         for (int c = 0; c < HEAD_C; ++c) d = fmaf(dl[r][c], w[c], d);
         const __nv_bfloat16 o = __float2bfloat16(__bfloat162float(av[j][r]) > 0.f ? d : 0.f);
-        p.dact[static_cast<size_t>(row0 + r) * p.lddact + h] = o;
+        if (p.dact != nullptr) p.dact[static_cast<size_t>(row0 + r) * p.lddact + h] = o;
         colsum += __bfloat162float(o);
       }
       if (p.dprev_bias_accum != nullptr) atomicAdd(&p.dprev_bias_accum[h], colsum);
+      if (p.dw_accum != nullptr) {
+        // this CTA's rows of dW[h, :] = sum_r act[r, h] * dlogits[r, :]
+        float* dwr = p.dw_accum + static_cast<size_t>(h) * p.C;
+#pragma unroll
+        for (int c = 0; c < HEAD_C; ++c) {
+          if (c >= p.C) break;
+          float t = 0.f;
+#pragma unroll
+          for (int r = 0; r < HEAD_ROWS; ++r) t = fmaf(__bfloat162float(av[j][r]), dl[r][c], t);
+          red_add_f32_gpu(dwr + c, t);
+        }
+      }
     }
   }
 }
@@ -232,7 +245,7 @@ extern "C" int dtf_head_fused(const void* act, int lda, int H, const void* w_sha
                               const float* bias, const int* labels_sparse, const float* labels_dense,
                               int ldy, int B, int C, float* logits, int ldl, float* loss_accum,
                               void* dlogits, int ldd, float* dbias_accum, void* dact, int lddact,
-                              float* dprev_bias_accum, void* stream) {
+                              float* dprev_bias_accum, float* dw_accum, void* stream) {
   DTF_REQUIRE(C >= 1 && C <= HEAD_C && ldw == HEAD_C, "head_fused: needs C <= %d and a %d-wide serving copy (C=%d ldw=%d)",
               HEAD_C, HEAD_C, C, ldw);
   DTF_REQUIRE((reinterpret_cast<uintptr_t>(w_shadow) & 15) == 0, "head_fused: W is not 16-byte aligned");
@@ -246,6 +259,7 @@ extern "C" int dtf_head_fused(const void* act, int lda, int H, const void* w_sha
   p.B = B; p.C = C; p.logits = logits; p.ldl = ldl; p.loss_accum = loss_accum;
   p.dlogits = reinterpret_cast<__nv_bfloat16*>(dlogits); p.ldd = ldd; p.dbias_accum = dbias_accum;
   p.dact = reinterpret_cast<__nv_bfloat16*>(dact); p.lddact = lddact; p.dprev_bias_accum = dprev_bias_accum;
+  p.dw_accum = dw_accum;
   const dim3 grid(ceil_div(B, HEAD_ROWS));
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (labels_dense != nullptr) {

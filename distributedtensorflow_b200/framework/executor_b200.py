@@ -225,6 +225,8 @@ class StepState:
         self.res_seq_dev = torch.zeros(4, dtype=torch.int32, device=dev)
         self.res_expected = 0
         self.zero_copy = False
+        if not train:
+            self.head_dw = False
         self.counter = torch.zeros(4, dtype=torch.int32, device=dev)
         dims = [int(d.w.shape[0]) for d in p.dense] + [p.num_classes]
         self.dims = dims
@@ -240,6 +242,11 @@ class StepState:
             self.gw = [torch.zeros((dims[i], dims[i + 1]), dtype=f32, device=dev) for i in range(nl)]
             for i in range(nl):
                 zero.add(f"gb{i}", dims[i + 1])
+            # the fused head kernel also accumulates the logits layer's weight gradient (atomics):
+            # that buffer lives in the zeroed region
+            self.head_dw = bool(runner._head_is_fused())
+            if self.head_dw:
+                zero.add("gw_last", dims[nl - 1] * dims[nl])
         if p.kind == "cnn":
             self.pool1p = torch.zeros((B, 18, 18, 32), dtype=bf, device=dev)
             self.amax1 = torch.zeros((B, 14, 14, 32), dtype=torch.uint8, device=dev)
@@ -267,6 +274,8 @@ class StepState:
                 plan["ldws"] = ldws
             self.gemm_plans[key] = plan
         self.z = zero.build(dev)
+        if train and self.head_dw:
+            self.gw[nl - 1] = self.z["gw_last"][:dims[nl - 1] * dims[nl]].view(dims[nl - 1], dims[nl])
         for key, plan in self.gemm_plans.items():
             if plan["splits"] > 1:
                 M_ = B
@@ -689,7 +698,8 @@ class B200StepRunner:
                          dlogits=s.dlogits if s.train else None,
                          dbias_accum=s.z[f"gb{nl - 1}"] if s.train else None,
                          dact=s.dact[nl - 1] if s.train else None,
-                         dprev_bias_accum=s.z[f"gb{nl - 2}"] if (s.train and p.dense[nl - 2].b is not None) else None)
+                         dprev_bias_accum=s.z[f"gb{nl - 2}"] if (s.train and p.dense[nl - 2].b is not None) else None,
+                         dw_accum=s.gw[nl - 1] if (s.train and s.head_dw) else None)
             return
         dl = s.dlogits if s.train else self._scratch_dlogits(s)
         gb = s.z[f"gb{len(p.dense) - 1}"] if s.train else None
@@ -738,7 +748,6 @@ class B200StepRunner:
         dz = s.dlogits
         head_fused = self._head_is_fused()
         pre_dw: Dict[int, Any] = {}
-        deferred: List[tuple] = []
         fork(side)                               # dlogits (and every activation) is ready
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
@@ -755,10 +764,8 @@ class B200StepRunner:
                         K.gemm(s.act[i - 1], s.dact[i], s.gw[i - 1], s.dims[i - 1], s.dims[i], s.B,
                                a_mn=True, b_mn=True)
                         pre_dw[i - 1] = after(side)
-                    if i - 1 in pre_dw and p.kind == "cnn" and not early:
-                        # nothing needs the (tiny) logits-layer weight gradient before the final
-                        # apply: let conv2's filter gradient go first on this stream
-                        deferred.append((s.act[i], dz, s.gw[i], din, dout))
+                    if head_fused and i == nl - 1 and s.head_dw:
+                        dw_done = after(side) if par else None   # dW_i came out of the fused head kernel
                     else:
                         # dW_i = act_i^T dZ_i
                         K.gemm(s.act[i], dz, s.gw[i], din, dout, s.B, a_mn=True, b_mn=True)
@@ -797,9 +804,6 @@ class B200StepRunner:
             fork(side)                           # dconv2p is ready
             with torch.cuda.stream(side):
                 K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
-                for a_, dz_, gw_, din_, dout_ in deferred:
-                    K.gemm(a_, dz_, gw_, din_, dout_, s.B, a_mn=True, b_mn=True)
-                deferred = []
             K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if par:                                  # join
@@ -1001,7 +1005,7 @@ class B200StepRunner:
                 s.y_dev.copy_(s.y_pin, non_blocking=True)
                 s.y_ready = torch.cuda.Event()
                 s.y_ready.record(self.side_stream)
-        elif with_io:
+        elif with_io and not s.zero_copy:
             s.io_dev.copy_(s.io_pin, non_blocking=True)
         clear_end = s.train and self.clear_at_end and self.sync_opt is None
         if not clear_end:

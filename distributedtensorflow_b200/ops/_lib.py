@@ -198,7 +198,7 @@ def _declare(lib):
         "dtf_mbox_daemon_stop": [vp],
         "dtf_graph_launch": [vp, vp],
         "dtf_host_wait_u32": [vp, C.c_uint, C.c_longlong],
-        "dtf_head_fused": [vp, i, i, vp, i, vp, vp, vp, i, i, i, vp, i, vp, vp, i, vp, vp, i, vp, vp],
+        "dtf_head_fused": [vp, i, i, vp, i, vp, vp, vp, i, i, i, vp, i, vp, vp, i, vp, vp, i, vp, vp, vp],
         "dtf_host_alloc_pinned": [C.POINTER(vp), C.c_size_t],
         "dtf_host_free_pinned": [vp],
     }

@@ -257,7 +257,8 @@ def f32_to_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
 def head_fused(act: torch.Tensor, H: int, w_ptr: int, ldw: int, bias_ptr: Optional[int],
                labels: torch.Tensor, B: int, num_classes: int, logits: torch.Tensor, loss_accum: torch.Tensor,
                dlogits: Optional[torch.Tensor] = None, dbias_accum: Optional[torch.Tensor] = None,
-               dact: Optional[torch.Tensor] = None, dprev_bias_accum: Optional[torch.Tensor] = None) -> None:
+               dact: Optional[torch.Tensor] = None, dprev_bias_accum: Optional[torch.Tensor] = None,
+               dw_accum: Optional[torch.Tensor] = None) -> None:
     """Classifier head in one launch (csrc/kernels/head_fused.cu): logits + loss (+ dlogits, bias
     gradients and the previous layer's masked activation gradient when training)."""
     sparse = labels.dtype == torch.int32
@@ -267,7 +268,7 @@ def head_fused(act: torch.Tensor, H: int, w_ptr: int, ldw: int, bias_ptr: Option
                                 B, num_classes, logits.data_ptr(), logits.stride(0), loss_accum.data_ptr(),
                                 _ptr(dlogits), dlogits.stride(0) if dlogits is not None else 0,
                                 _ptr(dbias_accum), _ptr(dact), dact.stride(0) if dact is not None else 0,
-                                _ptr(dprev_bias_accum), L.current_stream())
+                                _ptr(dprev_bias_accum), _ptr(dw_accum), L.current_stream())
     L.check(rc, "dtf_head_fused")
     _count()
 

@@ -111,7 +111,8 @@ int dtf_softmax_xent_dense(const float* logits, int ldl, const float* labels, in
 int dtf_head_fused(const void* act, int lda, int H, const void* w_shadow, int ldw, const float* bias,
                    const int* labels_sparse, const float* labels_dense, int ldy, int B, int C,
                    float* logits, int ldl, float* loss_accum, void* dlogits, int ldd,
-                   float* dbias_accum, void* dact, int lddact, float* dprev_bias_accum, void* stream);
+                   float* dbias_accum, void* dact, int lddact, float* dprev_bias_accum,
+                   float* dw_accum /* [H, C] fp32, zero on entry: += act^T dlogits; or NULL */, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * K9/K10: gradient push fused with the owning shard's optimizer apply. One launch walks a list

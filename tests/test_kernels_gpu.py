@@ -665,8 +665,9 @@ def test_head_fused_matches_separate_ops(K, B, H, dense):
     db = torch.zeros(C, device=dev)
     dact = torch.zeros(B, ldh, dtype=torch.bfloat16, device=dev)
     dbp = torch.zeros(H, device=dev)
+    dw = torch.zeros(H, C, device=dev)
     K.head_fused(act, H, W.data_ptr(), 16, bias.data_ptr(), labels, B, C, logits, loss,
-                 dlogits=dlogits, dbias_accum=db, dact=dact, dprev_bias_accum=dbp)
+                 dlogits=dlogits, dbias_accum=db, dact=dact, dprev_bias_accum=dbp, dw_accum=dw)
     torch.cuda.synchronize()
     a32, w32 = act[:, :H].float(), W[:, :C].float()
     z = (a32 @ w32 + bias).requires_grad_(True)
@@ -682,6 +683,7 @@ def test_head_fused_matches_separate_ops(K, B, H, dense):
     assert torch.allclose(dlogits[:, :C].float(), g, rtol=2e-2, atol=1e-6 + 4e-3 * g.abs().max().item())
     assert (dlogits[:, C:] == 0).all()
     assert torch.allclose(db, g.sum(0), rtol=1e-3, atol=1e-5 + 1e-3 * g.abs().max().item())
+    assert _rel_err(dw, a32.t() @ dlogits[:, :C].float()) < 1e-3
     ref_dact = (dlogits[:, :C].float() @ w32.t()) * (a32 > 0)
     assert _rel_err(dact[:, :H].float(), ref_dact) < 1e-2
     assert (dact[:, H:] == 0).all()
