@@ -244,7 +244,7 @@ class StepState:
                 zero.add(f"gb{i}", dims[i + 1])
             # the fused head kernel also accumulates the logits layer's weight gradient (atomics):
             # that buffer lives in the zeroed region
-            self.head_dw = bool(runner._head_is_fused())
+            self.head_dw = bool(runner._head_is_fused() and runner.head_dw)
             if self.head_dw:
                 zero.add("gw_last", dims[nl - 1] * dims[nl])
         if p.kind == "cnn":
@@ -311,6 +311,9 @@ class B200StepRunner:
         # logits GEMM + softmax-xent + dX GEMM of the last layer + bias column-sum as ONE kernel
         # (csrc/kernels/head_fused.cu) when the head has <= 16 classes
         self.fused_head = bool(opts.get("fused_head", True))
+        # ... and the logits layer's weight gradient too (327 K float atomics for the CNN head: measured
+        # +7 us on the critical path for a 10 us GEMM saved on the side stream, so off by default)
+        self.head_dw = bool(opts.get("head_dw", False))
         # the step's last kernel writes loss / global_step into pinned host memory and the host
         # spins on a sequence word: no D2H copy nodes, no stream synchronise per step
         self.host_sink = bool(opts.get("host_sink", True))
