@@ -45,9 +45,6 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
   griddep_wait();
   griddep_launch();
   if (threadIdx.x == 0) {
-    int it = 0;
-    while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
-    s_item = it;
     float lr_t = a.h.lr;
     if (OPT == DTF_OPT_ADAM) {
       // beta powers live on the PS (shared by all workers): t counts applies from everyone.
@@ -57,10 +54,18 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
     }
     s_lr_t = lr_t;
   }
+  // grid-stride over the 4096-element chunks: the grid may be capped (max_ctas) so that a big
+  // apply running beside compute kernels holds one slot per SM instead of flooding them
+  for (int vb = blockIdx.x; vb < a.total_blocks; vb += gridDim.x) {
+  if (threadIdx.x == 0) {
+    int it = 0;
+    while (it + 1 < a.n_items && vb >= a.block_start[it + 1]) ++it;
+    s_item = it;
+  }
   __syncthreads();
   const dtf_apply_item& it = a.items[s_item];
   const float lr_t = s_lr_t;
-  const long long base = static_cast<long long>(blockIdx.x - a.block_start[s_item]) * APPLY_CHUNK;
+  const long long base = static_cast<long long>(vb - a.block_start[s_item]) * APPLY_CHUNK;
   const bool vec_ok =
       ((reinterpret_cast<uintptr_t>(it.var) | reinterpret_cast<uintptr_t>(it.grad) |
         reinterpret_cast<uintptr_t>(it.slot0) | reinterpret_cast<uintptr_t>(it.slot1)) & 15) == 0;
@@ -149,6 +154,9 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
     }
   }
 
+  __syncthreads();   // s_item is rewritten by the next chunk
+  }  // grid-stride loop
+
   if (!a.finish) return;
   // ---- elect the last CTA; it performs _finish (K10) ----
   // bar.sync, then ONE thread fences (cumulative: it orders the whole CTA's stores) and takes a
@@ -160,8 +168,8 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
-    const unsigned int old = atomicInc(a.block_counter, static_cast<unsigned int>(a.total_blocks - 1));
-    s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
+    const unsigned int old = atomicInc(a.block_counter, gridDim.x - 1u);
+    s_last = (old == gridDim.x - 1u) ? 1u : 0u;
   }
   __syncthreads();
   if (!s_last) return;
@@ -220,14 +228,14 @@ extern "C" int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
                               unsigned long long* step_out, unsigned int* block_counter,
                               void* stream_) {
   return dtf_push_apply_ex(opt, items, n_items, hyper, ctrl_for_powers, ctrl_for_step, finish,
-                           worker_id, step_out, block_counter, nullptr, stream_);
+                           worker_id, step_out, block_counter, nullptr, 0, stream_);
 }
 
 extern "C" int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_items,
                                  const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
                                  dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                                  unsigned long long* step_out, unsigned int* block_counter,
-                                 const dtf_result_sink* sink, void* stream_) {
+                                 const dtf_result_sink* sink, int max_ctas, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "push_apply: %d items (max %d)",
               n_items, DTF_MAX_APPLY_ITEMS);
@@ -269,11 +277,12 @@ extern "C" int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_ite
     DTF_REQUIRE(sink->loss_src && sink->host_dst && sink->seq_dev, "push_apply: incomplete result sink");
     a.sink = *sink;
   }
+  const int grid = (max_ctas > 0 && blocks > max_ctas) ? max_ctas : blocks;
   switch (opt) {
-    case DTF_OPT_SGD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_SGD>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
-    case DTF_OPT_MOMENTUM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_MOMENTUM>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
-    case DTF_OPT_ADAGRAD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAGRAD>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
-    case DTF_OPT_ADAM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAM>, dim3(blocks), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_SGD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_SGD>, dim3(grid), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_MOMENTUM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_MOMENTUM>, dim3(grid), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAGRAD: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAGRAD>, dim3(grid), dim3(APPLY_THREADS), 0, stream, a)); break;
+    case DTF_OPT_ADAM: DTF_CHECK_CUDA(launch_kernel(push_apply_kernel<DTF_OPT_ADAM>, dim3(grid), dim3(APPLY_THREADS), 0, stream, a)); break;
     default: DTF_REQUIRE(false, "push_apply: unknown optimizer %d", opt);
   }
   DTF_LAUNCH_CHECK();

@@ -323,6 +323,7 @@ class B200StepRunner:
         # with the rest of the backward pass). With every shard local the applies are pure HBM work
         # that only fights the compute kernels for SMs: one apply kernel at the end is faster.
         self.early_apply = opts.get("early_apply", None)
+        self.early_apply_ctas = int(opts.get("early_apply_ctas", 0))   # cap the grid of overlapped applies
         # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
         # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
         # daemon (csrc/kernels/mailbox.cu, csrc/runtime/mbox_daemon.cu); "auto" = mailbox whenever
@@ -980,7 +981,8 @@ class B200StepRunner:
             items = K.make_apply_items(ch)
             K.push_apply(spec.code, items, len(ch), hyper, st.powers_ctrl, st.step_ctrl, last,
                          self.worker_id, s.step_dev.data_ptr() if last else None,
-                         s.counter.data_ptr(), sink=sink if last else None)
+                         s.counter.data_ptr(), sink=sink if last else None,
+                         max_ctas=0 if finish else self.early_apply_ctas)
 
     def _pull(self, s: StepState) -> None:
         if self.sync_opt is not None:

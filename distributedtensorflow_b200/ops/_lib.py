@@ -159,7 +159,7 @@ def _declare(lib):
         "dtf_softmax_xent_dense": [vp, i, vp, i, i, i, vp, vp, i, vp, vp],
         "dtf_push_apply": [i, C.POINTER(ApplyItem), i, C.POINTER(ApplyHyper), vp, vp, i, i, vp, vp, vp],
         "dtf_push_apply_ex": [i, C.POINTER(ApplyItem), i, C.POINTER(ApplyHyper), vp, vp, i, i, vp, vp,
-                              C.POINTER(ResultSink), vp],
+                              C.POINTER(ResultSink), i, vp],
         "dtf_pull_bulk": [C.POINTER(CopyItem), i, vp, vp, vp],
         "dtf_refresh_shadow": [vp, vp, ll, ll, i, i, vp],
         "dtf_u8_to_bf16": [vp, vp, i, i, i, f, vp],

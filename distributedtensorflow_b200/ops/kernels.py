@@ -161,11 +161,11 @@ def make_sink(loss_ptr: int, host_ptr: int, seq_ptr: int) -> L.ResultSink:
 def push_apply(opt: int, items, n_items: int, hyper: L.ApplyHyper, ctrl_powers: Optional[int],
                ctrl_step: Optional[int], finish: bool, worker_id: int,
                step_out: Optional[int], block_counter: Optional[int],
-               sink: Optional[L.ResultSink] = None) -> None:
+               sink: Optional[L.ResultSink] = None, max_ctas: int = 0) -> None:
     rc = L.lib().dtf_push_apply_ex(opt, items, n_items, C.byref(hyper), ctrl_powers, ctrl_step,
                                    int(finish), worker_id, step_out, block_counter,
                                    C.byref(sink) if (sink is not None and finish) else None,
-                                   L.current_stream())
+                                   int(max_ctas), L.current_stream())
     L.check(rc, "dtf_push_apply")
     _count()
 

@@ -157,12 +157,14 @@ int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
                    const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
                    dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                    unsigned long long* step_out, unsigned int* block_counter, void* stream);
-/* Same, and the finishing thread also fills `sink` (may be NULL). */
+/* Same, and the finishing thread also fills `sink` (may be NULL). max_ctas > 0 caps the grid (the
+ * kernel strides over its 4096-element chunks): an apply that overlaps compute kernels then holds
+ * one CTA slot per SM instead of flooding the SMs. */
 int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_items,
                       const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
                       dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                       unsigned long long* step_out, unsigned int* block_counter,
-                      const dtf_result_sink* sink, void* stream);
+                      const dtf_result_sink* sink, int max_ctas, void* stream);
 
 /* dtf_push_apply for callers that cannot allocate device memory (no counterpart in the reference:
  * TensorFlow's ApplyAdam kernels allocate through the TF runtime). Same arguments and result as
