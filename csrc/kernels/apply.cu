@@ -84,6 +84,8 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
     ldg_[u] = ldv_[u] = ld0_[u] = ld1_[u] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (vec_ok && i + APPLY_VEC <= it.n) {
       ldg_[u] = *reinterpret_cast<const float4*>(it.grad + i);
+      if (it.zero_grad)  // self-cleaning accumulator: ready for the next step's atomics
+        *reinterpret_cast<float4*>(const_cast<float*>(it.grad) + i) = make_float4(0.f, 0.f, 0.f, 0.f);
       if (rmw) {
         ldv_[u] = *reinterpret_cast<const float4*>(it.var + i);
         if (OPT != DTF_OPT_SGD) ld0_[u] = *reinterpret_cast<const float4*>(it.slot0 + i);
@@ -135,6 +137,7 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
     } else {
       for (int j = 0; j < APPLY_VEC && i + j < it.n; ++j) {
         const float g = it.grad[i + j] * a.h.grad_scale;
+        if (it.zero_grad) const_cast<float*>(it.grad)[i + j] = 0.f;
         if (OPT == DTF_OPT_SGD && a.h.atomic_sgd) {
           red_add_f32_sys(it.var + i + j, -a.h.lr * g);
           continue;
@@ -191,6 +194,7 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
     atomicAdd(&a.ctrl_step->apply_count, 1u);
   } else if (threadIdx.x == 32 && sink) {
     s_loss = *reinterpret_cast<const volatile float*>(a.sink.loss_src);
+    if (a.sink.clear_loss) *const_cast<volatile float*>(a.sink.loss_src) = 0.f;
   } else if (threadIdx.x == 64 && sink) {
     const unsigned int q = *reinterpret_cast<volatile unsigned int*>(a.sink.seq_dev) + 1u;
     *reinterpret_cast<volatile unsigned int*>(a.sink.seq_dev) = q;

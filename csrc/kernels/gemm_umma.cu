@@ -403,7 +403,11 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
               float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (nb + j < p.ldws) t = __ldcg(reinterpret_cast<const float4*>(wrow + j));
+              if (nb + j < p.ldws) {
+                t = __ldcg(reinterpret_cast<const float4*>(wrow + j));
+                // self-resetting workspace: the next GEMM's partial sums start from zero again
+                __stcg(reinterpret_cast<float4*>(const_cast<float*>(wrow) + j), make_float4(0.f, 0.f, 0.f, 0.f));
+              }
               v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
             }
             gemm_epilogue_store(p, m, nb, v);

@@ -319,6 +319,9 @@ class B200StepRunner:
         self.host_sink = bool(opts.get("host_sink", True))
         # the step's first kernel reads the input batch in place from pinned host memory
         self.zero_copy_input = bool(opts.get("zero_copy_input", True))
+        # accumulators clean themselves (the apply zeroes the gradients it consumed, the split-K
+        # fix-up its workspace, the finishing thread the loss): no fill kernel at the end of the step
+        self.self_clean = bool(opts.get("self_clean", True))
         # push(+apply) of each dense kernel as soon as its gradient exists (overlaps NVLink traffic
         # with the rest of the backward pass). With every shard local the applies are pure HBM work
         # that only fights the compute kernels for SMs: one apply kernel at the end is faster.
@@ -954,7 +957,8 @@ class B200StepRunner:
             self._mbox_wait(self._pushes)
 
     def _sink(self, s: StepState):
-        return K.make_sink(s.z["loss"].data_ptr(), s.res_pin.data_ptr(), s.res_seq_dev.data_ptr())
+        return K.make_sink(s.z["loss"].data_ptr(), s.res_pin.data_ptr(), s.res_seq_dev.data_ptr(),
+                           clear_loss=self._self_cleans(s))
 
     def _apply_vars(self, s: StepState, variables: Sequence[G.Variable], finish: bool) -> None:
         """push+apply of ``variables`` on the current stream; ``finish`` adds TF's _finish (beta
@@ -965,12 +969,16 @@ class B200StepRunner:
         st, spec = self.store, self.spec
         sink = self._sink(s) if (finish and self._uses_sink(s)) else None
         entries = []
+        zb = s.zero.buf.data_ptr()
+        ze = zb + s.zero.buf.numel() * 4
+        clean = self._self_cleans(s)
         for var in variables:
             gptr = self._grad_ptr(s, var)
             for r in self._regions_rotated(var):
                 entries.append(dict(var=st.var_ptr(r), slot0=st.slot_ptr(r, 0), slot1=st.slot_ptr(r, 1),
                                     shadow=st.shadow_ptr(r), grad=gptr + r.sl.first * 4, n=r.sl.n,
-                                    first=0, cols=r.cols, shadow_ld=r.shadow_ld))
+                                    first=0, cols=r.cols, shadow_ld=r.shadow_ld,
+                                    zero_grad=int(clean and zb <= gptr < ze)))
         hyper = K.make_hyper(spec.learning_rate, spec.beta1, spec.beta2, spec.epsilon, spec.momentum,
                              1.0, spec.use_nesterov, self.atomic_sgd and spec.kind == "sgd")
         chunks = [entries[i:i + L.MAX_APPLY_ITEMS] for i in range(0, len(entries), L.MAX_APPLY_ITEMS)]
@@ -991,6 +999,12 @@ class B200StepRunner:
             self.mirror_filled = True
         if self.copies:
             K.pull_bulk(self.copies, self.store.step_ctrl, s.step_dev.data_ptr() + 8)
+
+    def _self_cleans(self, s: StepState) -> bool:
+        """True when every buffer of the zeroed region is reset by its consumer (worker-side apply
+        with a result sink, every dense layer has a bias so each column sum is consumed)."""
+        return (self.self_clean and self._uses_sink(s) and not self.use_mailbox and self.clear_at_end
+                and not (self.fused_apply) and all(d.b is not None for d in self.plan.dense))
 
     def _uses_sink(self, s: StepState) -> bool:
         return self.host_sink and s.train and self.sync_opt is None
@@ -1027,7 +1041,7 @@ class B200StepRunner:
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
             if self.sync_opt is None or not s.train:
                 s.step_pin.copy_(s.step_dev, non_blocking=True)
-        if clear_end:
+        if clear_end and not self._self_cleans(s):
             # the accumulators were consumed by the applies above: clearing them now (instead of at
             # the start of the next step) takes the fill kernel off the next step's critical path
             K.fill_u32(s.zero.buf, 0)

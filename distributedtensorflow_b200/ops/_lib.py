@@ -91,6 +91,8 @@ class ApplyItem(C.Structure):
         ("first", C.c_longlong),
         ("cols", C.c_int),
         ("shadow_ld", C.c_int),
+        ("zero_grad", C.c_int),
+        ("reserved", C.c_int),
     ]
 
 
@@ -135,7 +137,8 @@ MBOX_OFF_PRODUCED, MBOX_OFF_CONSUMED, MBOX_OFF_DONE = 0, 128, 256
 
 class ResultSink(C.Structure):
     """Mirror of ``dtf_result_sink``."""
-    _fields_ = [("loss_src", C.c_void_p), ("host_dst", C.c_void_p), ("seq_dev", C.c_void_p)]
+    _fields_ = [("loss_src", C.c_void_p), ("host_dst", C.c_void_p), ("seq_dev", C.c_void_p),
+                ("clear_loss", C.c_int), ("reserved", C.c_int)]
 
 
 class NativeError(RuntimeError):

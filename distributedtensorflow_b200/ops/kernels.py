@@ -139,6 +139,7 @@ def make_apply_items(entries: Sequence[dict]) -> "C.Array":
         it.first = e.get("first", 0)
         it.cols = e.get("cols", 1)
         it.shadow_ld = e.get("shadow_ld", e.get("cols", 1))
+        it.zero_grad = int(e.get("zero_grad", 0))
     return arr
 
 
@@ -152,9 +153,10 @@ def make_hyper(lr: float, beta1: float = 0.9, beta2: float = 0.999, epsilon: flo
     return h
 
 
-def make_sink(loss_ptr: int, host_ptr: int, seq_ptr: int) -> L.ResultSink:
+def make_sink(loss_ptr: int, host_ptr: int, seq_ptr: int, clear_loss: bool = False) -> L.ResultSink:
     sk = L.ResultSink()
     sk.loss_src, sk.host_dst, sk.seq_dev = loss_ptr, host_ptr, seq_ptr
+    sk.clear_loss = int(clear_loss)
     return sk
 
 

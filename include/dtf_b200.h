@@ -61,7 +61,8 @@ typedef struct dtf_gemm_epilogue {
   /* split-K with in-kernel fix-up (splits > 1 and reduce = 0): K-slices sum into this fp32
    * workspace and the last slice of each tile runs the epilogue above. Both must be zero on
    * entry; the counters reset themselves, the workspace does not. */
-  float* splitk_ws;             /* [M, ldws] fp32, 16-byte aligned, ldws % 4 == 0, ldws >= N */
+  float* splitk_ws;             /* [M, ldws] fp32, 16-byte aligned, ldws % 4 == 0, ldws >= N; zero on
+                                   entry, and left zero again by the fix-up */
   int ldws;
   unsigned int* tile_counters;  /* ceil(M/128) * ceil(N/block_n) words */
   /* Fused gradient push + optimizer apply (weight-gradient GEMMs, K2 + K9 in one kernel): when
@@ -134,6 +135,9 @@ typedef struct dtf_apply_item {
   long long first;     /* flat index of the slice's first element inside the variable */
   int cols;            /* variable's innermost dim (for the padded shadow layout) */
   int shadow_ld;       /* shadow row pitch in elements */
+  int zero_grad;       /* dtf_push_apply: store 0 back into grad after reading it (the gradient is an
+                          atomically accumulated buffer that must be clear for the next step) */
+  int reserved;
 } dtf_apply_item;
 typedef struct dtf_apply_hyper {
   float lr, beta1, beta2, epsilon, momentum, grad_scale;
@@ -152,6 +156,8 @@ typedef struct dtf_result_sink {
   const float* loss_src;     /* device: the step's accumulated loss */
   unsigned int* host_dst;    /* pinned host memory, 4 words */
   unsigned int* seq_dev;     /* device counter of steps reported */
+  int clear_loss;            /* dtf_push_apply_ex: reset *loss_src to 0 after reading it */
+  int reserved;
 } dtf_result_sink;
 int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
                    const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,
