@@ -69,6 +69,7 @@ struct GemmParams {
   float* ws;                // [M, ldws] fp32, zero on entry
   int ldws;
   unsigned int* counters;   // one per output tile, zero on entry (self-resetting)
+  int ws_clean;             // the fix-up leaves the workspace zeroed
   // fused push + optimizer apply (see dtf_gemm_epilogue)
   int apply_opt;
   int apply_rows_per_slice;
@@ -406,7 +407,8 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
               if (nb + j < p.ldws) {
                 t = __ldcg(reinterpret_cast<const float4*>(wrow + j));
                 // self-resetting workspace: the next GEMM's partial sums start from zero again
-                __stcg(reinterpret_cast<float4*>(const_cast<float*>(wrow) + j), make_float4(0.f, 0.f, 0.f, 0.f));
+                if (p.ws_clean)
+                  __stcg(reinterpret_cast<float4*>(const_cast<float*>(wrow) + j), make_float4(0.f, 0.f, 0.f, 0.f));
               }
               v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
             }
@@ -713,6 +715,13 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
   p.ws = epi->splitk_ws;
   p.ldws = epi->ldws;
   p.counters = epi->tile_counters;
+  {
+    static int ws_clean = -1;
+    // measured: re-zeroing the tile from the fix-up CTA (load + store to the same lines) costs
+    // 6-20 us per GEMM on the MNIST shapes, a separate fill of the workspace is cheaper -> opt-in
+    if (ws_clean < 0) ws_clean = getenv("DTF_GEMM_WS_CLEAN") ? 1 : 0;
+    p.ws_clean = ws_clean;
+  }
   p.apply_opt = epi->apply_enable ? epi->apply_opt : -1;
   if (epi->apply_enable) {
     DTF_REQUIRE(p.apply_opt >= 0, "gemm: unknown optimizer %d", p.apply_opt);

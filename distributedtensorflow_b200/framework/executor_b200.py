@@ -171,7 +171,10 @@ class _Zero:
         total = sum(n for _, n in self.sizes)
         self.buf = torch.zeros(max(total, 64), dtype=torch.float32, device=device)
         out, o = {}, 0
+        self.ws_off = None                 # split-K workspaces / counters are added last: [ws_off, end)
         for name, n in self.sizes:
+            if self.ws_off is None and (name.startswith("ws_") or name.startswith("ct_")):
+                self.ws_off = o
             out[name] = self.buf[o:o + n]
             o += n
         return out
@@ -804,6 +807,7 @@ class B200StepRunner:
                     else:
                         self._apply_vars(s, [d.w], finish=False)
                 applied.append(d.w)
+        clean_ws = self._self_cleans(s) and s.zero.ws_off is not None
         if p.kind == "cnn":
             c1, c2 = p.convs
             scale = 1.0 / 255.0 if s.x_dev.dtype == torch.uint8 else 1.0
@@ -811,6 +815,13 @@ class B200StepRunner:
             fork(side)                           # dconv2p is ready
             with torch.cuda.stream(side):
                 K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
+                if clean_ws:                     # every split-K GEMM of the step is done: re-zero
+                    K.fill_u32(s.zero.buf[s.zero.ws_off:], 0)   # their workspaces beside the conv backward
+                    clean_ws = False
+        if clean_ws:
+            fork(side)
+            with torch.cuda.stream(side):
+                K.fill_u32(s.zero.buf[s.zero.ws_off:], 0)
             K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if par:                                  # join

@@ -62,7 +62,8 @@ typedef struct dtf_gemm_epilogue {
    * workspace and the last slice of each tile runs the epilogue above. Both must be zero on
    * entry; the counters reset themselves, the workspace does not. */
   float* splitk_ws;             /* [M, ldws] fp32, 16-byte aligned, ldws % 4 == 0, ldws >= N; zero on
-                                   entry, and left zero again by the fix-up */
+                                   entry (the caller re-zeroes it; DTF_GEMM_WS_CLEAN=1 makes the
+                                   fix-up do it, which measured slower) */
   int ldws;
   unsigned int* tile_counters;  /* ceil(M/128) * ceil(N/block_n) words */
   /* Fused gradient push + optimizer apply (weight-gradient GEMMs, K2 + K9 in one kernel): when
