@@ -818,12 +818,12 @@ class B200StepRunner:
                 if clean_ws:                     # every split-K GEMM of the step is done: re-zero
                     K.fill_u32(s.zero.buf[s.zero.ws_off:], 0)   # their workspaces beside the conv backward
                     clean_ws = False
+            K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
+            K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if clean_ws:
             fork(side)
             with torch.cuda.stream(side):
                 K.fill_u32(s.zero.buf[s.zero.ws_off:], 0)
-            K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
-            K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if par:                                  # join
             main.wait_event(after(side))
             if apl is not main:
