@@ -135,30 +135,35 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   }
 }
 
-// Two CTAs (800 threads = 25 taps x 32 channels) per image: thread (tap, c) accumulates
-// dW1[tap, c] over its half of the image's 196 pooled pixels; warp 0 also accumulates db1.
-__global__ void __launch_bounds__(800)
+// conv1 filter / bias gradient. One CTA (8 warps) per image. lane = output channel, warp w walks the
+// pooled pixels w, w+8, ...: for each (pixel, channel) it reads the argmax position and the
+// ReLU-masked gradient ONCE and sweeps the 25 taps with 25 register accumulators (1 smem load per
+// FMA; the previous thread-per-(tap, channel) layout needed 3). The 8 warps' partial filters are
+// combined in shared memory, so an image costs 800 + 32 global atomics.
+constexpr int C1B_WARPS = 8;
+constexpr int C1_PIX = C1_OUT * C1_OUT;  // 196 pooled pixels
+
+__global__ void __launch_bounds__(C1B_WARPS * 32)
 conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
                  float scale, const __nv_bfloat16* __restrict__ dpool1,
                  const __nv_bfloat16* __restrict__ pool1p, const unsigned char* __restrict__ amax1,
                  float* __restrict__ dw1_accum, float* __restrict__ db1_accum) {
   __shared__ float img[C1_PAD][C1_PITCH];
-  __shared__ float g[C1_OUT * C1_OUT][C1_CH];          // 25 KB
-  __shared__ __align__(16) unsigned char am[C1_OUT * C1_OUT][C1_CH]; // 6 KB
+  // g [196][32] fp32 followed by am [196][32] u8; reused for the cross-warp reduction afterwards
+  __shared__ __align__(16) unsigned char buf[C1_PIX * C1_CH * 4 + C1_PIX * C1_CH];
+  float (*g)[C1_CH] = reinterpret_cast<float (*)[C1_CH]>(buf);
+  unsigned char (*am)[C1_CH] = reinterpret_cast<unsigned char (*)[C1_CH]>(buf + C1_PIX * C1_CH * 4);
   const int n = blockIdx.x;
   griddep_wait();
   griddep_launch();
   load_image_padded(img, x_u8, x_f32, scale, n);
-  // stage the ReLU-masked gradient and the argmax map: one (pooled pixel, 8 channels) item per
-  // thread, 16-byte loads, a single pass (784 items <= 800 threads)
-  constexpr int HALF = C1_OUT * C1_OUT / 2;       // blockIdx.y picks the upper / lower 7 pooled rows
-  const int pp0 = blockIdx.y * HALF;
-  for (int item = threadIdx.x; item < HALF * 4; item += blockDim.x) {
-    const int pp = pp0 + (item >> 2), cg = item & 3;
+  // stage the ReLU-masked gradient and the argmax map: (pooled pixel, 8 channels) items, 16-byte loads
+  for (int item = threadIdx.x; item < C1_PIX * 4; item += blockDim.x) {
+    const int pp = item >> 2, cg = item & 3;
     const int py = pp / C1_OUT, px = pp % C1_OUT;
     const uint4 av = *reinterpret_cast<const uint4*>(
         pool1p + ((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + cg * 8);
-    const size_t o = (static_cast<size_t>(n) * (C1_OUT * C1_OUT) + pp) * C1_CH + cg * 8;
+    const size_t o = (static_cast<size_t>(n) * C1_PIX + pp) * C1_CH + cg * 8;
     const uint4 dv = *reinterpret_cast<const uint4*>(dpool1 + o);
     const uint2 mv = *reinterpret_cast<const uint2*>(amax1 + o);
     const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(&av);
@@ -169,21 +174,37 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
     *reinterpret_cast<uint2*>(&am[pp][cg * 8]) = mv;
   }
   __syncthreads();
-  const int tap = threadIdx.x >> 5, c = threadIdx.x & 31;
-  const int r = tap / 5, s = tap % 5;
-  float acc[4] = {0.f, 0.f, 0.f, 0.f}, accb = 0.f;
-  for (int py = blockIdx.y * (C1_OUT / 2); py < (blockIdx.y + 1) * (C1_OUT / 2); ++py) {
+  const int warp = threadIdx.x >> 5, c = threadIdx.x & 31;
+  float acc[25];
 #pragma unroll
-    for (int px = 0; px < C1_OUT; ++px) {  // 14 independent smem chains per row
-      const int pp = py * C1_OUT + px;
-      const int a = am[pp][c];
-      const float gv = g[pp][c];
-      acc[px & 3] = fmaf(img[2 * py + (a >> 1) + r][2 * px + (a & 1) + s], gv, acc[px & 3]);
-      accb += gv;
-    }
+  for (int t = 0; t < 25; ++t) acc[t] = 0.f;
+  float accb = 0.f;
+  for (int pp = warp; pp < C1_PIX; pp += C1B_WARPS) {
+    const int py = pp / C1_OUT, px = pp - py * C1_OUT;
+    const int a = am[pp][c];
+    const float gv = g[pp][c];
+    const float* base = &img[2 * py + (a >> 1)][2 * px + (a & 1)];
+#pragma unroll
+    for (int r = 0; r < 5; ++r)
+#pragma unroll
+      for (int q = 0; q < 5; ++q) acc[r * 5 + q] = fmaf(base[r * C1_PITCH + q], gv, acc[r * 5 + q]);
+    accb += gv;
   }
-  atomicAdd(&dw1_accum[tap * C1_CH + c], (acc[0] + acc[1]) + (acc[2] + acc[3]));
-  if (tap == 0) atomicAdd(&db1_accum[c], accb);
+  __syncthreads();  // g / am are dead: their storage becomes red[warp][26][32]
+  float (*red)[26][C1_CH] = reinterpret_cast<float (*)[26][C1_CH]>(buf);
+  static_assert(C1B_WARPS * 26 * C1_CH * 4 <= C1_PIX * C1_CH * 4 + C1_PIX * C1_CH, "reduction buffer");
+#pragma unroll
+  for (int t = 0; t < 25; ++t) red[warp][t][c] = acc[t];
+  red[warp][25][c] = accb;
+  __syncthreads();
+  for (int i = threadIdx.x; i < 26 * C1_CH; i += blockDim.x) {
+    const int t = i / C1_CH, cc = i % C1_CH;
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < C1B_WARPS; ++w) v += red[w][t][cc];
+    if (t < 25) atomicAdd(&dw1_accum[t * C1_CH + cc], v);
+    else atomicAdd(&db1_accum[cc], v);
+  }
 }
 
 // pool2 gradient + ReLU gradient, scattered into the zero-bordered [B,18,18,64] layout conv2's
@@ -277,7 +298,7 @@ extern "C" int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, floa
                              const void* dpool1, const void* pool1p, const unsigned char* amax1,
                              float* dw1_accum, float* db1_accum, int B, void* stream) {
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_bwd: pass exactly one of x_u8/x_f32");
-  DTF_CHECK_CUDA(launch_kernel(conv1_bwd_kernel, dim3(B, 2), dim3(800), 0,
+  DTF_CHECK_CUDA(launch_kernel(conv1_bwd_kernel, dim3(B), dim3(C1B_WARPS * 32), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale,
                                reinterpret_cast<const __nv_bfloat16*>(dpool1),
                                reinterpret_cast<const __nv_bfloat16*>(pool1p),
