@@ -135,13 +135,15 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   }
 }
 
-// conv1 filter / bias gradient. One CTA (8 warps) per image. lane = output channel, warp w walks the
-// pooled pixels w, w+8, ...: for each (pixel, channel) it reads the argmax position and the
-// ReLU-masked gradient ONCE and sweeps the 25 taps with 25 register accumulators (1 smem load per
-// FMA; the previous thread-per-(tap, channel) layout needed 3). The 8 warps' partial filters are
-// combined in shared memory, so an image costs 800 + 32 global atomics.
-constexpr int C1B_WARPS = 8;
-constexpr int C1_PIX = C1_OUT * C1_OUT;  // 196 pooled pixels
+// conv1 filter / bias gradient. Two CTAs of 16 warps per image (upper / lower 7 pooled rows).
+// lane = output channel, warp w walks the pooled pixels w, w+16, ...: for each (pixel, channel) it
+// reads the argmax position and the ReLU-masked gradient ONCE and sweeps the 25 taps with 25
+// register accumulators (1 smem load per FMA; a thread-per-(tap, channel) layout needs 3). The
+// image arrives with 16-byte loads and every staging loop is a single pass, so the kernel is one
+// global round trip deep. The 16 warps' partial filters are combined in shared memory (two
+// rounds), so a CTA issues 26 coalesced 128-byte reductions.
+constexpr int C1B_WARPS = 16;
+constexpr int C1_HALF = C1_OUT * C1_OUT / 2;  // 98 pooled pixels per CTA
 
 __global__ void __launch_bounds__(C1B_WARPS * 32)
 conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
@@ -149,29 +151,36 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
                  const __nv_bfloat16* __restrict__ pool1p, const unsigned char* __restrict__ amax1,
                  float* __restrict__ dw1_accum, float* __restrict__ db1_accum) {
   __shared__ float img[C1_PAD][C1_PITCH];
-  // g [196][32] fp32 followed by am [196][32] u8; reused for the cross-warp reduction afterwards
-  __shared__ __align__(16) unsigned char buf[C1_PIX * C1_CH * 4 + C1_PIX * C1_CH];
-  float (*g)[C1_CH] = reinterpret_cast<float (*)[C1_CH]>(buf);
-  unsigned char (*am)[C1_CH] = reinterpret_cast<unsigned char (*)[C1_CH]>(buf + C1_PIX * C1_CH * 4);
+  __shared__ float g[C1_HALF][C1_CH];                                 // 12.5 KB
+  __shared__ __align__(16) unsigned char am[C1_HALF][C1_CH];          // 3 KB
+  __shared__ __align__(16) float red[C1B_WARPS / 2][26][C1_CH];       // 26.6 KB (also the raw image)
   const int n = blockIdx.x;
+  const int pp0 = blockIdx.y * C1_HALF;
   griddep_wait();
   griddep_launch();
-  load_image_padded(img, x_u8, x_f32, scale, n);
-  // stage the ReLU-masked gradient and the argmax map: (pooled pixel, 8 channels) items, 16-byte loads
-  for (int item = threadIdx.x; item < C1_PIX * 4; item += blockDim.x) {
-    const int pp = item >> 2, cg = item & 3;
+  // (pooled pixel, 8 channels) items: issue their global loads first, the image's next
+  const int item = threadIdx.x;
+  uint4 av = make_uint4(0, 0, 0, 0), dv = av;
+  uint2 mv = make_uint2(0, 0);
+  const int ipp = item >> 2, icg = item & 3;
+  if (item < C1_HALF * 4) {
+    const int pp = pp0 + ipp;
     const int py = pp / C1_OUT, px = pp % C1_OUT;
-    const uint4 av = *reinterpret_cast<const uint4*>(
-        pool1p + ((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + cg * 8);
-    const size_t o = (static_cast<size_t>(n) * C1_PIX + pp) * C1_CH + cg * 8;
-    const uint4 dv = *reinterpret_cast<const uint4*>(dpool1 + o);
-    const uint2 mv = *reinterpret_cast<const uint2*>(amax1 + o);
+    av = *reinterpret_cast<const uint4*>(
+        pool1p + ((static_cast<size_t>(n) * C1_HP + (py + 2)) * C1_HP + (px + 2)) * C1_CH + icg * 8);
+    const size_t o = (static_cast<size_t>(n) * (C1_OUT * C1_OUT) + pp) * C1_CH + icg * 8;
+    dv = *reinterpret_cast<const uint4*>(dpool1 + o);
+    mv = *reinterpret_cast<const uint2*>(amax1 + o);
+  }
+  ingest_image_padded(img, reinterpret_cast<unsigned char*>(red), x_u8, x_f32, nullptr, nullptr, scale,
+                      n, false);
+  if (item < C1_HALF * 4) {
     const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(&av);
     const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(&dv);
 #pragma unroll
     for (int j = 0; j < 8; ++j)  // ReLU gradient through the max-pool
-      g[pp][cg * 8 + j] = (__bfloat162float(a[j]) > 0.f) ? __bfloat162float(d[j]) : 0.f;
-    *reinterpret_cast<uint2*>(&am[pp][cg * 8]) = mv;
+      g[ipp][icg * 8 + j] = (__bfloat162float(a[j]) > 0.f) ? __bfloat162float(d[j]) : 0.f;
+    *reinterpret_cast<uint2*>(&am[ipp][icg * 8]) = mv;
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, c = threadIdx.x & 31;
@@ -179,10 +188,11 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
 #pragma unroll
   for (int t = 0; t < 25; ++t) acc[t] = 0.f;
   float accb = 0.f;
-  for (int pp = warp; pp < C1_PIX; pp += C1B_WARPS) {
+  for (int lp = warp; lp < C1_HALF; lp += C1B_WARPS) {
+    const int pp = pp0 + lp;
     const int py = pp / C1_OUT, px = pp - py * C1_OUT;
-    const int a = am[pp][c];
-    const float gv = g[pp][c];
+    const int a = am[lp][c];
+    const float gv = g[lp][c];
     const float* base = &img[2 * py + (a >> 1)][2 * px + (a & 1)];
 #pragma unroll
     for (int r = 0; r < 5; ++r)
@@ -190,18 +200,24 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
       for (int q = 0; q < 5; ++q) acc[r * 5 + q] = fmaf(base[r * C1_PITCH + q], gv, acc[r * 5 + q]);
     accb += gv;
   }
-  __syncthreads();  // g / am are dead: their storage becomes red[warp][26][32]
-  float (*red)[26][C1_CH] = reinterpret_cast<float (*)[26][C1_CH]>(buf);
-  static_assert(C1B_WARPS * 26 * C1_CH * 4 <= C1_PIX * C1_CH * 4 + C1_PIX * C1_CH, "reduction buffer");
+  // cross-warp reduction in two rounds (warps 0-7 store, warps 8-15 add), then 26 x 32 sums
+  if (warp < C1B_WARPS / 2) {
 #pragma unroll
-  for (int t = 0; t < 25; ++t) red[warp][t][c] = acc[t];
-  red[warp][25][c] = accb;
+    for (int t = 0; t < 25; ++t) red[warp][t][c] = acc[t];
+    red[warp][25][c] = accb;
+  }
+  __syncthreads();
+  if (warp >= C1B_WARPS / 2) {
+#pragma unroll
+    for (int t = 0; t < 25; ++t) red[warp - C1B_WARPS / 2][t][c] += acc[t];
+    red[warp - C1B_WARPS / 2][25][c] += accb;
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < 26 * C1_CH; i += blockDim.x) {
     const int t = i / C1_CH, cc = i % C1_CH;
     float v = 0.f;
 #pragma unroll
-    for (int w = 0; w < C1B_WARPS; ++w) v += red[w][t][cc];
+    for (int w = 0; w < C1B_WARPS / 2; ++w) v += red[w][t][cc];
     if (t < 25) atomicAdd(&dw1_accum[t * C1_CH + cc], v);
     else atomicAdd(&db1_accum[cc], v);
   }
@@ -298,7 +314,7 @@ extern "C" int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, floa
                              const void* dpool1, const void* pool1p, const unsigned char* amax1,
                              float* dw1_accum, float* db1_accum, int B, void* stream) {
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_bwd: pass exactly one of x_u8/x_f32");
-  DTF_CHECK_CUDA(launch_kernel(conv1_bwd_kernel, dim3(B), dim3(C1B_WARPS * 32), 0,
+  DTF_CHECK_CUDA(launch_kernel(conv1_bwd_kernel, dim3(B, 2), dim3(C1B_WARPS * 32), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale,
                                reinterpret_cast<const __nv_bfloat16*>(dpool1),
                                reinterpret_cast<const __nv_bfloat16*>(pool1p),
