@@ -679,9 +679,14 @@ class B200StepRunner:
                    relu=d.relu, b_ptr=wp, ldb=ld, **self._plan_kw(s, f"fwd{i}"))
 
     def _head_is_fused(self) -> bool:
+        """The one-kernel head is a latency optimisation for the reference models' small heads
+        (128 x 1024 -> 10, 100 x 100 -> 10). A wide hidden layer (the 8192-unit MLP) keeps the
+        tensor-core GEMMs: the CUDA-core head would need B/4 CTAs x H atomics for the bias gradient."""
         p = self.plan
         nl = len(p.dense)
         if not self.fused_head or nl < 2 or p.num_classes > 16:
+            return False
+        if int(p.dense[-1].w.shape[0]) > 2048:
             return False
         return self.wptr[p.dense[-1].w.name][1] == 16
 
