@@ -295,6 +295,10 @@ def main() -> int:
                        "cuda_graph": not args.no_cuda_graph, "pdl": not args.no_pdl,
                        "split_k": not args.no_split_k, "overlap": not args.no_overlap,
                        "fused_apply": args.fused_apply,
+                       "step_io": ("inputs: the step's first kernel reads the batch in place from pinned host memory "
+                                   "over PCIe (%d B/step); results: the last kernel stores loss + global_step into "
+                                   "pinned host memory (%d B/step)" % (h2d, d2h)) if runner.zero_copy_input and runner.host_sink
+                                  else "cudaMemcpyAsync H2D of the pinned batch, D2H of loss + global_step",
                        "push": ("mailbox: posted gradient stores + owner-side apply daemon, depth %d"
                                 % runner.store.arena.mailbox_depth) if runner.use_mailbox
                                else "rmw: worker-side fused push+apply"},

@@ -149,3 +149,56 @@ def test_device_setter_edge_cases():
     assert fn(P.OpInfo("m", type="MatMul")) == "/job:worker"
     # merge_devices: an outer, more specific device wins over the setter's fields
     assert fn(P.OpInfo("v", device="/job:ps/task:2")) == "/job:ps/task:2"
+
+
+def test_arena_layout_with_async_mailboxes_is_consistent():
+    """Device arena of the B200 data plane (parallel/nvl.py): var / slots / serving copy regions,
+    the per-shard mailbox flag block and `depth` mailbox buffers per worker must never overlap,
+    every region must keep the alignment its kernels assume, and every task must derive the same
+    layout (between-graph replication: nobody ships offsets around)."""
+    from distributedtensorflow_b200.ops import _lib as L
+    from distributedtensorflow_b200.parallel.nvl import build_arena_layout
+    from distributedtensorflow_b200.train.optimizers import OptimizerSpec
+    vs = _build_cnn(8, P.FlatSlicedStrategy(8))
+    layout = build_layout(vs, 8)
+    names = [v.name for v in tf.trainable_variables()]
+    spec = OptimizerSpec("adam", 5e-4)
+    W, depth = 8, 4
+    al = build_arena_layout(layout, 8, spec, names, sync_workers=W, mailbox_depth=depth, mirrors=False)
+    again = build_arena_layout(layout, 8, spec, names, sync_workers=W, mailbox_depth=depth, mirrors=False)
+    assert al.shard_bytes == again.shard_bytes and al.mailbox_off == again.mailbox_off
+    for sh in range(8):
+        spans = [(0, L.CTRL_BYTES)]
+        for name, regs in al.regions.items():
+            for r in regs:
+                if r.shard != sh:
+                    continue
+                assert r.var_off % 256 == 0
+                spans.append((r.var_off, r.var_off + r.var_bytes))
+                for so in r.slot_off:
+                    spans.append((so, so + r.var_bytes))
+                if r.shadow_off is not None:
+                    assert r.shadow_off % 256 == 0 and r.shadow_ld % 8 == 0
+                    spans.append((r.shadow_off, r.shadow_off + r.shadow_bytes))
+        f = al.mbox_flags_off[sh]
+        assert f % 256 == 0 and al.mbox_slot_base[sh] == f + L.MBOX_FLAGS_BYTES
+        spans.append((f, f + L.MBOX_FLAGS_BYTES))
+        stride = al.mailbox_stride[sh]
+        assert stride % 256 == 0
+        slices_here = [(n_, r) for n_ in names for r in al.regions[n_] if r.shard == sh]
+        assert stride >= sum(r.var_bytes for _, r in slices_here)
+        for w in range(W):
+            for b in range(depth):
+                lo = al.mbox_slot_base[sh] + (w * depth + b) * stride
+                spans.append((lo, lo + stride))
+        for n_, r in slices_here:        # a slice's place inside a slot lies within the slot
+            off = al.mailbox_off[(n_, sh)] - al.mbox_slot_base[sh]
+            assert 0 <= off and off + r.var_bytes <= stride and off % 256 == 0
+        spans.sort()
+        for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+            assert a1 <= b0, f"shard {sh}: regions [{a0},{a1}) and [{b0},{b1}) overlap"
+        assert spans[-1][1] <= al.shard_bytes[sh]
+    # synchronous layout (depth 1 + mirrors at the same offset in every arena) still lines up
+    sync = build_arena_layout(layout, 8, spec, names, sync_workers=8)
+    assert sync.mailbox_depth == 1 and set(sync.mirror_f32) == set(n for n in sync.regions if sync.regions[n])
+    assert len(set(sync.shard_bytes)) == 1
