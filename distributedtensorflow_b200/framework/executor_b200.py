@@ -462,6 +462,27 @@ class B200StepRunner:
         return self.client.uninitialized_variables(self.layout)
 
     def snapshot_shards(self) -> List[Dict[str, np.ndarray]]:
+        """Per-shard tensors for the Saver. In owner-applies mode the shards' apply daemons are parked
+        while their memory is read, so each shard's tensors are a consistent cut (no half-applied
+        gradient); workers that keep pushing meanwhile just fill their mailboxes (bounded by depth)."""
+        self.stream.synchronize()
+        if not self.use_mailbox:
+            return self._snapshot_shards()
+        self.flush_pushes()
+        paused = []
+        try:
+            for sh in range(self.client.num_shards):
+                self.client.call(sh, "mbox_pause", True)
+                paused.append(sh)
+            return self._snapshot_shards()
+        finally:
+            for sh in paused:
+                try:
+                    self.client.call(sh, "mbox_pause", False)
+                except Exception:
+                    pass
+
+    def _snapshot_shards(self) -> List[Dict[str, np.ndarray]]:
         st = self.store
         shards: List[Dict[str, np.ndarray]] = [dict() for _ in range(st.num_shards)]
         slot_names = self.spec.slot_names() if self.spec is not None else []

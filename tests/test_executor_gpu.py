@@ -207,6 +207,17 @@ def test_mailbox_push_mode_owner_applies_every_gradient(num_ps, depth):
         assert np.isfinite(w).all()
         np.testing.assert_array_equal(runner.store.read_shadow("hid_w"),
                                       _bf16_round(w))
+        # checkpoint: the daemons are parked while their shards are read, then resume
+        import tempfile, os
+        from distributedtensorflow_b200.ckpt import BundleReader
+        with tempfile.TemporaryDirectory() as d:
+            path = tf.train.Saver().save(raw, os.path.join(d, "model.ckpt"), global_step=steps + 25)
+            with BundleReader(path) as r:
+                np.testing.assert_array_equal(r.get_tensor("hid_w"), w)
+                assert int(r.get_tensor("global_step")) == steps + 25
+        for i in range(3):
+            sess.run([train_op, loss, gs], feed_dict={x_ph: batches[0][0], y_ph: batches[0][1]})
+        assert int(sess.run(gs)) == steps + 28
     server.stop()
     assert np.mean(losses[-5:]) < 0.7 * np.mean(losses[:3])
 
