@@ -583,11 +583,20 @@ class B200StepRunner:
             want_f32(p.convs[0].b, True)
             want_shadow(p.convs[1].k, False)   # w2 is read by fwd AND dgrad: needs one snapshot
             want_f32(p.convs[1].b, False)
+        # copies[:late_mark] are needed by the step's first kernels; the rest (the dense stack behind
+        # the convolutions / behind an MLP's first layer — the bulk of the bytes) is pulled on the
+        # side stream while those kernels run, and layer `late_layer` waits for it
+        self.late_mark = len(self.copies) if p.kind == "cnn" else None
+        self.late_layer = 0 if p.kind == "cnn" else 1
         for i, d in enumerate(p.dense):
+            if self.late_mark is None and i == 1:
+                self.late_mark = len(self.copies)
             # first GEMM layer of an MLP: weights are used by the forward only -> fused pull
             want_shadow(d.w, allow_in_place=(p.kind == "mlp" and i == 0))
             if d.b is not None:
                 want_f32(d.b, False)
+        if self.late_mark is None:
+            self.late_mark = len(self.copies)
 
     def _setup_params_sync(self) -> None:
         """Synchronous mode: kernels read the worker's MIRROR inside its own arena; the owners'
@@ -691,6 +700,9 @@ class B200StepRunner:
         nl = len(p.dense)
         fused_head = self._head_is_fused()
         for i, d in enumerate(p.dense):
+            if getattr(s, "pull_late", None) is not None and i == self.late_layer:
+                torch.cuda.current_stream().wait_event(s.pull_late)   # the dense stack's weights have landed
+                s.pull_late = None
             if fused_head and i == nl - 1:
                 break                      # the logits layer is part of the fused head kernel (_loss)
             wp, ld = self.wptr[d.w.name]
@@ -1034,7 +1046,20 @@ class B200StepRunner:
             if self.mirror_filled:
                 return
             self.mirror_filled = True
-        if self.copies:
+        s.pull_late = None
+        mark = getattr(self, "late_mark", None)
+        if self.sync_opt is None and self.overlap and mark is not None and len(self.copies) > mark:
+            main = torch.cuda.current_stream()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            self.side_stream.wait_event(ev)
+            with torch.cuda.stream(self.side_stream):
+                K.pull_bulk(self.copies[mark:])
+                s.pull_late = torch.cuda.Event()
+                s.pull_late.record(self.side_stream)
+            if mark > 0:
+                K.pull_bulk(self.copies[:mark], self.store.step_ctrl, s.step_dev.data_ptr() + 8)
+        elif self.copies:
             K.pull_bulk(self.copies, self.store.step_ctrl, s.step_dev.data_ptr() + 8)
 
     def _self_cleans(self, s: StepState) -> bool:
