@@ -124,7 +124,8 @@ def main() -> int:
     ap.add_argument("--placement", default="auto", choices=["auto", "round_robin", "flat"])
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--no-cuda-graph", action="store_true")
-    ap.add_argument("--no-pdl", action="store_true", help="disable programmatic dependent launch")
+    ap.add_argument("--no-pdl", action="store_true", help="(default) no programmatic dependent launch")
+    ap.add_argument("--pdl", action="store_true", help="enable programmatic dependent launch (measured slower)")
     ap.add_argument("--no-split-k", action="store_true", help="disable split-K for skinny GEMMs")
     ap.add_argument("--no-overlap", action="store_true", help="single-stream backward (no side stream)")
     ap.add_argument("--fused-apply", action="store_true", help="dW GEMM epilogue does the push+apply")
@@ -202,7 +203,7 @@ def main() -> int:
             raise SystemExit("--model mlp is benchmarked by bench/step_time.py")
 
     cfg = tf.ConfigProto(allow_soft_placement=True, backend="b200", device="cuda:%d" % local_rank,
-                         cuda_graph=not args.no_cuda_graph, pdl=not args.no_pdl,
+                         cuda_graph=not args.no_cuda_graph, pdl=bool(args.pdl and not args.no_pdl),
                          split_k=not args.no_split_k, overlap=not args.no_overlap, fused_apply=args.fused_apply,
                          push_mode=args.push_mode,
                          **{k: (v == "1") if v in ("0", "1") else (int(v) if v.isdigit() else v)
@@ -292,7 +293,7 @@ def main() -> int:
                        "parallelism": "async PS: %d PS shard(s) + %d worker(s), one of each per GPU, %s placement"
                                       % (N, N, placement),
                        "l2": "not flushed" if args.no_l2_flush else "flushed between timed steps (256 MiB write)",
-                       "cuda_graph": not args.no_cuda_graph, "pdl": not args.no_pdl,
+                       "cuda_graph": not args.no_cuda_graph, "pdl": bool(args.pdl and not args.no_pdl),
                        "split_k": not args.no_split_k, "overlap": not args.no_overlap,
                        "fused_apply": args.fused_apply,
                        "step_io": ("inputs: the step's first kernel reads the batch in place from pinned host memory "
