@@ -58,7 +58,7 @@ __device__ __forceinline__ void ingest_image_padded(float (*img)[C1_PITCH], unsi
 }
 
 // Two CTAs per image (grid B x 2). Work item = (pooled pixel, group of 8 output channels).
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(392)
 conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict__ x_f32,
                  float scale, const float* __restrict__ w1, const float* __restrict__ b1,
                  __nv_bfloat16* __restrict__ pool1p, unsigned char* __restrict__ amax1,
@@ -74,7 +74,7 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   if (ingest) {
     // the labels ride along: the last CTA mirrors them host -> device (16-byte words), so the step
     // needs no copy node and no cross-stream join in front of the loss
-    if (y_src != nullptr && blockIdx.x == gridDim.x - 1 && blockIdx.y == 1)
+    if (y_src != nullptr && blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1)
       for (int i = threadIdx.x; i < y_vecs; i += blockDim.x) y_dst[i] = y_src[i];
     ingest_image_padded(img, raw, x_u8, x_f32, copy_u8, copy_f32, scale, n, blockIdx.y == 0);
   }
@@ -84,10 +84,11 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   if (threadIdx.x < C1_CH) bias[threadIdx.x] = b1[threadIdx.x];
   __syncthreads();
 
-  // two CTAs per image (blockIdx.y = upper / lower 7 pooled rows): 2 CTAs per SM, twice the warps
-  constexpr int HALF = C1_OUT * C1_OUT / 2;
-  for (int item = threadIdx.x; item < HALF * 4; item += blockDim.x) {
-    const int pp = blockIdx.y * HALF + (item >> 2), cg = item & 3;
+  // gridDim.y CTAs per image (1 when the batch is ingested from host memory, so every image crosses
+  // PCIe once; 2 otherwise: upper / lower 7 pooled rows)
+  const int part = C1_OUT * C1_OUT / gridDim.y;
+  for (int item = threadIdx.x; item < part * 4; item += blockDim.x) {
+    const int pp = blockIdx.y * part + (item >> 2), cg = item & 3;
     const int py = pp / C1_OUT, px = pp % C1_OUT;
     float patch[6][6];
 #pragma unroll
@@ -303,7 +304,7 @@ extern "C" int dtf_conv1_fwd_ingest(const unsigned char* x_u8, const float* x_f3
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_fwd_ingest: pass exactly one of x_u8/x_f32");
   const void* x = x_u8 ? static_cast<const void*>(x_u8) : static_cast<const void*>(x_f32);
   DTF_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "conv1_fwd_ingest: x must be 16-byte aligned");
-  DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B, 2), dim3(196), 0,
+  DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B, 1), dim3(392), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale, w1, b1,
                                reinterpret_cast<__nv_bfloat16*>(pool1p), amax1, copy_u8, copy_f32, 1,
                                static_cast<const uint4*>(y_src), static_cast<uint4*>(y_dst), y_bytes / 16));
