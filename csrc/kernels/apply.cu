@@ -185,13 +185,15 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
       *b1 = *b1 * a.h.beta1;
       *b2 = *b2 * a.h.beta2;
     }
-    const unsigned long long old = atom_add_u64_sys(&a.ctrl_step->global_step, 1ull);
-    s_step = old + 1ull;
-    if (a.step_out != nullptr) *a.step_out = old + 1ull;
-    if (a.worker_id >= 0 && a.worker_id < DTF_MAX_WORKERS)
-      *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[a.worker_id]) =
-          old + 1ull;
-    atomicAdd(&a.ctrl_step->apply_count, 1u);
+    if (a.finish != 2) {  // finish == 2: global_step / results were already reported (dtf_step_report)
+      const unsigned long long old = atom_add_u64_sys(&a.ctrl_step->global_step, 1ull);
+      s_step = old + 1ull;
+      if (a.step_out != nullptr) *a.step_out = old + 1ull;
+      if (a.worker_id >= 0 && a.worker_id < DTF_MAX_WORKERS)
+        *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[a.worker_id]) =
+            old + 1ull;
+      atomicAdd(&a.ctrl_step->apply_count, 1u);
+    }
   } else if (threadIdx.x == 32 && sink) {
     s_loss = *reinterpret_cast<const volatile float*>(a.sink.loss_src);
     if (a.sink.clear_loss) *const_cast<volatile float*>(a.sink.loss_src) = 0.f;
@@ -208,6 +210,33 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
     asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(a.sink.host_dst),
                  "r"(__float_as_uint(s_loss)), "r"(s_seq), "r"(static_cast<unsigned int>(st)),
                  "r"(static_cast<unsigned int>(st >> 32))
+                 : "memory");
+  }
+}
+
+// Early step report (see dtf_step_report): one thread bumps / reads global_step and hands the step's
+// loss and step number to the host while the rest of the backward pass is still running.
+__global__ void step_report_kernel(dtf_ps_ctrl* ctrl_step, int worker_id, int bump,
+                                   unsigned long long* step_out, dtf_result_sink sink) {
+  if (threadIdx.x != 0) return;
+  unsigned long long step;
+  if (bump) {
+    step = atom_add_u64_sys(&ctrl_step->global_step, 1ull) + 1ull;
+    if (worker_id >= 0 && worker_id < DTF_MAX_WORKERS)
+      *reinterpret_cast<volatile unsigned long long*>(&ctrl_step->heartbeat[worker_id]) = step;
+    atomicAdd(&ctrl_step->apply_count, 1u);
+  } else {
+    step = ld_acquire_sys_u64(&ctrl_step->global_step);
+  }
+  if (step_out != nullptr) *step_out = step;
+  if (sink.host_dst != nullptr) {
+    const float loss = *reinterpret_cast<const volatile float*>(sink.loss_src);
+    if (sink.clear_loss) *const_cast<volatile float*>(sink.loss_src) = 0.f;
+    const unsigned int q = *reinterpret_cast<volatile unsigned int*>(sink.seq_dev) + 1u;
+    *reinterpret_cast<volatile unsigned int*>(sink.seq_dev) = q;
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(sink.host_dst),
+                 "r"(__float_as_uint(loss)), "r"(q), "r"(static_cast<unsigned int>(step)),
+                 "r"(static_cast<unsigned int>(step >> 32))
                  : "memory");
   }
 }
@@ -414,5 +443,21 @@ extern "C" int dtf_push_apply_static(int opt, const dtf_apply_item* items, int n
     default: DTF_REQUIRE(false, "push_apply_static: unknown optimizer %d", opt);
   }
   DTF_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int dtf_step_report(dtf_ps_ctrl* ctrl_for_step, int worker_id, int bump,
+                               unsigned long long* step_out, const dtf_result_sink* sink,
+                               void* stream) {
+  DTF_REQUIRE(ctrl_for_step != nullptr, "step_report: ctrl_for_step is null");
+  dtf_result_sink sk;
+  memset(&sk, 0, sizeof(sk));
+  if (sink != nullptr) {
+    DTF_REQUIRE(sink->loss_src && sink->host_dst && sink->seq_dev, "step_report: incomplete result sink");
+    sk = *sink;
+  }
+  DTF_CHECK_CUDA(launch_kernel(dtf::step_report_kernel, dim3(1), dim3(32), 0,
+                               reinterpret_cast<cudaStream_t>(stream), ctrl_for_step, worker_id, bump,
+                               step_out, sk));
   return 0;
 }

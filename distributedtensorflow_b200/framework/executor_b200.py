@@ -324,6 +324,10 @@ class B200StepRunner:
         # the step's last kernel writes loss / global_step into pinned host memory and the host
         # spins on a sequence word: no D2H copy nodes, no stream synchronise per step
         self.host_sink = bool(opts.get("host_sink", True))
+        # report loss / global_step to the host right after the loss kernel, while the backward pass
+        # and the applies are still running: the host's per-step work overlaps the rest of the step
+        # (the next step is stream-ordered behind it; host reads of shard memory sync the stream)
+        self.early_report = bool(opts.get("early_report", True))
         # the step's first kernel reads the input batch in place from pinned host memory
         self.zero_copy_input = bool(opts.get("zero_copy_input", True))
         # accumulators clean themselves (the apply zeroes the gradients it consumed, the split-K
@@ -442,6 +446,7 @@ class B200StepRunner:
                               mirrors=mirrors)
         self.sync_round_no: Optional[int] = None
         self.mirror_filled = False
+        self.store.sync_hook = self.stream.synchronize
         if self.use_mailbox:
             self._mbox_setup()
 
@@ -803,6 +808,12 @@ class B200StepRunner:
         head_fused = self._head_is_fused()
         pre_dw: Dict[int, Any] = {}
         fork(side)                               # dlogits (and every activation) is ready
+        s.reported = bool(self.early_report and self._uses_sink(s))
+        if s.reported:
+            with torch.cuda.stream(side):
+                # the loss is final: hand loss + global_step to the host now
+                K.step_report(self.store.step_ctrl, self.worker_id, not self.use_mailbox,
+                              s.step_dev.data_ptr(), self._sink(s))
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
@@ -968,7 +979,8 @@ class B200StepRunner:
         K.mailbox_push(items, al.mailbox_depth, me, flags, publish, self.mbox_seq.data_ptr(),
                        s.counter.data_ptr(), self.mbox_host.data_ptr() if publish else None,
                        st.step_ctrl if publish else None, s.step_dev.data_ptr() if publish else None,
-                       sink=self._sink(s) if (publish and self._uses_sink(s)) else None)
+                       sink=self._sink(s) if (publish and self._uses_sink(s)
+                                              and not getattr(s, "reported", False)) else None)
 
     def _mbox_consumed(self) -> int:
         """min over owners of how many of MY gradients they have applied (host-side read)."""
@@ -1022,7 +1034,8 @@ class B200StepRunner:
             self._push_vars(s, variables, publish=finish)
             return
         st, spec = self.store, self.spec
-        sink = self._sink(s) if (finish and self._uses_sink(s)) else None
+        reported = bool(getattr(s, "reported", False))
+        sink = self._sink(s) if (finish and self._uses_sink(s) and not reported) else None
         entries = []
         zb = s.zero.buf.data_ptr()
         ze = zb + s.zero.buf.numel() * 4
@@ -1042,8 +1055,9 @@ class B200StepRunner:
         for ci, ch in enumerate(chunks):
             last = finish and ci == len(chunks) - 1
             items = K.make_apply_items(ch)
-            K.push_apply(spec.code, items, len(ch), hyper, st.powers_ctrl, st.step_ctrl, last,
-                         self.worker_id, s.step_dev.data_ptr() if last else None,
+            K.push_apply(spec.code, items, len(ch), hyper, st.powers_ctrl, st.step_ctrl,
+                         (2 if reported else 1) if last else 0,
+                         self.worker_id, s.step_dev.data_ptr() if (last and not reported) else None,
                          s.counter.data_ptr(), sink=sink if last else None,
                          max_ctas=0 if finish else self.early_apply_ctas)
 

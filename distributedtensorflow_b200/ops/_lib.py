@@ -200,6 +200,7 @@ def _declare(lib):
         "dtf_mbox_daemon_stats": [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)],
         "dtf_mbox_daemon_stop": [vp],
         "dtf_graph_launch": [vp, vp],
+        "dtf_step_report": [vp, i, i, vp, C.POINTER(ResultSink), vp],
         "dtf_host_wait_u32": [vp, C.c_uint, C.c_longlong],
         "dtf_head_fused": [vp, i, i, vp, i, vp, vp, vp, i, i, i, vp, i, vp, vp, i, vp, vp, i, vp, vp, vp],
         "dtf_host_alloc_pinned": [C.POINTER(vp), C.c_size_t],

@@ -153,6 +153,14 @@ def make_hyper(lr: float, beta1: float = 0.9, beta2: float = 0.999, epsilon: flo
     return h
 
 
+def step_report(ctrl_step: int, worker_id: int, bump: bool, step_out: Optional[int],
+                sink: Optional[L.ResultSink]) -> None:
+    rc = L.lib().dtf_step_report(ctrl_step, worker_id, int(bump), step_out,
+                                 C.byref(sink) if sink is not None else None, L.current_stream())
+    L.check(rc, "dtf_step_report")
+    _count()
+
+
 def make_sink(loss_ptr: int, host_ptr: int, seq_ptr: int, clear_loss: bool = False) -> L.ResultSink:
     sk = L.ResultSink()
     sk.loss_src, sk.host_dst, sk.seq_dev = loss_ptr, host_ptr, seq_ptr
@@ -166,7 +174,7 @@ def push_apply(opt: int, items, n_items: int, hyper: L.ApplyHyper, ctrl_powers: 
                sink: Optional[L.ResultSink] = None, max_ctas: int = 0) -> None:
     rc = L.lib().dtf_push_apply_ex(opt, items, n_items, C.byref(hyper), ctrl_powers, ctrl_step,
                                    int(finish), worker_id, step_out, block_counter,
-                                   C.byref(sink) if (sink is not None and finish) else None,
+                                   C.byref(sink) if (sink is not None and int(finish) == 1) else None,
                                    int(max_ctas), L.current_stream())
     L.check(rc, "dtf_push_apply")
     _count()

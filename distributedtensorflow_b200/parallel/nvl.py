@@ -241,13 +241,21 @@ class NvlStore:
         return self.ctrl_ptr(self.arena.powers_shard)
 
     # -- host <-> arena (init, restore, checkpoint): plain synchronous copies ------------------------
+    # set by the executor: host-side reads / writes of shard memory must wait for the step stream
+    # (a training step reports its results to the host before its applies have finished)
+    sync_hook = None
+
     def _h2d(self, dst: int, arr: np.ndarray) -> None:
+        if self.sync_hook is not None:
+            self.sync_hook()
         a = np.ascontiguousarray(arr)
         lib = L.lib()
         L.check(lib.dtf_memcpy_h2d(dst, a.ctypes.data_as(C.c_void_p), a.nbytes, None), "h2d")
         L.check(lib.dtf_stream_sync(None), "sync")
 
     def _d2h(self, src: int, nbytes: int, dtype) -> np.ndarray:
+        if self.sync_hook is not None:
+            self.sync_hook()
         out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype)
         lib = L.lib()
         L.check(lib.dtf_memcpy_d2h(out.ctypes.data_as(C.c_void_p), src, nbytes, None), "d2h")

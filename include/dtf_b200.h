@@ -147,7 +147,7 @@ typedef struct dtf_apply_hyper {
 } dtf_apply_hyper;
 /* ctrl_for_powers: control block holding beta powers (shard of the first variable).
  * ctrl_for_step: control block holding global_step. finish: 1 = bump global_step, update beta
- * powers, heartbeat[worker_id]. step_out (device u64, local) receives the new global step.
+ * powers, heartbeat[worker_id]; 2 = update beta powers only (after dtf_step_report). step_out (device u64, local) receives the new global step.
  * block_counter: a zero-initialised local u32 the kernel uses to elect the last CTA. */
 /* Where the step's LAST kernel reports the step's results, so no D2H copy nodes trail the step:
  * the finishing thread stores {loss bits, sequence number, global_step} straight into a pinned,
@@ -172,6 +172,14 @@ int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_items,
                       dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                       unsigned long long* step_out, unsigned int* block_counter,
                       const dtf_result_sink* sink, int max_ctas, void* stream);
+
+/* Early step report: bumps (bump = 1) or just reads (bump = 0) global_step and fills `sink` as soon
+ * as the loss is known, long before the step's applies have finished, so the host overlaps its
+ * per-step work with the rest of the backward pass. The step's last dtf_push_apply is then called
+ * with finish = 2 (beta powers only). The next step is stream-ordered behind this one, and host
+ * reads of shard memory must synchronise the stream first. */
+int dtf_step_report(dtf_ps_ctrl* ctrl_for_step, int worker_id, int bump, unsigned long long* step_out,
+                    const dtf_result_sink* sink, void* stream);
 
 /* dtf_push_apply for callers that cannot allocate device memory (no counterpart in the reference:
  * TensorFlow's ApplyAdam kernels allocate through the TF runtime). Same arguments and result as
