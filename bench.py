@@ -131,6 +131,8 @@ def main() -> int:
     ap.add_argument("--fused-apply", action="store_true", help="dW GEMM epilogue does the push+apply")
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=0|1",
                     help="extra executor option, e.g. --opt zero_copy_input=0 --opt host_sink=0")
+    ap.add_argument("--num-ps", type=int, default=0,
+                    help="PS shards (default: one per GPU). --gpus 2 --num-ps 1 is the README's '1 PS, 2 workers'")
     ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"],
                     help="gradient push: worker-side remote read-modify-write, or posted stores + the "
                          "owner's apply daemon (auto = mailbox when there is more than one worker)")
@@ -169,18 +171,19 @@ def main() -> int:
 
     # -- cluster: PS shard r and worker r on GPU r --------------------------------------------------
     base_port = int(os.environ.get("MASTER_PORT", "29500"))
-    ps_addrs = ["127.0.0.1:%d/gpu:%d" % (base_port + 101 + i, i) for i in range(N)]
+    NPS = args.num_ps if 0 < args.num_ps <= N else N
+    ps_addrs = ["127.0.0.1:%d/gpu:%d" % (base_port + 101 + i, i) for i in range(NPS)]
     wk_addrs = ["127.0.0.1:%d/gpu:%d" % (base_port + 201 + i, i) for i in range(N)]
     cluster = tf.train.ClusterSpec({"ps": ps_addrs, "worker": wk_addrs})
-    ps_server = tf.train.Server(cluster, job_name="ps", task_index=rank)
+    ps_server = tf.train.Server(cluster, job_name="ps", task_index=rank) if rank < NPS else None
     wk_server = tf.train.Server(cluster, job_name="worker", task_index=rank)
     if world > 1:
         dist.barrier()
 
     placement = args.placement
     if placement == "auto":
-        placement = "flat" if N > 1 else "round_robin"
-    strategy = tf.train.FlatSlicedStrategy(N) if placement == "flat" else None
+        placement = "flat" if NPS > 1 else "round_robin"
+    strategy = tf.train.FlatSlicedStrategy(NPS) if placement == "flat" else None
 
     # -- input pipeline: synthetic MNIST-shaped uint8 images in pinned host memory ------------------
     imgs, labels = mnist.synthetic_arrays(BATCH * 64, seed=rank)
@@ -290,8 +293,9 @@ def main() -> int:
             "impl": "ours",
             "config": {"model": model_name, "global_batch": BATCH * N, "batch_per_worker": BATCH,
                        "seq_len": None, "optimizer": "Adam lr=5e-4 (TF1 rule), fp32 master + bf16 serving copy",
-                       "parallelism": "async PS: %d PS shard(s) + %d worker(s), one of each per GPU, %s placement"
-                                      % (N, N, placement),
+                       "parallelism": "async PS: %d PS shard(s) + %d worker(s), %s, %s placement"
+                                      % (NPS, N, "one of each per GPU" if NPS == N else
+                                         "PS task(s) on the first GPU(s), one worker per GPU", placement),
                        "l2": "not flushed" if args.no_l2_flush else "flushed between timed steps (256 MiB write)",
                        "cuda_graph": not args.no_cuda_graph, "pdl": bool(args.pdl and not args.no_pdl),
                        "split_k": not args.no_split_k, "overlap": not args.no_overlap,
@@ -314,7 +318,8 @@ def main() -> int:
         }
     if world > 1:
         dist.barrier()
-    ps_server.stop()
+    if ps_server is not None:
+        ps_server.stop()
     wk_server.stop()
     if rank == 0:
         print(json.dumps(result))
