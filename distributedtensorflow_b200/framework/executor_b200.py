@@ -1319,6 +1319,30 @@ class B200StepRunner:
             if self._incarnations.setdefault(s, inc) != inc:
                 raise AbortedError(f"/job:ps/task:{s} restarted (state lost)")
 
+    def traffic_per_step(self) -> Dict[str, Any]:
+        """Bytes one training step moves, from the layout (no measurement): what is pulled from /
+        pushed to REMOTE shards (crosses NVLink) and in total. Used by DataPlaneStatsHook."""
+        st = self.store
+        pull_remote = pull_total = 0
+        for src, _dst, nbytes in getattr(self, "copies", []):
+            pull_total += nbytes
+            sh = next((i for i in range(st.num_shards)
+                       if st.base[i] <= src < st.base[i] + st.arena.shard_bytes[i]), None)
+            if sh is not None and not st.is_local[sh]:
+                pull_remote += nbytes
+        push_remote = push_total = 0
+        per_elem = 4 if self.use_mailbox else {0: 8, 1: 16, 2: 16, 3: 24}.get(getattr(self.spec, "code", 3), 24)
+        if self.train_op is not None:
+            for var in self.train_op.var_list:
+                for r in self._regions(var):
+                    b = r.sl.n * per_elem + (0 if self.use_mailbox or r.shadow_off is None else r.sl.n * 2)
+                    push_total += b
+                    if not st.is_local[r.shard]:
+                        push_remote += b
+        return dict(pull_remote_bytes=pull_remote, pull_total_bytes=pull_total,
+                    push_remote_bytes=push_remote, push_total_bytes=push_total,
+                    push_mode="mailbox" if self.use_mailbox else "rmw")
+
     def worker_heartbeats(self) -> List[int]:
         """Last global step each worker published in the step-owning shard's control block."""
         return self.store.read_ctrl(self.store.arena.step_shard)["heartbeat"]

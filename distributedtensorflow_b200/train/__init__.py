@@ -4,7 +4,8 @@ from ..framework.graph import (create_global_step, get_global_step,  # noqa: F40
                                get_or_create_global_step)
 from ..placement import (FlatSlicedStrategy, GreedyLoadBalancingStrategy,  # noqa: F401
                          RoundRobinStrategy, byte_size_load_fn, replica_device_setter)
-from .hooks import (CheckpointSaverHook, CheckpointSaverListener, FaultInjectionHook,  # noqa: F401
+from .hooks import (CheckpointSaverHook, CheckpointSaverListener, DataPlaneStatsHook,  # noqa: F401
+                    FaultInjectionHook,
                     FeedFnHook, FinalOpsHook, GlobalStepWaiterHook, LoggingTensorHook,
                     NanLossDuringTrainingError, NanTensorHook, SecondOrStepTimer, SessionRunArgs,
                     SessionRunContext, SessionRunHook, SessionRunValues, StepCounterHook,

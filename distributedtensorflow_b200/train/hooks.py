@@ -189,6 +189,61 @@ class StepCounterHook(SessionRunHook):
             self._summary_writer.flush()
 
 
+class DataPlaneStatsHook(SessionRunHook):
+    """Observability for the B200 data plane ("global_step/sec, per-path achieved GB/s
+    and %-of-roofline as logged keys"). Every ``every_n_steps`` LOCAL steps it puts into the
+    reference-style logger (``logger.logkv``; emitted by the next ``dumpkvs``):
+
+        local_step/sec, pull_GB/s, push_GB/s, pull_pct_nvlink, push_pct_nvlink, push_mode
+
+    from the byte counts the executor derives from its layout (remote bytes only: what actually
+    crosses NVLink). A CPU-backend session logs the step rate only. No device synchronisation and no
+    extra fetch: the hook only counts ``after_run`` calls and reads a clock."""
+
+    NVLINK_GBS = 770.0   # measured peer-copy rate per direction (profiles/pushpull_sweep_n8.json)
+
+    def __init__(self, every_n_steps: int = 100, dump: bool = False):
+        self._every = max(1, int(every_n_steps))
+        self._dump = dump
+        self._n = 0
+        self._t0: Optional[float] = None
+        self.last: Dict[str, Any] = {}
+
+    def begin(self) -> None:
+        self._n = 0
+        self._t0 = None
+
+    def after_run(self, run_context, run_values) -> None:
+        now = time.time()
+        if self._t0 is None:
+            self._t0, self._n = now, 0
+            return
+        self._n += 1
+        if self._n < self._every:
+            return
+        dt = max(now - self._t0, 1e-9)
+        rate = self._n / dt
+        from .. import logger
+        stats: Dict[str, Any] = {"local_step/sec": rate}
+        sess = run_context.session
+        raw = sess._tf_sess() if hasattr(sess, "_tf_sess") else sess
+        runner = getattr(raw, "_runner", None)
+        traffic = getattr(runner, "traffic_per_step", None)
+        if callable(traffic):
+            t = traffic()
+            stats["pull_GB/s"] = t["pull_remote_bytes"] * rate / 1e9
+            stats["push_GB/s"] = t["push_remote_bytes"] * rate / 1e9
+            stats["pull_pct_nvlink"] = 100.0 * stats["pull_GB/s"] / self.NVLINK_GBS
+            stats["push_pct_nvlink"] = 100.0 * stats["push_GB/s"] / self.NVLINK_GBS
+            stats["push_mode"] = t["push_mode"]
+        for k, v in stats.items():
+            logger.logkv(k, v)
+        if self._dump:
+            logger.dumpkvs()
+        self.last = stats
+        self._t0, self._n = now, 0
+
+
 class NanLossDuringTrainingError(RuntimeError):
     def __str__(self):
         return "NaN loss during training."

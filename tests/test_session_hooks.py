@@ -218,3 +218,34 @@ def test_tracing_helpers_are_noops_without_nvtx():
     with tracing.nvtx_range("dtf/test"):
         pass
     assert tracing.nvtx_range("a") is tracing.nvtx_range("b")      # shared null context when off
+
+
+def test_data_plane_stats_hook_logs_rates_and_roofline_fractions():
+    import time as _time
+    import distributedtensorflow_b200 as tf
+    from distributedtensorflow_b200 import logger
+
+    class FakeRunner:
+        def traffic_per_step(self):
+            return dict(pull_remote_bytes=5_000_000, pull_total_bytes=6_000_000,
+                        push_remote_bytes=11_000_000, push_total_bytes=13_000_000, push_mode="mailbox")
+
+    class FakeSess:
+        _runner = FakeRunner()
+
+        def _tf_sess(self):
+            return self
+
+    class Ctx:
+        session = FakeSess()
+
+    hook = tf.train.DataPlaneStatsHook(every_n_steps=5)
+    hook.begin()
+    for _ in range(6):
+        _time.sleep(0.002)
+        hook.after_run(Ctx(), None)
+    st = hook.last
+    assert st["push_mode"] == "mailbox" and 50 < st["local_step/sec"] < 1000
+    assert abs(st["push_GB/s"] - 11e6 * st["local_step/sec"] / 1e9) < 1e-9
+    assert abs(st["pull_pct_nvlink"] - 100 * st["pull_GB/s"] / 770.0) < 1e-9
+    assert logger.getkvs()["push_GB/s"] == st["push_GB/s"]
