@@ -248,11 +248,16 @@ class PsShard:
         with self._lock:
             if self._arena is None:
                 raise RuntimeError("mbox_start before nvl_alloc")
-            if getattr(self, "_mbox_daemon", None) is not None:
-                if sig != self._mbox_sig:
-                    raise ValueError("apply daemon already running with a different layout / optimizer")
-                return {"started": False}
             base = self._arena["ptr"]
+            sig = sig + "@%x" % base
+            old = getattr(self, "_mbox_daemon", None)
+            if old is not None:
+                if sig == self._mbox_sig:
+                    return {"started": False}
+                # a new graph / optimizer / arena on this PS task (new session in the same process):
+                # retire the daemon that serves the previous layout
+                self._mbox_daemon = None
+                L.lib().dtf_mbox_daemon_stop(old)
 
             def at(off):
                 return None if off is None or off < 0 else base + int(off)
@@ -281,11 +286,12 @@ class PsShard:
     def mbox_stats(self) -> dict:
         import ctypes as C
         from ..ops import _lib as L
-        d = getattr(self, "_mbox_daemon", None)
-        if d is None:
-            return {"running": False}
         polls, drains, applied = C.c_ulonglong(), C.c_ulonglong(), C.c_ulonglong()
-        rc = L.lib().dtf_mbox_daemon_stats(d, C.byref(polls), C.byref(drains), C.byref(applied))
+        with self._lock:                       # not while mbox_stop frees the handle
+            d = getattr(self, "_mbox_daemon", None)
+            if d is None:
+                return {"running": False}
+            rc = L.lib().dtf_mbox_daemon_stats(d, C.byref(polls), C.byref(drains), C.byref(applied))
         L.check(rc, "apply daemon")
         return {"running": True, "polls": polls.value, "drains": drains.value, "applied": applied.value}
 
