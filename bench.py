@@ -209,7 +209,7 @@ def main() -> int:
                          cuda_graph=not args.no_cuda_graph, pdl=bool(args.pdl and not args.no_pdl),
                          split_k=not args.no_split_k, overlap=not args.no_overlap, fused_apply=args.fused_apply,
                          push_mode=args.push_mode,
-                         **{k: (v == "1") if v in ("0", "1") else (int(v) if v.isdigit() else v)
+                         **{k: (v == "1") if v in ("0", "1") else (int(v) if v.lstrip("-").isdigit() else v)
                             for k, v in (o.split("=", 1) for o in args.opt)})
     result = {}
     with tf.train.MonitoredTrainingSession(master=wk_server.target, is_chief=(rank == 0), config=cfg,

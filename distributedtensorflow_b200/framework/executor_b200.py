@@ -373,7 +373,10 @@ class B200StepRunner:
                 return torch.cuda.Stream(device=self.device, priority=max(prio, -1))
         self.stream = mk(-3)
         self.side_stream = mk(-2)
-        self.apply_stream = mk(0)
+        # pushes: the mailbox push is a light copy kernel that should start as soon as its gradient
+        # exists (NVLink time overlaps compute), so it gets the side stream's priority; the remote
+        # read-modify-write apply is heavy and yields to the compute kernels
+        self.apply_stream = mk(int(opts.get("apply_stream_priority", 0 if self.push_mode == "rmw" else -2)))
         self.overlap = bool(opts.get("overlap", True))
         self._stream_handle = self.stream.cuda_stream
         self._graph_launch = L.lib().dtf_graph_launch
