@@ -44,6 +44,7 @@ struct dtf_mbox_daemon {
   std::atomic<int> idle{0};
   std::atomic<int> failed{0};
   std::atomic<unsigned long long> polls{0}, drains{0}, applied{0};
+  unsigned int last_consumed[DTF_MAX_WORKERS] = {0};
   std::mutex err_mu;
   char err[512] = {0};
 
@@ -86,6 +87,14 @@ void daemon_main(dtf_mbox_daemon* d) {
       return;
     }
     d->polls.fetch_add(1, std::memory_order_relaxed);
+    // exact accounting: gradients retired since the previous poll (a drain may retire more than the
+    // poll that triggered it saw; a worker that re-attaches resets its counters to zero)
+    for (int w = 0; w < d->n_workers; ++w) {
+      const unsigned int c = d->host_flags->consumed[w];
+      const int delta = d->polls.load(std::memory_order_relaxed) > 1 ? static_cast<int>(c - d->last_consumed[w]) : 0;
+      if (delta > 0) d->applied.fetch_add(static_cast<unsigned long long>(delta), std::memory_order_relaxed);
+      d->last_consumed[w] = c;
+    }
     const int n = pending_count(d->host_flags, d->n_workers);
     if (n == 0) {
       if (d->poll_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(d->poll_us));
@@ -103,7 +112,6 @@ void daemon_main(dtf_mbox_daemon* d) {
       return;
     }
     d->drains.fetch_add(1, std::memory_order_relaxed);
-    d->applied.fetch_add(static_cast<unsigned long long>(n), std::memory_order_relaxed);
   }
 }
 

@@ -200,8 +200,13 @@ def test_mailbox_push_mode_owner_applies_every_gradient(num_ps, depth):
         runner.replay(25)                                  # pipelined device steps go through the same admission
         runner.flush_pushes()
         assert runner.store.read_global_step() == steps + 25
+        import time as _time
         for sh in range(num_ps):
-            st = raw.ps_client.call(sh, "mbox_stats")
+            for _ in range(200):           # the daemon books retired gradients at its next poll
+                st = raw.ps_client.call(sh, "mbox_stats")
+                if st["applied"] == steps + 25:
+                    break
+                _time.sleep(0.005)
             assert st["running"] and st["applied"] == steps + 25
         w = runner.store.read_variable("hid_w")
         assert np.isfinite(w).all()
