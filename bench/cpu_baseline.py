@@ -2,7 +2,7 @@
 """BASELINE config 1: the reference loop (CNN, batch 128, Adam 5e-4, 1000 global steps, async) as
 1 PS + 2 workers = three OS processes on localhost over the TCP transport, CPU backend.
 Prints wall-clock seconds of the chief's training loop and global steps/s (README.md:21 = 162 s)."""
-import json, os, re, socket, subprocess, sys, tempfile, time
+import json, os, re, socket, subprocess, sys, tempfile
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 

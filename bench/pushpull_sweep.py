@@ -72,7 +72,6 @@ def main() -> int:
             L.check(lib.dtf_ipc_import(handles[r], C.byref(p)), "ipc_import")
             bases.append(int(p.value))
     # fill my variable with a rank-specific pattern through a torch view of the arena
-    import numpy as np
     pattern = (torch.arange(n_max, device="cuda", dtype=torch.float32) % 1024) + rank * 1000.0
     L.check(lib.dtf_memcpy_h2d(bases[rank] + off_var, pattern.cpu().numpy().ctypes.data_as(C.c_void_p),
                                max_bytes, None), "h2d")

@@ -6,7 +6,6 @@ import collections
 import os
 import re
 import subprocess
-import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "distributedtensorflow_b200", "lib", "libdtf_b200_cuda.so")

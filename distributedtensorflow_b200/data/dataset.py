@@ -12,7 +12,7 @@ is for.
 """
 from __future__ import annotations
 
-from typing import Any, Callable, Iterator as PyIterator, List, Optional, Sequence, Tuple
+from typing import Callable, Iterator as PyIterator, List, Optional, Sequence, Tuple
 
 import numpy as np
 

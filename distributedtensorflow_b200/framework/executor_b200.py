@@ -17,10 +17,9 @@ else raises and can run with ``ConfigProto(backend="cpu")``.
 """
 from __future__ import annotations
 
-import math
 import os
 import time
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np

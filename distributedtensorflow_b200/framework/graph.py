@@ -17,9 +17,8 @@ only because variable names and PS placements coincide.
 from __future__ import annotations
 
 import math
-import threading
-from dataclasses import dataclass, field
-from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple, Union
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 

@@ -28,7 +28,7 @@ import sys
 import tempfile
 import time
 from collections import defaultdict
-from typing import Any, Dict, Iterable, List, Optional
+from typing import List
 
 DEBUG = 10
 INFO = 20

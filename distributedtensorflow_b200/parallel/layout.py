@@ -10,8 +10,8 @@ Optimizer slots and Adam's beta powers follow their variable (TF colocation rule
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
-from typing import Dict, List, Optional, Sequence
+from dataclasses import dataclass
+from typing import Dict, List, Sequence
 
 from .. import placement as P
 

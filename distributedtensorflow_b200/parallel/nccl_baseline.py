@@ -18,7 +18,7 @@ Every rank is one PS shard and one worker (the flat-sliced placement). Optimizer
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Sequence, Tuple
+from typing import Dict, Sequence, Tuple
 
 import torch
 import torch.distributed as dist

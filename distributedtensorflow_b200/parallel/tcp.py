@@ -19,7 +19,7 @@ import socketserver
 import struct
 import threading
 import time
-from typing import Any, List, Optional, Sequence
+from typing import Any, Optional, Sequence
 
 import msgpack
 import numpy as np

@@ -20,7 +20,6 @@ shard that owns the variable where the optimizer is applied, then ``_finish`` (b
 from __future__ import annotations
 
 import dataclasses
-import time
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np

@@ -17,7 +17,7 @@ from __future__ import annotations
 import contextlib
 import math
 import threading
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Callable, List, Optional, Sequence, Tuple, Union
 
 from .cluster import ClusterSpec

@@ -10,10 +10,9 @@ templates/00_between_graph_replication_async_mnist.py:38) and the hooks
 """
 from __future__ import annotations
 
-import math
 import os
 import time
-from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence
+from typing import Any, Callable, Dict, List, Optional, Sequence
 
 import numpy as np
 

@@ -24,8 +24,8 @@ same spec onto the fused ``dtf_push_apply`` kernel.
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
-from typing import Dict, List, Optional, Sequence, Tuple
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
 
 from ..framework import graph as G
 

@@ -26,8 +26,7 @@ reference semantics, the CPU path and the fallback for backup-worker mode.
 from __future__ import annotations
 
 import threading
-import time
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, List, Optional
 
 import numpy as np
 

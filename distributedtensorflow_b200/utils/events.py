@@ -9,7 +9,6 @@ record is ``Event(file_version="brain.Event:2")``.
 from __future__ import annotations
 
 import ctypes as C
-import glob
 import os
 import socket
 import struct

@@ -13,7 +13,7 @@ from __future__ import annotations
 
 import contextlib
 import os
-from typing import Iterator, List, Optional
+from typing import Iterator, List
 
 _NVTX = os.environ.get("DTF_B200_NVTX", "0") == "1"
 
