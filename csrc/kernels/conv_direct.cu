@@ -11,7 +11,7 @@
 namespace dtf {
 
 constexpr int C1_IMG = 28, C1_PAD = 32, C1_OUT = 14, C1_CH = 32, C1_HP = 18;
-constexpr int C1_PITCH = C1_PAD + 1;  // odd row pitch: rows y and y+1 fall into different smem banks
+constexpr int C1_PITCH = C1_PAD + 2;  // pitch 34: the four argmax positions {0, 1, P, P+1} hit four different banks
 
 __device__ __forceinline__ void load_image_padded(float (*img)[C1_PITCH], const unsigned char* x_u8,
                                                   const float* x_f32, float scale, int n) {
@@ -152,7 +152,7 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
                  const __nv_bfloat16* __restrict__ pool1p, const unsigned char* __restrict__ amax1,
                  float* __restrict__ dw1_accum, float* __restrict__ db1_accum) {
   __shared__ float img[C1_PAD][C1_PITCH];
-  __shared__ float g[C1_HALF][C1_CH];                                 // 12.5 KB
+  __shared__ __align__(16) float g[C1_HALF][C1_CH];                   // 12.5 KB
   __shared__ __align__(16) unsigned char am[C1_HALF][C1_CH];          // 3 KB
   __shared__ __align__(16) float red[C1B_WARPS / 2][26][C1_CH];       // 26.6 KB (also the raw image)
   const int n = blockIdx.x;
@@ -178,9 +178,13 @@ conv1_bwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   if (item < C1_HALF * 4) {
     const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(&av);
     const __nv_bfloat16* d = reinterpret_cast<const __nv_bfloat16*>(&dv);
+    float gv8[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j)  // ReLU gradient through the max-pool
-      g[ipp][icg * 8 + j] = (__bfloat162float(a[j]) > 0.f) ? __bfloat162float(d[j]) : 0.f;
+      gv8[j] = (__bfloat162float(a[j]) > 0.f) ? __bfloat162float(d[j]) : 0.f;
+    // two 16-byte stores (scalar stores here would be 8-way bank conflicts: lanes are 8 words apart)
+    *reinterpret_cast<float4*>(&g[ipp][icg * 8]) = make_float4(gv8[0], gv8[1], gv8[2], gv8[3]);
+    *reinterpret_cast<float4*>(&g[ipp][icg * 8 + 4]) = make_float4(gv8[4], gv8[5], gv8[6], gv8[7]);
     *reinterpret_cast<uint2*>(&am[ipp][icg * 8]) = mv;
   }
   __syncthreads();
