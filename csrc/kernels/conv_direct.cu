@@ -71,17 +71,19 @@ conv1_fwd_kernel(const unsigned char* __restrict__ x_u8, const float* __restrict
   const int n = blockIdx.x;
   griddep_wait();
   griddep_launch();
-  if (ingest) {
-    // the labels ride along: the last CTA mirrors them host -> device (16-byte words), so the step
+  if (ingest && y_src != nullptr && blockIdx.x == gridDim.x - 1) {
+    // the labels ride along: one extra CTA mirrors them host -> device (16-byte words), so the step
     // needs no copy node and no cross-stream join in front of the loss
-    if (y_src != nullptr && blockIdx.x == gridDim.x - 1 && blockIdx.y == gridDim.y - 1)
-      for (int i = threadIdx.x; i < y_vecs; i += blockDim.x) y_dst[i] = y_src[i];
-    ingest_image_padded(img, raw, x_u8, x_f32, copy_u8, copy_f32, scale, n, blockIdx.y == 0);
+    for (int i = threadIdx.x; i < y_vecs; i += blockDim.x) y_dst[i] = y_src[i];
+    return;
   }
-  else
-    load_image_padded(img, x_u8, x_f32, scale, n);
+  // filter bank and bias first: their loads are in flight while the image crosses PCIe
   for (int i = threadIdx.x; i < 25 * C1_CH; i += blockDim.x) w[i / C1_CH][i % C1_CH] = w1[i];
   if (threadIdx.x < C1_CH) bias[threadIdx.x] = b1[threadIdx.x];
+  if (ingest)
+    ingest_image_padded(img, raw, x_u8, x_f32, copy_u8, copy_f32, scale, n, blockIdx.y == 0);
+  else
+    load_image_padded(img, x_u8, x_f32, scale, n);
   __syncthreads();
 
   // gridDim.y CTAs per image (1 when the batch is ingested from host memory, so every image crosses
@@ -308,7 +310,7 @@ extern "C" int dtf_conv1_fwd_ingest(const unsigned char* x_u8, const float* x_f3
   DTF_REQUIRE((x_u8 != nullptr) != (x_f32 != nullptr), "conv1_fwd_ingest: pass exactly one of x_u8/x_f32");
   const void* x = x_u8 ? static_cast<const void*>(x_u8) : static_cast<const void*>(x_f32);
   DTF_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "conv1_fwd_ingest: x must be 16-byte aligned");
-  DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B, 1), dim3(392), 0,
+  DTF_CHECK_CUDA(launch_kernel(conv1_fwd_kernel, dim3(B + (y_src != nullptr ? 1 : 0), 1), dim3(392), 0,
                                reinterpret_cast<cudaStream_t>(stream), x_u8, x_f32, scale, w1, b1,
                                reinterpret_cast<__nv_bfloat16*>(pool1p), amax1, copy_u8, copy_f32, 1,
                                static_cast<const uint4*>(y_src), static_cast<uint4*>(y_dst), y_bytes / 16));
