@@ -80,6 +80,13 @@ struct GemmParams {
   float* aslot0[8];
   float* aslot1[8];
   __nv_bfloat16* ashadow[8];
+  // scatter store into gradient mailboxes (see dtf_gemm_epilogue.scatter_*)
+  int scatter_enable;
+  int scatter_rows_per_slice;
+  int scatter_depth;
+  const unsigned int* scatter_seq;
+  float* scatter_base[8];
+  long long scatter_buf_stride[8];
 };
 
 __device__ __forceinline__ void gemm_apply_one(int opt, const dtf_apply_hyper& h, float lr_t, float g,
@@ -166,6 +173,28 @@ __device__ __forceinline__ void gemm_epilogue_apply(const GemmParams& p, int m, 
 __device__ __forceinline__ void gemm_epilogue_store(const GemmParams& p, int m, int nb, float (&v)[32]) {
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+  if (p.scatter_enable) {
+    // weight-gradient rows go straight into this worker's current mailbox buffer on the shard that
+    // owns them: posted stores over NVLink (or local), no gradient buffer, no copy kernel
+    const int slice = m / p.scatter_rows_per_slice;
+    const long long r = m - static_cast<long long>(slice) * p.scatter_rows_per_slice;
+    const unsigned int buf = *reinterpret_cast<const volatile unsigned int*>(p.scatter_seq) %
+                             static_cast<unsigned int>(p.scatter_depth);
+    float* orow = reinterpret_cast<float*>(reinterpret_cast<char*>(p.scatter_base[slice]) +
+                                           static_cast<long long>(buf) * p.scatter_buf_stride[slice]) +
+                  r * p.N + nb;
+    if ((p.N & 3) == 0 && nb + 32 <= p.N) {
+#pragma unroll
+      for (int g = 0; g < 8; ++g)
+        *reinterpret_cast<float4*>(orow + g * 4) =
+            make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (nb + j < p.N) orow[j] = v[j];
+    }
+    return;
+  }
   if (p.bias != nullptr) {
 #pragma unroll
     for (int j = 0; j < 32; ++j)
@@ -651,7 +680,8 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
                              int block_n, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
-  DTF_REQUIRE(epi != nullptr && (epi->out != nullptr || epi->apply_enable), "gemm: epilogue/out is null");
+  DTF_REQUIRE(epi != nullptr && (epi->out != nullptr || epi->apply_enable || epi->scatter_enable),
+              "gemm: epilogue/out is null");
   DTF_REQUIRE(lda % 8 == 0 && ldb % 8 == 0,
               "gemm: lda=%d ldb=%d must be multiples of 8 elements (TMA 16 B rule)", lda, ldb);
   const int num_kb = ceil_div(K, GEMM_BK);
@@ -721,6 +751,27 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
     // 6-20 us per GEMM on the MNIST shapes, a separate fill of the workspace is cheaper -> opt-in
     if (ws_clean < 0) ws_clean = getenv("DTF_GEMM_WS_CLEAN") ? 1 : 0;
     p.ws_clean = ws_clean;
+  }
+  if (epi->scatter_enable) {
+    DTF_REQUIRE(!epi->apply_enable && !epi->reduce && p.splits == 1,
+                "gemm: the scatter epilogue cannot be combined with fused apply, reduce or split-K");
+    DTF_REQUIRE(epi->scatter_rows_per_slice > 0 && ceil_div(M, epi->scatter_rows_per_slice) <= 8 &&
+                    epi->scatter_depth >= 1 && epi->scatter_seq != nullptr,
+                "gemm: scatter needs 1..8 row slices, depth >= 1 and the sequence word");
+    p.scatter_enable = 1;
+    p.scatter_rows_per_slice = epi->scatter_rows_per_slice;
+    p.scatter_depth = epi->scatter_depth;
+    p.scatter_seq = epi->scatter_seq;
+    for (int i = 0; i < ceil_div(M, epi->scatter_rows_per_slice); ++i) {
+      DTF_REQUIRE(epi->scatter_base[i] != nullptr &&
+                      (reinterpret_cast<uintptr_t>(epi->scatter_base[i]) & 15) == 0 &&
+                      epi->scatter_buf_stride[i] % 16 == 0,
+                  "gemm: scatter slice %d needs a 16-byte aligned base and stride", i);
+      p.scatter_base[i] = epi->scatter_base[i];
+      p.scatter_buf_stride[i] = epi->scatter_buf_stride[i];
+    }
+    p.out_f32 = 1;
+    p.n_store = N;
   }
   p.apply_opt = epi->apply_enable ? epi->apply_opt : -1;
   if (epi->apply_enable) {

@@ -336,6 +336,10 @@ class B200StepRunner:
         # with the rest of the backward pass). With every shard local the applies are pure HBM work
         # that only fights the compute kernels for SMs: one apply kernel at the end is faster.
         self.early_apply = opts.get("early_apply", None)
+        # owner-applies mode: the dense kernels' weight-gradient GEMMs store straight into the owners'
+        # mailboxes from their epilogue (no gradient buffer, no copy kernel). Off until it has been
+        # measured on more than one GPU.
+        self.fused_push = bool(opts.get("fused_push", False))
         self.early_apply_ctas = int(opts.get("early_apply_ctas", 0))   # cap the grid of overlapped applies
         # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
         # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
@@ -821,11 +825,14 @@ class B200StepRunner:
             din, dout = s.dims[i], s.dims[i + 1]
             fused = self._fused_apply_spec(d.w) if (par and early and self.fused_apply
                                                     and not self.use_mailbox) else None
+            push_spec = self._fused_push_spec(d.w) if (par and early and self.fused_push
+                                                       and self.use_mailbox) else None
             dz_i = dz
             dw_done = pre_dw.pop(i, None)
-            if fused is None and dw_done is None:
+            if fused is None and push_spec is None and dw_done is None:
                 with torch.cuda.stream(side):
-                    if head_fused and i == nl - 1 and par and not (self.fused_apply and not self.use_mailbox):
+                    if head_fused and i == nl - 1 and par and not (self.fused_apply and not self.use_mailbox) \
+                            and not (self.fused_push and self.use_mailbox):
                         # the fused head already produced dZ_{i-1}: issue the LARGER weight-gradient
                         # GEMM of the layer below first, so its (big) apply can start earliest
                         K.gemm(s.act[i - 1], s.dact[i], s.gw[i - 1], s.dims[i - 1], s.dims[i], s.B,
@@ -861,6 +868,10 @@ class B200StepRunner:
                         # dW_i GEMM whose epilogue IS the push+apply: the gradient never exists in
                         # memory, the TMEM accumulator goes straight into the owner's var / m / v
                         K.gemm(s.act[i], dz_i, None, din, dout, s.B, a_mn=True, b_mn=True, apply=fused)
+                    elif push_spec is not None:
+                        # dW_i GEMM whose epilogue IS the push: rows are stored straight into this
+                        # worker's mailbox buffer on each owning shard (published at the end of the step)
+                        K.gemm(s.act[i], dz_i, None, din, dout, s.B, a_mn=True, b_mn=True, scatter=push_spec)
                     else:
                         self._apply_vars(s, [d.w], finish=False)
                 applied.append(d.w)
@@ -1024,6 +1035,23 @@ class B200StepRunner:
         """Wait until every gradient this worker has pushed is applied (exact global_step reads)."""
         if self.use_mailbox:
             self._mbox_wait(self._pushes)
+
+    def _fused_push_spec(self, var: G.Variable) -> Optional[dict]:
+        """Arguments of the GEMM's scatter epilogue (rows -> this worker's mailbox buffer on the slice's
+        owner) for a 2-D variable, or None when its slicing is not uniform row slices."""
+        regs = sorted(self._regions(var), key=lambda r: r.sl.first)
+        if len(var.shape) != 2 or not regs or len(regs) > 8:
+            return None
+        M, N = int(var.shape[0]), int(var.shape[1])
+        per = regs[0].rows if len(regs) > 1 else M
+        st, al, me = self.store, self.store.arena, self.worker_id
+        slices = []
+        for k, r in enumerate(regs):
+            if r.sl.first != k * per * N or (k + 1 < len(regs) and r.rows != per):
+                return None
+            slices.append((st.mbox_slot_ptr(r.shard, me, 0) + st.mbox_slice_off(var.name, r.shard),
+                           al.mailbox_stride[r.shard]))
+        return dict(rows_per_slice=per, depth=al.mailbox_depth, seq=self.mbox_seq.data_ptr(), slices=slices)
 
     def _sink(self, s: StepState):
         return K.make_sink(s.z["loss"].data_ptr(), s.res_pin.data_ptr(), s.res_seq_dev.data_ptr(),

@@ -77,6 +77,13 @@ class GemmEpilogue(C.Structure):
         ("apply_slot0", C.c_void_p * 8),
         ("apply_slot1", C.c_void_p * 8),
         ("apply_shadow", C.c_void_p * 8),
+        ("scatter_enable", C.c_int),
+        ("scatter_rows_per_slice", C.c_int),
+        ("scatter_depth", C.c_int),
+        ("scatter_reserved", C.c_int),
+        ("scatter_seq", C.c_void_p),
+        ("scatter_base", C.c_void_p * 8),
+        ("scatter_buf_stride", C.c_longlong * 8),
     ]
 
 

@@ -38,14 +38,15 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
          alpha: float = 1.0, splits: int = 1, block_n: int = 0,
          a_ptr: Optional[int] = None, b_ptr: Optional[int] = None, lda: Optional[int] = None,
          ldb: Optional[int] = None, ws: Optional[torch.Tensor] = None,
-         counters: Optional[torch.Tensor] = None, apply: Optional[dict] = None) -> None:
+         counters: Optional[torch.Tensor] = None, apply: Optional[dict] = None,
+         scatter: Optional[dict] = None) -> None:
     """out[M,N] = alpha * A @ B^T with the fused epilogue of ``dtf_gemm_bf16``.
 
     ``a``/``b`` are 2-D bf16 tensors whose row pitch (stride(0)) is a multiple of 8; with
     ``a_mn``/``b_mn`` they are stored transposed ([K,M] / [K,N]). ``a_ptr``/``b_ptr`` override
     the base address (peer-mapped PS memory) while ``lda``/``ldb`` give its pitch.
     """
-    if apply is None:
+    if apply is None and scatter is None:
         assert out.dim() == 2 and out.stride(1) == 1
     if a_ptr is None:
         assert a.dtype == torch.bfloat16 and a.stride(1) == 1
@@ -54,7 +55,17 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
         assert b.dtype == torch.bfloat16 and b.stride(1) == 1
         b_ptr, ldb = b.data_ptr(), b.stride(0)
     epi = L.GemmEpilogue()
-    if apply is None:
+    if scatter is not None:
+        # weight-gradient GEMM whose epilogue stores straight into the owners' mailboxes
+        epi.out, epi.ldo, epi.out_f32 = None, N, 1
+        epi.scatter_enable = 1
+        epi.scatter_rows_per_slice = scatter["rows_per_slice"]
+        epi.scatter_depth = scatter["depth"]
+        epi.scatter_seq = scatter["seq"]
+        for i, (base, stride) in enumerate(scatter["slices"]):
+            epi.scatter_base[i] = base
+            epi.scatter_buf_stride[i] = stride
+    elif apply is None:
         epi.out = out.data_ptr()
         epi.ldo = out.stride(0)
         epi.out_f32 = 1 if out.dtype == torch.float32 else 0

@@ -84,6 +84,22 @@ typedef struct dtf_gemm_epilogue {
   float* apply_slot0[8];
   float* apply_slot1[8];
   void* apply_shadow[8];        /* bf16 serving copy per slice, or NULL */
+  /* Scatter store (weight-gradient GEMM -> the owners' gradient MAILBOXES, K2 + K11 in one kernel):
+   * when scatter_enable != 0 row m of the [M, N] fp32 result belongs to row slice
+   * m / scatter_rows_per_slice and is stored at
+   *   scatter_base[slice] + (*scatter_seq % scatter_depth) * scatter_buf_stride[slice] (bytes)
+   *                       + ((m - slice * rows_per_slice) * N + n) * 4
+   * i.e. straight into this worker's current mailbox buffer on the shard that owns the slice (local or
+   * NVLink peer memory; posted 16-byte stores, issued tile by tile while the GEMM is still running).
+   * `out` is ignored; no gradient buffer and no copy kernel. The step's publishing
+   * dtf_mailbox_push (which advances *scatter_seq) must come after this GEMM in stream order. */
+  int scatter_enable;
+  int scatter_rows_per_slice;
+  int scatter_depth;
+  int scatter_reserved;
+  const unsigned int* scatter_seq;
+  float* scatter_base[8];
+  long long scatter_buf_stride[8];
 } dtf_gemm_epilogue;
 
 int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int b_mn, int M,

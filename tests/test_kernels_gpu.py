@@ -693,3 +693,31 @@ def test_head_fused_matches_separate_ops(K, B, H, dense):
     K.head_fused(act, H, W.data_ptr(), 16, bias.data_ptr(), labels, B, C, logits2, loss2)
     torch.cuda.synchronize()
     assert torch.equal(logits2, logits) and abs(loss2.item() - loss.item()) < 1e-5 * max(1.0, abs(loss.item()))
+
+
+@pytest.mark.parametrize("M,N,K_,rps,block_n", [(512, 256, 128, 192, 0), (300, 10, 96, 300, 0), (1024, 1024, 256, 512, 256)])
+def test_gemm_scatter_epilogue_stores_rows_into_mailbox_buffers(K, M, N, K_, rps, block_n):
+    """dW GEMM whose epilogue is the gradient push: row m lands in slice m // rps, inside buffer
+    (*seq % depth) of that slice's mailbox; the other buffers stay untouched."""
+    torch.manual_seed(M + N)
+    dev = "cuda"
+    A = torch.randn(K_, M, device=dev)          # a_mn: stored [K, M]
+    B = torch.randn(K_, N, device=dev)          # b_mn: stored [K, N]
+    a, b = _padded(K_, M, fill=A), _padded(K_, N, fill=B)
+    nsl = -(-M // rps)
+    depth = 3
+    stride = (rps * N * 4 + 255) // 256 * 256
+    boxes = [torch.full((depth * stride // 4,), float("nan"), device=dev) for _ in range(nsl)]
+    seq = torch.tensor([7], dtype=torch.int32, device=dev)       # 7 % 3 -> buffer 1
+    K.gemm(a, b, None, M, N, K_, a_mn=True, b_mn=True, block_n=block_n,
+           scatter=dict(rows_per_slice=rps, depth=depth, seq=seq.data_ptr(),
+                        slices=[(bx.data_ptr(), stride) for bx in boxes]))
+    torch.cuda.synchronize()
+    ref = _bf16(A).float().t() @ _bf16(B).float()
+    for i, bx in enumerate(boxes):
+        rows = min(rps, M - i * rps)
+        bufs = bx.view(depth, stride // 4)
+        got = bufs[1, :rows * N].view(rows, N)
+        assert _rel_err(got, ref[i * rps:i * rps + rows]) < 2e-3
+        assert torch.isnan(bufs[0]).all() and torch.isnan(bufs[2]).all()
+        assert torch.isnan(bufs[1, rows * N:]).all()
