@@ -168,8 +168,8 @@ def test_eval_fetch_and_validation_batch():
     assert v1 < v0
 
 
-@pytest.mark.parametrize("num_ps,depth", [(1, 2), (2, 4)])
-def test_mailbox_push_mode_owner_applies_every_gradient(num_ps, depth):
+@pytest.mark.parametrize("num_ps,depth,fused_push", [(1, 2, False), (2, 4, False), (2, 4, True)])
+def test_mailbox_push_mode_owner_applies_every_gradient(num_ps, depth, fused_push):
     """push_mode='mailbox': the worker only stores gradients into its mailboxes; the PS shards'
     native apply daemons apply them. Every push must be applied exactly once (global_step and the
     daemons' counters), the loss must fall, and staleness is bounded by the mailbox depth."""
@@ -184,7 +184,8 @@ def test_mailbox_push_mode_owner_applies_every_gradient(num_ps, depth):
                                                   ps_strategy=strategy)):
         x_ph, y_ph, loss, gs, train_op = _build_mlp("adam")(tf)
     batches = _batches(4, 100, one_hot=True)
-    cfg = tf.ConfigProto(backend="b200", device="cuda:0", push_mode="mailbox", mailbox_depth=depth)
+    cfg = tf.ConfigProto(backend="b200", device="cuda:0", push_mode="mailbox", mailbox_depth=depth,
+                         fused_push=fused_push)
     steps = 40
     losses = []
     with tf.train.MonitoredTrainingSession(master=server.target, is_chief=True, config=cfg) as sess:
