@@ -162,6 +162,7 @@ class Saver:
             raise ValueError("Can't load save_path when it is None.")
         if not checkpoint_exists(save_path):
             raise ValueError("The passed save_path is not a valid checkpoint: %s" % save_path)
+        print("INFO:tensorflow:Restoring parameters from %s" % save_path, flush=True)   # TF1's log line
         names = {v.name for v in self._variables(sess)}
         sess.restore_state(save_path, names)
 

@@ -135,3 +135,89 @@ def test_collective_ps_comparator_matches_local_adam_on_gloo():
     env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
     p = subprocess.run(cmd, cwd=root, capture_output=True, text=True, timeout=240, env=env)
     assert p.returncode == 0 and "SELFCHECK_OK" in p.stdout, p.stdout[-2000:] + p.stderr[-2000:]
+
+
+def _launch_template(script, args, tmp_path):
+    env = dict(os.environ, PYTHONPATH=ROOT, PYTHONUNBUFFERED="1", OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, os.path.join(ROOT, "templates", script), *args]
+    return subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, cwd=str(tmp_path))
+
+
+@pytest.mark.slow
+@pytest.mark.parametrize("sync", [False, True])
+def test_mlp_template_one_ps_two_workers(tmp_path, sync):
+    """templates/00_mnist_replica.py (the reference's MLP template: Supervisor, feed-dict loop,
+    optional SyncReplicasOptimizer) as 1 PS + 2 workers on the CPU backend."""
+    from distributedtensorflow_b200.data import mnist
+    data = tmp_path / "data"
+    mnist.synthetic_mnist(str(data), num_train=8192, num_test=256)     # read_data_sets keeps 5000 for validation
+    ports = _free_ports(3)
+    common = ["--ps_hosts", "127.0.0.1:%d" % ports[0],
+              "--worker_hosts", "127.0.0.1:%d,127.0.0.1:%d" % (ports[1], ports[2]),
+              "--data_dir", str(data), "--backend", "cpu", "--train_steps", "30", "--batch_size", "50"]
+    if sync:
+        common.append("--sync_replicas")
+    ps = _launch_template("00_mnist_replica.py", common + ["--job_name", "ps", "--task_index", "0"], tmp_path)
+    w1 = _launch_template("00_mnist_replica.py", common + ["--job_name", "worker", "--task_index", "1"], tmp_path)
+    time.sleep(1.0)
+    w0 = _launch_template("00_mnist_replica.py", common + ["--job_name", "worker", "--task_index", "0",
+                                                           "--shutdown_ps"], tmp_path)
+    out0 = _finish(w0, 240)
+    out1 = _finish(w1, 90)
+    outp = _finish(ps, 40)
+    assert w0.returncode == 0, out0[-3000:]
+    assert w1.returncode == 0, out1[-3000:]
+    assert ps.returncode == 0, outp[-2000:]
+    steps = [int(s) for s in re.findall(r"training step \d+ done \(global step: (\d+)\)", out0)]
+    assert steps and steps == sorted(steps) and steps[-1] >= 30
+    m = re.search(r"After \d+ training step\(s\), validation cross entropy = ([0-9.eE+-]+)", out0)
+    assert m is not None and float(m.group(1)) > 0.0, out0[-1500:]
+    assert "Training elapsed time" in out0
+
+
+@pytest.mark.slow
+def test_async_template_checkpoints_and_restores_after_a_full_restart(tmp_path):
+    """templates/00_between_graph_replication_async_mnist.py: Adagrad, MonitoredTrainingSession with
+    checkpoint_dir. Phase 1 trains to step 30 and leaves a TF1-format checkpoint; then EVERY task is
+    gone (the PS holds no state any more). Phase 2 starts a fresh PS + chief, which must restore the
+    checkpoint and continue from >= 30 to 45. The PS never exits by itself, like the
+    reference's (README TODO): SIGINT ends it cleanly."""
+    from distributedtensorflow_b200.ckpt import BundleReader
+    ckpt = tmp_path / "train_logs"
+    script = "00_between_graph_replication_async_mnist.py"
+
+    def run_phase(last_step, n_workers):
+        ports = _free_ports(1 + n_workers)
+        common = ["--ps_hosts", "127.0.0.1:%d" % ports[0],
+                  "--worker_hosts", ",".join("127.0.0.1:%d" % p for p in ports[1:]),
+                  "--backend", "cpu", "--last_step", str(last_step), "--checkpoint_dir", str(ckpt)]
+        ps = _launch_template(script, common + ["--job_name", "ps", "--task_index", "0"], tmp_path)
+        ws = [_launch_template(script, common + ["--job_name", "worker", "--task_index", str(i)], tmp_path)
+              for i in reversed(range(n_workers))]
+        outs = [_finish(w, 240) for w in ws]
+        for w, o in zip(ws, outs):
+            assert w.returncode == 0, o[-3000:]
+        ps.send_signal(signal.SIGINT)
+        outp = _finish(ps, 40)
+        assert ps.returncode == 0, outp[-2000:]
+        return "\n".join(outs)
+
+    def latest_step():
+        state = (ckpt / "checkpoint").read_text()
+        m = re.search(r'model_checkpoint_path: "([^"]+)"', state)
+        path = m.group(1)
+        path = path if os.path.isabs(path) else str(ckpt / path)
+        with BundleReader(path) as r:
+            keys = set(r.keys())
+            assert {"hid_w", "hid_b", "sm_w", "sm_b", "global_step", "hid_w/Adagrad"} <= keys, keys
+            return int(r.get_tensor("global_step")), r.get_tensor("hid_w").copy()
+
+    out1 = run_phase(30, 2)
+    assert "Restoring parameters from" not in out1
+    step1, w1 = latest_step()
+    assert 30 <= step1 <= 31
+    out2 = run_phase(45, 1)
+    assert "Restoring parameters from" in out2 and "model.ckpt-%d" % step1 in out2
+    step2, w2 = latest_step()
+    assert 45 <= step2 <= 46 and step2 > step1          # continued from the checkpoint, did not restart at 0
+    assert not (w1 == w2).all()
