@@ -168,7 +168,9 @@ class PsRpcServer:
         until the other tasks have been quiet for ``drain_idle`` seconds (bounded), so workers
         that are mid-step when the chief says "done" can finish that step and stop by themselves."""
         while not self.shard.shutdown_requested.wait(poll):
-            pass
+            if getattr(self.shard, "signal_pending", False):     # SIGINT / SIGTERM seen by Server.join
+                self.shard.signal_pending = False
+                self.shard.request_shutdown()
         deadline = time.monotonic() + self.drain_max
         while time.monotonic() < deadline and time.monotonic() - self.last_activity < self.drain_idle:
             time.sleep(poll)

@@ -105,7 +105,9 @@ class Server:
         """Blocks until shutdown is requested (Ctrl-C, SIGTERM or a control message)."""
         if threading.current_thread() is threading.main_thread() and not self._installed_signals:
             def handler(signum, frame):
-                self.shard.request_shutdown()
+                # no locks inside a signal handler (Event.set() could deadlock against the very
+                # Event.wait() this thread was interrupted in): leave a flag for the join loop
+                self.shard.signal_pending = True
             try:
                 signal.signal(signal.SIGINT, handler)
                 signal.signal(signal.SIGTERM, handler)

@@ -31,3 +31,21 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(skip_gpu)
         if "multigpu" in item.keywords and n < 2:
             item.add_marker(skip_multi)
+
+
+def pytest_sessionfinish(session, exitstatus):
+    session.config._dtf_exitstatus = int(exitstatus)
+
+
+def pytest_unconfigure(config):
+    """A test that leaves a non-daemon thread behind (a queue runner, a supervisor service, an RPC
+    client blocked on a dead peer) would keep the interpreter alive after the summary line and look
+    like a hung test run. Name the culprits and exit with pytest's own status instead."""
+    import threading
+    stuck = [t for t in threading.enumerate()
+             if t is not threading.main_thread() and t.is_alive() and not t.daemon]
+    if stuck:
+        sys.stderr.write("conftest: non-daemon threads still alive at exit: %s\n" % [t.name for t in stuck])
+        sys.stderr.flush()
+        sys.stdout.flush()
+        os._exit(getattr(config, "_dtf_exitstatus", 0))

@@ -94,7 +94,7 @@ def _cpu_sync_oracle(steps, batch, hidden, lr, world):
                     out.update(raw.ps_client.pull_all(raw.layout, names))
         except Exception as e:  # pragma: no cover
             errs.append(e)
-    ts = [threading.Thread(target=worker, args=(i,)) for i in range(world)]
+    ts = [threading.Thread(target=worker, args=(i,), daemon=True) for i in range(world)]
     [t.start() for t in ts]
     [t.join(120) for t in ts]
     assert not errs, errs

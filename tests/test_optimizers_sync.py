@@ -70,7 +70,7 @@ def test_conditional_accumulator_mean_stale_drop_and_blocking():
     acc.set_global_step(4)
     assert not acc.apply_grad(torch.ones(3), 3) and acc.apply_grad(torch.ones(3), 4)
     got = {}
-    t = threading.Thread(target=lambda: got.setdefault("v", acc.take_grad(2)))
+    t = threading.Thread(target=lambda: got.setdefault("v", acc.take_grad(2)), daemon=True)
     t.start()
     time.sleep(0.05)
     assert t.is_alive()                                         # blocks until 2 fresh gradients
@@ -179,7 +179,7 @@ def test_sync_replicas_equals_large_batch_sgd():
         except Exception as e:  # pragma: no cover
             errors.append(e)
 
-    threads = [threading.Thread(target=worker, args=(i,)) for i in range(N)]
+    threads = [threading.Thread(target=worker, args=(i,), daemon=True) for i in range(N)]
     for t in threads:
         t.start()
     for t in threads:

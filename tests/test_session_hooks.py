@@ -88,7 +88,7 @@ def test_chief_inits_others_wait():
         order.append("worker_ready")
         box["s"] = s
 
-    t = threading.Thread(target=non_chief)
+    t = threading.Thread(target=non_chief, daemon=True)
     t.start()
     time.sleep(0.3)
     assert order == [] and t.is_alive()                 # blocked: nothing is initialised yet
@@ -203,7 +203,7 @@ def test_coordinator_propagates_thread_exception():
     def bad():
         with coord.stop_on_exception():
             raise ValueError("boom")
-    t = threading.Thread(target=bad)
+    t = threading.Thread(target=bad, daemon=True)
     coord.register_thread(t)
     t.start()
     with pytest.raises(ValueError, match="boom"):
