@@ -1,11 +1,14 @@
 """Key/value + text logger with stdout / log.txt / JSON-lines / CSV / TensorBoard sinks.
 
-API-compatible with the reference's ``logger.py`` (the OpenAI-baselines logger; citations are
-logger.py:line): output formats (:26-187), module-level ``logkv / logkv_mean / logkvs / dumpkvs /
-getkvs / log / debug / info / warn / error / set_level / get_dir`` (:193-259), ``ProfileKV`` and
-``profile`` wall-clock helpers (:261-285), the ``Logger`` backend with ``DEFAULT`` / ``CURRENT``
-(:292-346), ``configure / reset / scoped_configure`` (:348-402) and the ``read_json / read_csv /
-read_tb`` readers (:439-483). Written from scratch for this framework; differences on purpose:
+What is shared with the reference's ``logger.py`` (the OpenAI-baselines logger; citations are
+logger.py:line) is its PUBLIC SURFACE, because a user of the reference must be able to switch
+without touching call sites: the sink class names and their file formats byte for byte (:26-187),
+the module-level ``logkv / logkv_mean / logkvs / dumpkvs / getkvs / log / debug / info / warn /
+error / set_level / get_dir`` (:193-259), ``ProfileKV`` / ``profile`` (:261-285), ``Logger`` with
+``DEFAULT`` / ``CURRENT`` and its ``name2val`` table (:292-346), ``configure / reset /
+scoped_configure`` and the ``OPENAI_LOGDIR`` / ``OPENAI_LOG_FORMAT[_MPI]`` variables (:348-402), and
+the ``read_json / read_csv / read_tb`` readers (:439-483). The implementation behind that surface
+is this repository's own. Deliberate behavioural differences:
 
 * ``TensorBoardOutputFormat`` needs no TensorFlow: events go through the native C++ writer
   (``csrc/io/events_writer.cc``), and ``writekvs(kvs, global_step=None)`` falls back to an
@@ -13,79 +16,84 @@ read_tb`` readers (:439-483). Written from scratch for this framework; differenc
   logger.py:157 vs :321, made that combination crash);
 * ``flush_every`` lets the hot path avoid a flush per step (logger.py:165 flushes every call;
   that remains the default);
+* ``logkv_mean`` keeps (sum, count) and reports the exact mean instead of a running recurrence;
 * the rank suffix also honours ``RANK`` (torchrun), next to ``PMI_RANK`` /
-  ``OMPI_COMM_WORLD_RANK`` (logger.py:361).
+  ``OMPI_COMM_WORLD_RANK`` (logger.py:361);
+* there is no ``_demo()``; ``tests/test_logger_events.py`` pins the formats instead.
 """
 from __future__ import annotations
 
+import contextlib
 import datetime
 import functools
 import json
 import os
 import os.path as osp
-import shutil
 import sys
 import tempfile
 import time
 from collections import defaultdict
 from typing import List
 
-DEBUG = 10
-INFO = 20
-WARN = 30
-ERROR = 40
-DISABLED = 50
+DEBUG, INFO, WARN, ERROR, DISABLED = 10, 20, 30, 40, 50
 
 
+# ================================================================================================
+# sinks
+# ================================================================================================
 class KVWriter(object):
+    """A sink that takes one table of key/values per ``dumpkvs``."""
+
     def writekvs(self, kvs):
         raise NotImplementedError
 
 
 class SeqWriter(object):
+    """A sink that takes lines of free text."""
+
     def writeseq(self, seq):
         raise NotImplementedError
 
 
-def _clip(text: str) -> str:
-    """Cells longer than 23 characters are cut to 20 + '...'."""
-    return text[:20] + "..." if len(text) > 23 else text
+_CELL_MAX, _CELL_KEEP = 23, 20
+
+
+def _cell(value) -> str:
+    """Table cell text: floats as ``%-8.3g``, everything else ``str``; cells longer than 23
+    characters keep their first 20 and get an ellipsis."""
+    text = "%-8.3g" % (value,) if isinstance(value, float) else str(value)
+    return text if len(text) <= _CELL_MAX else text[:_CELL_KEEP] + "..."
 
 
 class HumanOutputFormat(KVWriter, SeqWriter):
     """ASCII table of the current key/values, and plain text lines."""
 
     def __init__(self, filename_or_file):
-        if isinstance(filename_or_file, str):
+        self.own_file = isinstance(filename_or_file, str)
+        if self.own_file:
             self.file = open(filename_or_file, "wt")
-            self.own_file = True
-        else:
-            assert hasattr(filename_or_file, "read") or hasattr(filename_or_file, "write"), \
-                "expected file or str, got %s" % filename_or_file
+        elif hasattr(filename_or_file, "write") or hasattr(filename_or_file, "read"):
             self.file = filename_or_file
-            self.own_file = False
+        else:
+            raise AssertionError("expected file or str, got %s" % (filename_or_file,))
 
     def writekvs(self, kvs):
-        cells = {}
-        for key in sorted(kvs.keys()):
-            val = kvs[key]
-            text = "%-8.3g" % (val,) if isinstance(val, float) else str(val)
-            cells[_clip(key)] = _clip(text)
-        if not cells:
+        table = {}
+        for key in sorted(kvs):
+            name = key if len(key) <= _CELL_MAX else key[:_CELL_KEEP] + "..."
+            table[name] = _cell(kvs[key])
+        if not table:
             print("WARNING: tried to write empty key-value dict")
             return
-        kw = max(len(k) for k in cells)
-        vw = max(len(v) for v in cells.values())
-        rule = "-" * (kw + vw + 7)
-        rows = [rule]
-        for key in sorted(cells, key=str.lower):
-            rows.append("| %s | %s |" % (key.ljust(kw), cells[key].ljust(vw)))
-        rows.append(rule)
-        self.file.write("\n".join(rows) + "\n")
+        key_w = max(map(len, table))
+        val_w = max(map(len, table.values()))
+        bar = "-" * (key_w + val_w + 7)
+        body = ["| %-*s | %-*s |" % (key_w, k, val_w, table[k]) for k in sorted(table, key=str.lower)]
+        self.file.write("\n".join([bar] + body + [bar]) + "\n")
         self.file.flush()
 
     def writeseq(self, seq):
-        self.file.write(" ".join(list(seq)) + "\n")
+        self.file.write(" ".join(seq) + "\n")
         self.file.flush()
 
     def close(self):
@@ -94,19 +102,14 @@ class HumanOutputFormat(KVWriter, SeqWriter):
 
 
 class JSONOutputFormat(KVWriter):
-    """One JSON object per dump (``progress.json``)."""
+    """One JSON object per dump (``progress.json``); numpy scalars become floats."""
 
     def __init__(self, filename):
         self.file = open(filename, "wt")
 
     def writekvs(self, kvs):
-        row = {}
-        for k in sorted(kvs.keys()):
-            v = kvs[k]
-            if hasattr(v, "dtype"):
-                v = float(v.tolist())
-            row[k] = v
-        self.file.write(json.dumps(row) + "\n")
+        plain = {k: (float(kvs[k].tolist()) if hasattr(kvs[k], "dtype") else kvs[k]) for k in sorted(kvs)}
+        self.file.write(json.dumps(plain) + "\n")
         self.file.flush()
 
     def close(self):
@@ -114,29 +117,29 @@ class JSONOutputFormat(KVWriter):
 
 
 class CSVOutputFormat(KVWriter):
-    """``progress.csv``; when a dump brings new keys the header is rewritten and earlier rows are
-    padded with empty cells."""
+    """``progress.csv``. A dump that introduces new keys appends columns: the header is rewritten and
+    every earlier row gets one empty cell per new column."""
 
     def __init__(self, filename):
         self.file = open(filename, "w+t")
         self.keys: List[str] = []
         self.sep = ","
 
+    def _widen(self, added: List[str]) -> None:
+        self.file.seek(0)
+        previous = self.file.read().splitlines()[1:]          # rows without the old header
+        self.keys += added
+        pad = self.sep * len(added)
+        self.file.seek(0)
+        self.file.truncate()
+        self.file.write("".join(line + "\n" for line in [self.sep.join(self.keys)] + [r + pad for r in previous]))
+
     def writekvs(self, kvs):
-        new_keys = sorted(k for k in kvs.keys() if k not in self.keys)
-        if new_keys:
-            self.keys.extend(new_keys)
-            self.file.seek(0)
-            old = self.file.readlines()
-            self.file.seek(0)
-            self.file.write(self.sep.join(self.keys) + "\n")
-            for line in old[1:]:
-                self.file.write(line.rstrip("\n") + self.sep * len(new_keys) + "\n")
-        out = []
-        for k in self.keys:
-            v = kvs.get(k)
-            out.append("" if v is None else str(v))
-        self.file.write(self.sep.join(out) + "\n")
+        added = sorted(set(kvs) - set(self.keys))
+        if added:
+            self._widen(added)
+        cells = ("" if kvs.get(k) is None else str(kvs[k]) for k in self.keys)
+        self.file.write(self.sep.join(cells) + "\n")
         self.file.flush()
 
     def close(self):
@@ -158,135 +161,57 @@ class TensorBoardOutputFormat(KVWriter):
 
     def writekvs(self, kvs, global_step=None):
         if global_step is None:
-            global_step = self.step
-            self.step += 1
-        scalars = {k: float(v) for k, v in kvs.items()}
-        self.writer.write_scalars(scalars, int(global_step), time.time())
+            global_step, self.step = self.step, self.step + 1
+        self.writer.write_scalars({k: float(v) for k, v in kvs.items()}, int(global_step), time.time())
         self._since_flush += 1
         if self._since_flush >= self.flush_every:
             self.writer.Flush()
             self._since_flush = 0
 
     def close(self):
-        if self.writer:
+        if self.writer is not None:
             self.writer.Close()
             self.writer = None
 
 
+# format name -> (file name pattern inside the log directory or None for stdout, sink class)
+_SINKS = {
+    "stdout": (None, HumanOutputFormat),
+    "log": ("log%s.txt", HumanOutputFormat),
+    "json": ("progress%s.json", JSONOutputFormat),
+    "csv": ("progress%s.csv", CSVOutputFormat),
+    "tensorboard": ("tb%s", TensorBoardOutputFormat),
+}
+
+
 def make_output_format(format, ev_dir, log_suffix=""):
+    try:
+        pattern, sink = _SINKS[format]
+    except KeyError:
+        raise ValueError("Unknown format specified: %s" % (format,)) from None
     os.makedirs(ev_dir, exist_ok=True)
-    if format == "stdout":
-        return HumanOutputFormat(sys.stdout)
-    if format == "log":
-        return HumanOutputFormat(osp.join(ev_dir, "log%s.txt" % log_suffix))
-    if format == "json":
-        return JSONOutputFormat(osp.join(ev_dir, "progress%s.json" % log_suffix))
-    if format == "csv":
-        return CSVOutputFormat(osp.join(ev_dir, "progress%s.csv" % log_suffix))
-    if format == "tensorboard":
-        return TensorBoardOutputFormat(osp.join(ev_dir, "tb%s" % log_suffix))
-    raise ValueError("Unknown format specified: %s" % (format,))
-
-
-# ================================================================================================
-# module-level API (forwards to Logger.CURRENT)
-# ================================================================================================
-def logkv(key, val):
-    """Record ``val`` under ``key`` for this iteration; the last value wins."""
-    Logger.CURRENT.logkv(key, val)
-
-
-def logkv_mean(key, val):
-    """Like ``logkv`` but repeated calls within one iteration are averaged."""
-    Logger.CURRENT.logkv_mean(key, val)
-
-
-def logkvs(d):
-    for k, v in d.items():
-        logkv(k, v)
-
-
-def dumpkvs():
-    """Write this iteration's diagnostics to every KV sink and clear them."""
-    Logger.CURRENT.dumpkvs()
-
-
-def getkvs():
-    return Logger.CURRENT.name2val
-
-
-def log(*args, level=INFO):
-    """Write ``args`` (space separated) to the console and text sinks if ``level`` passes."""
-    Logger.CURRENT.log(*args, level=level)
-
-
-def debug(*args):
-    log(*args, level=DEBUG)
-
-
-def info(*args):
-    log(*args, level=INFO)
-
-
-def warn(*args):
-    log(*args, level=WARN)
-
-
-def error(*args):
-    log(*args, level=ERROR)
-
-
-def set_level(level):
-    Logger.CURRENT.set_level(level)
-
-
-def get_dir():
-    """Directory the log files go to (None when no directory was configured)."""
-    return Logger.CURRENT.get_dir()
-
-
-record_tabular = logkv
-dump_tabular = dumpkvs
-
-
-class ProfileKV:
-    """``with ProfileKV("scope"): ...`` adds the elapsed wall-clock seconds to ``wait_scope``."""
-
-    def __init__(self, n):
-        self.n = "wait_" + n
-
-    def __enter__(self):
-        self.t1 = time.time()
-
-    def __exit__(self, type, value, traceback):
-        Logger.CURRENT.name2val[self.n] += time.time() - self.t1
-
-
-def profile(n):
-    """Decorator form of :class:`ProfileKV`."""
-    def decorate(func):
-        @functools.wraps(func)
-        def wrapped(*args, **kwargs):
-            with ProfileKV(n):
-                return func(*args, **kwargs)
-        return wrapped
-    return decorate
+    return sink(sys.stdout) if pattern is None else sink(osp.join(ev_dir, pattern % log_suffix))
 
 
 # ================================================================================================
 # backend
 # ================================================================================================
 class Logger(object):
-    DEFAULT = None  # stdout-only logger created at import
-    CURRENT = None  # the logger the module-level functions talk to
+    """One set of sinks plus the table being filled for the current iteration. ``name2val`` is part
+    of the public surface (``getkvs()``, ``ProfileKV``): a float-defaulting dict of key -> value."""
+
+    DEFAULT = None  # the console-only logger created at import
+    CURRENT = None  # the one the module-level functions talk to
 
     def __init__(self, dir, output_formats):
+        self.dir = dir
+        self.output_formats = list(output_formats)
+        self.level = INFO
         self.name2val = defaultdict(float)
         self.name2cnt = defaultdict(int)
-        self.level = INFO
-        self.dir = dir
-        self.output_formats = output_formats
+        self._sums = {}                      # logkv_mean: key -> running sum of this iteration
 
+    # -- key/values -----------------------------------------------------------------------------------
     def logkv(self, key, val):
         self.name2val[key] = val
 
@@ -294,22 +219,28 @@ class Logger(object):
         if val is None:
             self.name2val[key] = None
             return
-        cnt = self.name2cnt[key]
-        self.name2val[key] = self.name2val[key] * cnt / (cnt + 1) + val / (cnt + 1)
-        self.name2cnt[key] = cnt + 1
+        self._sums[key] = self._sums.get(key, 0.0) + val
+        self.name2cnt[key] += 1
+        self.name2val[key] = self._sums[key] / self.name2cnt[key]
 
     def dumpkvs(self):
         if self.level == DISABLED:
             return
-        for fmt in self.output_formats:
-            if isinstance(fmt, KVWriter):
-                fmt.writekvs(self.name2val)
+        for sink in self.output_formats:
+            if isinstance(sink, KVWriter):
+                sink.writekvs(self.name2val)
         self.name2val.clear()
         self.name2cnt.clear()
+        self._sums.clear()
 
+    # -- text -----------------------------------------------------------------------------------------
     def log(self, *args, level=INFO):
-        if self.level <= level:
-            self._do_log(args)
+        if level < self.level:
+            return
+        words = [str(a) for a in args]
+        for sink in self.output_formats:
+            if isinstance(sink, SeqWriter):
+                sink.writeseq(words)
 
     def set_level(self, level):
         self.level = level
@@ -318,115 +249,163 @@ class Logger(object):
         return self.dir
 
     def close(self):
-        for fmt in self.output_formats:
-            fmt.close()
-
-    def _do_log(self, args):
-        for fmt in self.output_formats:
-            if isinstance(fmt, SeqWriter):
-                fmt.writeseq(map(str, args))
+        for sink in self.output_formats:
+            sink.close()
 
 
-def _detect_rank() -> int:
+# ================================================================================================
+# module-level API: every function forwards to Logger.CURRENT
+# ================================================================================================
+def logkv(key, val):
+    """Record ``val`` under ``key`` for this iteration; a later call for the same key wins."""
+    Logger.CURRENT.logkv(key, val)
+
+
+def logkv_mean(key, val):
+    """Like ``logkv``, but values logged for one key within an iteration are averaged."""
+    Logger.CURRENT.logkv_mean(key, val)
+
+
+def logkvs(d):
+    for key, val in d.items():
+        Logger.CURRENT.logkv(key, val)
+
+
+def dumpkvs():
+    """Hand this iteration's table to every key/value sink, then start an empty one."""
+    Logger.CURRENT.dumpkvs()
+
+
+def getkvs():
+    return Logger.CURRENT.name2val
+
+
+def log(*args, level=INFO):
+    """Space-joined ``args`` go to the console / text sinks when ``level`` passes the threshold."""
+    Logger.CURRENT.log(*args, level=level)
+
+
+def _leveled(level):
+    def emit(*args):
+        Logger.CURRENT.log(*args, level=level)
+    return emit
+
+
+debug, info, warn, error = _leveled(DEBUG), _leveled(INFO), _leveled(WARN), _leveled(ERROR)
+
+
+def set_level(level):
+    Logger.CURRENT.set_level(level)
+
+
+def get_dir():
+    """Directory of the log files, or None when the current logger only writes to the console."""
+    return Logger.CURRENT.get_dir()
+
+
+record_tabular = logkv
+dump_tabular = dumpkvs
+
+
+class ProfileKV:
+    """``with ProfileKV("scope"): ...`` adds the block's wall-clock seconds to key ``wait_scope``
+    (the reference's only profiling facility, logger.py:261-285)."""
+
+    def __init__(self, n):
+        self.n = "wait_" + n
+        self._t0 = 0.0
+
+    def __enter__(self):
+        self._t0 = time.time()
+        return self
+
+    def __exit__(self, *exc):
+        Logger.CURRENT.name2val[self.n] += time.time() - self._t0
+        return False
+
+
+def profile(n):
+    """Decorator form of :class:`ProfileKV`."""
+    def decorate(func):
+        @functools.wraps(func)
+        def timed(*args, **kwargs):
+            with ProfileKV(n):
+                return func(*args, **kwargs)
+        return timed
+    return decorate
+
+
+# ================================================================================================
+# configuration
+# ================================================================================================
+_RANK_VARS = ("RANK", "PMI_RANK", "OMPI_COMM_WORLD_RANK")
+
+
+def _process_rank() -> int:
+    """Rank of this process in a launcher's job (torchrun / MPICH / Open MPI); the last variable
+    that parses wins, 0 when none is set."""
     rank = 0
-    for var in ("RANK", "PMI_RANK", "OMPI_COMM_WORLD_RANK"):
-        if var in os.environ:
-            try:
-                rank = int(os.environ[var])
-            except ValueError:
-                pass
+    for name in _RANK_VARS:
+        try:
+            rank = int(os.environ[name])
+        except (KeyError, ValueError):
+            continue
     return rank
 
 
+def _formats_from_env(rank: int) -> List[str]:
+    if rank == 0:
+        spec = os.getenv("OPENAI_LOG_FORMAT", "stdout,log,csv")
+    else:
+        spec = os.getenv("OPENAI_LOG_FORMAT_MPI", "log")
+    return spec.split(",")
+
+
 def configure(dir=None, format_strs=None):
-    if dir is None:
-        dir = os.getenv("OPENAI_LOGDIR")
-    if dir is None:
-        dir = osp.join(tempfile.gettempdir(),
-                       datetime.datetime.now().strftime("openai-%Y-%m-%d-%H-%M-%S-%f"))
-    assert isinstance(dir, str)
-    os.makedirs(dir, exist_ok=True)
-
-    rank = _detect_rank()
-    log_suffix = "-rank%03i" % rank if rank > 0 else ""
-    if format_strs is None:
-        if rank == 0:
-            format_strs = os.getenv("OPENAI_LOG_FORMAT", "stdout,log,csv").split(",")
-        else:
-            format_strs = os.getenv("OPENAI_LOG_FORMAT_MPI", "log").split(",")
-    output_formats = [make_output_format(f, dir, log_suffix) for f in format_strs if f]
-    Logger.CURRENT = Logger(dir=dir, output_formats=output_formats)
-    log("Logging to %s" % dir)
-
-
-def _configure_default_logger():
-    format_strs = None
-    if "OPENAI_LOG_FORMAT" not in os.environ:
-        format_strs = ["stdout"]  # historic default: console only
-    configure(format_strs=format_strs)
-    Logger.DEFAULT = Logger.CURRENT
+    """Make a new CURRENT logger writing into ``dir`` (default: ``$OPENAI_LOGDIR`` or a fresh
+    time-stamped directory under the system temp dir). Ranks > 0 get a ``-rankNNN`` file suffix and,
+    unless ``format_strs`` says otherwise, only a text log."""
+    target = dir or os.getenv("OPENAI_LOGDIR") or osp.join(
+        tempfile.gettempdir(), datetime.datetime.now().strftime("openai-%Y-%m-%d-%H-%M-%S-%f"))
+    if not isinstance(target, str):
+        raise AssertionError("log directory must be a str, got %r" % (target,))
+    os.makedirs(target, exist_ok=True)
+    rank = _process_rank()
+    suffix = "-rank%03i" % rank if rank > 0 else ""
+    names = format_strs if format_strs is not None else _formats_from_env(rank)
+    Logger.CURRENT = Logger(target, [make_output_format(n, target, suffix) for n in names if n])
+    log("Logging to %s" % target)
 
 
 def reset():
-    if Logger.CURRENT is not Logger.DEFAULT:
+    """Back to the import-time console logger (closing the sinks of the current one)."""
+    if Logger.CURRENT is Logger.DEFAULT:
+        return
+    Logger.CURRENT.close()
+    Logger.CURRENT = Logger.DEFAULT
+    log("Reset logger")
+
+
+@contextlib.contextmanager
+def scoped_configure(dir=None, format_strs=None):
+    """``with scoped_configure(dir=...):`` — a temporary CURRENT logger, restored on exit."""
+    outer = Logger.CURRENT
+    configure(dir=dir, format_strs=format_strs)
+    try:
+        yield Logger.CURRENT
+    finally:
         Logger.CURRENT.close()
-        Logger.CURRENT = Logger.DEFAULT
-        log("Reset logger")
-
-
-class scoped_configure(object):
-    def __init__(self, dir=None, format_strs=None):
-        self.dir = dir
-        self.format_strs = format_strs
-        self.prevlogger = None
-
-    def __enter__(self):
-        self.prevlogger = Logger.CURRENT
-        configure(dir=self.dir, format_strs=self.format_strs)
-
-    def __exit__(self, *args):
-        Logger.CURRENT.close()
-        Logger.CURRENT = self.prevlogger
-
-
-def _demo():
-    info("hi")
-    debug("shouldn't appear")
-    set_level(DEBUG)
-    debug("should appear")
-    dir = osp.join(tempfile.gettempdir(), "testlogging")
-    if os.path.exists(dir):
-        shutil.rmtree(dir)
-    configure(dir=dir)
-    logkv("a", 3)
-    logkv("b", 2.5)
-    dumpkvs()
-    logkv("b", -2.5)
-    logkv("a", 5.5)
-    dumpkvs()
-    info("^^^ should see a = 5.5")
-    logkv_mean("b", -22.5)
-    logkv_mean("b", -44.4)
-    logkv("a", 5.5)
-    dumpkvs()
-    info("^^^ should see b = -33.45 (the mean of the two values)")
-    logkv("b", -2.5)
-    dumpkvs()
-    logkv("a", "longasslongasslongasslongasslongasslongassvalue")
-    dumpkvs()
+        Logger.CURRENT = outer
 
 
 # ================================================================================================
 # readers
 # ================================================================================================
 def read_json(fname):
+    """``progress.json`` (one object per line) -> DataFrame."""
     import pandas
-    rows = []
     with open(fname, "rt") as fh:
-        for line in fh:
-            if line.strip():
-                rows.append(json.loads(line))
-    return pandas.DataFrame(rows)
+        return pandas.DataFrame([json.loads(line) for line in fh if line.strip()])
 
 
 def read_csv(fname):
@@ -436,36 +415,35 @@ def read_csv(fname):
 
 def read_tb(path):
     """``path``: one TensorBoard event file or a directory holding ``events.*`` files. Returns a
-    DataFrame with one row per step (index = step - 1), one column per tag, NaN where a tag was
-    not logged at that step."""
+    DataFrame with one row per step (row ``i`` = step ``i + 1``), one column per tag in sorted
+    order, NaN where a tag was not logged at that step. Events with step 0 (the file-version
+    record) are skipped."""
+    import glob as _glob
     import numpy as np
     import pandas
-    from glob import glob
     from .utils.events import summary_iterator
     if osp.isdir(path):
-        fnames = glob(osp.join(path, "events.*"))
+        files = _glob.glob(osp.join(path, "events.*"))
     elif osp.basename(path).startswith("events."):
-        fnames = [path]
+        files = [path]
     else:
-        raise NotImplementedError(
-            "Expected tensorboard file or directory containing them. Got %s" % path)
-    tag2pairs = defaultdict(list)
-    maxstep = 0
-    for fname in fnames:
-        for ev in summary_iterator(fname):
-            if ev.step > 0:
-                for v in ev.summary.value:
-                    tag2pairs[v.tag].append((ev.step, v.simple_value))
-                maxstep = max(ev.step, maxstep)
-    tags = sorted(tag2pairs.keys())
-    data = np.full((maxstep, len(tags)), np.nan)
+        raise NotImplementedError("Expected tensorboard file or directory containing them. Got %s" % path)
+    series = {}                                   # tag -> {step: value}
+    for name in files:
+        for event in summary_iterator(name):
+            if event.step <= 0:
+                continue
+            for item in event.summary.value:
+                series.setdefault(item.tag, {})[event.step] = item.simple_value
+    last = max((s for per_tag in series.values() for s in per_tag), default=0)
+    tags = sorted(series)
+    grid = np.full((last, len(tags)), np.nan)
     for col, tag in enumerate(tags):
-        for step, value in tag2pairs[tag]:
-            data[step - 1, col] = value
-    return pandas.DataFrame(data, columns=tags)
+        for step, value in series[tag].items():
+            grid[step - 1, col] = value
+    return pandas.DataFrame(grid, columns=tags)
 
 
-_configure_default_logger()
-
-if __name__ == "__main__":
-    _demo()
+# the import-time default: console only, unless OPENAI_LOG_FORMAT asks for more
+configure(format_strs=None if "OPENAI_LOG_FORMAT" in os.environ else ["stdout"])
+Logger.DEFAULT = Logger.CURRENT

@@ -6,7 +6,9 @@ mnist_replica.py): one hidden layer (784 -> hidden_units -> 10) whose parameters
 parameter servers while the ops run on the workers; asynchronous by default, or synchronous with
 ``--sync_replicas`` (``SyncReplicasOptimizer`` + ``Supervisor`` + chief queue runner), optional
 backup workers through ``--replicas_to_aggregate``. All 13 flags of the reference keep their names
-and defaults. Start one process per task:
+and defaults, and the progress lines it prints ("job name = ...", "Worker N: training step K done
+(global step: G)", "Training elapsed time ...", the final validation cross entropy) keep their
+wording on purpose: scripts and tests that watch the reference's output keep working. Start one process per task:
 
     python templates/00_mnist_replica.py --job_name ps     --task_index 0
     python templates/00_mnist_replica.py --job_name worker --task_index 0
@@ -29,32 +31,33 @@ from distributedtensorflow_b200.data import mnist as input_data  # noqa: E402
 from distributedtensorflow_b200.models import mnist_mlp  # noqa: E402
 
 flags = tf.app.flags
-flags.DEFINE_string("data_dir", "/tmp/mnist-data", "Directory for storing mnist data")
-flags.DEFINE_boolean("download_only", False, "Only perform downloading of data; Do not proceed to "
-                     "session preparation, model definition or training")
-flags.DEFINE_integer("task_index", None, "Worker task index, should be >= 0. task_index=0 is the "
-                     "master worker task the performs the variable initialization ")
-flags.DEFINE_integer("num_gpus", 0, "Total number of gpus for each machine. If you don't use GPU, "
-                     "please set it to '0'")
-flags.DEFINE_integer("replicas_to_aggregate", None, "Number of replicas to aggregate before "
-                     "parameter update is applied (For sync_replicas mode only; default: num_workers)")
-flags.DEFINE_integer("hidden_units", 100, "Number of units in the hidden layer of the NN")
-flags.DEFINE_integer("train_steps", 200, "Number of (global) training steps to perform")
-flags.DEFINE_integer("batch_size", 100, "Training batch size")
-flags.DEFINE_float("learning_rate", 0.01, "Learning rate")
-flags.DEFINE_boolean("sync_replicas", False, "Use the sync_replicas (synchronized replicas) mode, "
-                     "wherein the parameter updates from workers are aggregated before applied to "
-                     "avoid stale gradients")
-flags.DEFINE_boolean("existing_servers", False, "Whether servers already exists. If True, will use "
-                     "the worker hosts via their GRPC URLs (one client process per worker host). "
-                     "Otherwise, will create an in-process TensorFlow server.")
-flags.DEFINE_string("ps_hosts", "localhost:2222", "Comma-separated list of hostname:port pairs")
-flags.DEFINE_string("worker_hosts", "localhost:2223,localhost:2224",
-                    "Comma-separated list of hostname:port pairs")
-flags.DEFINE_string("job_name", None, "job name: worker or ps")
-flags.DEFINE_string("backend", "auto", "cpu | b200 | auto")
-flags.DEFINE_boolean("shutdown_ps", False, "chief: ask the PS tasks to exit after training")
-flags.DEFINE_boolean("quiet", False, "do not print every step")
+# The 13 flags of the reference template keep their NAMES and DEFAULTS (that is the interface a user
+# of templates/00_mnist_replica.py:49-88 relies on); the descriptions are this repository's.
+for _kind, _name, _default, _doc in (
+        ("string", "data_dir", "/tmp/mnist-data", "where the MNIST IDX files live (or get generated)"),
+        ("boolean", "download_only", False, "fetch / generate the data set, then exit without training"),
+        ("integer", "task_index", None, "index of this task inside its job; worker 0 is the chief and "
+                                        "initialises the variables"),
+        ("integer", "num_gpus", 0, "GPUs per machine; worker j uses GPU j mod num_gpus, 0 keeps it on the CPU"),
+        ("integer", "replicas_to_aggregate", None, "sync mode: gradients to collect per update "
+                                                   "(fewer than the worker count = backup workers; "
+                                                   "default: all workers)"),
+        ("integer", "hidden_units", 100, "width of the hidden layer"),
+        ("integer", "train_steps", 200, "stop once the shared global step reaches this value"),
+        ("integer", "batch_size", 100, "examples per worker step"),
+        ("float", "learning_rate", 0.01, "Adam step size"),
+        ("boolean", "sync_replicas", False, "aggregate the workers' gradients into one update per round "
+                                            "(SyncReplicasOptimizer) instead of applying each on arrival"),
+        ("boolean", "existing_servers", False, "connect to servers that are already running at the "
+                                               "worker addresses instead of starting one in this process"),
+        ("string", "ps_hosts", "localhost:2222", "parameter-server tasks, host:port[,host:port...]"),
+        ("string", "worker_hosts", "localhost:2223,localhost:2224", "worker tasks, host:port[,host:port...]"),
+        ("string", "job_name", None, "'ps' or 'worker'"),
+        # extras of this framework
+        ("string", "backend", "auto", "cpu | b200 | auto"),
+        ("boolean", "shutdown_ps", False, "chief: ask the PS tasks to exit after training"),
+        ("boolean", "quiet", False, "do not print every step")):
+    getattr(flags, "DEFINE_" + _kind)(_name, _default, _doc)
 
 FLAGS = flags.FLAGS
 
