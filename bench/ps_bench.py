@@ -73,6 +73,12 @@ def main() -> int:
     ap.add_argument("--ckpt-dir", default="")
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"])
+    ap.add_argument("--opt", action="append", default=[], metavar="KEY=VAL", help="extra executor option")
+    ap.add_argument("--lockstep", action="store_true",
+                    help="async correctness mode: workers take turns, one step each, and every push is "
+                         "flushed before the next worker steps - the run is then a deterministic "
+                         "sequence of applies that a single-process oracle can replay")
+    ap.add_argument("--dump-params", default="", help="write the final parameters (+ this worker's mirror) as npz")
     args = ap.parse_args()
 
     import numpy as np
@@ -126,12 +132,26 @@ def main() -> int:
                 opt = tf.train.SyncReplicasOptimizer(opt, replicas_to_aggregate=nw, total_num_replicas=nw)
             train_op = opt.minimize(loss, global_step=gs)
         hooks = [opt.make_session_run_hook(wk_index == 0)] if args.mode == "sync" else []
-        cfg = tf.ConfigProto(backend="b200", device="cuda:%d" % local_rank, push_mode=args.push_mode)
+        cfg = tf.ConfigProto(backend="b200", device="cuda:%d" % local_rank, push_mode=args.push_mode,
+                             **{k: (v == "1") if v in ("0", "1") else (int(v) if v.lstrip("-").isdigit() else v)
+                                for k, v in (o.split("=", 1) for o in args.opt)})
         batches = make_batches(args, wk_index)
         with tf.train.MonitoredTrainingSession(master=servers[-1].target, is_chief=(wk_index == 0), config=cfg,
                                                hooks=hooks, recovery_wait_secs=0.05,
                                                checkpoint_dir=None) as sess:
             raw = sess._tf_sess()
+            if args.lockstep:
+                # round-robin turns over the workers; PS-only ranks just keep the barriers company
+                for i in range(args.warmup + args.steps):
+                    for turn in range(nw):
+                        if turn == wk_index:
+                            bx, by = batches[i % len(batches)]
+                            _, l, g = sess.run([train_op, loss, gs], feed_dict={X: bx, Y: by})
+                            raw._runner.flush_pushes()
+                            raw._runner.stream.synchronize()
+                        if world > 1:
+                            dist.barrier()
+                args.steps_done, args.steps, args.warmup = args.warmup + args.steps, 0, 0
             for i in range(args.warmup):
                 bx, by = batches[i % len(batches)]
                 _, l, g = sess.run([train_op, loss, gs], feed_dict={X: bx, Y: by})
@@ -158,6 +178,22 @@ def main() -> int:
             if runner.use_mailbox:
                 runner.flush_pushes()        # my last gradients have been applied by their owners
                 extra["push"] = "mailbox"
+            if args.dump_params:
+                if world > 1:
+                    dist.barrier()           # every worker's last gradient is applied and broadcast
+                names = [v.name for v in tf.trainable_variables()]
+                dump = {}
+                for n in names:
+                    dump[n.replace("/", "__")] = runner.store.read_variable(n)
+                    if runner.use_mirror:
+                        for form, arr in runner.store.read_mirror(n).items():
+                            dump["mirror_%s__%s" % (form, n.replace("/", "__"))] = arr
+                if runner.use_mirror:
+                    dump["mirror_version"] = runner.store.mirror_hdr_u32(128, nps)
+                    dump["mirror_consumed"] = runner.store.mirror_hdr_u32(256, nps)
+                    extra["mirror"] = True
+                    extra["graph_drain_shards"] = list(runner.my_shards)
+                np.savez(args.dump_params % rank if "%" in args.dump_params else args.dump_params, **dump)
             if args.check and args.mode == "sync":
                 names = [v.name for v in tf.trainable_variables()]
                 got = {n: runner.store.read_variable(n) for n in names}
@@ -184,6 +220,11 @@ def main() -> int:
             result = dict(final_step=final_step, final_loss=final_loss, launches_per_step=runner.train_state().launches_per_step,
                           **extra)
     else:
+        if args.lockstep and world > 1:
+            for _ in range((args.warmup + args.steps) * len(worker_ranks)):
+                dist.barrier()
+        if args.dump_params and world > 1:
+            dist.barrier()
         if world > 1:
             dist.barrier()
     if world > 1:
@@ -197,8 +238,8 @@ def main() -> int:
         dev_ms, wall_ms = [float(t) for t in times.tolist()]
         steps_total = args.steps * (nw if args.mode == "async" else 1)
         print(json.dumps(dict(
-            metric="global_steps_per_sec", value=round(steps_total / (dev_ms / 1e3), 2), n_gpus=world,
-            ms_per_step=round(dev_ms / args.steps, 5), e2e_value=round(steps_total / (wall_ms / 1e3), 2),
+            metric="global_steps_per_sec", value=round(steps_total / max(dev_ms / 1e3, 1e-9), 2), n_gpus=world,
+            ms_per_step=round(dev_ms / max(args.steps, 1), 5), e2e_value=round(steps_total / max(wall_ms / 1e3, 1e-9), 2),
             config=dict(model=args.model, mode=args.mode, topology=args.topology, placement=args.placement,
                         optimizer=args.optimizer, batch_per_worker=args.batch, hidden=args.hidden,
                         workers=nw, ps_shards=nps, push_mode=args.push_mode, l2="not flushed" if args.no_l2_flush else "flushed per step"),

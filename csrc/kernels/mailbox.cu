@@ -43,6 +43,7 @@ struct MboxPushArgs {
   const dtf_ps_ctrl* ctrl_step;
   unsigned long long* step_out;
   dtf_result_sink sink;
+  const dtf_mirror_hdr* my_hdr;
 };
 
 __global__ void __launch_bounds__(MBOX_THREADS)
@@ -92,8 +93,12 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
   if (static_cast<int>(threadIdx.x) < a.n_owners) {
     dtf_mbox_flags* f = a.owner_flags[threadIdx.x];
     st_release_sys_u32(&f->produced[a.worker_id], seq + 1u);
-    // how far has this owner got with MY gradients (flow control for the next pushes)
-    const unsigned int c = ld_acquire_sys_u32(&f->consumed[a.worker_id]);
+    // how far has this owner got with MY gradients (flow control for the next pushes): from my
+    // mirror's header when the owners keep one fresh (local read), else over NVLink
+    const unsigned int c =
+        a.my_hdr != nullptr
+            ? *reinterpret_cast<const volatile unsigned int*>(&a.my_hdr->consumed[threadIdx.x])
+            : ld_acquire_sys_u32(&f->consumed[a.worker_id]);
     atomicMin(&s_min, c);
   }
   __syncthreads();
@@ -102,8 +107,11 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
     if (a.min_consumed_out != nullptr) *a.min_consumed_out = s_min;
     // what sess.run([train_op, global_step]) reports: the shared counter as this step ends
     unsigned long long gs = 0;
-    if (a.ctrl_step != nullptr) gs = ld_acquire_sys_u64(&a.ctrl_step->global_step);
-    if (a.step_out != nullptr && a.ctrl_step != nullptr) *a.step_out = gs;
+    if (a.my_hdr != nullptr)
+      gs = *reinterpret_cast<const volatile unsigned long long*>(&a.my_hdr->global_step);
+    else if (a.ctrl_step != nullptr)
+      gs = ld_acquire_sys_u64(&a.ctrl_step->global_step);
+    if (a.step_out != nullptr && (a.ctrl_step != nullptr || a.my_hdr != nullptr)) *a.step_out = gs;
     if (a.sink.host_dst != nullptr) {
       const float loss = *reinterpret_cast<const volatile float*>(a.sink.loss_src);
       const unsigned int q = *reinterpret_cast<volatile unsigned int*>(a.sink.seq_dev) + 1u;
@@ -117,14 +125,25 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
   }
 }
 
+// Claims the shard's drain lock and records which workers have an unconsumed gradient.
+// todo[w] = 1 + buffer index of worker w's oldest pending gradient (0 = nothing);
+// todo[DTF_MAX_WORKERS] = 1 when this launch holds the lock (the drain kernel releases it).
 __global__ void mailbox_snapshot_kernel(dtf_mbox_flags* flags, unsigned int* todo, int n_workers,
                                         int depth) {
   griddep_wait();
   griddep_launch();
   const int w = threadIdx.x;
+  unsigned int claimed = 0;
+  if (w == 0) {
+    if (*reinterpret_cast<volatile unsigned int*>(&flags->paused) == 0)
+      claimed = (atomicCAS(&flags->lock, 0u, 1u) == 0u) ? 1u : 0u;
+    __threadfence();   // acquire: the previous holder's consumed[] / state precede its unlock
+    todo[DTF_MAX_WORKERS] = claimed;
+  }
+  claimed = __shfl_sync(0xffffffffu, claimed, 0);
   if (w >= DTF_MAX_WORKERS) return;
   unsigned int t = 0;
-  if (w < n_workers) {
+  if (claimed && w < n_workers) {
     const unsigned int p = ld_acquire_sys_u32(&flags->produced[w]);
     const unsigned int c = *reinterpret_cast<volatile unsigned int*>(&flags->consumed[w]);
     if (static_cast<int>(p - c) > 0) t = c % static_cast<unsigned int>(depth) + 1u;  // oldest first
@@ -133,12 +152,12 @@ __global__ void mailbox_snapshot_kernel(dtf_mbox_flags* flags, unsigned int* tod
 }
 
 constexpr int DRAIN_THREADS = 256;
-constexpr int DRAIN_VEC = 4;
-constexpr int DRAIN_UNROLL = 2;
-constexpr int DRAIN_CHUNK = DRAIN_THREADS * DRAIN_VEC * DRAIN_UNROLL;  // 2048 elements / CTA
+constexpr int DRAIN_VEC = 8;                              // elements per thread: two float4 / one bf16x8
+constexpr int DRAIN_CHUNK = DRAIN_THREADS * DRAIN_VEC;    // 2048 elements / CTA
 
 struct DrainArgs {
   dtf_apply_item items[DTF_MAX_APPLY_ITEMS];
+  dtf_drain_mirror_item mirror[DTF_MAX_APPLY_ITEMS];
   int block_start[DTF_MAX_APPLY_ITEMS + 1];
   int n_items;
   int total_blocks;
@@ -150,9 +169,30 @@ struct DrainArgs {
   long long slot_stride;  // bytes
   int depth;
   int n_workers;
+  int bcast;              // mirror[] is valid: broadcast into flags->mirror_base[*]
+  int shard;
   unsigned long long* step_out;
   unsigned int* block_counter;
 };
+
+// bf16 store of cnt (<= 8) consecutive elements of a [rows, cols] tensor kept with row pitch ld,
+// f = flat index of v[0]. vec8: cols, ld, f are multiples of 8 and base is 16-byte aligned.
+__device__ __forceinline__ void put_bf16(__nv_bfloat16* base, long long f, int cols, int ld,
+                                         const float* v, int cnt, bool vec8) {
+  if (vec8 && cnt == 8) {
+    const long long r = f / cols, c = f - r * cols;
+    *reinterpret_cast<uint4*>(base + r * ld + c) =
+        make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                   pack_bf16x2(v[6], v[7]));
+    return;
+  }
+  long long r = f / cols;
+  int c = static_cast<int>(f - r * cols);
+  for (int j = 0; j < cnt; ++j) {
+    base[r * ld + c] = __float2bfloat16(v[j]);
+    if (++c == cols) { c = 0; ++r; }
+  }
+}
 
 template <int OPT>
 __global__ void __launch_bounds__(DRAIN_THREADS)
@@ -161,7 +201,10 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
   __shared__ int s_n;
   __shared__ long long s_off[DTF_MAX_WORKERS];  // element offset of pending gradient k from item.grad
   __shared__ float s_lr[DTF_MAX_WORKERS];
+  __shared__ unsigned long long s_mbase[DTF_MAX_WORKERS];
+  __shared__ int s_nm;
   __shared__ unsigned int s_last;
+  __shared__ unsigned long long s_step;
   griddep_wait();
   griddep_launch();
   if (threadIdx.x == 0) {
@@ -185,93 +228,128 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
       ++n;
     }
     s_n = n;
+    int nm = 0;   // registered mirrors, packed
+    if (a.bcast && n > 0) {
+      for (int w = 0; w < DTF_MAX_WORKERS; ++w) {
+        const unsigned long long b =
+            *reinterpret_cast<volatile unsigned long long*>(&a.flags->mirror_base[w]);
+        if (b != 0ull) s_mbase[nm++] = b;
+      }
+    }
+    s_nm = nm;
   }
   __syncthreads();
   const int n_pending = s_n;
+  const int n_mirror = s_nm;
   const dtf_apply_item& it = a.items[s_item];
+  const dtf_drain_mirror_item& mi = a.mirror[s_item];
   if (n_pending > 0 && it.n > 0) {
     const long long base = static_cast<long long>(blockIdx.x - a.block_start[s_item]) * DRAIN_CHUNK;
+    const long long i = base + static_cast<long long>(threadIdx.x) * DRAIN_VEC;
     const bool vec_ok =
         ((reinterpret_cast<uintptr_t>(it.var) | reinterpret_cast<uintptr_t>(it.grad) |
           reinterpret_cast<uintptr_t>(it.slot0) | reinterpret_cast<uintptr_t>(it.slot1)) & 15) == 0 &&
         (a.slot_stride % 16 == 0);
     __nv_bfloat16* shadow = reinterpret_cast<__nv_bfloat16*>(it.shadow);
-    const bool shadow_vec = shadow != nullptr && (it.cols % 4 == 0) && (it.shadow_ld % 4 == 0) &&
-                            (it.first % 4 == 0) && ((reinterpret_cast<uintptr_t>(shadow) & 7) == 0);
-    float4 v4[DRAIN_UNROLL], m4[DRAIN_UNROLL], u4[DRAIN_UNROLL];
-    bool full[DRAIN_UNROLL];
+    const bool geo8 = (it.cols % 8 == 0) && (it.shadow_ld % 8 == 0);
+    if (i < it.n) {
+      const int cnt = static_cast<int>(min(static_cast<long long>(DRAIN_VEC), it.n - i));
+      const bool full = vec_ok && cnt == DRAIN_VEC;
+      float v[DRAIN_VEC], m[DRAIN_VEC], u[DRAIN_VEC];
+      if (full) {
 #pragma unroll
-    for (int u = 0; u < DRAIN_UNROLL; ++u) {
-      const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
-      full[u] = vec_ok && i + DRAIN_VEC <= it.n;
-      v4[u] = m4[u] = u4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (full[u]) {
-        v4[u] = *reinterpret_cast<const float4*>(it.var + i);
-        if (OPT != DTF_OPT_SGD) m4[u] = *reinterpret_cast<const float4*>(it.slot0 + i);
-        if (OPT == DTF_OPT_ADAM) u4[u] = *reinterpret_cast<const float4*>(it.slot1 + i);
-      }
-    }
-#pragma unroll 1
-    for (int k = 0; k < n_pending; ++k) {
-      const float* g = it.grad + s_off[k];
-      const float lr_t = s_lr[k];
-      float4 g4[DRAIN_UNROLL];
-#pragma unroll
-      for (int u = 0; u < DRAIN_UNROLL; ++u) {
-        const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
-        if (full[u]) {  // written by a peer GPU since the last drain: read at L2, not through .nc
-          const uint4 r = ld_relaxed_u4(reinterpret_cast<const uint4*>(g + i));
-          g4[u] = make_float4(__uint_as_float(r.x), __uint_as_float(r.y), __uint_as_float(r.z),
-                              __uint_as_float(r.w));
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < DRAIN_UNROLL; ++u) {
-        if (!full[u]) continue;
-        const float s = a.h.grad_scale;
-        update_one<OPT>(g4[u].x * s, v4[u].x, m4[u].x, u4[u].x, a.h, lr_t);
-        update_one<OPT>(g4[u].y * s, v4[u].y, m4[u].y, u4[u].y, a.h, lr_t);
-        update_one<OPT>(g4[u].z * s, v4[u].z, m4[u].z, u4[u].z, a.h, lr_t);
-        update_one<OPT>(g4[u].w * s, v4[u].w, m4[u].w, u4[u].w, a.h, lr_t);
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < DRAIN_UNROLL; ++u) {
-      const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
-      if (i >= it.n) continue;
-      if (full[u]) {
-        *reinterpret_cast<float4*>(it.var + i) = v4[u];
-        if (OPT != DTF_OPT_SGD) *reinterpret_cast<float4*>(it.slot0 + i) = m4[u];
-        if (OPT == DTF_OPT_ADAM) *reinterpret_cast<float4*>(it.slot1 + i) = u4[u];
-        if (shadow != nullptr) {
-          const long long f = it.first + i;
-          const float v[4] = {v4[u].x, v4[u].y, v4[u].z, v4[u].w};
-          if (shadow_vec) {
-            const long long r = f / it.cols, c = f % it.cols;
-            *reinterpret_cast<uint2*>(shadow + r * it.shadow_ld + c) =
-                make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
-          } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const long long r = (f + j) / it.cols, c = (f + j) % it.cols;
-              shadow[r * it.shadow_ld + c] = __float2bfloat16(v[j]);
-            }
+        for (int h = 0; h < 2; ++h) {
+          const float4 x = *reinterpret_cast<const float4*>(it.var + i + 4 * h);
+          v[4 * h] = x.x; v[4 * h + 1] = x.y; v[4 * h + 2] = x.z; v[4 * h + 3] = x.w;
+          if (OPT != DTF_OPT_SGD) {
+            const float4 y = *reinterpret_cast<const float4*>(it.slot0 + i + 4 * h);
+            m[4 * h] = y.x; m[4 * h + 1] = y.y; m[4 * h + 2] = y.z; m[4 * h + 3] = y.w;
+          }
+          if (OPT == DTF_OPT_ADAM) {
+            const float4 z = *reinterpret_cast<const float4*>(it.slot1 + i + 4 * h);
+            u[4 * h] = z.x; u[4 * h + 1] = z.y; u[4 * h + 2] = z.z; u[4 * h + 3] = z.w;
           }
         }
       } else {
-        // ragged tail / unaligned slice: element by element
-        for (int j = 0; j < DRAIN_VEC && i + j < it.n; ++j) {
-          float v = it.var[i + j];
-          float s0 = (OPT != DTF_OPT_SGD) ? it.slot0[i + j] : 0.f;
-          float s1 = (OPT == DTF_OPT_ADAM) ? it.slot1[i + j] : 0.f;
-          for (int k = 0; k < n_pending; ++k)
-            update_one<OPT>(it.grad[s_off[k] + i + j] * a.h.grad_scale, v, s0, s1, a.h, s_lr[k]);
-          it.var[i + j] = v;
-          if (OPT != DTF_OPT_SGD) it.slot0[i + j] = s0;
-          if (OPT == DTF_OPT_ADAM) it.slot1[i + j] = s1;
-          if (shadow != nullptr) {
-            const long long f = it.first + i + j;
-            shadow[(f / it.cols) * it.shadow_ld + (f % it.cols)] = __float2bfloat16(v);
+#pragma unroll
+        for (int j = 0; j < DRAIN_VEC; ++j) {
+          v[j] = m[j] = u[j] = 0.f;
+          if (j < cnt) {
+            v[j] = it.var[i + j];
+            if (OPT != DTF_OPT_SGD) m[j] = it.slot0[i + j];
+            if (OPT == DTF_OPT_ADAM) u[j] = it.slot1[i + j];
+          }
+        }
+      }
+      if (OPT == DTF_OPT_SGD) {
+#pragma unroll
+        for (int j = 0; j < DRAIN_VEC; ++j) m[j] = u[j] = 0.f;
+      } else if (OPT != DTF_OPT_ADAM) {
+#pragma unroll
+        for (int j = 0; j < DRAIN_VEC; ++j) u[j] = 0.f;
+      }
+#pragma unroll 1
+      for (int k = 0; k < n_pending; ++k) {
+        const float* g = it.grad + s_off[k];
+        const float lr_t = s_lr[k];
+        float gv[DRAIN_VEC];
+        if (full) {  // written by a peer GPU since the last drain: read at L2, not through .nc
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const uint4 r = ld_relaxed_u4(reinterpret_cast<const uint4*>(g + i + 4 * h));
+            gv[4 * h] = __uint_as_float(r.x); gv[4 * h + 1] = __uint_as_float(r.y);
+            gv[4 * h + 2] = __uint_as_float(r.z); gv[4 * h + 3] = __uint_as_float(r.w);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < DRAIN_VEC; ++j)
+            gv[j] = (j < cnt) ? *reinterpret_cast<const volatile float*>(g + i + j) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < DRAIN_VEC; ++j)
+          update_one<OPT>(gv[j] * a.h.grad_scale, v[j], m[j], u[j], a.h, lr_t);
+      }
+      if (full) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          *reinterpret_cast<float4*>(it.var + i + 4 * h) =
+              make_float4(v[4 * h], v[4 * h + 1], v[4 * h + 2], v[4 * h + 3]);
+          if (OPT != DTF_OPT_SGD)
+            *reinterpret_cast<float4*>(it.slot0 + i + 4 * h) =
+                make_float4(m[4 * h], m[4 * h + 1], m[4 * h + 2], m[4 * h + 3]);
+          if (OPT == DTF_OPT_ADAM)
+            *reinterpret_cast<float4*>(it.slot1 + i + 4 * h) =
+                make_float4(u[4 * h], u[4 * h + 1], u[4 * h + 2], u[4 * h + 3]);
+        }
+      } else {
+        for (int j = 0; j < cnt; ++j) {
+          it.var[i + j] = v[j];
+          if (OPT != DTF_OPT_SGD) it.slot0[i + j] = m[j];
+          if (OPT == DTF_OPT_ADAM) it.slot1[i + j] = u[j];
+        }
+      }
+      if (shadow != nullptr)
+        put_bf16(shadow, it.first + i, it.cols, it.shadow_ld, v, cnt,
+                 geo8 && ((it.first + i) % 8 == 0) && ((reinterpret_cast<uintptr_t>(shadow) & 15) == 0));
+      // ---- owner pushes: the new values go straight into every worker's mirror (posted stores) ----
+      if (n_mirror > 0) {
+        const long long f = mi.first + i;
+        if (mi.bf16_off >= 0) {
+          const bool v8 = geo8 && (f % 8 == 0) && (mi.bf16_off % 16 == 0);
+          for (int q = 0; q < n_mirror; ++q)
+            put_bf16(reinterpret_cast<__nv_bfloat16*>(s_mbase[q] + mi.bf16_off), f, it.cols,
+                     it.shadow_ld, v, cnt, v8);
+        }
+        if (mi.f32_off >= 0) {
+          const bool v4 = cnt == DRAIN_VEC && (f % 4 == 0) && (mi.f32_off % 16 == 0);
+          for (int q = 0; q < n_mirror; ++q) {
+            float* dst = reinterpret_cast<float*>(s_mbase[q] + mi.f32_off) + f;
+            if (v4) {
+              *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+              *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
+            } else {
+              for (int j = 0; j < cnt; ++j) dst[j] = v[j];
+            }
           }
         }
       }
@@ -286,36 +364,67 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
     s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
   }
   __syncthreads();
-  if (!s_last || threadIdx.x != 0) return;
-  __threadfence_system();
-  unsigned long long step = 0;
-  if (n_pending > 0) {
-    if (OPT == DTF_OPT_ADAM) {
-      volatile float* b1 = &a.ctrl_powers->beta1_power;
-      volatile float* b2 = &a.ctrl_powers->beta2_power;
-      float p1 = *b1, p2 = *b2;
-      for (int k = 0; k < n_pending; ++k) { p1 *= a.h.beta1; p2 *= a.h.beta2; }
-      *b1 = p1;
-      *b2 = p2;
+  if (!s_last) return;
+  const bool holds_lock = a.todo[DTF_MAX_WORKERS] != 0u;
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    unsigned long long step = 0;
+    if (n_pending > 0) {
+      if (OPT == DTF_OPT_ADAM) {
+        volatile float* b1 = &a.ctrl_powers->beta1_power;
+        volatile float* b2 = &a.ctrl_powers->beta2_power;
+        float p1 = *b1, p2 = *b2;
+        for (int k = 0; k < n_pending; ++k) { p1 *= a.h.beta1; p2 *= a.h.beta2; }
+        *b1 = p1;
+        *b2 = p2;
+      }
+      if (a.ctrl_step != nullptr) {
+        step = atom_add_u64_sys(&a.ctrl_step->global_step, static_cast<unsigned long long>(n_pending)) +
+               static_cast<unsigned long long>(n_pending);
+        atomicAdd(&a.ctrl_step->apply_count, static_cast<unsigned int>(n_pending));
+      }
+      for (int w = 0; w < a.n_workers; ++w) {
+        if (a.todo[w] == 0) continue;
+        if (a.ctrl_step != nullptr)
+          *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[w]) = step;
+        // the mailbox buffer may be overwritten by worker w from here on
+        const unsigned int c = *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
+        st_release_sys_u32(&a.flags->consumed[w], c + 1u);
+      }
+      *reinterpret_cast<volatile unsigned int*>(&a.flags->drains) =
+          *reinterpret_cast<volatile unsigned int*>(&a.flags->drains) + 1u;
+      *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total) =
+          *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total) +
+          static_cast<unsigned int>(n_pending);
     }
-    if (a.ctrl_step != nullptr) {
-      step = atom_add_u64_sys(&a.ctrl_step->global_step, static_cast<unsigned long long>(n_pending)) +
-             static_cast<unsigned long long>(n_pending);
-      atomicAdd(&a.ctrl_step->apply_count, static_cast<unsigned int>(n_pending));
-    }
-    for (int w = 0; w < a.n_workers; ++w) {
-      if (a.todo[w] == 0) continue;
-      if (a.ctrl_step != nullptr)
-        *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[w]) = step;
-      // the mailbox buffer may be overwritten by worker w from here on
-      const unsigned int c = *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
-      st_release_sys_u32(&a.flags->consumed[w], c + 1u);
+    s_step = step;
+    if (a.step_out != nullptr) {
+      *a.step_out = (a.ctrl_step != nullptr && n_pending == 0)
+                        ? ld_acquire_sys_u64(&a.ctrl_step->global_step)
+                        : step;
     }
   }
-  if (a.step_out != nullptr) {
-    *a.step_out = (a.ctrl_step != nullptr && n_pending == 0)
-                      ? ld_acquire_sys_u64(&a.ctrl_step->global_step)
-                      : step;
+  __syncthreads();
+  // mirror headers, one thread per worker: what the worker would otherwise read over NVLink
+  if (a.bcast && n_pending > 0 && static_cast<int>(threadIdx.x) < DTF_MAX_WORKERS) {
+    const int w = threadIdx.x;
+    const unsigned long long b =
+        *reinterpret_cast<volatile unsigned long long*>(&a.flags->mirror_base[w]);
+    if (b != 0ull) {
+      dtf_mirror_hdr* hdr = reinterpret_cast<dtf_mirror_hdr*>(b);
+      *reinterpret_cast<volatile unsigned int*>(&hdr->consumed[a.shard]) =
+          *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
+      if (a.ctrl_step != nullptr)
+        *reinterpret_cast<volatile unsigned long long*>(&hdr->global_step) = s_step;
+      // every CTA fenced its data stores before the election: the version follows the data
+      st_release_sys_u32(&hdr->version[a.shard],
+                         *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total));
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && holds_lock) {
+    __threadfence();
+    atomicExch(&a.flags->lock, 0u);
   }
 }
 
@@ -328,7 +437,7 @@ extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, in
                                 int publish, unsigned int* seq, unsigned int* block_counter,
                                 unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
                                 unsigned long long* step_out, const dtf_result_sink* sink,
-                                void* stream) {
+                                const dtf_mirror_hdr* my_hdr, void* stream) {
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_MBOX_ITEMS, "mailbox_push: %d items (max %d)",
               n_items, DTF_MAX_MBOX_ITEMS);
   DTF_REQUIRE(depth >= 1 && seq != nullptr, "mailbox_push: depth %d / seq", depth);
@@ -371,6 +480,9 @@ extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, in
   a.min_consumed_out = min_consumed_out;
   a.ctrl_step = ctrl_step;
   a.step_out = step_out;
+  a.my_hdr = publish ? my_hdr : nullptr;
+  DTF_REQUIRE(my_hdr == nullptr || n_owners <= DTF_MIRROR_MAX_SHARDS,
+              "mailbox_push: %d owners exceed the mirror header (%d)", n_owners, DTF_MIRROR_MAX_SHARDS);
   if (sink != nullptr && publish) {
     DTF_REQUIRE(sink->loss_src && sink->host_dst && sink->seq_dev, "mailbox_push: incomplete result sink");
     a.sink = *sink;
@@ -386,6 +498,17 @@ extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_ite
                                  dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, unsigned int* todo,
                                  unsigned int* block_counter, unsigned long long* step_out,
                                  void* stream_) {
+  return dtf_mailbox_drain_ex(opt, items, n_items, slot_stride, depth, n_workers, hyper, ctrl_powers,
+                              ctrl_step, flags, todo, block_counter, step_out, nullptr, 0, stream_);
+}
+
+extern "C" int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_items,
+                                    long long slot_stride, int depth, int n_workers,
+                                    const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
+                                    dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, unsigned int* todo,
+                                    unsigned int* block_counter, unsigned long long* step_out,
+                                    const dtf_drain_mirror_item* mirror_items, int shard_index,
+                                    void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "mailbox_drain: %d items (max %d)",
               n_items, DTF_MAX_APPLY_ITEMS);
@@ -394,6 +517,8 @@ extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_ite
   DTF_REQUIRE(hyper && flags && todo && block_counter, "mailbox_drain: null argument");
   DTF_REQUIRE(opt != DTF_OPT_ADAM || ctrl_powers != nullptr, "mailbox_drain: Adam needs the beta powers");
   DTF_REQUIRE(slot_stride % 4 == 0, "mailbox_drain: slot stride %lld", slot_stride);
+  DTF_REQUIRE(mirror_items == nullptr || (shard_index >= 0 && shard_index < DTF_MIRROR_MAX_SHARDS),
+              "mailbox_drain: shard index %d outside the mirror header", shard_index);
   DrainArgs a;
   memset(&a, 0, sizeof(a));
   int blocks = 0;
@@ -402,6 +527,11 @@ extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_ite
     DTF_REQUIRE(opt == DTF_OPT_SGD || items[i].slot0, "mailbox_drain: item %d lacks slot0", i);
     DTF_REQUIRE(opt != DTF_OPT_ADAM || items[i].slot1, "mailbox_drain: item %d lacks slot1", i);
     a.items[i] = items[i];
+    if (mirror_items != nullptr) {
+      a.mirror[i] = mirror_items[i];
+    } else {
+      a.mirror[i].bf16_off = a.mirror[i].f32_off = -1;
+    }
     a.block_start[i] = blocks;
     blocks += static_cast<int>((items[i].n + DRAIN_CHUNK - 1) / DRAIN_CHUNK);
   }
@@ -410,6 +540,7 @@ extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_ite
     blocks = 1;
     if (n_items == 0) {
       n_items = 1;
+      a.mirror[0].bf16_off = a.mirror[0].f32_off = -1;
       a.block_start[1] = 1;
     }
   }
@@ -423,6 +554,8 @@ extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_ite
   a.slot_stride = slot_stride;
   a.depth = depth;
   a.n_workers = n_workers;
+  a.bcast = mirror_items != nullptr ? 1 : 0;
+  a.shard = shard_index;
   a.step_out = step_out;
   a.block_counter = block_counter;
   DTF_CHECK_CUDA(launch_kernel(mailbox_snapshot_kernel, dim3(1), dim3(32), 0, stream, flags, todo,

@@ -80,7 +80,7 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
 
 extern "C" const char* dtf_last_error() { return dtf::g_err; }
 
-extern "C" int dtf_abi_version() { return 1; }
+extern "C" int dtf_abi_version() { return 2; }
 
 extern "C" int dtf_set_pdl(int enabled) {
   const int old = dtf::g_pdl_enabled;

@@ -9,6 +9,7 @@
 //      from local HBM) on that stream, concurrently with whatever the colocated worker computes.
 // No Python and no GIL on this path; kernels never wait on other kernels (the drain only touches
 // gradients whose sequence number was already published), so nothing can deadlock on the device.
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cstdarg>
@@ -25,6 +26,10 @@ struct dtf_mbox_daemon {
   int device = 0;
   int opt = 0;
   dtf_apply_item items[DTF_MAX_APPLY_ITEMS];
+  dtf_drain_mirror_item mirror[DTF_MAX_APPLY_ITEMS];
+  bool has_mirror = false;
+  int shard = 0;
+  std::atomic<int> backstop_us{0};
   int n_items = 0;
   long long slot_stride = 0;
   int depth = 1;
@@ -37,7 +42,7 @@ struct dtf_mbox_daemon {
 
   cudaStream_t stream = nullptr;
   dtf_mbox_flags* host_flags = nullptr;  // pinned
-  unsigned int* scratch = nullptr;       // device: todo[16] | block counter
+  unsigned int* scratch = nullptr;       // device: todo[16] + lock-held word | block counter at +32
   std::thread thread;
   std::atomic<int> stop{0};
   std::atomic<int> paused{0};
@@ -45,6 +50,10 @@ struct dtf_mbox_daemon {
   std::atomic<int> failed{0};
   std::atomic<unsigned long long> polls{0}, drains{0}, applied{0};
   unsigned int last_consumed[DTF_MAX_WORKERS] = {0};
+  // backstop mode: when worker w's oldest pending gradient was first seen, and at which consumed[w]
+  unsigned int seen_consumed[DTF_MAX_WORKERS] = {0};
+  std::chrono::steady_clock::time_point seen_at[DTF_MAX_WORKERS];
+  bool seen[DTF_MAX_WORKERS] = {false};
   std::mutex err_mu;
   char err[512] = {0};
 
@@ -95,14 +104,40 @@ void daemon_main(dtf_mbox_daemon* d) {
       if (delta > 0) d->applied.fetch_add(static_cast<unsigned long long>(delta), std::memory_order_relaxed);
       d->last_consumed[w] = c;
     }
-    const int n = pending_count(d->host_flags, d->n_workers);
+    int n = pending_count(d->host_flags, d->n_workers);
+    const int backstop = d->backstop_us.load(std::memory_order_relaxed);
+    if (backstop > 0) {
+      // the shard's drains normally run inside a colocated worker's step graph: step in only for
+      // gradients that have been waiting for `backstop` microseconds (that worker has stopped)
+      const auto now = std::chrono::steady_clock::now();
+      bool overdue = false;
+      for (int w = 0; w < d->n_workers; ++w) {
+        const unsigned int c = d->host_flags->consumed[w];
+        if (static_cast<int>(d->host_flags->produced[w] - c) <= 0) {
+          d->seen[w] = false;
+          continue;
+        }
+        if (!d->seen[w] || d->seen_consumed[w] != c) {
+          d->seen[w] = true;
+          d->seen_consumed[w] = c;
+          d->seen_at[w] = now;
+        } else if (std::chrono::duration_cast<std::chrono::microseconds>(now - d->seen_at[w]).count() >= backstop) {
+          overdue = true;
+        }
+      }
+      if (!overdue) {
+        std::this_thread::sleep_for(std::chrono::microseconds(std::max(d->poll_us, backstop / 4)));
+        continue;
+      }
+    }
     if (n == 0) {
       if (d->poll_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(d->poll_us));
       continue;
     }
-    if (dtf_mailbox_drain(d->opt, d->items, d->n_items, d->slot_stride, d->depth, d->n_workers,
-                          &d->hyper, d->ctrl_powers, d->ctrl_step, d->flags, d->scratch,
-                          d->scratch + DTF_MAX_WORKERS, nullptr, d->stream) != 0) {
+    if (dtf_mailbox_drain_ex(d->opt, d->items, d->n_items, d->slot_stride, d->depth, d->n_workers,
+                             &d->hyper, d->ctrl_powers, d->ctrl_step, d->flags, d->scratch,
+                             d->scratch + 32, nullptr, d->has_mirror ? d->mirror : nullptr, d->shard,
+                             d->stream) != 0) {
       d->fail("apply daemon: %s", dtf_last_error());
       return;
     }
@@ -121,7 +156,9 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
                                      const dtf_apply_item* items, int n_items, long long slot_stride,
                                      int depth, int n_workers, const dtf_apply_hyper* hyper,
                                      dtf_ps_ctrl* ctrl_powers, dtf_ps_ctrl* ctrl_step,
-                                     dtf_mbox_flags* flags, int poll_us) {
+                                     dtf_mbox_flags* flags, int poll_us,
+                                     const dtf_drain_mirror_item* mirror_items, int shard_index,
+                                     int backstop_us) {
   DTF_REQUIRE(out != nullptr && hyper != nullptr && flags != nullptr, "mbox_daemon_start: null argument");
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "mbox_daemon_start: %d items (max %d)",
               n_items, DTF_MAX_APPLY_ITEMS);
@@ -134,6 +171,10 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
   d->device = device;
   d->opt = opt;
   for (int i = 0; i < n_items; ++i) d->items[i] = items[i];
+  d->has_mirror = mirror_items != nullptr;
+  for (int i = 0; i < n_items && mirror_items != nullptr; ++i) d->mirror[i] = mirror_items[i];
+  d->shard = shard_index;
+  d->backstop_us.store(backstop_us > 0 ? backstop_us : 0);
   d->n_items = n_items;
   d->slot_stride = slot_stride;
   d->depth = depth;
@@ -147,8 +188,8 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
   cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
   if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&d->stream, cudaStreamNonBlocking, lo);
   if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&d->host_flags), sizeof(dtf_mbox_flags));
-  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&d->scratch), (DTF_MAX_WORKERS + 16) * 4);
-  if (e == cudaSuccess) e = cudaMemset(d->scratch, 0, (DTF_MAX_WORKERS + 16) * 4);
+  if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&d->scratch), (DTF_MAX_WORKERS + 48) * 4);
+  if (e == cudaSuccess) e = cudaMemset(d->scratch, 0, (DTF_MAX_WORKERS + 48) * 4);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     set_error("mbox_daemon_start: %s", cudaGetErrorString(e));
@@ -162,6 +203,12 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
   d->thread = std::thread(daemon_main, d);
   cudaSetDevice(prev);
   *out = d;
+  return 0;
+}
+
+extern "C" int dtf_mbox_daemon_set_backstop(dtf_mbox_daemon* d, int backstop_us) {
+  DTF_REQUIRE(d != nullptr, "mbox_daemon_set_backstop: null daemon");
+  d->backstop_us.store(backstop_us > 0 ? backstop_us : 0, std::memory_order_relaxed);
   return 0;
 }
 

@@ -349,6 +349,17 @@ class B200StepRunner:
         self.mailbox_depth = int(opts.get("mailbox_depth", 4))      # = max pushes in flight per worker
         self.mailbox_timeout = float(opts.get("mailbox_timeout", 60.0))
         self.mailbox_poll_us = int(opts.get("mailbox_poll_us", 20))
+        # owner-applies mode, "owner pushes, worker never pulls": every worker keeps a mirror of the
+        # parameters in its own HBM that the owners' drains rewrite (csrc/kernels/mailbox.cu); the
+        # step then contains no NVLink read at all (no pull, no flow-control / global_step round trip)
+        self.mirror = bool(opts.get("mirror", os.environ.get("DTF_B200_MIRROR", "1") != "0"))
+        # a shard that lives in this worker's process is drained by a node of the worker's own step
+        # graph (device-driven apply); the shard's daemon stays as the backstop for an idle owner
+        self.graph_drain = bool(opts.get("graph_drain", os.environ.get("DTF_B200_GRAPH_DRAIN", "1") != "0"))
+        self.drain_at = str(opts.get("drain_at", os.environ.get("DTF_B200_DRAIN_AT", "start")))
+        self.drain_backstop_us = int(opts.get("drain_backstop_us", 400))
+        self.use_mirror = False
+        self.my_shards: List[int] = []
         self.use_mailbox = False
         self._pushes = 0
         self._min_consumed = 0
@@ -453,6 +464,10 @@ class B200StepRunner:
         self.sync_round_no: Optional[int] = None
         self.mirror_filled = False
         self.store.sync_hook = self.stream.synchronize
+        self.use_mirror = bool(self.use_mailbox and self.mirror
+                               and self.store.num_shards <= L.MIRROR_MAX_SHARDS)
+        if self.use_mirror:
+            self.store.alloc_mirror()
         if self.use_mailbox:
             self._mbox_setup()
 
@@ -567,6 +582,9 @@ class B200StepRunner:
         if self.sync_opt is not None:
             self._setup_params_sync()
             return
+        if self.use_mirror:
+            self._setup_params_mirror()
+            return
 
         def want_shadow(var: G.Variable, allow_in_place: bool) -> None:
             regs = self._regions(var)
@@ -635,6 +653,40 @@ class B200StepRunner:
             self.fptr[var.name] = me + al.mirror_f32[var.name]
             for r in self._regions_rotated(var):
                 self.copies.append((st.var_ptr(r), me + al.mirror_f32[var.name] + r.sl.first * 4,
+                                    (r.sl.n * 4 + 15) // 16 * 16))
+
+        if p.kind == "cnn":
+            use_f32(p.convs[0].k)
+            use_f32(p.convs[0].b)
+            use_bf16(p.convs[1].k)
+            use_f32(p.convs[1].b)
+        for d in p.dense:
+            use_bf16(d.w)
+            if d.b is not None:
+                use_f32(d.b)
+
+    def _setup_params_mirror(self) -> None:
+        """Owner-pushes mode: every tensor the kernels read is this worker's MIRROR (local HBM),
+        rewritten by the owners' drains. ``copies`` fills it once after init / restore."""
+        st, p = self.store, self.plan
+        ml, me = st.mirror, st.mirror_base
+        self.late_mark, self.late_layer = None, 0
+
+        def use_bf16(var):
+            regs = self._regions(var)
+            ld = regs[0].shadow_ld
+            self.wptr[var.name] = (me + ml.bf16[var.name], ld)
+            for r in self._regions_rotated(var):
+                row = r.sl.first // r.cols
+                self.copies.append((st.shadow_ptr(r), me + ml.bf16[var.name] + row * ld * 2, r.rows * ld * 2))
+
+        def use_f32(var):
+            if var.name not in ml.f32:
+                raise UnsupportedGraphError("variable %s (%d elements) has no fp32 mirror" %
+                                            (var.name, self.layout[var.name].num_elements))
+            self.fptr[var.name] = me + ml.f32[var.name]
+            for r in self._regions_rotated(var):
+                self.copies.append((st.var_ptr(r), me + ml.f32[var.name] + r.sl.first * 4,
                                     (r.sl.n * 4 + 15) // 16 * 16))
 
         if p.kind == "cnn":
@@ -818,8 +870,10 @@ class B200StepRunner:
         if s.reported:
             with torch.cuda.stream(side):
                 # the loss is final: hand loss + global_step to the host now
-                K.step_report(self.store.step_ctrl, self.worker_id, not self.use_mailbox,
-                              s.step_dev.data_ptr(), self._sink(s))
+                # (owner-pushes mode: global_step is read from my mirror's header, offset 0, which the
+                # step-owning shard's drain keeps fresh - no NVLink round trip)
+                K.step_report(self.store.mirror_base if self.use_mirror else self.store.step_ctrl,
+                              self.worker_id, not self.use_mailbox, s.step_dev.data_ptr(), self._sink(s))
         for i in range(nl - 1, -1, -1):
             d = p.dense[i]
             din, dout = s.dims[i], s.dims[i + 1]
@@ -943,12 +997,17 @@ class B200StepRunner:
         hyper = dict(lr=float(spec.learning_rate), beta1=float(spec.beta1), beta2=float(spec.beta2),
                      epsilon=float(spec.epsilon), momentum=float(spec.momentum),
                      use_nesterov=bool(spec.use_nesterov))
+        ml = st.mirror if self.use_mirror else None
+        self._drain_desc: Dict[int, dict] = {}
         for sh in range(st.num_shards):
             items = []
+            mitems = []
             for name in self.trainable_names:
                 for r in al.regions.get(name, []):
                     if r.shard != sh:
                         continue
+                    if ml is not None:
+                        mitems.append((ml.bf16.get(name, -1), ml.f32.get(name, -1), int(r.sl.first)))
                     items.append(dict(var_off=r.var_off,
                                       slot0_off=r.slot_off[0] if len(r.slot_off) > 0 else -1,
                                       slot1_off=r.slot_off[1] if len(r.slot_off) > 1 else -1,
@@ -958,7 +1017,9 @@ class B200StepRunner:
             desc = dict(opt=int(spec.code), items=items, slot_stride=int(al.mailbox_stride[sh]),
                         depth=int(al.mailbox_depth), n_workers=int(al.sync_workers), hyper=hyper,
                         owns_step=bool(al.step_shard == sh), flags_off=int(al.mbox_flags_off[sh]),
-                        poll_us=int(self.mailbox_poll_us))
+                        poll_us=int(self.mailbox_poll_us), shard=int(sh),
+                        mirror_items=[list(m) for m in mitems] if ml is not None else None)
+            self._drain_desc[sh] = desc
             self.client.call(sh, "mbox_start", desc)
         zero = np.zeros(1, np.uint32)
         for sh in range(st.num_shards):
@@ -976,6 +1037,17 @@ class B200StepRunner:
         self.mbox_host = torch.zeros(16, dtype=torch.int32).pin_memory()
         self._mbox_host_np = self.mbox_host.numpy()
         torch.cuda.synchronize(self.device)
+        if self.use_mirror:
+            st.register_mirror(me)
+        # shards whose arena lives in THIS process on THIS GPU: their drains become nodes of my step graph
+        self.my_shards = []
+        if self.graph_drain:
+            self.my_shards = [sh for sh in range(st.num_shards) if st.same_process[sh] and st.is_local[sh]]
+            for sh in self.my_shards:
+                self.client.call(sh, "mbox_attach", me, True, self.drain_backstop_us)
+            self._drain_scratch = torch.zeros(64 * max(1, len(self.my_shards)), dtype=torch.int32,
+                                              device=self.device)
+            torch.cuda.synchronize(self.device)
 
     def _push_vars(self, s: StepState, variables: Sequence[G.Variable], publish: bool) -> None:
         """Posted stores of the gradients into this worker's mailbox on every owning shard;
@@ -993,7 +1065,33 @@ class B200StepRunner:
                        s.counter.data_ptr(), self.mbox_host.data_ptr() if publish else None,
                        st.step_ctrl if publish else None, s.step_dev.data_ptr() if publish else None,
                        sink=self._sink(s) if (publish and self._uses_sink(s)
-                                              and not getattr(s, "reported", False)) else None)
+                                              and not getattr(s, "reported", False)) else None,
+                       my_hdr=st.mirror_base if (publish and self.use_mirror) else None)
+
+    def _drain_local(self, s: StepState) -> None:
+        """Device-driven owner-side apply: drain the mailboxes of the shard(s) living in this process
+        (claim lock + snapshot, then apply from local HBM and broadcast into the workers' mirrors).
+        A node of the step graph; whatever has been published when it runs gets applied."""
+        st, spec = self.store, self.spec
+        hyper = K.make_hyper(spec.learning_rate, spec.beta1, spec.beta2, spec.epsilon, spec.momentum,
+                             1.0, spec.use_nesterov, False)
+        for k, sh in enumerate(self.my_shards):
+            desc = self._drain_desc[sh]
+            base = st.base[sh]
+
+            def at(off):
+                return None if off is None or off < 0 else base + int(off)
+
+            entries = [dict(var=at(it["var_off"]), slot0=at(it["slot0_off"]), slot1=at(it["slot1_off"]),
+                            shadow=at(it["shadow_off"]), grad=at(it["grad_off"]), n=int(it["n"]), first=0,
+                            cols=int(it["cols"]), shadow_ld=int(it["shadow_ld"])) for it in desc["items"]]
+            mitems = K.make_mirror_items([tuple(m) for m in desc["mirror_items"]]) \
+                if desc.get("mirror_items") is not None else None
+            scratch = self._drain_scratch.data_ptr() + 256 * k
+            K.mailbox_drain(spec.code, K.make_apply_items(entries), len(entries), int(desc["slot_stride"]),
+                            int(desc["depth"]), int(desc["n_workers"]), hyper, base,
+                            base if desc["owns_step"] else None, base + int(desc["flags_off"]),
+                            scratch, scratch + 128, None, mirror_items=mitems, shard_index=sh)
 
     def _mbox_consumed(self) -> int:
         """min over owners of how many of MY gradients they have applied (host-side read)."""
@@ -1092,10 +1190,12 @@ class B200StepRunner:
                          max_ctas=0 if finish else self.early_apply_ctas)
 
     def _pull(self, s: StepState) -> None:
-        if self.sync_opt is not None:
+        if self.sync_opt is not None or self.use_mirror:
             if self.mirror_filled:
                 return
             self.mirror_filled = True
+            if self.use_mirror:
+                self._mirror_seed()
         s.pull_late = None
         mark = getattr(self, "late_mark", None)
         if self.sync_opt is None and self.overlap and mark is not None and len(self.copies) > mark:
@@ -1111,6 +1211,13 @@ class B200StepRunner:
                 K.pull_bulk(self.copies[:mark], self.store.step_ctrl, s.step_dev.data_ptr() + 8)
         elif self.copies:
             K.pull_bulk(self.copies, self.store.step_ctrl, s.step_dev.data_ptr() + 8)
+
+    def _mirror_seed(self) -> None:
+        """First use of the mirror (after init / restore): global_step into its header; the
+        parameters follow through ``copies`` on the stream."""
+        st = self.store
+        gs = np.asarray([st.read_global_step()], np.uint64)
+        st._h2d(st.mirror_base + L.MIRROR_OFF_GLOBAL_STEP, gs)
 
     def _self_cleans(self, s: StepState) -> bool:
         """True when every buffer of the zeroed region is reset by its consumer (worker-side apply
@@ -1141,6 +1248,17 @@ class B200StepRunner:
         clear_end = s.train and self.clear_at_end and self.sync_opt is None
         if not clear_end:
             K.fill_u32(s.zero.buf, 0)
+        drain_ev = None
+        if s.train and self.my_shards and self.use_mailbox and self.drain_at == "start":
+            # the owner-side apply of whatever the workers have published, beside the forward pass
+            main = torch.cuda.current_stream()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            self.apply_stream.wait_event(ev)
+            with torch.cuda.stream(self.apply_stream):
+                self._drain_local(s)
+                drain_ev = torch.cuda.Event()
+                drain_ev.record(self.apply_stream)
         with nvtx_range("dtf/pull"):
             self._pull(s)
         with nvtx_range("dtf/forward"):
@@ -1149,6 +1267,10 @@ class B200StepRunner:
         if s.train:
             with nvtx_range("dtf/backward_push_apply"):
                 self._backward(s)      # includes the push+apply of every variable
+            if drain_ev is not None:
+                torch.cuda.current_stream().wait_event(drain_ev)     # join (the apply stream is ordered anyway)
+            if self.my_shards and self.use_mailbox and self.drain_at == "end":
+                self._drain_local(s)
         if with_io and not self._uses_sink(s):
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
             if self.sync_opt is None or not s.train:
@@ -1354,7 +1476,7 @@ class B200StepRunner:
         pushed to REMOTE shards (crosses NVLink) and in total. Used by DataPlaneStatsHook."""
         st = self.store
         pull_remote = pull_total = 0
-        for src, _dst, nbytes in getattr(self, "copies", []):
+        for src, _dst, nbytes in ([] if self.use_mirror else getattr(self, "copies", [])):
             pull_total += nbytes
             sh = next((i for i in range(st.num_shards)
                        if st.base[i] <= src < st.base[i] + st.arena.shard_bytes[i]), None)
@@ -1412,6 +1534,13 @@ class B200StepRunner:
                     self.store._h2d(self.store.mbox_flags_ptr(sh) + L.MBOX_OFF_DONE + 4 * self.worker_id, one)
             except Exception:
                 pass
+        if self.use_mailbox and self.store is not None:
+            for sh in self.my_shards:
+                try:
+                    self.client.call(sh, "mbox_attach", self.worker_id, False, 0)
+                except Exception:
+                    pass
+            self.my_shards = []
         self.states.clear()
         if self.store is not None:
             self.store.close()

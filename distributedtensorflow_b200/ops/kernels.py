@@ -194,7 +194,8 @@ def push_apply(opt: int, items, n_items: int, hyper: L.ApplyHyper, ctrl_powers: 
 def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags: Sequence[int],
                  publish: bool, seq: int, block_counter: Optional[int],
                  min_consumed_out: Optional[int], ctrl_step: Optional[int] = None,
-                 step_out: Optional[int] = None, sink: Optional[L.ResultSink] = None) -> None:
+                 step_out: Optional[int] = None, sink: Optional[L.ResultSink] = None,
+                 my_hdr: Optional[int] = None) -> None:
     """Worker side of the "owner applies" push (csrc/kernels/mailbox.cu).
 
     items: (src_ptr, dst0_ptr, nbytes, buf_stride) — gradient slice -> its place in MY buffer 0 on
@@ -214,18 +215,29 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
                                       int(last), seq, block_counter, min_consumed_out if last else None,
                                       ctrl_step if last else None, step_out if last else None,
                                       C.byref(sink) if (sink is not None and last) else None,
-                                      L.current_stream())
+                                      my_hdr if last else None, L.current_stream())
         L.check(rc, "dtf_mailbox_push")
         _count()
 
 
+def make_mirror_items(entries: Sequence[tuple]) -> "C.Array":
+    """entries: (bf16_off or -1, f32_off or -1, first) per drained slice."""
+    arr = (L.DrainMirrorItem * max(1, len(entries)))()
+    for i, (b, f, first) in enumerate(entries):
+        arr[i].bf16_off, arr[i].f32_off, arr[i].first = int(b), int(f), int(first)
+    return arr
+
+
 def mailbox_drain(opt: int, items, n_items: int, slot_stride: int, depth: int, n_workers: int,
                   hyper: L.ApplyHyper, ctrl_powers: Optional[int], ctrl_step: Optional[int],
-                  flags: int, todo: int, block_counter: int, step_out: Optional[int]) -> None:
-    """Owner side: snapshot pending mailboxes + apply them from local HBM (two launches)."""
-    rc = L.lib().dtf_mailbox_drain(opt, items, n_items, slot_stride, depth, n_workers, C.byref(hyper),
-                                   ctrl_powers, ctrl_step, flags, todo, block_counter, step_out,
-                                   L.current_stream())
+                  flags: int, todo: int, block_counter: int, step_out: Optional[int],
+                  mirror_items=None, shard_index: int = 0) -> None:
+    """Owner side: claim the lock + snapshot pending mailboxes, then apply them from local HBM and
+    (``mirror_items``) broadcast the new values into the registered worker mirrors. Two launches.
+    ``todo`` needs MAX_WORKERS + 1 words."""
+    rc = L.lib().dtf_mailbox_drain_ex(opt, items, n_items, slot_stride, depth, n_workers, C.byref(hyper),
+                                      ctrl_powers, ctrl_step, flags, todo, block_counter, step_out,
+                                      mirror_items, shard_index, L.current_stream())
     L.check(rc, "dtf_mailbox_drain")
     _count(2)
 

@@ -158,6 +158,36 @@ def build_arena_layout(layout: Dict[str, VarLayout], num_shards: int, spec: Opti
     return al
 
 
+@dataclass
+class MirrorLayout:
+    """A worker's private mirror of the parameters (``dtf_mirror_hdr`` + copies): byte offsets
+    from the mirror base. Matrices get the bf16 row-padded form the tensor-core kernels read,
+    vectors and small tensors an fp32 copy (a small matrix gets both)."""
+    nbytes: int
+    f32: Dict[str, int]
+    bf16: Dict[str, int]
+
+
+MIRROR_F32_MAX_ELEMS = 4096
+
+
+def build_mirror_layout(layout: Dict[str, VarLayout], regions: Dict[str, List[SliceRegion]]) -> MirrorLayout:
+    o = L.MIRROR_HDR_BYTES
+    f32: Dict[str, int] = {}
+    bf16: Dict[str, int] = {}
+    for vl in sorted(layout.values(), key=lambda v: v.index):
+        regs = regions.get(vl.name)
+        if not regs:
+            continue
+        if len(vl.shape) < 2 or vl.num_elements <= MIRROR_F32_MAX_ELEMS:
+            f32[vl.name] = o
+            o += _align(vl.num_elements * 4)
+        if regs[0].shadow_off is not None:
+            bf16[vl.name] = o
+            o += _align(vl.rows * regs[0].shadow_ld * 2)
+    return MirrorLayout(_align(o, 4096), f32, bf16)
+
+
 class NvlStore:
     """Maps every shard's arena into this process and answers "where is X" with raw pointers."""
 
@@ -173,6 +203,10 @@ class NvlStore:
         self.arena = build_arena_layout(layout, self.num_shards, spec, trainable_names, sync_workers,
                                         mailbox_depth, mirrors)
         self.base: List[int] = [0] * self.num_shards
+        self.same_process: List[bool] = [False] * self.num_shards
+        self.mirror: Optional[MirrorLayout] = None
+        self.mirror_base = 0
+        self._mirror_worker: Optional[int] = None
         self.is_local: List[bool] = [False] * self.num_shards
         self.shard_device: List[int] = [local_device] * self.num_shards
         self._imported: List[int] = []
@@ -185,6 +219,7 @@ class NvlStore:
             self.shard_device[s] = int(info["device"])
             if int(info["pid"]) == os.getpid():
                 self.base[s] = int(info["ptr"])
+                self.same_process[s] = True
                 if self.shard_device[s] != local_device:
                     L.check(lib.dtf_set_device(local_device), "set_device")
                     L.check(lib.dtf_enable_peer_access(self.shard_device[s]), "enable_peer_access")
@@ -332,8 +367,69 @@ class NvlStore:
             rows.append(t.float().numpy().reshape(r.rows, r.shadow_ld)[:, :r.cols])
         return np.concatenate(rows, 0).reshape(vl.shape)
 
+    # -- worker mirror ("owner pushes, worker never pulls") -------------------------------------------
+    def alloc_mirror(self) -> MirrorLayout:
+        """Allocate this worker's mirror on its own GPU (zeroed; the header starts at 0)."""
+        if self.mirror is None:
+            self.mirror = build_mirror_layout(self.layout, self.arena.regions)
+            lib = L.lib()
+            L.check(lib.dtf_set_device(self.local_device), "set_device")
+            ptr = C.c_void_p()
+            L.check(lib.dtf_arena_alloc(C.byref(ptr), self.mirror.nbytes), "mirror alloc")
+            self.mirror_base = int(ptr.value)
+        return self.mirror
+
+    def register_mirror(self, worker_id: int) -> None:
+        """Hand the mirror to every shard's owner process (CUDA IPC handle through the control
+        plane, or the plain pointer inside one process): from now on each drain of a shard also
+        stores the fresh parameters and this worker's flow-control counters into it."""
+        lib = L.lib()
+        handle = C.create_string_buffer(L.IPC_HANDLE_BYTES)
+        L.check(lib.dtf_ipc_export(self.mirror_base, handle), "ipc_export(mirror)")
+        info = dict(handle=bytes(handle.raw), pid=os.getpid(), ptr=self.mirror_base,
+                    device=int(self.local_device), nbytes=int(self.mirror.nbytes))
+        for s in range(self.num_shards):
+            self.client.call(s, "mirror_register", int(worker_id), info)
+        self._mirror_worker = int(worker_id)
+
+    def unregister_mirror(self) -> None:
+        if self._mirror_worker is None:
+            return
+        w, self._mirror_worker = self._mirror_worker, None
+        for s in range(self.num_shards):
+            try:
+                self.client.call(s, "mirror_unregister", w)
+            except Exception:
+                pass
+
+    def mirror_hdr_u32(self, byte_off: int, count: int) -> np.ndarray:
+        return self._d2h(self.mirror_base + byte_off, 4 * count, np.uint32)
+
+    def read_mirror(self, name: str) -> Dict[str, np.ndarray]:
+        """This worker's mirrored copies of a variable as float32 arrays (tests / diagnostics):
+        ``{"bf16": ..., "f32": ...}`` with the forms the mirror holds."""
+        import torch
+        vl = self.layout[name]
+        out: Dict[str, np.ndarray] = {}
+        if name in self.mirror.f32:
+            out["f32"] = self._d2h(self.mirror_base + self.mirror.f32[name], vl.num_elements * 4,
+                                   np.float32).reshape(vl.shape)
+        if name in self.mirror.bf16:
+            ld = self.arena.regions[name][0].shadow_ld
+            raw = self._d2h(self.mirror_base + self.mirror.bf16[name], vl.rows * ld * 2, np.uint16)
+            t = torch.from_numpy(raw.view(np.int16).copy()).view(torch.bfloat16)
+            out["bf16"] = t.float().numpy().reshape(vl.rows, ld)[:, :vl.cols].reshape(vl.shape)
+        return out
+
     def close(self) -> None:
         lib = L.lib()
+        self.unregister_mirror()
+        if self.mirror_base:
+            try:
+                lib.dtf_arena_free(self.mirror_base)
+            except Exception:
+                pass
+            self.mirror_base = 0
         for p in self._imported:
             try:
                 lib.dtf_ipc_close(p)

@@ -255,13 +255,26 @@ class PsShard:
                 if sig == self._mbox_sig:
                     return {"started": False}
                 # a new graph / optimizer / arena on this PS task (new session in the same process):
-                # retire the daemon that serves the previous layout
+                # retire the daemon that serves the previous layout, and forget the mirrors that were
+                # registered for it (their layout belongs to the old graph)
                 self._mbox_daemon = None
                 L.lib().dtf_mbox_daemon_stop(old)
+                self._drop_mirrors()
 
             def at(off):
                 return None if off is None or off < 0 else base + int(off)
 
+            self._mbox_flags_off = int(desc["flags_off"])
+            # a (re)started daemon begins from a clean flag block: after a layout change that
+            # region of the arena held something else (a stale lock or mirror address would be fatal)
+            L.check(L.lib().dtf_set_device(self._arena["device"]), "set_device")
+            zeros = (C.c_ubyte * L.MBOX_FLAGS_BYTES)()
+            L.check(L.lib().dtf_memcpy_h2d(self._flags_ptr(), zeros, L.MBOX_FLAGS_BYTES, None), "h2d")
+            L.check(L.lib().dtf_stream_sync(None), "sync")
+            self.__dict__.setdefault("_mirrors", {}).clear()
+            mirror_items = None
+            if desc.get("mirror_items") is not None:
+                mirror_items = K.make_mirror_items([tuple(m) for m in desc["mirror_items"]])
             entries = [dict(var=at(it["var_off"]), slot0=at(it["slot0_off"]), slot1=at(it["slot1_off"]),
                             shadow=at(it["shadow_off"]), grad=at(it["grad_off"]), n=int(it["n"]),
                             first=0, cols=int(it["cols"]), shadow_ld=int(it["shadow_ld"]))
@@ -276,7 +289,9 @@ class PsShard:
                                            len(entries), int(desc["slot_stride"]), int(desc["depth"]),
                                            int(desc["n_workers"]), C.byref(hyper), base,
                                            base if desc["owns_step"] else None,
-                                           base + int(desc["flags_off"]), int(desc.get("poll_us", 20)))
+                                           base + int(desc["flags_off"]), int(desc.get("poll_us", 20)),
+                                           mirror_items, int(desc.get("shard", self.task_index)),
+                                           int(getattr(self, "_mbox_backstop_us", 0)))
             L.check(rc, "dtf_mbox_daemon_start")
             self._mbox_daemon = handle
             self._mbox_sig = sig
@@ -296,10 +311,127 @@ class PsShard:
         return {"running": True, "polls": polls.value, "drains": drains.value, "applied": applied.value}
 
     def mbox_pause(self, pause: bool) -> None:
+        """Quiesce the shard for a consistent read (checkpoint): parks the daemon, makes drains
+        launched from a colocated worker's step graph no-ops (``flags.paused``) and waits for a
+        drain in flight to retire."""
         from ..ops import _lib as L
         d = getattr(self, "_mbox_daemon", None)
         if d is not None:
             L.check(L.lib().dtf_mbox_daemon_pause(d, 1 if pause else 0), "dtf_mbox_daemon_pause")
+        if self._arena is not None and getattr(self, "_mbox_flags_off", None) is not None:
+            self._flags_write_u32(L.MBOX_OFF_PAUSED, 1 if pause else 0)
+            if pause:
+                self._wait_drain_idle()
+
+    def mbox_attach(self, worker: int, attach: bool, backstop_us: int = 400) -> None:
+        """A worker living in this process runs this shard's drains as nodes of its own step graph
+        (device-driven: no host thread between a gradient's arrival and its apply). The daemon
+        stays as the backstop for gradients that wait longer than ``backstop_us`` (that worker has
+        stopped stepping); detaching returns the shard to the daemon alone."""
+        from ..ops import _lib as L
+        with self._lock:
+            self._mbox_backstop_us = int(backstop_us) if attach else 0
+            d = getattr(self, "_mbox_daemon", None)
+            if d is not None:
+                L.check(L.lib().dtf_mbox_daemon_set_backstop(d, self._mbox_backstop_us), "set_backstop")
+
+    # -- worker mirrors (csrc/kernels/mailbox.cu: the drain broadcasts fresh parameters) ------------
+    def _flags_ptr(self) -> int:
+        return self._arena["ptr"] + self._mbox_flags_off
+
+    def _flags_write_u32(self, off: int, value: int) -> None:
+        import ctypes as C
+        from ..ops import _lib as L
+        lib = L.lib()
+        L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
+        buf = (C.c_uint * 1)(int(value))
+        L.check(lib.dtf_memcpy_h2d(self._flags_ptr() + off, buf, 4, None), "h2d")
+        L.check(lib.dtf_stream_sync(None), "sync")
+
+    def _flags_read_u32(self, off: int) -> int:
+        import ctypes as C
+        from ..ops import _lib as L
+        lib = L.lib()
+        L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
+        buf = (C.c_uint * 1)(0)
+        L.check(lib.dtf_memcpy_d2h(buf, self._flags_ptr() + off, 4, None), "d2h")
+        L.check(lib.dtf_stream_sync(None), "sync")
+        return int(buf[0])
+
+    def _wait_drain_idle(self, timeout: float = 2.0) -> None:
+        from ..ops import _lib as L
+        t0 = time.monotonic()
+        while self._flags_read_u32(L.MBOX_OFF_LOCK) != 0 and time.monotonic() - t0 < timeout:
+            time.sleep(50e-6)
+
+    def _drop_mirrors(self) -> None:
+        """Clear every registered mirror address (caller holds the lock, no drain is running)."""
+        import ctypes as C
+        from ..ops import _lib as L
+        mirrors = self.__dict__.get("_mirrors") or {}
+        if self._arena is None or getattr(self, "_mbox_flags_off", None) is None:
+            mirrors.clear()
+            return
+        lib = L.lib()
+        L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
+        zeros = (C.c_ulonglong * L.MAX_WORKERS)()
+        L.check(lib.dtf_memcpy_h2d(self._flags_ptr() + L.MBOX_OFF_MIRROR_BASE, zeros, 8 * L.MAX_WORKERS, None), "h2d")
+        L.check(lib.dtf_stream_sync(None), "sync")
+        for ent in mirrors.values():
+            if ent["imported"]:
+                lib.dtf_ipc_close(ent["ptr"])
+        mirrors.clear()
+
+    def mirror_register(self, worker: int, info: dict) -> dict:
+        """Map worker ``worker``'s mirror into this (the owner's) process and publish its address in
+        ``flags.mirror_base[worker]``; every later drain stores the fresh parameters there."""
+        import ctypes as C
+        import os
+        from ..ops import _lib as L
+        if self._arena is None or getattr(self, "_mbox_flags_off", None) is None:
+            raise RuntimeError("mirror_register before mbox_start")
+        if not 0 <= int(worker) < L.MAX_WORKERS:
+            raise ValueError("mirror_register: worker %r out of range" % (worker,))
+        lib = L.lib()
+        with self._lock:
+            mirrors = self.__dict__.setdefault("_mirrors", {})
+            L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
+            imported = False
+            if int(info["pid"]) == os.getpid():
+                ptr = int(info["ptr"])
+                if int(info["device"]) != self._arena["device"]:
+                    L.check(lib.dtf_enable_peer_access(int(info["device"])), "enable_peer_access")
+            else:
+                p = C.c_void_p()
+                L.check(lib.dtf_ipc_import(bytes(info["handle"]), C.byref(p)), "ipc_import(mirror)")
+                ptr, imported = int(p.value), True
+            old = mirrors.get(int(worker))
+            buf = (C.c_ulonglong * 1)(ptr)
+            L.check(lib.dtf_memcpy_h2d(self._flags_ptr() + L.MBOX_OFF_MIRROR_BASE + 8 * int(worker), buf, 8, None), "h2d")
+            L.check(lib.dtf_stream_sync(None), "sync")
+            mirrors[int(worker)] = dict(ptr=ptr, imported=imported)
+        if old is not None and old["imported"] and old["ptr"] != ptr:
+            self._wait_drain_idle()
+            lib.dtf_ipc_close(old["ptr"])
+        return {"ok": True}
+
+    def mirror_unregister(self, worker: int) -> None:
+        import ctypes as C
+        from ..ops import _lib as L
+        lib = L.lib()
+        with self._lock:
+            ent = self.__dict__.setdefault("_mirrors", {}).pop(int(worker), None)
+            if ent is None or self._arena is None:
+                return
+            L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
+            buf = (C.c_ulonglong * 1)(0)
+            L.check(lib.dtf_memcpy_h2d(self._flags_ptr() + L.MBOX_OFF_MIRROR_BASE + 8 * int(worker), buf, 8, None), "h2d")
+            L.check(lib.dtf_stream_sync(None), "sync")
+        # a drain that read the old address may still be storing: let it retire before unmapping
+        time.sleep(200e-6)
+        self._wait_drain_idle()
+        if ent["imported"]:
+            lib.dtf_ipc_close(ent["ptr"])
 
     def mbox_stop(self) -> None:
         from ..ops import _lib as L

@@ -238,8 +238,46 @@ typedef struct dtf_mbox_flags {               /* 512 bytes, zero = idle */
   unsigned int consumed[DTF_MAX_WORKERS];     /* +128 owner: gradients of worker w applied so far */
   unsigned int pad1[16];
   unsigned int done[DTF_MAX_WORKERS];         /* +256 worker w has finished training */
-  unsigned int pad2[48];
+  unsigned int lock;                          /* +320 a drain is in flight (device-scope CAS: every drain of a
+                                                      shard runs on the shard's GPU, whoever launches it) */
+  unsigned int paused;                        /* +324 owner: drains are no-ops while set (checkpoint cut) */
+  unsigned int drains;                        /* +328 drains that applied at least one gradient */
+  unsigned int applied_total;                 /* +332 gradients applied so far (all workers) */
+  unsigned int pad2[12];
+  unsigned long long mirror_base[DTF_MAX_WORKERS]; /* +384 address of worker w's mirror IN THE OWNER'S PROCESS
+                                                      (0 = none): the drain broadcasts fresh parameters there */
 } dtf_mbox_flags;
+
+/* ------------------------------------------------------------------------------------------
+ * Worker mirrors ("owner pushes, worker never pulls"). The reference fetches every parameter
+ * from the PS at the start of every mon_sess.run (run_mnist_distributed.py:150,161) - an NVLink
+ * READ round trip at the head of the step. Here every worker owns a mirror of the parameters in
+ * its own HBM (bf16 row-padded copies of the matrices its tensor-core kernels read, fp32 copies
+ * of the small tensors); the owner's drain, which has just computed the new values, also stores
+ * them into every registered mirror with posted 16-byte writes. The worker's step reads only
+ * local memory. Reads are unlocked, like TF1's use_locking=False: a step may see a slice that a
+ * drain is half-way through rewriting. The header carries what the worker otherwise had to read
+ * over NVLink: per owner the count of its own pushes applied (flow control), a version, and the
+ * shared global_step.
+ * ------------------------------------------------------------------------------------------ */
+#define DTF_MIRROR_MAX_SHARDS 32
+typedef struct dtf_mirror_hdr {               /* 512 bytes at offset 0 of every worker mirror */
+  unsigned long long global_step;             /* +0   last value broadcast by the step-owning shard */
+  unsigned int epoch;                         /* +8   sync mode: completed rounds */
+  unsigned int pad0[29];
+  unsigned int version[DTF_MIRROR_MAX_SHARDS];   /* +128 shard s: gradients applied (all workers) when it
+                                                         last rewrote this mirror; stored after the data */
+  unsigned int consumed[DTF_MIRROR_MAX_SHARDS];  /* +256 shard s: how many of THIS worker's pushes it applied */
+  unsigned int pad1[32];
+} dtf_mirror_hdr;
+/* Where a drained slice goes inside every mirror (byte offsets from the mirror base, -1 = the
+ * mirror does not hold that form) and the slice's first element inside its variable. */
+typedef struct dtf_drain_mirror_item {
+  long long bf16_off;     /* bf16 [rows, shadow_ld] copy of the WHOLE variable */
+  long long f32_off;      /* fp32 flat copy of the WHOLE variable */
+  long long first;        /* flat index of the slice's first element inside the variable */
+} dtf_drain_mirror_item;
+
 #define DTF_MAX_MBOX_ITEMS 64
 typedef struct dtf_mbox_push_item {
   const void* src;        /* local fp32 gradient slice */
@@ -249,28 +287,44 @@ typedef struct dtf_mbox_push_item {
 } dtf_mbox_push_item;
 /* Copies every item into buffer (*seq % depth) of the caller's mailboxes. With publish = 1 the
  * last CTA then stores produced[worker_id] = *seq + 1 on EVERY owner (owner_flags[0..n_owners)),
- * advances *seq, and writes min over owners of consumed[worker_id] to *min_consumed_out — the
+ * advances *seq, and writes min over owners of consumed[worker_id] to *min_consumed_out - the
  * host's flow control: push k may only be issued once every owner has consumed push k - depth.
  * With ctrl_step / step_out it also reads the shared global_step into *step_out (local u64).
- * Several non-publishing calls followed by one publishing call form one push. */
+ * my_hdr (optional): this worker's mirror header; consumed[] and global_step are then read from
+ * it (local memory, kept fresh by the owners' drains; owner i of owner_flags is shard i) instead
+ * of over NVLink. Several non-publishing calls followed by one publishing call form one push. */
 int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, int depth, int worker_id,
                      dtf_mbox_flags* const* owner_flags, int n_owners, int publish,
                      unsigned int* seq, unsigned int* block_counter,
                      unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
-                     unsigned long long* step_out, const dtf_result_sink* sink, void* stream);
-/* Owner side, two launches: (1) snapshot which workers have an unconsumed gradient (at most one
- * per worker per call, the oldest) into `todo` (local scratch, DTF_MAX_WORKERS words);
- * (2) for every item read var / slots once, apply the pending gradients one after another with
- * the beta powers each apply would have seen, write var / slots / bf16 serving copy once. Items
+                     unsigned long long* step_out, const dtf_result_sink* sink,
+                     const dtf_mirror_hdr* my_hdr, void* stream);
+/* Owner side, two launches: (1) claim the shard's drain lock and snapshot which workers have an
+ * unconsumed gradient (at most one per worker per call, the oldest) into `todo` (local scratch,
+ * DTF_MAX_WORKERS + 1 words; nothing is claimed while flags->paused or another drain holds the
+ * lock); (2) for every item read var / slots once, apply the pending gradients one after another
+ * with the beta powers each apply would have seen, write var / slots / bf16 serving copy once. Items
  * are dtf_apply_item whose `grad` points at the slice inside slot (worker 0, buffer 0). The last
- * CTA publishes consumed[w] += 1, multiplies the shard's beta powers, and — when ctrl_step is not
- * NULL (this shard owns global_step) — adds the number of applied gradients to global_step and
- * refreshes the workers' heartbeats. step_out (optional, local u64) receives global_step. */
+ * CTA publishes consumed[w] += 1, multiplies the shard's beta powers, and - when ctrl_step is not
+ * NULL (this shard owns global_step) - adds the number of applied gradients to global_step and
+ * refreshes the workers' heartbeats; then it releases the lock. step_out (optional, local u64)
+ * receives global_step. The drain may be launched by the owner's daemon thread or as a node of a
+ * colocated worker's step graph: the lock makes concurrent launches safe. */
 int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_items, long long slot_stride,
                       int depth, int n_workers, const dtf_apply_hyper* hyper,
                       dtf_ps_ctrl* ctrl_powers, dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags,
                       unsigned int* todo, unsigned int* block_counter,
                       unsigned long long* step_out, void* stream);
+/* Same, and every updated element is also stored into each mirror registered in
+ * flags->mirror_base (mirror_items[i] belongs to items[i]; NULL = no broadcast); afterwards the
+ * mirrors' headers receive consumed[shard_index], global_step (step owner only) and, last,
+ * version[shard_index] with release semantics. */
+int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_items, long long slot_stride,
+                         int depth, int n_workers, const dtf_apply_hyper* hyper,
+                         dtf_ps_ctrl* ctrl_powers, dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags,
+                         unsigned int* todo, unsigned int* block_counter,
+                         unsigned long long* step_out, const dtf_drain_mirror_item* mirror_items,
+                         int shard_index, void* stream);
 
 /* Host-side spin on a pinned word written by a kernel (see dtf_result_sink): 0 = reached
  * `expected`, 1 = timeout. */
@@ -284,10 +338,17 @@ int dtf_graph_launch(void* graph_exec, void* stream);
  * the ApplyAdam ops placed on /job:ps (run_mnist_distributed.py:96-98,107,116). Pointers are
  * device addresses in the OWNER's address space. */
 typedef struct dtf_mbox_daemon dtf_mbox_daemon;
+/* mirror_items (may be NULL) / shard_index: see dtf_mailbox_drain_ex. backstop_us > 0 turns the
+ * daemon into a backstop for a shard whose drains normally run inside a colocated worker's step
+ * graph: it then only drains gradients that have been pending for at least that long (an owner
+ * whose worker has stopped stepping must still serve the other workers). */
 int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt, const dtf_apply_item* items,
                           int n_items, long long slot_stride, int depth, int n_workers,
                           const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
-                          dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, int poll_us);
+                          dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, int poll_us,
+                          const dtf_drain_mirror_item* mirror_items, int shard_index,
+                          int backstop_us);
+int dtf_mbox_daemon_set_backstop(dtf_mbox_daemon* d, int backstop_us);
 int dtf_mbox_daemon_pause(dtf_mbox_daemon* d, int pause);   /* 1: returns once parked; 0: resume */
 int dtf_mbox_daemon_stats(dtf_mbox_daemon* d, unsigned long long* polls,
                           unsigned long long* drains, unsigned long long* applied); /* -1: daemon died */

@@ -567,7 +567,7 @@ def test_mailbox_push_and_drain_apply_pending_gradients_in_worker_order(K):
     stride = off1 + 256                            # bytes per (worker, buffer) slot
     slots = torch.zeros(W * depth * stride // 4, device=dev)
     flags = torch.zeros(128, dtype=torch.int32, device=dev)
-    todo = torch.zeros(16, dtype=torch.int32, device=dev)
+    todo = torch.zeros(32, dtype=torch.int32, device=dev)
     counter = torch.zeros(4, dtype=torch.int32, device=dev)
     ctrl = torch.zeros(64, dtype=torch.int32, device=dev)
     lr, b1, b2, eps = 1e-2, 0.9, 0.999, 1e-8
@@ -640,6 +640,121 @@ def test_mailbox_push_and_drain_apply_pending_gradients_in_worker_order(K):
         b1p, b2p = b1p * b1, b2p * b2
         assert torch.allclose(var[0], ref[0][0], rtol=1e-5, atol=1e-6)
     assert flags[32 + 1].item() == 4 and ctrl.view(torch.int64)[0].item() == total + 2
+
+
+@pytest.mark.parametrize("cols,ld", [(64, 64), (10, 16), (40, 40)])
+def test_mailbox_drain_broadcasts_into_worker_mirrors(K, cols, ld):
+    """Owner pushes, worker never pulls: the drain stores every updated element into each registered
+    mirror (bf16 row-padded and fp32 forms, at the slice's place inside the whole variable) and then
+    the header words the worker would otherwise read over NVLink. A paused shard and a held lock
+    make the drain a no-op."""
+    from distributedtensorflow_b200.ops import _lib as L
+    torch.manual_seed(5)
+    dev = "cuda"
+    W, depth, shard = 2, 2, 3
+    rows_total, row0, rows = 96, 32, 40            # this shard owns rows [32, 72) of a [96, cols] matrix
+    n0, nb = rows * cols, 24                       # ... and elements [8, 32) of a 40-element vector
+    off1 = (n0 * 4 + 255) // 256 * 256
+    stride = off1 + 256
+    slots = torch.zeros(W * depth * stride // 4, device=dev)
+    flags = torch.zeros(128, dtype=torch.int32, device=dev)
+    todo = torch.zeros(32, dtype=torch.int32, device=dev)
+    counter = torch.zeros(4, dtype=torch.int32, device=dev)
+    ctrl = torch.zeros(64, dtype=torch.int32, device=dev)
+    lr = 0.5
+    var = [torch.randn(n0, device=dev), torch.randn(nb, device=dev)]
+    shadow = torch.zeros(rows, ld, dtype=torch.bfloat16, device=dev)
+    # two mirrors: header (512 B) | bf16 [rows_total, ld] | fp32 [40]
+    bf_off, f32_off = 512, 512 + (rows_total * ld * 2 + 255) // 256 * 256
+    mbytes = f32_off + 256
+    mirrors = [torch.zeros(mbytes // 4, dtype=torch.int32, device=dev) for _ in range(W)]
+    fl64 = flags.view(torch.int64)
+    fl64[48 + 0] = mirrors[0].data_ptr()           # worker 0 and worker 1 registered
+    fl64[48 + 1] = mirrors[1].data_ptr()
+    items = K.make_apply_items([
+        dict(var=var[0].data_ptr(), shadow=shadow.data_ptr(), grad=slots.data_ptr(), n=n0, cols=cols, shadow_ld=ld),
+        dict(var=var[1].data_ptr(), shadow=None, grad=slots.data_ptr() + off1, n=nb, cols=nb, shadow_ld=nb)])
+    mitems = K.make_mirror_items([(bf_off, -1, row0 * cols), (-1, f32_off, 8)])
+    hyper = K.make_hyper(lr)
+    seq = [torch.zeros(1, dtype=torch.int32, device=dev) for _ in range(W)]
+    pcount = torch.zeros(4, dtype=torch.int32, device=dev)
+    minc = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def push(w, g0, g1):
+        base = slots.data_ptr() + w * depth * stride
+        g1p = torch.zeros(32, device=dev)
+        g1p[:nb] = g1
+        K.mailbox_push([(g0.data_ptr(), base, n0 * 4, stride)], depth, w, [flags.data_ptr()], False,
+                       seq[w].data_ptr(), None, None)
+        K.mailbox_push([(g1p.data_ptr(), base + off1, 32 * 4, stride)], depth, w, [flags.data_ptr()], True,
+                       seq[w].data_ptr(), pcount.data_ptr(), minc.data_ptr())
+        torch.cuda.synchronize()
+
+    def drain():
+        K.mailbox_drain(L.OPT_SGD, items, 2, stride, depth, W, hyper, None, ctrl.data_ptr(),
+                        flags.data_ptr(), todo.data_ptr(), counter.data_ptr(), None,
+                        mirror_items=mitems, shard_index=shard)
+        torch.cuda.synchronize()
+
+    ref = [x.clone() for x in var]
+    g = [(torch.randn(n0, device=dev), torch.randn(nb, device=dev)) for _ in range(3)]
+    push(0, *g[0])
+    push(1, *g[1])
+    # paused shard: nothing is claimed, nothing applied
+    flags[L.MBOX_OFF_PAUSED // 4] = 1
+    drain()
+    assert torch.equal(var[0], ref[0]) and flags[32].item() == 0 and todo[16].item() == 0
+    flags[L.MBOX_OFF_PAUSED // 4] = 0
+    # a drain in flight elsewhere holds the lock: this launch backs off
+    flags[L.MBOX_OFF_LOCK // 4] = 1
+    drain()
+    assert torch.equal(var[0], ref[0]) and flags[32].item() == 0
+    flags[L.MBOX_OFF_LOCK // 4] = 0
+    drain()
+    for k in (0, 1):
+        ref[0] -= lr * g[k][0]
+        ref[1] -= lr * g[k][1]
+    assert torch.allclose(var[0], ref[0], rtol=1e-6, atol=1e-6) and torch.allclose(var[1], ref[1], rtol=1e-6, atol=1e-6)
+    assert flags[L.MBOX_OFF_LOCK // 4].item() == 0 and flags[L.MBOX_OFF_APPLIED // 4].item() == 2
+
+    def check_mirrors(applied, consumed):
+        want_bf = var[0].view(rows, cols).to(torch.bfloat16)
+        for w, mir in enumerate(mirrors):
+            raw = mir.view(torch.uint8)
+            bf = raw[bf_off:bf_off + rows_total * ld * 2].view(torch.bfloat16).view(rows_total, ld)
+            assert torch.equal(bf[row0:row0 + rows, :cols], want_bf), f"mirror {w} bf16"
+            assert bf[:row0].abs().sum().item() == 0 and bf[row0 + rows:].abs().sum().item() == 0
+            if ld > cols:
+                assert bf[:, cols:].abs().sum().item() == 0            # the row padding is never written
+            f32 = raw[f32_off:f32_off + 160].view(torch.float32)
+            assert torch.equal(f32[8:32], var[1]) and f32[:8].abs().sum().item() == 0 and f32[32:].abs().sum().item() == 0
+            hdr = mir[:128]
+            assert hdr.view(torch.int64)[0].item() == applied                      # global_step
+            assert hdr[L.MIRROR_OFF_VERSION // 4 + shard].item() == applied
+            assert hdr[L.MIRROR_OFF_CONSUMED // 4 + shard].item() == consumed[w]
+        assert torch.equal(shadow[:, :cols], want_bf)
+
+    check_mirrors(2, [1, 1])
+    # worker 1 unregisters: its mirror is left alone from now on
+    fl64[48 + 1] = 0
+    keep = mirrors[1].clone()
+    push(0, *g[2])
+    drain()
+    ref[0] -= lr * g[2][0]
+    assert torch.allclose(var[0], ref[0], rtol=1e-6, atol=1e-6)
+    assert torch.equal(mirrors[1], keep)
+    mirrors_all, mirrors[:] = list(mirrors), mirrors[:1]
+    check_mirrors(3, [2])
+    # the push kernel takes flow control and global_step from the worker's own header
+    hdr_ptr = mirrors_all[0].data_ptr()
+    step_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    base = slots.data_ptr()
+    K.mailbox_push([(g[0][0].data_ptr(), base, n0 * 4, stride)], depth, 0, [flags.data_ptr()] * (shard + 1), True,
+                   seq[0].data_ptr(), pcount.data_ptr(), minc.data_ptr(), ctrl_step=None,
+                   step_out=step_out.data_ptr(), my_hdr=hdr_ptr)
+    torch.cuda.synchronize()
+    assert int(step_out.item()) == 3
+    assert int(minc.item()) == 0          # min over header consumed[0..3]: shards 0..2 never wrote theirs
 
 
 @pytest.mark.parametrize("B,H,dense", [(128, 1024, False), (100, 100, True), (37, 300, False)])
