@@ -133,6 +133,8 @@ def main() -> int:
                     help="extra executor option, e.g. --opt zero_copy_input=0 --opt host_sink=0")
     ap.add_argument("--num-ps", type=int, default=0,
                     help="PS shards (default: one per GPU). --gpus 2 --num-ps 1 is the README's '1 PS, 2 workers'")
+    ap.add_argument("--timeline", default="", metavar="PATH",
+                    help="after the measurements: CUPTI kernel timeline of 6 more replayed steps on rank 0 (json)")
     ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"],
                     help="gradient push: worker-side remote read-modify-write, or posted stores + the "
                          "owner's apply daemon (auto = mailbox when there is more than one worker)")
@@ -160,9 +162,21 @@ def main() -> int:
     torch.cuda.set_device(local_rank)
     if local_rank == 0:
         entry.build()
+    if os.environ.get("DTF_B200_HANG_DUMP"):
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["DTF_B200_HANG_DUMP"]), exit=True)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
+        # Barriers between phases run on the CPU (gloo): a rank parked inside an NCCL barrier keeps a
+        # spinning kernel on its GPU, and while that kernel runs the same process cannot map a late
+        # peer's mirror (cudaIpcOpenMemHandle waits for the device) - the peer it is waiting for.
+        cpu_group = dist.new_group(backend="gloo")
+
+    def barrier():
+        if world > 1:
+            dist.barrier(group=cpu_group)
 
     import distributedtensorflow_b200 as tf
     from distributedtensorflow_b200.data import mnist
@@ -177,8 +191,7 @@ def main() -> int:
     cluster = tf.train.ClusterSpec({"ps": ps_addrs, "worker": wk_addrs})
     ps_server = tf.train.Server(cluster, job_name="ps", task_index=rank) if rank < NPS else None
     wk_server = tf.train.Server(cluster, job_name="worker", task_index=rank)
-    if world > 1:
-        dist.barrier()
+    barrier()
 
     placement = args.placement
     if placement == "auto":
@@ -222,8 +235,7 @@ def main() -> int:
         runner = raw._runner
         state = runner.train_state()
         launches_per_step = state.launches_per_step
-        if world > 1:
-            dist.barrier()
+        barrier()
         torch.cuda.synchronize()
 
         # -- device-timed region: K steps, L2 flushed between them ------------------------------
@@ -233,8 +245,7 @@ def main() -> int:
         sampler = ClockSampler(range(N)) if rank == 0 else None
         if sampler:
             sampler.start()
-        if world > 1:
-            dist.barrier()
+        barrier()
         torch.cuda.synchronize()
         t_wall0 = time.perf_counter()
         with torch.cuda.stream(runner.stream):
@@ -246,8 +257,7 @@ def main() -> int:
                 ends[i].record(runner.stream)
         runner.stream.synchronize()
         torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+        barrier()
         t_wall = time.perf_counter() - t_wall0
         dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
 
@@ -263,8 +273,7 @@ def main() -> int:
         clocks = sampler.stop() if sampler else None
 
         # -- end-to-end through the public API ---------------------------------------------------
-        if world > 1:
-            dist.barrier()
+        barrier()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for _ in range(args.steps):
@@ -273,9 +282,28 @@ def main() -> int:
         e2e_s = time.perf_counter() - t0
         final_loss = float(l)
         runner.flush_pushes()        # "owner applies" mode: my last gradients have been applied
-        if world > 1:
-            dist.barrier()           # every worker has finished: the shared counter is final
+        barrier()                    # every worker has finished: the shared counter is final
         final_step = int(sess.run(global_step))
+
+        if args.timeline:
+            from torch.profiler import profile, ProfilerActivity
+            barrier()
+            if rank == 0:
+                with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                    runner.replay(6)
+                    runner.stream.synchronize()
+                evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+                evs.sort(key=lambda e: e.time_range.start)
+                t00 = evs[0].time_range.start if evs else 0
+                rows = [dict(t_us=round(e.time_range.start - t00, 2),
+                             dur_us=round(e.time_range.end - e.time_range.start, 2), name=e.name[:70]) for e in evs]
+                os.makedirs(os.path.dirname(os.path.abspath(args.timeline)), exist_ok=True)
+                json.dump(rows, open(args.timeline, "w"), indent=0)
+            else:
+                runner.replay(6)
+                runner.stream.synchronize()
+            runner.flush_pushes()
+            barrier()
 
         times = torch.tensor([dev_ms, b2b_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
         if world > 1:
@@ -316,8 +344,7 @@ def main() -> int:
             "launches_per_step": int(launches_per_step),
             "clocks": clocks, "final_global_step": final_step, "final_loss": round(final_loss, 5),
         }
-    if world > 1:
-        dist.barrier()
+    barrier()
     if ps_server is not None:
         ps_server.stop()
     wk_server.stop()

@@ -71,6 +71,14 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
         const long long i = static_cast<long long>(u) * MBOX_THREADS + threadIdx.x;
         if (i < nvec) v[u] = src[i];
       }
+      if (c.zero_src) {
+        uint4* z = const_cast<uint4*>(src);
+#pragma unroll
+        for (int u = 0; u < MBOX_UNROLL; ++u) {
+          const long long i = static_cast<long long>(u) * MBOX_THREADS + threadIdx.x;
+          if (i < nvec) z[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
 #pragma unroll
       for (int u = 0; u < MBOX_UNROLL; ++u) {
         const long long i = static_cast<long long>(u) * MBOX_THREADS + threadIdx.x;
@@ -80,16 +88,20 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
   }
   if (!a.publish) return;
   // ---- the last CTA publishes the push to every owner ----
-  __threadfence_system();
+  // A system-scope fence costs microseconds here, so exactly ONE sits on the critical path: every
+  // CTA orders its stores at GPU scope before taking its ticket (bar.sync, then one thread fences:
+  // cumulative over the CTA), and the elected CTA's release stores below carry the system-scope
+  // fence that makes everything that happened-before them visible to the owners.
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     const unsigned int old = atomicInc(a.block_counter, static_cast<unsigned int>(a.total_blocks - 1));
     s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
     s_min = 0xffffffffu;
+    if (s_last) __threadfence();  // acquire side of the election
   }
   __syncthreads();
   if (!s_last) return;
-  __threadfence_system();  // acquire side of the election: every CTA's stores precede the flags
   if (static_cast<int>(threadIdx.x) < a.n_owners) {
     dtf_mbox_flags* f = a.owner_flags[threadIdx.x];
     st_release_sys_u32(&f->produced[a.worker_id], seq + 1u);
@@ -152,15 +164,16 @@ __global__ void mailbox_snapshot_kernel(dtf_mbox_flags* flags, unsigned int* tod
 }
 
 constexpr int DRAIN_THREADS = 256;
-constexpr int DRAIN_VEC = 8;                              // elements per thread: two float4 / one bf16x8
-constexpr int DRAIN_CHUNK = DRAIN_THREADS * DRAIN_VEC;    // 2048 elements / CTA
+constexpr int DRAIN_VEC = 4;                                           // one float4 per access, lane-contiguous
+constexpr int DRAIN_UNROLL = 4;                                        // independent vectors per thread
+constexpr int DRAIN_CHUNK = DRAIN_THREADS * DRAIN_VEC * DRAIN_UNROLL;  // 4096 elements / CTA pass
 
 struct DrainArgs {
   dtf_apply_item items[DTF_MAX_APPLY_ITEMS];
   dtf_drain_mirror_item mirror[DTF_MAX_APPLY_ITEMS];
   int block_start[DTF_MAX_APPLY_ITEMS + 1];
   int n_items;
-  int total_blocks;
+  int total_chunks;
   dtf_apply_hyper h;
   dtf_ps_ctrl* ctrl_powers;
   dtf_ps_ctrl* ctrl_step;
@@ -175,20 +188,30 @@ struct DrainArgs {
   unsigned int* block_counter;
 };
 
-// bf16 store of cnt (<= 8) consecutive elements of a [rows, cols] tensor kept with row pitch ld,
-// f = flat index of v[0]. vec8: cols, ld, f are multiples of 8 and base is 16-byte aligned.
-__device__ __forceinline__ void put_bf16(__nv_bfloat16* base, long long f, int cols, int ld,
-                                         const float* v, int cnt, bool vec8) {
-  if (vec8 && cnt == 8) {
-    const long long r = f / cols, c = f - r * cols;
-    *reinterpret_cast<uint4*>(base + r * ld + c) =
-        make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-                   pack_bf16x2(v[6], v[7]));
+// bf16 store of 4 consecutive elements of a [rows, cols] tensor kept with row pitch ld; f = flat
+// index of v[0]. vec: cols, ld, f are multiples of 4 and base is 8-byte aligned (one 8-byte store
+// per lane, lane-contiguous: a warp writes 256 contiguous bytes).
+__device__ __forceinline__ void put_bf16x4(__nv_bfloat16* base, long long f, int cols, int ld,
+                                           const float* v, bool vec) {
+  // 32-bit index math whenever it fits (a 64-bit division costs ~10x a 32-bit one)
+  long long r;
+  int c;
+  if (f < 0x7fffffffLL) {
+    const unsigned int fu = static_cast<unsigned int>(f), cu = static_cast<unsigned int>(cols);
+    const unsigned int ru = fu / cu;
+    r = ru;
+    c = static_cast<int>(fu - ru * cu);
+  } else {
+    r = f / cols;
+    c = static_cast<int>(f - r * cols);
+  }
+  if (vec) {
+    *reinterpret_cast<uint2*>(base + r * ld + c) =
+        make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
     return;
   }
-  long long r = f / cols;
-  int c = static_cast<int>(f - r * cols);
-  for (int j = 0; j < cnt; ++j) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
     base[r * ld + c] = __float2bfloat16(v[j]);
     if (++c == cols) { c = 0; ++r; }
   }
@@ -197,7 +220,6 @@ __device__ __forceinline__ void put_bf16(__nv_bfloat16* base, long long f, int c
 template <int OPT>
 __global__ void __launch_bounds__(DRAIN_THREADS)
 mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
-  __shared__ int s_item;
   __shared__ int s_n;
   __shared__ long long s_off[DTF_MAX_WORKERS];  // element offset of pending gradient k from item.grad
   __shared__ float s_lr[DTF_MAX_WORKERS];
@@ -208,9 +230,6 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
   griddep_wait();
   griddep_launch();
   if (threadIdx.x == 0) {
-    int it = 0;
-    while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
-    s_item = it;
     float b1p = 0.f, b2p = 0.f;
     if (OPT == DTF_OPT_ADAM) {
       b1p = *reinterpret_cast<volatile float*>(&a.ctrl_powers->beta1_power);
@@ -241,133 +260,149 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
   __syncthreads();
   const int n_pending = s_n;
   const int n_mirror = s_nm;
-  const dtf_apply_item& it = a.items[s_item];
-  const dtf_drain_mirror_item& mi = a.mirror[s_item];
-  if (n_pending > 0 && it.n > 0) {
-    const long long base = static_cast<long long>(blockIdx.x - a.block_start[s_item]) * DRAIN_CHUNK;
-    const long long i = base + static_cast<long long>(threadIdx.x) * DRAIN_VEC;
+  // the grid may be capped (a drain that runs beside compute kernels should hold a few CTA slots,
+  // not flood the SMs): every CTA strides over the 4096-element chunks
+  for (int chunk = blockIdx.x; n_pending > 0 && chunk < a.total_chunks; chunk += gridDim.x) {
+  int item = 0;
+  while (item + 1 < a.n_items && chunk >= a.block_start[item + 1]) ++item;
+  const dtf_apply_item& it = a.items[item];
+  const dtf_drain_mirror_item& mi = a.mirror[item];
+  if (it.n > 0) {
+    const long long base = static_cast<long long>(chunk - a.block_start[item]) * DRAIN_CHUNK;
     const bool vec_ok =
         ((reinterpret_cast<uintptr_t>(it.var) | reinterpret_cast<uintptr_t>(it.grad) |
           reinterpret_cast<uintptr_t>(it.slot0) | reinterpret_cast<uintptr_t>(it.slot1)) & 15) == 0 &&
         (a.slot_stride % 16 == 0);
     __nv_bfloat16* shadow = reinterpret_cast<__nv_bfloat16*>(it.shadow);
-    const bool geo8 = (it.cols % 8 == 0) && (it.shadow_ld % 8 == 0);
-    if (i < it.n) {
-      const int cnt = static_cast<int>(min(static_cast<long long>(DRAIN_VEC), it.n - i));
-      const bool full = vec_ok && cnt == DRAIN_VEC;
-      float v[DRAIN_VEC], m[DRAIN_VEC], u[DRAIN_VEC];
-      if (full) {
+    const bool geo4 = (it.cols % 4 == 0) && (it.shadow_ld % 4 == 0);
+    const bool shadow_vec = geo4 && (it.first % 4 == 0) && ((reinterpret_cast<uintptr_t>(shadow) & 7) == 0);
+    const bool mirror_vec = geo4 && (mi.first % 4 == 0) && (mi.bf16_off % 8 == 0);
+    const bool mirror_f32_vec = (mi.first % 4 == 0) && (mi.f32_off % 16 == 0);
+    float4 v4[DRAIN_UNROLL], m4[DRAIN_UNROLL], u4[DRAIN_UNROLL], g4[DRAIN_UNROLL];
+    bool full[DRAIN_UNROLL];
+    // phase 1: every 16-byte load of this thread's vectors (state + the first gradient) is issued
+    // before any is used: up to 16 requests in flight per thread
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const float4 x = *reinterpret_cast<const float4*>(it.var + i + 4 * h);
-          v[4 * h] = x.x; v[4 * h + 1] = x.y; v[4 * h + 2] = x.z; v[4 * h + 3] = x.w;
-          if (OPT != DTF_OPT_SGD) {
-            const float4 y = *reinterpret_cast<const float4*>(it.slot0 + i + 4 * h);
-            m[4 * h] = y.x; m[4 * h + 1] = y.y; m[4 * h + 2] = y.z; m[4 * h + 3] = y.w;
-          }
-          if (OPT == DTF_OPT_ADAM) {
-            const float4 z = *reinterpret_cast<const float4*>(it.slot1 + i + 4 * h);
-            u[4 * h] = z.x; u[4 * h + 1] = z.y; u[4 * h + 2] = z.z; u[4 * h + 3] = z.w;
-          }
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < DRAIN_VEC; ++j) {
-          v[j] = m[j] = u[j] = 0.f;
-          if (j < cnt) {
-            v[j] = it.var[i + j];
-            if (OPT != DTF_OPT_SGD) m[j] = it.slot0[i + j];
-            if (OPT == DTF_OPT_ADAM) u[j] = it.slot1[i + j];
-          }
-        }
+    for (int u = 0; u < DRAIN_UNROLL; ++u) {
+      const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
+      full[u] = vec_ok && i + DRAIN_VEC <= it.n;
+      v4[u] = m4[u] = u4[u] = g4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (full[u]) {
+        v4[u] = *reinterpret_cast<const float4*>(it.var + i);
+        if (OPT != DTF_OPT_SGD) m4[u] = *reinterpret_cast<const float4*>(it.slot0 + i);
+        if (OPT == DTF_OPT_ADAM) u4[u] = *reinterpret_cast<const float4*>(it.slot1 + i);
+        // written by a peer GPU since the last drain: read at L2, not through .nc
+        const uint4 r = ld_relaxed_u4(reinterpret_cast<const uint4*>(it.grad + s_off[0] + i));
+        g4[u] = make_float4(__uint_as_float(r.x), __uint_as_float(r.y), __uint_as_float(r.z),
+                            __uint_as_float(r.w));
       }
-      if (OPT == DTF_OPT_SGD) {
-#pragma unroll
-        for (int j = 0; j < DRAIN_VEC; ++j) m[j] = u[j] = 0.f;
-      } else if (OPT != DTF_OPT_ADAM) {
-#pragma unroll
-        for (int j = 0; j < DRAIN_VEC; ++j) u[j] = 0.f;
-      }
+    }
+    // phase 2: apply the pending gradients in worker order; gradient k + 1 is in flight while
+    // gradient k is applied
 #pragma unroll 1
-      for (int k = 0; k < n_pending; ++k) {
-        const float* g = it.grad + s_off[k];
-        const float lr_t = s_lr[k];
-        float gv[DRAIN_VEC];
-        if (full) {  // written by a peer GPU since the last drain: read at L2, not through .nc
+    for (int k = 0; k < n_pending; ++k) {
+      const float lr_t = s_lr[k];
+      float4 gn[DRAIN_UNROLL];
+      if (k + 1 < n_pending) {
+        const float* g = it.grad + s_off[k + 1];
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const uint4 r = ld_relaxed_u4(reinterpret_cast<const uint4*>(g + i + 4 * h));
-            gv[4 * h] = __uint_as_float(r.x); gv[4 * h + 1] = __uint_as_float(r.y);
-            gv[4 * h + 2] = __uint_as_float(r.z); gv[4 * h + 3] = __uint_as_float(r.w);
+        for (int u = 0; u < DRAIN_UNROLL; ++u) {
+          const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
+          gn[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (full[u]) {
+            const uint4 r = ld_relaxed_u4(reinterpret_cast<const uint4*>(g + i));
+            gn[u] = make_float4(__uint_as_float(r.x), __uint_as_float(r.y), __uint_as_float(r.z),
+                                __uint_as_float(r.w));
           }
-        } else {
-#pragma unroll
-          for (int j = 0; j < DRAIN_VEC; ++j)
-            gv[j] = (j < cnt) ? *reinterpret_cast<const volatile float*>(g + i + j) : 0.f;
         }
-#pragma unroll
-        for (int j = 0; j < DRAIN_VEC; ++j)
-          update_one<OPT>(gv[j] * a.h.grad_scale, v[j], m[j], u[j], a.h, lr_t);
       }
-      if (full) {
+      const float s = a.h.grad_scale;
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          *reinterpret_cast<float4*>(it.var + i + 4 * h) =
-              make_float4(v[4 * h], v[4 * h + 1], v[4 * h + 2], v[4 * h + 3]);
-          if (OPT != DTF_OPT_SGD)
-            *reinterpret_cast<float4*>(it.slot0 + i + 4 * h) =
-                make_float4(m[4 * h], m[4 * h + 1], m[4 * h + 2], m[4 * h + 3]);
-          if (OPT == DTF_OPT_ADAM)
-            *reinterpret_cast<float4*>(it.slot1 + i + 4 * h) =
-                make_float4(u[4 * h], u[4 * h + 1], u[4 * h + 2], u[4 * h + 3]);
+      for (int u = 0; u < DRAIN_UNROLL; ++u) {
+        if (!full[u]) continue;
+        update_one<OPT>(g4[u].x * s, v4[u].x, m4[u].x, u4[u].x, a.h, lr_t);
+        update_one<OPT>(g4[u].y * s, v4[u].y, m4[u].y, u4[u].y, a.h, lr_t);
+        update_one<OPT>(g4[u].z * s, v4[u].z, m4[u].z, u4[u].z, a.h, lr_t);
+        update_one<OPT>(g4[u].w * s, v4[u].w, m4[u].w, u4[u].w, a.h, lr_t);
+      }
+      if (k + 1 < n_pending) {
+#pragma unroll
+        for (int u = 0; u < DRAIN_UNROLL; ++u) g4[u] = gn[u];
+      }
+    }
+    // phase 3: write back, refresh the serving copy, and push the new values into the mirrors
+#pragma unroll
+    for (int u = 0; u < DRAIN_UNROLL; ++u) {
+      const long long i = base + (static_cast<long long>(u) * DRAIN_THREADS + threadIdx.x) * DRAIN_VEC;
+      if (i >= it.n) continue;
+      if (full[u]) {
+        *reinterpret_cast<float4*>(it.var + i) = v4[u];
+        if (OPT != DTF_OPT_SGD) *reinterpret_cast<float4*>(it.slot0 + i) = m4[u];
+        if (OPT == DTF_OPT_ADAM) *reinterpret_cast<float4*>(it.slot1 + i) = u4[u];
+        const float v[4] = {v4[u].x, v4[u].y, v4[u].z, v4[u].w};
+        if (shadow != nullptr) put_bf16x4(shadow, it.first + i, it.cols, it.shadow_ld, v, shadow_vec);
+        if (n_mirror > 0) {   // owner pushes: posted stores into every worker's mirror
+          const long long f = mi.first + i;
+          if (mi.bf16_off >= 0) {
+            for (int q = 0; q < n_mirror; ++q)
+              put_bf16x4(reinterpret_cast<__nv_bfloat16*>(s_mbase[q] + mi.bf16_off), f, it.cols,
+                         it.shadow_ld, v, mirror_vec);
+          }
+          if (mi.f32_off >= 0) {
+            for (int q = 0; q < n_mirror; ++q) {
+              float* dst = reinterpret_cast<float*>(s_mbase[q] + mi.f32_off) + f;
+              if (mirror_f32_vec) {
+                *reinterpret_cast<float4*>(dst) = v4[u];
+              } else {
+                dst[0] = v[0]; dst[1] = v[1]; dst[2] = v[2]; dst[3] = v[3];
+              }
+            }
+          }
         }
       } else {
-        for (int j = 0; j < cnt; ++j) {
-          it.var[i + j] = v[j];
-          if (OPT != DTF_OPT_SGD) it.slot0[i + j] = m[j];
-          if (OPT == DTF_OPT_ADAM) it.slot1[i + j] = u[j];
-        }
-      }
-      if (shadow != nullptr)
-        put_bf16(shadow, it.first + i, it.cols, it.shadow_ld, v, cnt,
-                 geo8 && ((it.first + i) % 8 == 0) && ((reinterpret_cast<uintptr_t>(shadow) & 15) == 0));
-      // ---- owner pushes: the new values go straight into every worker's mirror (posted stores) ----
-      if (n_mirror > 0) {
-        const long long f = mi.first + i;
-        if (mi.bf16_off >= 0) {
-          const bool v8 = geo8 && (f % 8 == 0) && (mi.bf16_off % 16 == 0);
-          for (int q = 0; q < n_mirror; ++q)
-            put_bf16(reinterpret_cast<__nv_bfloat16*>(s_mbase[q] + mi.bf16_off), f, it.cols,
-                     it.shadow_ld, v, cnt, v8);
-        }
-        if (mi.f32_off >= 0) {
-          const bool v4 = cnt == DRAIN_VEC && (f % 4 == 0) && (mi.f32_off % 16 == 0);
+        // ragged tail / unaligned slice: element by element
+        for (int j = 0; j < DRAIN_VEC && i + j < it.n; ++j) {
+          float v = it.var[i + j];
+          float s0 = (OPT != DTF_OPT_SGD) ? it.slot0[i + j] : 0.f;
+          float s1 = (OPT == DTF_OPT_ADAM) ? it.slot1[i + j] : 0.f;
+          for (int k = 0; k < n_pending; ++k)
+            update_one<OPT>(*reinterpret_cast<const volatile float*>(it.grad + s_off[k] + i + j) *
+                                a.h.grad_scale, v, s0, s1, a.h, s_lr[k]);
+          it.var[i + j] = v;
+          if (OPT != DTF_OPT_SGD) it.slot0[i + j] = s0;
+          if (OPT == DTF_OPT_ADAM) it.slot1[i + j] = s1;
+          if (shadow != nullptr) {
+            const long long f = it.first + i + j;
+            shadow[(f / it.cols) * it.shadow_ld + (f % it.cols)] = __float2bfloat16(v);
+          }
+          const long long f = mi.first + i + j;
           for (int q = 0; q < n_mirror; ++q) {
-            float* dst = reinterpret_cast<float*>(s_mbase[q] + mi.f32_off) + f;
-            if (v4) {
-              *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
-              *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
-            } else {
-              for (int j = 0; j < cnt; ++j) dst[j] = v[j];
-            }
+            if (mi.bf16_off >= 0)
+              reinterpret_cast<__nv_bfloat16*>(s_mbase[q] + mi.bf16_off)[(f / it.cols) * it.shadow_ld + (f % it.cols)] =
+                  __float2bfloat16(v);
+            if (mi.f32_off >= 0) reinterpret_cast<float*>(s_mbase[q] + mi.f32_off)[f] = v;
           }
         }
       }
     }
   }
+  }  // chunk loop
 
   // ---- the last CTA retires the drained gradients ----
-  __threadfence_system();
+  // Fences: system scope costs microseconds, so the CTAs order their stores at GPU scope before the
+  // election and the elected CTA issues its system-scope release stores from parallel threads (one
+  // per worker): two fence latencies on the critical path instead of 3 + n_workers.
   __syncthreads();
   if (threadIdx.x == 0) {
-    const unsigned int old = atomicInc(a.block_counter, static_cast<unsigned int>(a.total_blocks - 1));
-    s_last = (old == static_cast<unsigned int>(a.total_blocks - 1)) ? 1u : 0u;
+    __threadfence();
+    const unsigned int old = atomicInc(a.block_counter, gridDim.x - 1u);
+    s_last = (old == gridDim.x - 1u) ? 1u : 0u;
+    if (s_last) __threadfence();  // acquire side of the election
   }
   __syncthreads();
   if (!s_last) return;
   const bool holds_lock = a.todo[DTF_MAX_WORKERS] != 0u;
   if (threadIdx.x == 0) {
-    __threadfence_system();
     unsigned long long step = 0;
     if (n_pending > 0) {
       if (OPT == DTF_OPT_ADAM) {
@@ -383,14 +418,6 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
                static_cast<unsigned long long>(n_pending);
         atomicAdd(&a.ctrl_step->apply_count, static_cast<unsigned int>(n_pending));
       }
-      for (int w = 0; w < a.n_workers; ++w) {
-        if (a.todo[w] == 0) continue;
-        if (a.ctrl_step != nullptr)
-          *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[w]) = step;
-        // the mailbox buffer may be overwritten by worker w from here on
-        const unsigned int c = *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
-        st_release_sys_u32(&a.flags->consumed[w], c + 1u);
-      }
       *reinterpret_cast<volatile unsigned int*>(&a.flags->drains) =
           *reinterpret_cast<volatile unsigned int*>(&a.flags->drains) + 1u;
       *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total) =
@@ -405,18 +432,26 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
     }
   }
   __syncthreads();
-  // mirror headers, one thread per worker: what the worker would otherwise read over NVLink
-  if (a.bcast && n_pending > 0 && static_cast<int>(threadIdx.x) < DTF_MAX_WORKERS) {
+  // one thread per worker: retire its gradient (the mailbox buffer may be overwritten by worker w
+  // from here on) and refresh its mirror's header - what the worker would otherwise read over NVLink
+  if (n_pending > 0 && static_cast<int>(threadIdx.x) < DTF_MAX_WORKERS) {
     const int w = threadIdx.x;
+    const bool drained = w < a.n_workers && a.todo[w] != 0u;
+    unsigned int c = *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
+    if (drained) {
+      if (a.ctrl_step != nullptr)
+        *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[w]) = s_step;
+      c += 1u;
+      st_release_sys_u32(&a.flags->consumed[w], c);
+    }
     const unsigned long long b =
-        *reinterpret_cast<volatile unsigned long long*>(&a.flags->mirror_base[w]);
+        a.bcast ? *reinterpret_cast<volatile unsigned long long*>(&a.flags->mirror_base[w]) : 0ull;
     if (b != 0ull) {
       dtf_mirror_hdr* hdr = reinterpret_cast<dtf_mirror_hdr*>(b);
-      *reinterpret_cast<volatile unsigned int*>(&hdr->consumed[a.shard]) =
-          *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
+      *reinterpret_cast<volatile unsigned int*>(&hdr->consumed[a.shard]) = c;
       if (a.ctrl_step != nullptr)
         *reinterpret_cast<volatile unsigned long long*>(&hdr->global_step) = s_step;
-      // every CTA fenced its data stores before the election: the version follows the data
+      // the release fence orders every CTA's data stores (GPU-scope fences + the election) first
       st_release_sys_u32(&hdr->version[a.shard],
                          *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total));
     }
@@ -499,7 +534,7 @@ extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_ite
                                  unsigned int* block_counter, unsigned long long* step_out,
                                  void* stream_) {
   return dtf_mailbox_drain_ex(opt, items, n_items, slot_stride, depth, n_workers, hyper, ctrl_powers,
-                              ctrl_step, flags, todo, block_counter, step_out, nullptr, 0, stream_);
+                              ctrl_step, flags, todo, block_counter, step_out, nullptr, 0, 0, stream_);
 }
 
 extern "C" int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_items,
@@ -508,7 +543,7 @@ extern "C" int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_
                                     dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, unsigned int* todo,
                                     unsigned int* block_counter, unsigned long long* step_out,
                                     const dtf_drain_mirror_item* mirror_items, int shard_index,
-                                    void* stream_) {
+                                    int max_ctas, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "mailbox_drain: %d items (max %d)",
               n_items, DTF_MAX_APPLY_ITEMS);
@@ -545,7 +580,8 @@ extern "C" int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_
     }
   }
   a.n_items = n_items;
-  a.total_blocks = blocks;
+  a.total_chunks = blocks;
+  if (max_ctas > 0 && blocks > max_ctas) blocks = max_ctas;
   a.h = *hyper;
   a.ctrl_powers = ctrl_powers;
   a.ctrl_step = ctrl_step;

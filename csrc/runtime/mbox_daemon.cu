@@ -30,6 +30,7 @@ struct dtf_mbox_daemon {
   bool has_mirror = false;
   int shard = 0;
   std::atomic<int> backstop_us{0};
+  std::atomic<int> max_ctas{0};   // grid cap of the drains (0 = one CTA per chunk)
   int n_items = 0;
   long long slot_stride = 0;
   int depth = 1;
@@ -137,7 +138,7 @@ void daemon_main(dtf_mbox_daemon* d) {
     if (dtf_mailbox_drain_ex(d->opt, d->items, d->n_items, d->slot_stride, d->depth, d->n_workers,
                              &d->hyper, d->ctrl_powers, d->ctrl_step, d->flags, d->scratch,
                              d->scratch + 32, nullptr, d->has_mirror ? d->mirror : nullptr, d->shard,
-                             d->stream) != 0) {
+                             d->max_ctas.load(std::memory_order_relaxed), d->stream) != 0) {
       d->fail("apply daemon: %s", dtf_last_error());
       return;
     }
@@ -203,6 +204,12 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
   d->thread = std::thread(daemon_main, d);
   cudaSetDevice(prev);
   *out = d;
+  return 0;
+}
+
+extern "C" int dtf_mbox_daemon_set_max_ctas(dtf_mbox_daemon* d, int max_ctas) {
+  DTF_REQUIRE(d != nullptr, "mbox_daemon_set_max_ctas: null daemon");
+  d->max_ctas.store(max_ctas > 0 ? max_ctas : 0, std::memory_order_relaxed);
   return 0;
 }
 

@@ -358,6 +358,9 @@ class B200StepRunner:
         self.graph_drain = bool(opts.get("graph_drain", os.environ.get("DTF_B200_GRAPH_DRAIN", "1") != "0"))
         self.drain_at = str(opts.get("drain_at", os.environ.get("DTF_B200_DRAIN_AT", "start")))
         self.drain_backstop_us = int(opts.get("drain_backstop_us", 400))
+        # grid cap of the in-graph drain: it runs beside the forward pass, where a flood of CTAs
+        # doubled the convolutions' time; a few dozen CTAs over a longer window are free
+        self.drain_ctas = int(opts.get("drain_ctas", os.environ.get("DTF_B200_DRAIN_CTAS", "64")))
         self.use_mirror = False
         self.my_shards: List[int] = []
         self.use_mailbox = False
@@ -1054,12 +1057,16 @@ class B200StepRunner:
         ``publish`` releases the push (one sequence number per owner) and must be the step's last."""
         st, al, me = self.store, self.store.arena, self.worker_id
         items = []
+        zb = s.zero.buf.data_ptr()
+        ze = zb + s.zero.buf.numel() * 4
+        clean = self._self_cleans(s)
         for var in variables:
             gptr = self._grad_ptr(s, var)
             for r in self._regions_rotated(var):
                 dst0 = st.mbox_slot_ptr(r.shard, me, 0) + st.mbox_slice_off(var.name, r.shard)
+                # an accumulated gradient (bias / conv filter sums) is cleared by the kernel that consumes it
                 items.append((gptr + r.sl.first * 4, dst0, (r.sl.n * 4 + 15) // 16 * 16,
-                              al.mailbox_stride[r.shard]))
+                              al.mailbox_stride[r.shard], int(clean and zb <= gptr < ze)))
         flags = [st.mbox_flags_ptr(sh) for sh in range(st.num_shards)]
         K.mailbox_push(items, al.mailbox_depth, me, flags, publish, self.mbox_seq.data_ptr(),
                        s.counter.data_ptr(), self.mbox_host.data_ptr() if publish else None,
@@ -1091,7 +1098,8 @@ class B200StepRunner:
             K.mailbox_drain(spec.code, K.make_apply_items(entries), len(entries), int(desc["slot_stride"]),
                             int(desc["depth"]), int(desc["n_workers"]), hyper, base,
                             base if desc["owns_step"] else None, base + int(desc["flags_off"]),
-                            scratch, scratch + 128, None, mirror_items=mitems, shard_index=sh)
+                            scratch, scratch + 128, None, mirror_items=mitems, shard_index=sh,
+                            max_ctas=self.drain_ctas)
 
     def _mbox_consumed(self) -> int:
         """min over owners of how many of MY gradients they have applied (host-side read)."""
@@ -1222,7 +1230,9 @@ class B200StepRunner:
     def _self_cleans(self, s: StepState) -> bool:
         """True when every buffer of the zeroed region is reset by its consumer (worker-side apply
         with a result sink, every dense layer has a bias so each column sum is consumed)."""
-        return (self.self_clean and self._uses_sink(s) and not self.use_mailbox and self.clear_at_end
+        if self.use_mailbox and not (self.early_report and not self.fused_push):
+            return False      # the loss is cleared by the early report; the scatter epilogue has no source to clear
+        return (self.self_clean and self._uses_sink(s) and self.clear_at_end
                 and not (self.fused_apply) and all(d.b is not None for d in self.plan.dense))
 
     def _uses_sink(self, s: StepState) -> bool:

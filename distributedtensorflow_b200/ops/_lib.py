@@ -134,7 +134,7 @@ class CopyItem(C.Structure):
 class MboxPushItem(C.Structure):
     """Mirror of ``dtf_mbox_push_item``."""
     _fields_ = [("src", C.c_void_p), ("dst0", C.c_void_p), ("bytes", C.c_longlong),
-                ("buf_stride", C.c_longlong)]
+                ("buf_stride", C.c_longlong), ("zero_src", C.c_int), ("reserved", C.c_int)]
 
 
 MAX_MBOX_ITEMS = 64
@@ -211,12 +211,13 @@ def _declare(lib):
         "dtf_mailbox_push": [C.POINTER(MboxPushItem), i, i, i, C.POINTER(vp), i, i, vp, vp, vp, vp, vp,
                              C.POINTER(ResultSink), vp, vp],
         "dtf_mailbox_drain_ex": [i, C.POINTER(ApplyItem), i, C.c_longlong, i, i, C.POINTER(ApplyHyper), vp, vp,
-                                 vp, vp, vp, vp, C.POINTER(DrainMirrorItem), i, vp],
+                                 vp, vp, vp, vp, C.POINTER(DrainMirrorItem), i, i, vp],
         "dtf_mailbox_drain": [i, C.POINTER(ApplyItem), i, C.c_longlong, i, i, C.POINTER(ApplyHyper), vp, vp,
                               vp, vp, vp, vp, vp],
         "dtf_mbox_daemon_start": [C.POINTER(vp), i, i, C.POINTER(ApplyItem), i, C.c_longlong, i, i,
                                   C.POINTER(ApplyHyper), vp, vp, vp, i, C.POINTER(DrainMirrorItem), i, i],
         "dtf_mbox_daemon_set_backstop": [vp, i],
+        "dtf_mbox_daemon_set_max_ctas": [vp, i],
         "dtf_mbox_daemon_pause": [vp, i],
         "dtf_mbox_daemon_stats": [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)],
         "dtf_mbox_daemon_stop": [vp],

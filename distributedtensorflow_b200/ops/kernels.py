@@ -198,16 +198,18 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
                  my_hdr: Optional[int] = None) -> None:
     """Worker side of the "owner applies" push (csrc/kernels/mailbox.cu).
 
-    items: (src_ptr, dst0_ptr, nbytes, buf_stride) — gradient slice -> its place in MY buffer 0 on
-    the owning shard. ``publish`` makes the last CTA release the sequence number to every owner in
+    items: (src_ptr, dst0_ptr, nbytes, buf_stride[, zero_src]) — gradient slice -> its place in MY
+    buffer 0 on the owning shard (zero_src: clear the source after reading it). ``publish`` makes the last CTA release the sequence number to every owner in
     ``owner_flags`` (pointers to their ``dtf_mbox_flags``)."""
     n = len(items)
     chunks = [items[i:i + L.MAX_MBOX_ITEMS] for i in range(0, n, L.MAX_MBOX_ITEMS)] or [[]]
     flags = (C.c_void_p * max(1, len(owner_flags)))(*owner_flags)
     for ci, chunk in enumerate(chunks):
         arr = (L.MboxPushItem * max(1, len(chunk)))()
-        for i, (s, d, b, st) in enumerate(chunk):
+        for i, item in enumerate(chunk):
+            s, d, b, st = item[:4]
             arr[i].src, arr[i].dst0, arr[i].bytes, arr[i].buf_stride = s, d, b, st
+            arr[i].zero_src = int(item[4]) if len(item) > 4 else 0
         last = publish and ci == len(chunks) - 1
         if not chunk and not last:
             continue
@@ -231,13 +233,13 @@ def make_mirror_items(entries: Sequence[tuple]) -> "C.Array":
 def mailbox_drain(opt: int, items, n_items: int, slot_stride: int, depth: int, n_workers: int,
                   hyper: L.ApplyHyper, ctrl_powers: Optional[int], ctrl_step: Optional[int],
                   flags: int, todo: int, block_counter: int, step_out: Optional[int],
-                  mirror_items=None, shard_index: int = 0) -> None:
+                  mirror_items=None, shard_index: int = 0, max_ctas: int = 0) -> None:
     """Owner side: claim the lock + snapshot pending mailboxes, then apply them from local HBM and
     (``mirror_items``) broadcast the new values into the registered worker mirrors. Two launches.
     ``todo`` needs MAX_WORKERS + 1 words."""
     rc = L.lib().dtf_mailbox_drain_ex(opt, items, n_items, slot_stride, depth, n_workers, C.byref(hyper),
                                       ctrl_powers, ctrl_step, flags, todo, block_counter, step_out,
-                                      mirror_items, shard_index, L.current_stream())
+                                      mirror_items, shard_index, int(max_ctas), L.current_stream())
     L.check(rc, "dtf_mailbox_drain")
     _count(2)
 

@@ -284,6 +284,9 @@ typedef struct dtf_mbox_push_item {
   void* dst0;             /* the slice's place inside MY buffer 0 on the owning shard (peer pointer) */
   long long bytes;        /* multiple of 16 */
   long long buf_stride;   /* bytes from buffer b to buffer b + 1 of the same worker on that shard */
+  int zero_src;           /* store 0 back into src after reading it (src is an atomically accumulated
+                             buffer that must be clear for the next step: no fill kernel trails the step) */
+  int reserved;
 } dtf_mbox_push_item;
 /* Copies every item into buffer (*seq % depth) of the caller's mailboxes. With publish = 1 the
  * last CTA then stores produced[worker_id] = *seq + 1 on EVERY owner (owner_flags[0..n_owners)),
@@ -318,13 +321,15 @@ int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_items, long lo
 /* Same, and every updated element is also stored into each mirror registered in
  * flags->mirror_base (mirror_items[i] belongs to items[i]; NULL = no broadcast); afterwards the
  * mirrors' headers receive consumed[shard_index], global_step (step owner only) and, last,
- * version[shard_index] with release semantics. */
+ * version[shard_index] with release semantics. max_ctas > 0 caps the grid (the CTAs stride over
+ * the 2048-element chunks): a drain that runs beside a worker's compute kernels then holds a few
+ * CTA slots for longer instead of flooding every SM. */
 int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_items, long long slot_stride,
                          int depth, int n_workers, const dtf_apply_hyper* hyper,
                          dtf_ps_ctrl* ctrl_powers, dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags,
                          unsigned int* todo, unsigned int* block_counter,
                          unsigned long long* step_out, const dtf_drain_mirror_item* mirror_items,
-                         int shard_index, void* stream);
+                         int shard_index, int max_ctas, void* stream);
 
 /* Host-side spin on a pinned word written by a kernel (see dtf_result_sink): 0 = reached
  * `expected`, 1 = timeout. */
@@ -349,6 +354,7 @@ int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt, const dtf_
                           const dtf_drain_mirror_item* mirror_items, int shard_index,
                           int backstop_us);
 int dtf_mbox_daemon_set_backstop(dtf_mbox_daemon* d, int backstop_us);
+int dtf_mbox_daemon_set_max_ctas(dtf_mbox_daemon* d, int max_ctas);   /* grid cap of its drains, 0 = none */
 int dtf_mbox_daemon_pause(dtf_mbox_daemon* d, int pause);   /* 1: returns once parked; 0: resume */
 int dtf_mbox_daemon_stats(dtf_mbox_daemon* d, unsigned long long* polls,
                           unsigned long long* drains, unsigned long long* applied); /* -1: daemon died */
