@@ -275,11 +275,13 @@ def main() -> int:
         # -- end-to-end through the public API ---------------------------------------------------
         barrier()
         torch.cuda.synchronize()
+        runner.host_prof = dict(stage=0.0, admit=0.0, launch=0.0, wait=0.0, n=0)
         t0 = time.perf_counter()
         for _ in range(args.steps):
             _, l, g = sess.run([train_op, loss, global_step])
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
+        host_prof, runner.host_prof = runner.host_prof, None
         final_loss = float(l)
         runner.flush_pushes()        # "owner applies" mode: my last gradients have been applied
         barrier()                    # every worker has finished: the shared counter is final
@@ -339,7 +341,9 @@ def main() -> int:
             "back_to_back_ms_per_step": round(b2b_ms / args.steps, 5),
             "e2e": {"value": round(N * args.steps / (e2e_ms / 1e3), 2), "unit": "global steps/s",
                     "ms_per_step": round(e2e_ms / args.steps, 5),
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "host_us_per_step_rank0": {k: round(v / max(1, host_prof["n"]) * 1e6, 1)
+                                               for k, v in host_prof.items() if k != "n"}},
             "gpu_launches": int(launches_per_step * args.steps),
             "launches_per_step": int(launches_per_step),
             "clocks": clocks, "final_global_step": final_step, "final_loss": round(final_loss, 5),

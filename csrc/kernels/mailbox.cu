@@ -44,6 +44,7 @@ struct MboxPushArgs {
   unsigned long long* step_out;
   dtf_result_sink sink;
   const dtf_mirror_hdr* my_hdr;
+  const dtf_mirror_hdr* flow_hdr;   // device-side flow control against this header's consumed[]
 };
 
 __global__ void __launch_bounds__(MBOX_THREADS)
@@ -61,6 +62,28 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
     while (it + 1 < a.n_items && static_cast<int>(blockIdx.x) >= a.block_start[it + 1]) ++it;
     const dtf_mbox_push_item& c = a.items[it];
     const long long base = static_cast<long long>(blockIdx.x - a.block_start[it]) * MBOX_CHUNK;
+    if (a.flow_hdr != nullptr && base < c.bytes && seq >= static_cast<unsigned int>(a.depth)) {
+      // Device-side flow control (bounded staleness): buffer seq % depth still holds push
+      // seq - depth until its owner has consumed it. The owners' drains keep consumed[] fresh in MY
+      // mirror's header, so this polls local memory and the host never blocks on admission. A worker
+      // only ever waits for owners that are behind it, so the waits cannot form a cycle.
+      if (threadIdx.x == 0) {
+        const volatile unsigned int* cons = &a.flow_hdr->consumed[c.owner];
+        const unsigned int need = seq - static_cast<unsigned int>(a.depth) + 1u;
+        const long long t0 = clock64();
+        while (static_cast<int>(*cons - need) < 0) {
+          if (*reinterpret_cast<const volatile unsigned int*>(&a.flow_hdr->abort) != 0u) break;
+          __nanosleep(200);
+          if (clock64() - t0 > 100ll * DTF_WAIT_TIMEOUT_CYCLES) {   // minutes: an owner may be paused for a checkpoint
+            printf("dtf mailbox: worker %d waited too long for owner %d to consume push %u\n",
+                   a.worker_id, c.owner, need);
+            __trap();
+          }
+        }
+        __threadfence();
+      }
+      __syncthreads();
+    }
     if (base < c.bytes) {
       const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(c.src) + base);
       uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<char*>(c.dst0) + buf * c.buf_stride + base);
@@ -516,6 +539,12 @@ extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, in
   a.ctrl_step = ctrl_step;
   a.step_out = step_out;
   a.my_hdr = publish ? my_hdr : nullptr;
+  a.flow_hdr = nullptr;
+  if (my_hdr != nullptr) {
+    bool flow = n_items > 0;
+    for (int i = 0; i < n_items; ++i) flow = flow && items[i].owner >= 0 && items[i].owner < DTF_MIRROR_MAX_SHARDS;
+    if (flow) a.flow_hdr = my_hdr;
+  }
   DTF_REQUIRE(my_hdr == nullptr || n_owners <= DTF_MIRROR_MAX_SHARDS,
               "mailbox_push: %d owners exceed the mirror header (%d)", n_owners, DTF_MIRROR_MAX_SHARDS);
   if (sink != nullptr && publish) {

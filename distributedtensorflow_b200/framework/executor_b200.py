@@ -17,6 +17,7 @@ else raises and can run with ``ConfigProto(backend="cpu")``.
 """
 from __future__ import annotations
 
+import ctypes as C
 import os
 import time
 from dataclasses import dataclass
@@ -67,6 +68,11 @@ class Plan:
 
 class UnsupportedGraphError(NotImplementedError):
     pass
+
+
+def opts_flag(config, key: str, default: bool) -> bool:
+    opts = getattr(config, "b200_options", {}) or {}
+    return bool(opts.get(key, default))
 
 
 def _is_input(n: G.Tensor) -> bool:
@@ -309,6 +315,8 @@ class B200StepRunner:
         self.atomic_sgd = bool(opts.get("atomic_sgd", False))
         self.health_every = int(opts.get("health_every", 256))   # control-plane ping period (steps)
         self._runs = 0
+        # host-side breakdown of run() (seconds): set to a dict(stage=0, admit=0, launch=0, wait=0, n=0) to collect
+        self.host_prof: Optional[Dict[str, float]] = None
         self._incarnations: Dict[int, int] = {}
         # dW GEMM whose epilogue is the push+apply (no gradient buffer). Measured on the reference CNN it
         # is slower than GEMM + the coalesced apply kernel (180 vs 158 us/step), so it is opt-in.
@@ -341,6 +349,10 @@ class B200StepRunner:
         # measured on more than one GPU.
         self.fused_push = bool(opts.get("fused_push", False))
         self.early_apply_ctas = int(opts.get("early_apply_ctas", 0))   # cap the grid of overlapped applies
+        # owner-applies mode: only gradients at least this large get their own early push kernel (its
+        # NVLink time hides behind the backward pass); smaller ones would just serialise the push
+        # stream in front of the big one and ride in the final push instead
+        self.early_push_min_bytes = int(opts.get("early_push_min_bytes", 256 * 1024))
         # asynchronous gradient push: "rmw" = the worker's SMs read-modify-write the owner's state
         # over NVLink (dtf_push_apply); "mailbox" = posted gradient stores + the owner's native apply
         # daemon (csrc/kernels/mailbox.cu, csrc/runtime/mbox_daemon.cu); "auto" = mailbox whenever
@@ -362,6 +374,8 @@ class B200StepRunner:
         # doubled the convolutions' time; a few dozen CTAs over a longer window are free
         self.drain_ctas = int(opts.get("drain_ctas", os.environ.get("DTF_B200_DRAIN_CTAS", "64")))
         self.use_mirror = False
+        self.device_flow = False
+        self.max_queue = int(opts.get("max_queue", 64))     # steps the host may run ahead of the device
         self.my_shards: List[int] = []
         self.use_mailbox = False
         self._pushes = 0
@@ -471,6 +485,10 @@ class B200StepRunner:
                                and self.store.num_shards <= L.MIRROR_MAX_SHARDS)
         if self.use_mirror:
             self.store.alloc_mirror()
+        # flow control on the device needs the mirror header (and pushes made by the push kernel, not
+        # by a GEMM epilogue)
+        self.device_flow = bool(self.use_mirror and not self.fused_push
+                                and opts_flag(self.config, "device_flow", True))
         if self.use_mailbox:
             self._mbox_setup()
 
@@ -855,6 +873,7 @@ class B200StepRunner:
             early = self.use_mailbox or self.fused_apply or not all(self.store.is_local)
         apl = self.apply_stream if (par and early) else main
         applied: List[G.Variable] = []
+        late_dw: List[Any] = []
 
         def after(stream):
             ev = torch.cuda.Event()
@@ -914,7 +933,11 @@ class B200StepRunner:
                 fork(side)                       # dZ_{i-1} is ready
             elif p.kind == "cnn":
                 K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld, **self._plan_kw(s, "dx0"))
-            if par and early:
+            small_push = (self.use_mailbox and fused is None and push_spec is None
+                          and self.layout[d.w.name].num_elements * 4 < self.early_push_min_bytes)
+            if small_push and dw_done is not None:
+                late_dw.append(dw_done)      # a small gradient rides in the step's final, publishing push
+            if par and early and not small_push:
                 # W_i may be read in place from the local shard by the dX GEMM above: order the
                 # apply after it, and after the gradient it consumes
                 fork(apl)
@@ -939,10 +962,10 @@ class B200StepRunner:
             K.pool2_bwd(s.dpool2, s.act[0].view(s.B, 7, 7, 64), s.amax2, s.dconv2p, s.z["gkb2"])
             fork(side)                           # dconv2p is ready
             with torch.cuda.stream(side):
-                K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
                 if clean_ws:                     # every split-K GEMM of the step is done: re-zero
                     K.fill_u32(s.zero.buf[s.zero.ws_off:], 0)   # their workspaces beside the conv backward
                     clean_ws = False
+                K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
             K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if clean_ws:
@@ -1066,14 +1089,15 @@ class B200StepRunner:
                 dst0 = st.mbox_slot_ptr(r.shard, me, 0) + st.mbox_slice_off(var.name, r.shard)
                 # an accumulated gradient (bias / conv filter sums) is cleared by the kernel that consumes it
                 items.append((gptr + r.sl.first * 4, dst0, (r.sl.n * 4 + 15) // 16 * 16,
-                              al.mailbox_stride[r.shard], int(clean and zb <= gptr < ze)))
+                              al.mailbox_stride[r.shard], int(clean and zb <= gptr < ze),
+                              r.shard if self.device_flow else -1))
         flags = [st.mbox_flags_ptr(sh) for sh in range(st.num_shards)]
         K.mailbox_push(items, al.mailbox_depth, me, flags, publish, self.mbox_seq.data_ptr(),
                        s.counter.data_ptr(), self.mbox_host.data_ptr() if publish else None,
                        st.step_ctrl if publish else None, s.step_dev.data_ptr() if publish else None,
                        sink=self._sink(s) if (publish and self._uses_sink(s)
                                               and not getattr(s, "reported", False)) else None,
-                       my_hdr=st.mirror_base if (publish and self.use_mirror) else None)
+                       my_hdr=st.mirror_base if self.use_mirror else None)
 
     def _drain_local(self, s: StepState) -> None:
         """Device-driven owner-side apply: drain the mailboxes of the shard(s) living in this process
@@ -1104,6 +1128,8 @@ class B200StepRunner:
     def _mbox_consumed(self) -> int:
         """min over owners of how many of MY gradients they have applied (host-side read)."""
         st, me = self.store, self.worker_id
+        if self.use_mirror:     # one local copy: the owners keep these words fresh in my mirror's header
+            return int(st.mirror_hdr_u32(L.MIRROR_OFF_CONSUMED, st.num_shards).min())
         return min(int(st._d2h(st.mbox_flags_ptr(sh) + L.MBOX_OFF_CONSUMED + 4 * me, 4, np.uint32)[0])
                    for sh in range(st.num_shards))
 
@@ -1133,8 +1159,15 @@ class B200StepRunner:
 
     def _mbox_admit(self) -> None:
         """Called right before a training step is enqueued: push k reuses the mailbox buffer of
-        push k - depth, which the owners must have applied. Bounds staleness to ``depth`` pushes."""
-        self._mbox_wait(self._pushes + 1 - self.store.arena.mailbox_depth)
+        push k - depth, which the owners must have applied. Bounds staleness to ``depth`` pushes.
+        With mirrors the push kernels enforce this themselves on the device (they poll the
+        consumed[] words the owners keep fresh in this worker's mirror header), so the host just
+        counts; it only holds back when it is a whole ``max_queue`` of steps ahead of the device."""
+        if self.device_flow:
+            if self._pushes - self._min_consumed > self.max_queue:
+                self._mbox_wait(self._pushes + 1 - self.max_queue)
+        else:
+            self._mbox_wait(self._pushes + 1 - self.store.arena.mailbox_depth)
         self._pushes += 1
 
     def flush_pushes(self) -> None:
@@ -1387,23 +1420,36 @@ class B200StepRunner:
         if x.dtype not in (np.uint8, np.float32):
             x = x.astype(np.float32)
         s = self._state(B, top is not None, x.reshape(B, -1), y)
+        prof = self.host_prof
+        t_a = time.perf_counter() if prof is not None else 0.0
         with nvtx_range("dtf/stage_inputs"):
             self._stage(s, x.reshape(B, -1), y)
+        t_b = time.perf_counter() if prof is not None else 0.0
         with nvtx_range("dtf/launch_step"):
             if top is not None:
                 if self.use_mailbox:
                     self._mbox_admit()
+                t_c = time.perf_counter() if prof is not None else 0.0
                 s.res_expected += 1
                 self._launch(s)
             else:
+                t_c = t_b
                 with torch.cuda.stream(self.stream):
                     self._enqueue_step(s)
+        t_d = time.perf_counter() if prof is not None else 0.0
         sink = top is not None and self._uses_sink(s)
         with nvtx_range("dtf/wait_step"):
             if sink:
                 self._wait_result(s)
             else:
                 self.stream.synchronize()
+        if prof is not None:
+            t_e = time.perf_counter()
+            prof["stage"] += t_b - t_a
+            prof["admit"] += t_c - t_b
+            prof["launch"] += t_d - t_c
+            prof["wait"] += t_e - t_d
+            prof["n"] += 1
         if sink:
             loss_val = np.float32(s.res_f32[0])
             step_val = int(s.res_u64[1])
@@ -1435,11 +1481,17 @@ class B200StepRunner:
         exp = s.res_expected & 0xffffffff
         wait = L.lib().dtf_host_wait_u32
         ptr = s.res_pin.data_ptr() + 4          # word 1 = sequence number
+        waited = 0
         while wait(ptr, exp, 200000) != 0:
             if self.stream.query():                # drained without reporting: surface the error
                 self.stream.synchronize()
                 if int(s.res_u32[1]) != exp:
                     raise RuntimeError("training step finished without reporting its results")
+            waited += 1
+            if waited % 10 == 0 and self.health_every > 0:
+                # two seconds without a result: a step may be parked in its device-side flow control
+                # behind an owner that died; ask the control plane (raises AbortedError if so)
+                self.check_health()
 
     def _as_step(self, step: int):
         gs = G.get_global_step(self.graph)
@@ -1532,6 +1584,15 @@ class B200StepRunner:
                     self._enqueue_step(s)
 
     def close(self) -> None:
+        if self.use_mirror and self.store is not None and self.store.mirror_base:
+            # release kernels of mine that are parked in device-side flow control (dead owner)
+            try:
+                lib = L.lib()
+                one = (C.c_uint * 1)(1)
+                L.check(lib.dtf_memcpy_h2d(self.store.mirror_base + L.MIRROR_OFF_ABORT, one, 4, None), "h2d")
+                L.check(lib.dtf_stream_sync(None), "sync")
+            except Exception:
+                pass
         try:
             self.stream.synchronize()
         except Exception:

@@ -134,7 +134,7 @@ class CopyItem(C.Structure):
 class MboxPushItem(C.Structure):
     """Mirror of ``dtf_mbox_push_item``."""
     _fields_ = [("src", C.c_void_p), ("dst0", C.c_void_p), ("bytes", C.c_longlong),
-                ("buf_stride", C.c_longlong), ("zero_src", C.c_int), ("reserved", C.c_int)]
+                ("buf_stride", C.c_longlong), ("zero_src", C.c_int), ("owner", C.c_int)]
 
 
 MAX_MBOX_ITEMS = 64
@@ -145,7 +145,7 @@ MBOX_OFF_LOCK, MBOX_OFF_PAUSED, MBOX_OFF_DRAINS, MBOX_OFF_APPLIED, MBOX_OFF_MIRR
 # worker mirror header (dtf_mirror_hdr, 512 bytes at offset 0 of every worker mirror)
 MIRROR_HDR_BYTES = 512
 MIRROR_MAX_SHARDS = 32
-MIRROR_OFF_GLOBAL_STEP, MIRROR_OFF_EPOCH, MIRROR_OFF_VERSION, MIRROR_OFF_CONSUMED = 0, 8, 128, 256
+MIRROR_OFF_GLOBAL_STEP, MIRROR_OFF_EPOCH, MIRROR_OFF_ABORT, MIRROR_OFF_VERSION, MIRROR_OFF_CONSUMED = 0, 8, 12, 128, 256
 
 
 class DrainMirrorItem(C.Structure):

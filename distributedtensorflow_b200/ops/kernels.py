@@ -199,7 +199,8 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
     """Worker side of the "owner applies" push (csrc/kernels/mailbox.cu).
 
     items: (src_ptr, dst0_ptr, nbytes, buf_stride[, zero_src]) — gradient slice -> its place in MY
-    buffer 0 on the owning shard (zero_src: clear the source after reading it). ``publish`` makes the last CTA release the sequence number to every owner in
+    buffer 0 on the owning shard (zero_src: clear the source after reading it; owner: the owning
+    shard, which with ``my_hdr`` turns on device-side flow control). ``publish`` makes the last CTA release the sequence number to every owner in
     ``owner_flags`` (pointers to their ``dtf_mbox_flags``)."""
     n = len(items)
     chunks = [items[i:i + L.MAX_MBOX_ITEMS] for i in range(0, n, L.MAX_MBOX_ITEMS)] or [[]]
@@ -210,6 +211,7 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
             s, d, b, st = item[:4]
             arr[i].src, arr[i].dst0, arr[i].bytes, arr[i].buf_stride = s, d, b, st
             arr[i].zero_src = int(item[4]) if len(item) > 4 else 0
+            arr[i].owner = int(item[5]) if len(item) > 5 else -1
         last = publish and ci == len(chunks) - 1
         if not chunk and not last:
             continue
@@ -217,7 +219,7 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
                                       int(last), seq, block_counter, min_consumed_out if last else None,
                                       ctrl_step if last else None, step_out if last else None,
                                       C.byref(sink) if (sink is not None and last) else None,
-                                      my_hdr if last else None, L.current_stream())
+                                      my_hdr, L.current_stream())
         L.check(rc, "dtf_mailbox_push")
         _count()
 

@@ -264,7 +264,9 @@ typedef struct dtf_mbox_flags {               /* 512 bytes, zero = idle */
 typedef struct dtf_mirror_hdr {               /* 512 bytes at offset 0 of every worker mirror */
   unsigned long long global_step;             /* +0   last value broadcast by the step-owning shard */
   unsigned int epoch;                         /* +8   sync mode: completed rounds */
-  unsigned int pad0[29];
+  unsigned int abort;                         /* +12  set by the worker's host: kernels of this worker that
+                                                      wait on this header give up (teardown / recovery) */
+  unsigned int pad0[28];
   unsigned int version[DTF_MIRROR_MAX_SHARDS];   /* +128 shard s: gradients applied (all workers) when it
                                                          last rewrote this mirror; stored after the data */
   unsigned int consumed[DTF_MIRROR_MAX_SHARDS];  /* +256 shard s: how many of THIS worker's pushes it applied */
@@ -286,7 +288,7 @@ typedef struct dtf_mbox_push_item {
   long long buf_stride;   /* bytes from buffer b to buffer b + 1 of the same worker on that shard */
   int zero_src;           /* store 0 back into src after reading it (src is an atomically accumulated
                              buffer that must be clear for the next step: no fill kernel trails the step) */
-  int reserved;
+  int owner;              /* shard that owns the slice (index into dtf_mirror_hdr.consumed), or -1 */
 } dtf_mbox_push_item;
 /* Copies every item into buffer (*seq % depth) of the caller's mailboxes. With publish = 1 the
  * last CTA then stores produced[worker_id] = *seq + 1 on EVERY owner (owner_flags[0..n_owners)),
@@ -295,7 +297,11 @@ typedef struct dtf_mbox_push_item {
  * With ctrl_step / step_out it also reads the shared global_step into *step_out (local u64).
  * my_hdr (optional): this worker's mirror header; consumed[] and global_step are then read from
  * it (local memory, kept fresh by the owners' drains; owner i of owner_flags is shard i) instead
- * of over NVLink. Several non-publishing calls followed by one publishing call form one push. */
+ * of over NVLink. When every item also names its owner (item.owner >= 0) flow control moves onto
+ * the device: before a CTA overwrites buffer (*seq % depth) it waits until
+ * my_hdr->consumed[owner] >= *seq - depth + 1 (watchdog-guarded spin on local memory), so the host
+ * may enqueue pushes without waiting. Several non-publishing calls followed by one publishing
+ * call form one push. */
 int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, int depth, int worker_id,
                      dtf_mbox_flags* const* owner_flags, int n_owners, int publish,
                      unsigned int* seq, unsigned int* block_counter,

@@ -757,6 +757,51 @@ def test_mailbox_drain_broadcasts_into_worker_mirrors(K, cols, ld):
     assert int(minc.item()) == 0          # min over header consumed[0..3]: shards 0..2 never wrote theirs
 
 
+def test_mailbox_push_device_flow_control_waits_for_the_owner(K):
+    """Bounded staleness on the device: a push that would overwrite a buffer its owner has not
+    consumed yet parks (polling consumed[] in the worker's own mirror header) until the owner's
+    drain moves that word - or until the worker's host raises the abort word."""
+    import time
+    from distributedtensorflow_b200.ops import _lib as L
+    dev = "cuda"
+    depth, owner, n = 2, 5, 4096
+    hdr = torch.zeros(128, dtype=torch.int32, device=dev)
+    flags = torch.zeros(128, dtype=torch.int32, device=dev)
+    slots = torch.zeros(depth * n, device=dev)
+    seq = torch.zeros(1, dtype=torch.int32, device=dev)
+    pc = torch.zeros(4, dtype=torch.int32, device=dev)
+    minc = torch.zeros(1, dtype=torch.int32, device=dev)
+    grads = [torch.full((n,), float(k + 1), device=dev) for k in range(4)]
+    side, poke = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def push(k):
+        with torch.cuda.stream(side):
+            K.mailbox_push([(grads[k].data_ptr(), slots.data_ptr(), n * 4, n * 4, 0, owner)], depth, 0,
+                           [flags.data_ptr()], True, seq.data_ptr(), pc.data_ptr(), minc.data_ptr(),
+                           my_hdr=hdr.data_ptr())
+
+    push(0)
+    push(1)                       # buffers 0 and 1: nothing to wait for
+    side.synchronize()
+    assert slots[:n].eq(1).all() and slots[n:].eq(2).all() and seq.item() == 2
+    push(2)                       # buffer 0 again: needs consumed[owner] >= 1
+    time.sleep(0.05)
+    assert not side.query() and slots[:n].eq(1).all()
+    with torch.cuda.stream(poke):
+        hdr[L.MIRROR_OFF_CONSUMED // 4 + owner] = 1
+    poke.synchronize()
+    side.synchronize()
+    assert slots[:n].eq(3).all() and seq.item() == 3
+    push(3)                       # buffer 1: needs consumed >= 2; the host gives up instead
+    time.sleep(0.05)
+    assert not side.query()
+    with torch.cuda.stream(poke):
+        hdr[L.MIRROR_OFF_ABORT // 4] = 1
+    poke.synchronize()
+    side.synchronize()
+    assert seq.item() == 4
+
+
 @pytest.mark.parametrize("B,H,dense", [(128, 1024, False), (100, 100, True), (37, 300, False)])
 def test_head_fused_matches_separate_ops(K, B, H, dense):
     """logits + softmax-xent + dlogits + bias grads + masked dX of the last layer in one kernel,
