@@ -216,7 +216,7 @@ def main() -> int:
             model_name = "mnist_cnn (run_mnist_distributed.py:46-70)"
         else:
             y1h = None
-            raise SystemExit("--model mlp is benchmarked by bench/step_time.py")
+            raise SystemExit("--model mlp is benchmarked by bench/ps_bench.py --model mlp")
 
     cfg = tf.ConfigProto(allow_soft_placement=True, backend="b200", device="cuda:%d" % local_rank,
                          cuda_graph=not args.no_cuda_graph, pdl=bool(args.pdl and not args.no_pdl),

@@ -2,8 +2,8 @@ cd $GRAFT_REPO_ROOT
 N=${1:-2}
 mkdir -p gpurun_out
 export DTF_B200_HANG_DUMP=100
-timeout 200 python -m pytest tests/test_kernels_gpu.py -x -q -k "mailbox" 2>&1 | tail -3
-timeout 300 python -m pytest tests/test_executor_gpu.py -x -q 2>&1 | tail -3
+
+
 run() {
   tag=$1; shift
   timeout 170 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29700 bench.py --gpus $N --steps 200 --warmup 10 "$@" > gpurun_out/bench_n${N}_$tag.log 2>&1
@@ -16,4 +16,4 @@ for l in sys.stdin:
   grep -q '^{' gpurun_out/bench_n${N}_$tag.log || tail -40 gpurun_out/bench_n${N}_$tag.log
 }
 run dflt
-run hostflow --opt device_flow=0
+

@@ -218,6 +218,8 @@ push_apply_kernel(const __grid_constant__ ApplyArgs a) {
 // loss and step number to the host while the rest of the backward pass is still running.
 __global__ void step_report_kernel(dtf_ps_ctrl* ctrl_step, int worker_id, int bump,
                                    unsigned long long* step_out, dtf_result_sink sink) {
+  griddep_wait();      // launched through launch_kernel(): honour the PDL contract (common.cuh)
+  griddep_launch();
   if (threadIdx.x != 0) return;
   unsigned long long step;
   if (bump) {
@@ -274,6 +276,8 @@ extern "C" int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_ite
               n_items, DTF_MAX_APPLY_ITEMS);
   DTF_REQUIRE(!finish || (ctrl_for_step != nullptr && block_counter != nullptr),
               "push_apply: finish needs ctrl_for_step and block_counter");
+  DTF_REQUIRE(!(sink != nullptr && finish == 2),
+              "push_apply: finish = 2 (results already reported by dtf_step_report) takes no result sink");
   DTF_REQUIRE(opt != DTF_OPT_ADAM || ctrl_for_powers != nullptr,
               "push_apply: Adam needs the control block that owns the beta powers");
   ApplyArgs a;
@@ -346,9 +350,9 @@ extern "C" int dtf_refresh_shadow(const float* var, void* shadow, long long n, l
 // bytes, which every GPU that loads the library keeps until the process exits.
 //
 // Rules that follow from sharing one array:
-//   * the first call on a device looks up the array's device address (cudaGetSymbolAddress, with
-//     that device current) and caches it; make that first call before starting any stream
-//     capture on that device;
+//   * every call looks up the array's device address (cudaGetSymbolAddress, with the target
+//     device current); the first call on a device also loads the module, so make that first call
+//     before starting any stream capture on that device;
 //   * every call clears the counter on `stream` before its kernel, because the array keeps
 //     whatever the previous call (or an aborted launch) left in it;
 //   * two calls whose kernels overlap on one GPU — different streams, or different host threads —
@@ -365,26 +369,22 @@ constexpr int kStaticMaxDevices = 64;
 // In host code this name is only a handle for cudaGetSymbolAddress; it is NOT a device pointer.
 static __device__ __align__(256) unsigned int g_push_apply_static_scratch[kStaticScratchWords];
 
-static unsigned int* g_static_scratch_dev_ptr[kStaticMaxDevices];  // per device, filled lazily
-
+// Resolved on EVERY call: the address belongs to the current context's instance of this module, so
+// a pointer remembered per device ordinal would go stale after cudaDeviceReset or under a caller's
+// own (non-primary) context. After the first call on a device - which loads the module and therefore
+// belongs before any stream capture - this is a host-side table lookup.
 static int static_scratch_for_current_device(unsigned int** out) {
   int dev = -1;
   DTF_CHECK_CUDA(cudaGetDevice(&dev));
   DTF_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "push_apply_static: device %d out of range", dev);
-  unsigned int* p = __atomic_load_n(&g_static_scratch_dev_ptr[dev], __ATOMIC_ACQUIRE);
-  if (p == nullptr) {
-    void* addr = nullptr;
-    cudaError_t e = cudaGetSymbolAddress(&addr, g_push_apply_static_scratch);
-    if (e != cudaSuccess || addr == nullptr) {
-      set_error("push_apply_static: cudaGetSymbolAddress failed on device %d: %s", dev,
-                cudaGetErrorString(e));
-      return -1;
-    }
-    p = static_cast<unsigned int*>(addr);
-    // concurrent first calls resolve the same address, so a plain publish is enough
-    __atomic_store_n(&g_static_scratch_dev_ptr[dev], p, __ATOMIC_RELEASE);
+  void* addr = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&addr, g_push_apply_static_scratch);
+  if (e != cudaSuccess || addr == nullptr) {
+    set_error("push_apply_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+              cudaGetErrorString(e));
+    return -1;
   }
-  *out = p;
+  *out = static_cast<unsigned int*>(addr);
   return 0;
 }
 

@@ -27,11 +27,18 @@ HOST_LIB = LIB_DIR / "libdtf_b200_host.so"
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
-    "--use_fast_math",
     "-Xcompiler", "-fPIC",
     "-Xcompiler", "-fvisibility=default",
     "--expt-relaxed-constexpr",
 ]
+# --use_fast_math only where it is harmless (GEMM / conv epilogues). The optimizer rules and the
+# losses are built with IEEE division, sqrt and expf and without flush-to-zero: they decide what goes
+# into a checkpoint, they are bandwidth- or latency-bound, and approximate math buys them nothing.
+PRECISE_SOURCES = {"apply.cu", "mailbox.cu", "sync_step.cu", "softmax_xent.cu", "head_fused.cu"}
+
+
+def nvcc_flags_for(src: Path) -> list:
+    return NVCC_FLAGS if src.name in PRECISE_SOURCES else NVCC_FLAGS + ["--use_fast_math"]
 
 
 def _nvcc() -> str:
@@ -65,7 +72,7 @@ def _stale(lib: Path, digest: str) -> bool:
 
 def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     srcs = cuda_sources()
-    digest = _digest(srcs, " ".join(NVCC_FLAGS))
+    digest = _digest(srcs, " ".join(NVCC_FLAGS) + "|precise:" + ",".join(sorted(PRECISE_SOURCES)))
     if not force and not _stale(CUDA_LIB, digest):
         return CUDA_LIB
     LIB_DIR.mkdir(parents=True, exist_ok=True)
@@ -77,7 +84,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     for s in srcs:
         o = obj_dir / (s.stem + ".o")
         objs.append(o)
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(s), "-o", str(o)]
+        cmd = [nvcc, *nvcc_flags_for(s), "-c", str(s), "-o", str(o)]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

@@ -70,6 +70,15 @@ class ConditionalAccumulator:
             self._global_step += 1
             return avg
 
+    def wait_ready(self, num_required: int, deadline: Optional[float]) -> None:
+        """Block until ``num_required`` gradients are accumulated WITHOUT consuming them."""
+        with self._cv:
+            while self._count < num_required:
+                remaining = None if deadline is None else deadline - time.monotonic()
+                if remaining is not None and remaining <= 0:
+                    raise TimeoutError("take_grad timed out")
+                self._cv.wait(remaining if remaining is not None else 1.0)
+
     def set_global_step(self, new_step: int) -> None:
         with self._cv:
             if new_step > self._global_step:
@@ -503,7 +512,13 @@ class PsShard:
                          powers: Optional[Dict[str, float]], timeout: Optional[float] = None) -> int:
         """The chief's sync_op as it executes ON this PS: block until ``num_required`` fresh
         gradients were accumulated for every listed variable, apply their mean once."""
-        grads = {n: self.accumulators[n].take_grad(num_required, timeout).numpy() for n in names}
+        # all-or-nothing for the shard: first wait (consuming nothing) until EVERY listed accumulator
+        # holds enough gradients, then take them. A timeout half-way can therefore never discard the
+        # means already taken and advance only some accumulators' step.
+        deadline = None if timeout is None else time.monotonic() + timeout
+        for n in names:
+            self.accumulators[n].wait_ready(num_required, deadline)
+        grads = {n: self.accumulators[n].take_grad(num_required, None).numpy() for n in names}
         self.push_apply(spec, grads, powers)
         return len(grads)
 

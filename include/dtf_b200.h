@@ -204,8 +204,11 @@ int dtf_step_report(dtf_ps_ctrl* ctrl_for_step, int worker_id, int bump, unsigne
  * Meant for a PS task whose whole HBM budget is already committed to its shard arena, for a host
  * thread that must not enter cudaMalloc (a device-wide synchronisation) while worker kernels are
  * in flight, and for foreign runtimes that reach this library only through the C ABI.
- *   - The first call on each device resolves the array's address (that device must be current);
- *     issue it before any stream capture on that device.
+ *   - Every call looks the array's address up for the current device and context (nothing is
+ *     remembered across calls, so cudaDeviceReset or a caller-owned context cannot leave a stale
+ *     pointer behind). The FIRST call on a device also loads the module: issue it before any
+ *     stream capture on that device.
+ *   - Unlike dtf_push_apply, a call with n_items == 0 (a finish-only call) is refused.
  *   - The counter is cleared on `stream` by every call; the array otherwise keeps the previous
  *     call's contents.
  *   - All calls on one GPU share the array: calls whose kernels overlap there race. Keep them
