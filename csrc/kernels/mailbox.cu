@@ -45,6 +45,7 @@ struct MboxPushArgs {
   dtf_result_sink sink;
   const dtf_mirror_hdr* my_hdr;
   const dtf_mirror_hdr* flow_hdr;   // device-side flow control against this header's consumed[]
+  const unsigned int* sync_tag;     // sync mode: local_step of this gradient (device word) or NULL
 };
 
 __global__ void __launch_bounds__(MBOX_THREADS)
@@ -127,6 +128,9 @@ mailbox_push_kernel(const __grid_constant__ MboxPushArgs a) {
   if (!s_last) return;
   if (static_cast<int>(threadIdx.x) < a.n_owners) {
     dtf_mbox_flags* f = a.owner_flags[threadIdx.x];
+    if (a.sync_tag != nullptr)   // ordered before produced[] by the release below
+      *reinterpret_cast<volatile unsigned int*>(buf == 0 ? &f->tag0[a.worker_id] : &f->tag1[a.worker_id]) =
+          *reinterpret_cast<const volatile unsigned int*>(a.sync_tag);
     st_release_sys_u32(&f->produced[a.worker_id], seq + 1u);
     // how far has this owner got with MY gradients (flow control for the next pushes): from my
     // mirror's header when the owners keep one fresh (local read), else over NVLink
@@ -186,6 +190,48 @@ __global__ void mailbox_snapshot_kernel(dtf_mbox_flags* flags, unsigned int* tod
   todo[w] = t;
 }
 
+// Synchronous variant (see dtf_mailbox_drain_sync): classifies every worker's oldest pending
+// gradient as fresh (tag == epoch) or stale (tag < epoch). todo[w] = 1 + buffer for the fresh ones
+// when at least R are pending (they are averaged and applied once), todo[16] = lock held,
+// todo[17] = bit mask of stale gradients to retire unapplied, todo[18] = number of fresh ones applied.
+__global__ void mailbox_snapshot_sync_kernel(dtf_mbox_flags* flags, const dtf_ps_ctrl* ctrl,
+                                             unsigned int* todo, int n_workers, int R) {
+  griddep_wait();
+  griddep_launch();
+  const int w = threadIdx.x;
+  unsigned int claimed = 0;
+  if (w == 0) {
+    if (*reinterpret_cast<volatile unsigned int*>(&flags->paused) == 0)
+      claimed = (atomicCAS(&flags->lock, 0u, 1u) == 0u) ? 1u : 0u;
+    __threadfence();
+  }
+  claimed = __shfl_sync(0xffffffffu, claimed, 0);
+  const unsigned int epoch = *reinterpret_cast<const volatile unsigned int*>(&ctrl->epoch);
+  bool fresh = false, stale = false;
+  unsigned int buf = 0;
+  if (claimed && w < n_workers && w < DTF_MAX_WORKERS) {
+    const unsigned int p = ld_acquire_sys_u32(&flags->produced[w]);
+    const unsigned int c = *reinterpret_cast<volatile unsigned int*>(&flags->consumed[w]);
+    if (static_cast<int>(p - c) > 0) {
+      buf = c & 1u;
+      const unsigned int tag =
+          *reinterpret_cast<volatile unsigned int*>(buf == 0 ? &flags->tag0[w] : &flags->tag1[w]);
+      fresh = tag == epoch;
+      stale = static_cast<int>(tag - epoch) < 0;
+    }
+  }
+  const unsigned int fresh_mask = __ballot_sync(0xffffffffu, fresh);
+  const unsigned int stale_mask = __ballot_sync(0xffffffffu, stale);
+  const int n_fresh = __popc(fresh_mask);
+  const bool apply = n_fresh >= R && n_fresh > 0;
+  if (w < DTF_MAX_WORKERS) todo[w] = (fresh && apply) ? buf + 1u : 0u;
+  if (w == 0) {
+    todo[DTF_MAX_WORKERS] = claimed;
+    todo[DTF_MAX_WORKERS + 1] = stale_mask;
+    todo[DTF_MAX_WORKERS + 2] = apply ? static_cast<unsigned int>(n_fresh) : 0u;
+  }
+}
+
 constexpr int DRAIN_THREADS = 256;
 constexpr int DRAIN_VEC = 4;                                           // one float4 per access, lane-contiguous
 constexpr int DRAIN_UNROLL = 4;                                        // independent vectors per thread
@@ -207,6 +253,7 @@ struct DrainArgs {
   int n_workers;
   int bcast;              // mirror[] is valid: broadcast into flags->mirror_base[*]
   int shard;
+  int mean;               // synchronous round: average the pending gradients, apply once, advance the epoch
   unsigned long long* step_out;
   unsigned int* block_counter;
 };
@@ -320,8 +367,11 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
                             __uint_as_float(r.w));
       }
     }
-    // phase 2: apply the pending gradients in worker order; gradient k + 1 is in flight while
-    // gradient k is applied
+    // phase 2: apply the pending gradients in worker order (synchronous round: sum them and apply
+    // their mean once); gradient k + 1 is in flight while gradient k is consumed
+    float4 acc[DRAIN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < DRAIN_UNROLL; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
     for (int k = 0; k < n_pending; ++k) {
       const float lr_t = s_lr[k];
@@ -340,6 +390,24 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
         }
       }
       const float s = a.h.grad_scale;
+      if (a.mean) {
+#pragma unroll
+        for (int u = 0; u < DRAIN_UNROLL; ++u) {
+          acc[u].x += g4[u].x; acc[u].y += g4[u].y; acc[u].z += g4[u].z; acc[u].w += g4[u].w;
+        }
+        if (k + 1 == n_pending) {
+          const float sm = s / static_cast<float>(n_pending);
+          const float lr0 = s_lr[0];
+#pragma unroll
+          for (int u = 0; u < DRAIN_UNROLL; ++u) {
+            if (!full[u]) continue;
+            update_one<OPT>(acc[u].x * sm, v4[u].x, m4[u].x, u4[u].x, a.h, lr0);
+            update_one<OPT>(acc[u].y * sm, v4[u].y, m4[u].y, u4[u].y, a.h, lr0);
+            update_one<OPT>(acc[u].z * sm, v4[u].z, m4[u].z, u4[u].z, a.h, lr0);
+            update_one<OPT>(acc[u].w * sm, v4[u].w, m4[u].w, u4[u].w, a.h, lr0);
+          }
+        }
+      } else {
 #pragma unroll
       for (int u = 0; u < DRAIN_UNROLL; ++u) {
         if (!full[u]) continue;
@@ -347,6 +415,7 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
         update_one<OPT>(g4[u].y * s, v4[u].y, m4[u].y, u4[u].y, a.h, lr_t);
         update_one<OPT>(g4[u].z * s, v4[u].z, m4[u].z, u4[u].z, a.h, lr_t);
         update_one<OPT>(g4[u].w * s, v4[u].w, m4[u].w, u4[u].w, a.h, lr_t);
+      }
       }
       if (k + 1 < n_pending) {
 #pragma unroll
@@ -388,9 +457,16 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
           float v = it.var[i + j];
           float s0 = (OPT != DTF_OPT_SGD) ? it.slot0[i + j] : 0.f;
           float s1 = (OPT == DTF_OPT_ADAM) ? it.slot1[i + j] : 0.f;
-          for (int k = 0; k < n_pending; ++k)
-            update_one<OPT>(*reinterpret_cast<const volatile float*>(it.grad + s_off[k] + i + j) *
-                                a.h.grad_scale, v, s0, s1, a.h, s_lr[k]);
+          if (a.mean) {
+            float gs = 0.f;
+            for (int k = 0; k < n_pending; ++k)
+              gs += *reinterpret_cast<const volatile float*>(it.grad + s_off[k] + i + j);
+            update_one<OPT>(gs * (a.h.grad_scale / static_cast<float>(n_pending)), v, s0, s1, a.h, s_lr[0]);
+          } else {
+            for (int k = 0; k < n_pending; ++k)
+              update_one<OPT>(*reinterpret_cast<const volatile float*>(it.grad + s_off[k] + i + j) *
+                                  a.h.grad_scale, v, s0, s1, a.h, s_lr[k]);
+          }
           it.var[i + j] = v;
           if (OPT != DTF_OPT_SGD) it.slot0[i + j] = s0;
           if (OPT == DTF_OPT_ADAM) it.slot1[i + j] = s1;
@@ -425,22 +501,27 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
   __syncthreads();
   if (!s_last) return;
   const bool holds_lock = a.todo[DTF_MAX_WORKERS] != 0u;
+  const unsigned int drop_mask = a.mean ? a.todo[DTF_MAX_WORKERS + 1] : 0u;   // stale: retire unapplied
   if (threadIdx.x == 0) {
     unsigned long long step = 0;
     if (n_pending > 0) {
+      const int n_applies = a.mean ? 1 : n_pending;   // a synchronous round is ONE apply of the mean
       if (OPT == DTF_OPT_ADAM) {
         volatile float* b1 = &a.ctrl_powers->beta1_power;
         volatile float* b2 = &a.ctrl_powers->beta2_power;
         float p1 = *b1, p2 = *b2;
-        for (int k = 0; k < n_pending; ++k) { p1 *= a.h.beta1; p2 *= a.h.beta2; }
+        for (int k = 0; k < n_applies; ++k) { p1 *= a.h.beta1; p2 *= a.h.beta2; }
         *b1 = p1;
         *b2 = p2;
       }
       if (a.ctrl_step != nullptr) {
-        step = atom_add_u64_sys(&a.ctrl_step->global_step, static_cast<unsigned long long>(n_pending)) +
-               static_cast<unsigned long long>(n_pending);
-        atomicAdd(&a.ctrl_step->apply_count, static_cast<unsigned int>(n_pending));
+        step = atom_add_u64_sys(&a.ctrl_step->global_step, static_cast<unsigned long long>(n_applies)) +
+               static_cast<unsigned long long>(n_applies);
+        atomicAdd(&a.ctrl_step->apply_count, static_cast<unsigned int>(n_applies));
       }
+      if (a.mean)
+        *reinterpret_cast<volatile unsigned int*>(&a.ctrl_powers->epoch) =
+            *reinterpret_cast<volatile unsigned int*>(&a.ctrl_powers->epoch) + 1u;
       *reinterpret_cast<volatile unsigned int*>(&a.flags->drains) =
           *reinterpret_cast<volatile unsigned int*>(&a.flags->drains) + 1u;
       *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total) =
@@ -457,12 +538,12 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
   __syncthreads();
   // one thread per worker: retire its gradient (the mailbox buffer may be overwritten by worker w
   // from here on) and refresh its mirror's header - what the worker would otherwise read over NVLink
-  if (n_pending > 0 && static_cast<int>(threadIdx.x) < DTF_MAX_WORKERS) {
+  if ((n_pending > 0 || drop_mask != 0u) && static_cast<int>(threadIdx.x) < DTF_MAX_WORKERS) {
     const int w = threadIdx.x;
-    const bool drained = w < a.n_workers && a.todo[w] != 0u;
+    const bool drained = w < a.n_workers && (a.todo[w] != 0u || ((drop_mask >> w) & 1u) != 0u);
     unsigned int c = *reinterpret_cast<volatile unsigned int*>(&a.flags->consumed[w]);
     if (drained) {
-      if (a.ctrl_step != nullptr)
+      if (a.ctrl_step != nullptr && n_pending > 0)
         *reinterpret_cast<volatile unsigned long long*>(&a.ctrl_step->heartbeat[w]) = s_step;
       c += 1u;
       st_release_sys_u32(&a.flags->consumed[w], c);
@@ -472,11 +553,15 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
     if (b != 0ull) {
       dtf_mirror_hdr* hdr = reinterpret_cast<dtf_mirror_hdr*>(b);
       *reinterpret_cast<volatile unsigned int*>(&hdr->consumed[a.shard]) = c;
-      if (a.ctrl_step != nullptr)
-        *reinterpret_cast<volatile unsigned long long*>(&hdr->global_step) = s_step;
-      // the release fence orders every CTA's data stores (GPU-scope fences + the election) first
-      st_release_sys_u32(&hdr->version[a.shard],
-                         *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total));
+      if (n_pending > 0) {
+        if (a.ctrl_step != nullptr)
+          *reinterpret_cast<volatile unsigned long long*>(&hdr->global_step) = s_step;
+        // the release fence orders every CTA's data stores (GPU-scope fences + the election) first;
+        // asynchronous: gradients applied so far, synchronous: rounds completed (the worker's token)
+        st_release_sys_u32(&hdr->version[a.shard],
+                           a.mean ? *reinterpret_cast<volatile unsigned int*>(&a.ctrl_powers->epoch)
+                                  : *reinterpret_cast<volatile unsigned int*>(&a.flags->applied_total));
+      }
     }
   }
   __syncthreads();
@@ -484,6 +569,34 @@ mailbox_drain_kernel(const __grid_constant__ DrainArgs a) {
     __threadfence();
     atomicExch(&a.flags->lock, 0u);
   }
+}
+
+// One thread: wait for this worker's next token (see dtf_sync_token_wait).
+__global__ void sync_token_wait_kernel(const dtf_mirror_hdr* hdr, int n_shards, unsigned int* last_round,
+                                       unsigned int* local_step_out, unsigned long long* step_out) {
+  griddep_wait();
+  griddep_launch();
+  if (threadIdx.x != 0) return;
+  const unsigned int last = *reinterpret_cast<volatile unsigned int*>(last_round);
+  const long long t0 = clock64();
+  unsigned int e;
+  for (;;) {
+    e = 0xffffffffu;
+    for (int s = 0; s < n_shards; ++s)
+      e = min(e, *reinterpret_cast<const volatile unsigned int*>(&hdr->version[s]));
+    if (last == 0xffffffffu || static_cast<int>(e - last) > 0) break;
+    if (*reinterpret_cast<const volatile unsigned int*>(&hdr->abort) != 0u) break;
+    __nanosleep(200);
+    if (clock64() - t0 > 100ll * DTF_WAIT_TIMEOUT_CYCLES) {
+      printf("dtf sync: no token after round %u (slowest shard has completed %u)\n", last, e);
+      __trap();
+    }
+  }
+  __threadfence();   // the parameters the owners stored before version[] are visible to the step
+  *local_step_out = e;
+  *last_round = e;
+  if (step_out != nullptr)
+    *step_out = *reinterpret_cast<const volatile unsigned long long*>(&hdr->global_step);
 }
 
 }  // namespace dtf
@@ -495,7 +608,8 @@ extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, in
                                 int publish, unsigned int* seq, unsigned int* block_counter,
                                 unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
                                 unsigned long long* step_out, const dtf_result_sink* sink,
-                                const dtf_mirror_hdr* my_hdr, void* stream) {
+                                const dtf_mirror_hdr* my_hdr, const unsigned int* sync_tag,
+                                void* stream) {
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_MBOX_ITEMS, "mailbox_push: %d items (max %d)",
               n_items, DTF_MAX_MBOX_ITEMS);
   DTF_REQUIRE(depth >= 1 && seq != nullptr, "mailbox_push: depth %d / seq", depth);
@@ -538,6 +652,8 @@ extern "C" int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, in
   a.min_consumed_out = min_consumed_out;
   a.ctrl_step = ctrl_step;
   a.step_out = step_out;
+  DTF_REQUIRE(sync_tag == nullptr || depth <= 2, "mailbox_push: tagged (synchronous) pushes need depth <= 2, got %d", depth);
+  a.sync_tag = publish ? sync_tag : nullptr;
   a.my_hdr = publish ? my_hdr : nullptr;
   a.flow_hdr = nullptr;
   if (my_hdr != nullptr) {
@@ -566,6 +682,13 @@ extern "C" int dtf_mailbox_drain(int opt, const dtf_apply_item* items, int n_ite
                               ctrl_step, flags, todo, block_counter, step_out, nullptr, 0, 0, stream_);
 }
 
+static int drain_impl(int opt, const dtf_apply_item* items, int n_items, long long slot_stride,
+                      int depth, int n_workers, const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
+                      dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, unsigned int* todo,
+                      unsigned int* block_counter, unsigned long long* step_out,
+                      const dtf_drain_mirror_item* mirror_items, int shard_index, int max_ctas,
+                      int sync_R, void* stream_);
+
 extern "C" int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_items,
                                     long long slot_stride, int depth, int n_workers,
                                     const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
@@ -573,6 +696,37 @@ extern "C" int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_
                                     unsigned int* block_counter, unsigned long long* step_out,
                                     const dtf_drain_mirror_item* mirror_items, int shard_index,
                                     int max_ctas, void* stream_) {
+  return drain_impl(opt, items, n_items, slot_stride, depth, n_workers, hyper, ctrl_powers, ctrl_step,
+                    flags, todo, block_counter, step_out, mirror_items, shard_index, max_ctas, 0, stream_);
+}
+
+extern "C" int dtf_mailbox_drain_sync(int opt, const dtf_apply_item* items, int n_items,
+                                      long long slot_stride, int n_workers, int replicas_to_aggregate,
+                                      const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl, dtf_ps_ctrl* ctrl_step,
+                                      dtf_mbox_flags* flags, unsigned int* todo, unsigned int* block_counter,
+                                      const dtf_drain_mirror_item* mirror_items, int shard_index,
+                                      int max_ctas, void* stream_) {
+  DTF_REQUIRE(replicas_to_aggregate >= 1 && ctrl != nullptr, "mailbox_drain_sync: needs replicas_to_aggregate >= 1 and the shard's control block");
+  return drain_impl(opt, items, n_items, slot_stride, 2, n_workers, hyper, ctrl, ctrl_step, flags, todo,
+                    block_counter, nullptr, mirror_items, shard_index, max_ctas, replicas_to_aggregate, stream_);
+}
+
+extern "C" int dtf_sync_token_wait(const dtf_mirror_hdr* my_hdr, int n_shards, unsigned int* last_round,
+                                   unsigned int* local_step_out, unsigned long long* step_out, void* stream) {
+  DTF_REQUIRE(my_hdr && last_round && local_step_out && n_shards >= 1 && n_shards <= DTF_MIRROR_MAX_SHARDS,
+              "sync_token_wait: bad arguments (%d shards)", n_shards);
+  DTF_CHECK_CUDA(launch_kernel(sync_token_wait_kernel, dim3(1), dim3(32), 0,
+                               reinterpret_cast<cudaStream_t>(stream), my_hdr, n_shards, last_round,
+                               local_step_out, step_out));
+  return 0;
+}
+
+static int drain_impl(int opt, const dtf_apply_item* items, int n_items, long long slot_stride,
+                      int depth, int n_workers, const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
+                      dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, unsigned int* todo,
+                      unsigned int* block_counter, unsigned long long* step_out,
+                      const dtf_drain_mirror_item* mirror_items, int shard_index, int max_ctas,
+                      int sync_R, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "mailbox_drain: %d items (max %d)",
               n_items, DTF_MAX_APPLY_ITEMS);
@@ -621,10 +775,16 @@ extern "C" int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_
   a.n_workers = n_workers;
   a.bcast = mirror_items != nullptr ? 1 : 0;
   a.shard = shard_index;
+  a.mean = sync_R > 0 ? 1 : 0;
   a.step_out = step_out;
   a.block_counter = block_counter;
-  DTF_CHECK_CUDA(launch_kernel(mailbox_snapshot_kernel, dim3(1), dim3(32), 0, stream, flags, todo,
-                               n_workers, depth));
+  if (sync_R > 0) {
+    DTF_CHECK_CUDA(launch_kernel(mailbox_snapshot_sync_kernel, dim3(1), dim3(32), 0, stream, flags,
+                                 static_cast<const dtf_ps_ctrl*>(ctrl_powers), todo, n_workers, sync_R));
+  } else {
+    DTF_CHECK_CUDA(launch_kernel(mailbox_snapshot_kernel, dim3(1), dim3(32), 0, stream, flags, todo,
+                                 n_workers, depth));
+  }
   switch (opt) {
     case DTF_OPT_SGD: DTF_CHECK_CUDA(launch_kernel(mailbox_drain_kernel<DTF_OPT_SGD>, dim3(blocks), dim3(DRAIN_THREADS), 0, stream, a)); break;
     case DTF_OPT_MOMENTUM: DTF_CHECK_CUDA(launch_kernel(mailbox_drain_kernel<DTF_OPT_MOMENTUM>, dim3(blocks), dim3(DRAIN_THREADS), 0, stream, a)); break;

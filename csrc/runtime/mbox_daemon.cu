@@ -31,6 +31,8 @@ struct dtf_mbox_daemon {
   int shard = 0;
   std::atomic<int> backstop_us{0};
   std::atomic<int> max_ctas{0};   // grid cap of the drains (0 = one CTA per chunk)
+  int sync_R = 0;                 // > 0: synchronous rounds (replicas_to_aggregate), see dtf_mailbox_drain_sync
+  unsigned int* host_epoch = nullptr;   // pinned
   int n_items = 0;
   long long slot_stride = 0;
   int depth = 1;
@@ -91,6 +93,9 @@ void daemon_main(dtf_mbox_daemon* d) {
     d->idle.store(0, std::memory_order_release);
     cudaError_t e = cudaMemcpyAsync(d->host_flags, d->flags, sizeof(dtf_mbox_flags),
                                     cudaMemcpyDeviceToHost, d->stream);
+    if (e == cudaSuccess && d->sync_R > 0)
+      e = cudaMemcpyAsync(d->host_epoch, &d->ctrl_powers->epoch, sizeof(unsigned int),
+                          cudaMemcpyDeviceToHost, d->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
     if (e != cudaSuccess) {
       d->fail("apply daemon: polling the mailbox flags failed: %s", cudaGetErrorString(e));
@@ -131,6 +136,36 @@ void daemon_main(dtf_mbox_daemon* d) {
         continue;
       }
     }
+    if (d->sync_R > 0) {
+      // a round is actionable when enough FRESH gradients are pending, or a stale one waits to be retired
+      const unsigned int epoch = *d->host_epoch;
+      int fresh = 0, stale = 0;
+      for (int w = 0; w < d->n_workers; ++w) {
+        const unsigned int c = d->host_flags->consumed[w];
+        if (static_cast<int>(d->host_flags->produced[w] - c) <= 0) continue;
+        const unsigned int tag = (c & 1u) ? d->host_flags->tag1[w] : d->host_flags->tag0[w];
+        if (tag == epoch) ++fresh;
+        else if (static_cast<int>(tag - epoch) < 0) ++stale;
+      }
+      if (fresh < d->sync_R && stale == 0) {
+        if (d->poll_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(d->poll_us));
+        continue;
+      }
+      if (dtf_mailbox_drain_sync(d->opt, d->items, d->n_items, d->slot_stride, d->n_workers, d->sync_R,
+                                 &d->hyper, d->ctrl_powers, d->ctrl_step, d->flags, d->scratch,
+                                 d->scratch + 32, d->has_mirror ? d->mirror : nullptr, d->shard,
+                                 d->max_ctas.load(std::memory_order_relaxed), d->stream) != 0) {
+        d->fail("apply daemon: %s", dtf_last_error());
+        return;
+      }
+      e = cudaStreamSynchronize(d->stream);
+      if (e != cudaSuccess) {
+        d->fail("apply daemon: sync drain kernel failed: %s", cudaGetErrorString(e));
+        return;
+      }
+      d->drains.fetch_add(1, std::memory_order_relaxed);
+      continue;
+    }
     if (n == 0) {
       if (d->poll_us > 0) std::this_thread::sleep_for(std::chrono::microseconds(d->poll_us));
       continue;
@@ -159,7 +194,7 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
                                      dtf_ps_ctrl* ctrl_powers, dtf_ps_ctrl* ctrl_step,
                                      dtf_mbox_flags* flags, int poll_us,
                                      const dtf_drain_mirror_item* mirror_items, int shard_index,
-                                     int backstop_us) {
+                                     int backstop_us, int sync_replicas_to_aggregate) {
   DTF_REQUIRE(out != nullptr && hyper != nullptr && flags != nullptr, "mbox_daemon_start: null argument");
   DTF_REQUIRE(n_items >= 0 && n_items <= DTF_MAX_APPLY_ITEMS, "mbox_daemon_start: %d items (max %d)",
               n_items, DTF_MAX_APPLY_ITEMS);
@@ -176,6 +211,9 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
   for (int i = 0; i < n_items && mirror_items != nullptr; ++i) d->mirror[i] = mirror_items[i];
   d->shard = shard_index;
   d->backstop_us.store(backstop_us > 0 ? backstop_us : 0);
+  d->sync_R = sync_replicas_to_aggregate > 0 ? sync_replicas_to_aggregate : 0;
+  DTF_REQUIRE(d->sync_R == 0 || (ctrl_powers != nullptr && depth <= 2),
+              "mbox_daemon_start: synchronous mode needs the shard's control block and depth <= 2");
   d->n_items = n_items;
   d->slot_stride = slot_stride;
   d->depth = depth;
@@ -189,6 +227,7 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
   cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
   if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&d->stream, cudaStreamNonBlocking, lo);
   if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&d->host_flags), sizeof(dtf_mbox_flags));
+  if (e == cudaSuccess) e = cudaMallocHost(reinterpret_cast<void**>(&d->host_epoch), 64);
   if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void**>(&d->scratch), (DTF_MAX_WORKERS + 48) * 4);
   if (e == cudaSuccess) e = cudaMemset(d->scratch, 0, (DTF_MAX_WORKERS + 48) * 4);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -196,6 +235,7 @@ extern "C" int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt,
     set_error("mbox_daemon_start: %s", cudaGetErrorString(e));
     if (d->scratch) cudaFree(d->scratch);
     if (d->host_flags) cudaFreeHost(d->host_flags);
+    if (d->host_epoch) cudaFreeHost(d->host_epoch);
     if (d->stream) cudaStreamDestroy(d->stream);
     delete d;
     cudaSetDevice(prev);
@@ -260,6 +300,7 @@ extern "C" int dtf_mbox_daemon_stop(dtf_mbox_daemon* d) {
   }
   cudaStreamDestroy(d->stream);
   cudaFreeHost(d->host_flags);
+  cudaFreeHost(d->host_epoch);
   cudaFree(d->scratch);
   if (prev >= 0) cudaSetDevice(prev);
   delete d;

@@ -30,8 +30,18 @@ extern "C" int dtf_arena_alloc(void** ptr_out, size_t bytes) {
   DTF_REQUIRE(ptr_out != nullptr && bytes > 0, "arena_alloc: bad arguments");
   void* p = nullptr;
   DTF_CHECK_CUDA(cudaMalloc(&p, bytes));
-  DTF_CHECK_CUDA(cudaMemset(p, 0, bytes));
-  DTF_CHECK_CUDA(cudaDeviceSynchronize());
+  // Zero it on a private stream and wait for THAT stream only: a device-wide synchronise here would
+  // wait for every kernel on the GPU, including a colocated worker's step that is parked in its
+  // device-side flow control / token wait until the very task that is allocating has joined.
+  cudaStream_t st = nullptr;
+  cudaError_t e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaMemsetAsync(p, 0, bytes, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (st != nullptr) cudaStreamDestroy(st);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    DTF_CHECK_CUDA(e);
+  }
   *ptr_out = p;
   return 0;
 }

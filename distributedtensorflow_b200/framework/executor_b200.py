@@ -374,6 +374,9 @@ class B200StepRunner:
         # doubled the convolutions' time; a few dozen CTAs over a longer window are free
         self.drain_ctas = int(opts.get("drain_ctas", os.environ.get("DTF_B200_DRAIN_CTAS", "64")))
         self.use_mirror = False
+        self.sync_generic = False
+        self.sync_path = str(opts.get("sync_path", os.environ.get("DTF_B200_SYNC_PATH", "auto")))   # auto | mailbox
+        self.sync_token_timeout = float(opts.get("sync_token_timeout", 20.0))
         self.device_flow = False
         self.max_queue = int(opts.get("max_queue", 64))     # steps the host may run ahead of the device
         self.my_shards: List[int] = []
@@ -439,7 +442,19 @@ class B200StepRunner:
         return out
 
     # -- variable lifecycle (called by Session) ---------------------------------------------------
-    handles_sync = True   # SyncReplicasOptimizer rounds run in csrc/kernels/sync_step.cu
+    handles_sync = True   # SyncReplicasOptimizer rounds run in csrc/kernels/sync_step.cu / mailbox.cu
+
+    def _num_workers(self) -> int:
+        if self.cluster is not None and "worker" in self.cluster.jobs:
+            return self.cluster.num_tasks("worker")
+        if self.sync_opt is not None:        # in-process cluster: the optimizer knows how many replicas there are
+            return int(self.sync_opt.total_num_replicas)
+        return 1
+
+    @property
+    def coop_sync(self) -> bool:
+        """Synchronous mode through the one-kernel cooperative round (symmetric topologies)."""
+        return self.sync_opt is not None and not self.sync_generic
 
     def create_variables(self, spec, trainable_names: Sequence[str]) -> None:
         self.spec = spec
@@ -447,20 +462,38 @@ class B200StepRunner:
         top = next((n for n in self.graph.nodes if type(n).__name__ == "TrainOp"), None)
         self.sync_opt = top.sync if top is not None else None
         sync_workers = 0
+        self.sync_generic = False
         if self.sync_opt is not None:
             world = self.client.num_shards
-            nw = self.cluster.num_tasks("worker") if (self.cluster is not None and "worker" in self.cluster.jobs) else 1
-            if nw != world or self.sync_opt.total_num_replicas != world or \
-                    self.sync_opt.replicas_to_aggregate != world:
-                raise NotImplementedError(
-                    "B200 synchronous mode needs one worker colocated with every PS shard and "
-                    "replicas_to_aggregate == total_num_replicas == number of shards (got %d workers, "
-                    "%d shards, aggregate %d of %d); use backend='cpu' for backup-worker mode"
-                    % (nw, world, self.sync_opt.replicas_to_aggregate, self.sync_opt.total_num_replicas))
-            sync_workers = world
+            nw = self._num_workers()
+            # (several worker threads of ONE process share a GPU: two all-SM cooperative kernels cannot
+            # be resident together, so an in-process cluster with more than one worker is not symmetric)
+            symmetric = (nw == world and self.sync_opt.total_num_replicas == world
+                         and self.sync_opt.replicas_to_aggregate == world
+                         and (self.cluster is not None or nw == 1))
+            # The one-kernel cooperative round needs a worker next to every shard and all of them in
+            # every round. Anything else - backup workers (replicas_to_aggregate < total_num_replicas),
+            # PS-only tasks, "1 PS + N workers" - runs the round on the mailboxes: tagged pushes, the
+            # owner's drain averages the fresh gradients and drops stale ones, tokens are epoch words
+            # in the workers' mirror headers (csrc/kernels/mailbox.cu, dtf_mailbox_drain_sync).
+            self.sync_generic = (not symmetric) or self.sync_path == "mailbox"
+            if self.sync_generic:
+                if nw > L.MAX_WORKERS or not self.mirror:
+                    raise NotImplementedError("synchronous mode on the mailboxes supports at most %d workers "
+                                              "and needs worker mirrors" % L.MAX_WORKERS)
+                if self.sync_opt.replicas_to_aggregate > nw:
+                    raise NotImplementedError("replicas_to_aggregate (%d) > number of workers (%d): gradient "
+                                              "accumulation over several steps of one worker is only on the "
+                                              "CPU backend" % (self.sync_opt.replicas_to_aggregate, nw))
+            else:
+                sync_workers = world
         depth, mirrors = 1, True
         self.use_mailbox = False
-        if self.sync_opt is None and spec is not None and self.trainable_names and self.push_mode != "rmw":
+        if self.sync_generic:
+            nw = self._num_workers()
+            self.use_mailbox = True
+            sync_workers, depth, mirrors = nw, 2, False
+        elif self.sync_opt is None and spec is not None and self.trainable_names and self.push_mode != "rmw":
             if self.push_mode not in ("auto", "mailbox"):
                 raise ValueError("push_mode must be 'auto', 'rmw' or 'mailbox' (got %r)" % self.push_mode)
             nw = self.cluster.num_tasks("worker") if (self.cluster is not None and "worker" in self.cluster.jobs) else 1
@@ -481,7 +514,7 @@ class B200StepRunner:
         self.sync_round_no: Optional[int] = None
         self.mirror_filled = False
         self.store.sync_hook = self.stream.synchronize
-        self.use_mirror = bool(self.use_mailbox and self.mirror
+        self.use_mirror = bool(self.use_mailbox and (self.mirror or self.sync_generic)
                                and self.store.num_shards <= L.MIRROR_MAX_SHARDS)
         if self.use_mirror:
             self.store.alloc_mirror()
@@ -600,7 +633,7 @@ class B200StepRunner:
         self.copies: List[Tuple[int, int, int]] = []
         self.wptr: Dict[str, Tuple[int, int]] = {}    # bf16 serving copy: name -> (ptr, ld)
         self.fptr: Dict[str, int] = {}                # fp32 tensor: name -> ptr
-        if self.sync_opt is not None:
+        if self.coop_sync:
             self._setup_params_sync()
             return
         if self.use_mirror:
@@ -865,7 +898,7 @@ class B200StepRunner:
         p = self.plan
         nl = len(p.dense)
         main = torch.cuda.current_stream()
-        sync = self.sync_opt is not None
+        sync = self.coop_sync
         par = self.overlap and not sync
         side = self.side_stream if par else main
         early = self.early_apply
@@ -1044,6 +1077,7 @@ class B200StepRunner:
                         depth=int(al.mailbox_depth), n_workers=int(al.sync_workers), hyper=hyper,
                         owns_step=bool(al.step_shard == sh), flags_off=int(al.mbox_flags_off[sh]),
                         poll_us=int(self.mailbox_poll_us), shard=int(sh),
+                        sync_R=int(self.sync_opt.replicas_to_aggregate) if self.sync_generic else 0,
                         mirror_items=[list(m) for m in mitems] if ml is not None else None)
             self._drain_desc[sh] = desc
             self.client.call(sh, "mbox_start", desc)
@@ -1062,18 +1096,21 @@ class B200StepRunner:
         # next step costs the host one memory read, not a stream sync or a copy
         self.mbox_host = torch.zeros(16, dtype=torch.int32).pin_memory()
         self._mbox_host_np = self.mbox_host.numpy()
-        torch.cuda.synchronize(self.device)
+        torch.cuda.current_stream(self.device).synchronize()   # (never device-wide: see dtf_arena_alloc)
         if self.use_mirror:
             st.register_mirror(me)
         # shards whose arena lives in THIS process on THIS GPU: their drains become nodes of my step graph
         self.my_shards = []
-        if self.graph_drain:
+        if self.sync_generic:
+            # two device words: the round this worker last contributed to (none yet) and its local_step
+            self.sync_words = torch.tensor([-1, 0, 0, 0], dtype=torch.int32, device=self.device)
+        if self.graph_drain and not self.sync_generic:
             self.my_shards = [sh for sh in range(st.num_shards) if st.same_process[sh] and st.is_local[sh]]
             for sh in self.my_shards:
                 self.client.call(sh, "mbox_attach", me, True, self.drain_backstop_us)
             self._drain_scratch = torch.zeros(64 * max(1, len(self.my_shards)), dtype=torch.int32,
                                               device=self.device)
-            torch.cuda.synchronize(self.device)
+            torch.cuda.current_stream(self.device).synchronize()   # (never device-wide: see dtf_arena_alloc)
 
     def _push_vars(self, s: StepState, variables: Sequence[G.Variable], publish: bool) -> None:
         """Posted stores of the gradients into this worker's mailbox on every owning shard;
@@ -1097,7 +1134,8 @@ class B200StepRunner:
                        st.step_ctrl if publish else None, s.step_dev.data_ptr() if publish else None,
                        sink=self._sink(s) if (publish and self._uses_sink(s)
                                               and not getattr(s, "reported", False)) else None,
-                       my_hdr=st.mirror_base if self.use_mirror else None)
+                       my_hdr=st.mirror_base if self.use_mirror else None,
+                       sync_tag=(self.sync_words.data_ptr() + 4) if (publish and self.sync_generic) else None)
 
     def _drain_local(self, s: StepState) -> None:
         """Device-driven owner-side apply: drain the mailboxes of the shard(s) living in this process
@@ -1172,7 +1210,7 @@ class B200StepRunner:
 
     def flush_pushes(self) -> None:
         """Wait until every gradient this worker has pushed is applied (exact global_step reads)."""
-        if self.use_mailbox:
+        if self.use_mailbox and not self.sync_generic:   # (a round may never complete once replicas stop)
             self._mbox_wait(self._pushes)
 
     def _fused_push_spec(self, var: G.Variable) -> Optional[dict]:
@@ -1231,7 +1269,7 @@ class B200StepRunner:
                          max_ctas=0 if finish else self.early_apply_ctas)
 
     def _pull(self, s: StepState) -> None:
-        if self.sync_opt is not None or self.use_mirror:
+        if self.coop_sync or self.use_mirror:
             if self.mirror_filled:
                 return
             self.mirror_filled = True
@@ -1239,7 +1277,7 @@ class B200StepRunner:
                 self._mirror_seed()
         s.pull_late = None
         mark = getattr(self, "late_mark", None)
-        if self.sync_opt is None and self.overlap and mark is not None and len(self.copies) > mark:
+        if not self.coop_sync and self.overlap and mark is not None and len(self.copies) > mark:
             main = torch.cuda.current_stream()
             ev = torch.cuda.Event()
             ev.record(main)
@@ -1269,7 +1307,7 @@ class B200StepRunner:
                 and not (self.fused_apply) and all(d.b is not None for d in self.plan.dense))
 
     def _uses_sink(self, s: StepState) -> bool:
-        return self.host_sink and s.train and self.sync_opt is None
+        return self.host_sink and s.train and not self.coop_sync
 
     def _enqueue_step(self, s: StepState, with_io: bool = True) -> None:
         """Everything one ``sess.run(train_op)`` does on the device, in stream order."""
@@ -1288,9 +1326,14 @@ class B200StepRunner:
                 s.y_ready.record(self.side_stream)
         elif with_io and not s.zero_copy:
             s.io_dev.copy_(s.io_pin, non_blocking=True)
-        clear_end = s.train and self.clear_at_end and self.sync_opt is None
+        clear_end = s.train and self.clear_at_end and not self.coop_sync
         if not clear_end:
             K.fill_u32(s.zero.buf, 0)
+        if s.train and self.sync_generic:
+            # the token: wait (on the device, polling my own mirror header) until the round I last
+            # contributed to is complete on every shard, and adopt the current round as local_step
+            K.sync_token_wait(self.store.mirror_base, self.store.num_shards, self.sync_words.data_ptr(),
+                              self.sync_words.data_ptr() + 4, None)
         drain_ev = None
         if s.train and self.my_shards and self.use_mailbox and self.drain_at == "start":
             # the owner-side apply of whatever the workers have published, beside the forward pass
@@ -1316,7 +1359,7 @@ class B200StepRunner:
                 self._drain_local(s)
         if with_io and not self._uses_sink(s):
             s.out_pin[:1].copy_(s.z["loss"][:1], non_blocking=True)
-            if self.sync_opt is None or not s.train:
+            if not self.coop_sync or not s.train:
                 s.step_pin.copy_(s.step_dev, non_blocking=True)
         if clear_end and not self._self_cleans(s):
             # the accumulators were consumed by the applies above: clearing them now (instead of at
@@ -1361,7 +1404,7 @@ class B200StepRunner:
         np.copyto(yn, y.reshape(yn.shape), casting="unsafe")
 
     def _launch(self, s: StepState) -> None:
-        sync = self.sync_opt is not None and s.train
+        sync = self.coop_sync and s.train
         if s.graph_exec and not sync:
             # hot path: one cudaGraphLaunch on our stream, no Python stream-context bookkeeping
             if self._graph_launch(s.graph_exec, self._stream_handle) != 0:
@@ -1488,10 +1531,35 @@ class B200StepRunner:
                 if int(s.res_u32[1]) != exp:
                     raise RuntimeError("training step finished without reporting its results")
             waited += 1
+            if self.sync_generic and waited * 0.2 >= self.sync_token_timeout and waited % 5 == 0:
+                self._sync_token_expired(waited * 0.2)
             if waited % 10 == 0 and self.health_every > 0:
                 # two seconds without a result: a step may be parked in its device-side flow control
                 # behind an owner that died; ask the control plane (raises AbortedError if so)
                 self.check_health()
+
+    def _sync_token_expired(self, waited_s: float) -> None:
+        """A synchronous step has been waiting for its token for a long time. If every other replica
+        has finished training the round can never complete: end this replica's training the way TF
+        does when the token queue is closed (OutOfRangeError = clean stop for MonitoredSession).
+        Otherwise keep waiting up to ``mailbox_timeout`` and then give the session a chance to recover."""
+        from ..parallel.ps_core import AbortedError, OutOfRangeError
+        st, lib = self.store, L.lib()
+        done = np.zeros(L.MAX_WORKERS, np.uint32)
+        L.check(lib.dtf_memcpy_d2h(done.ctypes.data_as(C.c_void_p),
+                                   st.mbox_flags_ptr(st.arena.step_shard) + L.MBOX_OFF_DONE, done.nbytes, None), "d2h")
+        L.check(lib.dtf_stream_sync(None), "sync")
+        nw = int(st.arena.sync_workers)
+        others_done = all(done[w] != 0 for w in range(nw) if w != self.worker_id)
+        if not others_done and waited_s < self.mailbox_timeout:
+            return
+        one = (C.c_uint * 1)(1)     # release my parked kernels, then let the stream drain
+        L.check(lib.dtf_memcpy_h2d(st.mirror_base + L.MIRROR_OFF_ABORT, one, 4, None), "h2d")
+        L.check(lib.dtf_stream_sync(None), "sync")
+        self.stream.synchronize()
+        if others_done:
+            raise OutOfRangeError("synchronization token queue closed: every other replica has finished")
+        raise AbortedError("no synchronization token for %.0f s (worker %d)" % (waited_s, self.worker_id))
 
     def _as_step(self, step: int):
         gs = G.get_global_step(self.graph)

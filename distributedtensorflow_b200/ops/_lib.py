@@ -140,6 +140,7 @@ class MboxPushItem(C.Structure):
 MAX_MBOX_ITEMS = 64
 MBOX_FLAGS_BYTES = 512
 MBOX_OFF_PRODUCED, MBOX_OFF_CONSUMED, MBOX_OFF_DONE = 0, 128, 256
+MBOX_OFF_TAG0, MBOX_OFF_TAG1 = 64, 192
 MBOX_OFF_LOCK, MBOX_OFF_PAUSED, MBOX_OFF_DRAINS, MBOX_OFF_APPLIED, MBOX_OFF_MIRROR_BASE = 320, 324, 328, 332, 384
 
 # worker mirror header (dtf_mirror_hdr, 512 bytes at offset 0 of every worker mirror)
@@ -209,13 +210,16 @@ def _declare(lib):
         "dtf_set_pdl": [i],
         "dtf_sync_round": [i, vp, i, i, i, C.c_uint, C.POINTER(ApplyHyper), C.POINTER(C.c_ulonglong), vp, vp, i, vp],
         "dtf_mailbox_push": [C.POINTER(MboxPushItem), i, i, i, C.POINTER(vp), i, i, vp, vp, vp, vp, vp,
-                             C.POINTER(ResultSink), vp, vp],
+                             C.POINTER(ResultSink), vp, vp, vp],
         "dtf_mailbox_drain_ex": [i, C.POINTER(ApplyItem), i, C.c_longlong, i, i, C.POINTER(ApplyHyper), vp, vp,
                                  vp, vp, vp, vp, C.POINTER(DrainMirrorItem), i, i, vp],
         "dtf_mailbox_drain": [i, C.POINTER(ApplyItem), i, C.c_longlong, i, i, C.POINTER(ApplyHyper), vp, vp,
                               vp, vp, vp, vp, vp],
         "dtf_mbox_daemon_start": [C.POINTER(vp), i, i, C.POINTER(ApplyItem), i, C.c_longlong, i, i,
-                                  C.POINTER(ApplyHyper), vp, vp, vp, i, C.POINTER(DrainMirrorItem), i, i],
+                                  C.POINTER(ApplyHyper), vp, vp, vp, i, C.POINTER(DrainMirrorItem), i, i, i],
+        "dtf_mailbox_drain_sync": [i, C.POINTER(ApplyItem), i, C.c_longlong, i, i, C.POINTER(ApplyHyper), vp, vp,
+                                   vp, vp, vp, C.POINTER(DrainMirrorItem), i, i, vp],
+        "dtf_sync_token_wait": [vp, i, vp, vp, vp, vp],
         "dtf_mbox_daemon_set_backstop": [vp, i],
         "dtf_mbox_daemon_set_max_ctas": [vp, i],
         "dtf_mbox_daemon_pause": [vp, i],

@@ -195,7 +195,7 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
                  publish: bool, seq: int, block_counter: Optional[int],
                  min_consumed_out: Optional[int], ctrl_step: Optional[int] = None,
                  step_out: Optional[int] = None, sink: Optional[L.ResultSink] = None,
-                 my_hdr: Optional[int] = None) -> None:
+                 my_hdr: Optional[int] = None, sync_tag: Optional[int] = None) -> None:
     """Worker side of the "owner applies" push (csrc/kernels/mailbox.cu).
 
     items: (src_ptr, dst0_ptr, nbytes, buf_stride[, zero_src]) — gradient slice -> its place in MY
@@ -219,9 +219,28 @@ def mailbox_push(items: Sequence[tuple], depth: int, worker_id: int, owner_flags
                                       int(last), seq, block_counter, min_consumed_out if last else None,
                                       ctrl_step if last else None, step_out if last else None,
                                       C.byref(sink) if (sink is not None and last) else None,
-                                      my_hdr, L.current_stream())
+                                      my_hdr, sync_tag if last else None, L.current_stream())
         L.check(rc, "dtf_mailbox_push")
         _count()
+
+
+def mailbox_drain_sync(opt: int, items, n_items: int, slot_stride: int, n_workers: int, replicas_to_aggregate: int,
+                       hyper: L.ApplyHyper, ctrl: int, ctrl_step: Optional[int], flags: int, todo: int,
+                       block_counter: int, mirror_items=None, shard_index: int = 0, max_ctas: int = 0) -> None:
+    """One synchronous-round attempt on a shard (snapshot + drain): retires stale gradients, and when
+    ``replicas_to_aggregate`` fresh ones are pending applies their mean once and advances the epoch."""
+    rc = L.lib().dtf_mailbox_drain_sync(opt, items, n_items, slot_stride, n_workers, replicas_to_aggregate,
+                                        C.byref(hyper), ctrl, ctrl_step, flags, todo, block_counter,
+                                        mirror_items, shard_index, int(max_ctas), L.current_stream())
+    L.check(rc, "dtf_mailbox_drain_sync")
+    _count(2)
+
+
+def sync_token_wait(my_hdr: int, n_shards: int, last_round: int, local_step_out: int,
+                    step_out: Optional[int]) -> None:
+    rc = L.lib().dtf_sync_token_wait(my_hdr, n_shards, last_round, local_step_out, step_out, L.current_stream())
+    L.check(rc, "dtf_sync_token_wait")
+    _count()
 
 
 def make_mirror_items(entries: Sequence[tuple]) -> "C.Array":

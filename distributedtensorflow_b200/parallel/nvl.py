@@ -327,7 +327,7 @@ class NvlStore:
             if r.shadow_off is not None:
                 K.refresh_shadow(self.var_ptr(r), self.shadow_ptr(r), r.sl.n, 0, r.cols, r.shadow_ld)
         import torch
-        torch.cuda.synchronize()
+        torch.cuda.current_stream().synchronize()
 
     def write_slot(self, name: str, slot: int, value) -> None:
         for r in self.arena.regions[name]:

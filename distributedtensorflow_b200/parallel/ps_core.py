@@ -300,7 +300,8 @@ class PsShard:
                                            base if desc["owns_step"] else None,
                                            base + int(desc["flags_off"]), int(desc.get("poll_us", 20)),
                                            mirror_items, int(desc.get("shard", self.task_index)),
-                                           int(getattr(self, "_mbox_backstop_us", 0)))
+                                           int(getattr(self, "_mbox_backstop_us", 0)),
+                                           int(desc.get("sync_R", 0) or 0))
             L.check(rc, "dtf_mbox_daemon_start")
             self._mbox_daemon = handle
             self._mbox_sig = sig

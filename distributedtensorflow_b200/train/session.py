@@ -134,7 +134,9 @@ class Session:
         self.config = config or ConfigProto()
         self.target = target or ""
         self._closed = False
-        self.worker_id = 0
+        # task index of this worker; an in-process (local://) cluster has no addresses to derive it from,
+        # so several worker threads of one process name themselves with ConfigProto(task_index=i)
+        self.worker_id = int((getattr(self.config, 'b200_options', None) or {}).get('task_index', 0))
         self.cluster: Optional[ClusterSpec] = None
         self._own_local: Optional[LocalCluster] = None
         self.ps_client: PsClient = self._connect()

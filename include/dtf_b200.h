@@ -237,9 +237,9 @@ int dtf_push_apply_static(int opt, const dtf_apply_item* items, int n_items,
  * ------------------------------------------------------------------------------------------ */
 typedef struct dtf_mbox_flags {               /* 512 bytes, zero = idle */
   unsigned int produced[DTF_MAX_WORKERS];     /* +0   worker w: gradients published so far (st.release.sys) */
-  unsigned int pad0[16];
-  unsigned int consumed[DTF_MAX_WORKERS];     /* +128 owner: gradients of worker w applied so far */
-  unsigned int pad1[16];
+  unsigned int tag0[DTF_MAX_WORKERS];         /* +64  sync mode: local_step of the gradient in worker w's buffer 0 */
+  unsigned int consumed[DTF_MAX_WORKERS];     /* +128 owner: gradients of worker w applied (or dropped) so far */
+  unsigned int tag1[DTF_MAX_WORKERS];         /* +192 sync mode: ... in buffer 1 (synchronous mailboxes are 2 deep) */
   unsigned int done[DTF_MAX_WORKERS];         /* +256 worker w has finished training */
   unsigned int lock;                          /* +320 a drain is in flight (device-scope CAS: every drain of a
                                                       shard runs on the shard's GPU, whoever launches it) */
@@ -303,14 +303,16 @@ typedef struct dtf_mbox_push_item {
  * of over NVLink. When every item also names its owner (item.owner >= 0) flow control moves onto
  * the device: before a CTA overwrites buffer (*seq % depth) it waits until
  * my_hdr->consumed[owner] >= *seq - depth + 1 (watchdog-guarded spin on local memory), so the host
- * may enqueue pushes without waiting. Several non-publishing calls followed by one publishing
- * call form one push. */
+ * may enqueue pushes without waiting. sync_tag (optional, device word; needs depth <= 2): the
+ * publishing CTA first stores *sync_tag - the local_step this gradient was computed at - into
+ * tag{buffer}[worker_id] of every owner (see dtf_mailbox_drain_sync). Several non-publishing
+ * calls followed by one publishing call form one push. */
 int dtf_mailbox_push(const dtf_mbox_push_item* items, int n_items, int depth, int worker_id,
                      dtf_mbox_flags* const* owner_flags, int n_owners, int publish,
                      unsigned int* seq, unsigned int* block_counter,
                      unsigned int* min_consumed_out, const dtf_ps_ctrl* ctrl_step,
                      unsigned long long* step_out, const dtf_result_sink* sink,
-                     const dtf_mirror_hdr* my_hdr, void* stream);
+                     const dtf_mirror_hdr* my_hdr, const unsigned int* sync_tag, void* stream);
 /* Owner side, two launches: (1) claim the shard's drain lock and snapshot which workers have an
  * unconsumed gradient (at most one per worker per call, the oldest) into `todo` (local scratch,
  * DTF_MAX_WORKERS + 1 words; nothing is claimed while flags->paused or another drain holds the
@@ -340,6 +342,33 @@ int dtf_mailbox_drain_ex(int opt, const dtf_apply_item* items, int n_items, long
                          unsigned long long* step_out, const dtf_drain_mirror_item* mirror_items,
                          int shard_index, int max_ctas, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Synchronous rounds on the same mailboxes (SyncReplicasOptimizer with backup workers and PS-only
+ * tasks; templates/00_mnist_replica.py:60-63,169-191). A worker pushes ONE gradient per token,
+ * tagged with its local_step. The owner's drain in sync mode looks at every worker's oldest
+ * pending gradient: one whose tag is older than the shard's epoch (= rounds completed) is stale
+ * and is retired without being applied (TF's ConditionalAccumulator drops it the same way); when
+ * at least `replicas_to_aggregate` fresh gradients (tag == epoch) are pending, ALL fresh ones are
+ * averaged and applied ONCE, the epoch advances, global_step (step owner) grows by one, and the
+ * new parameters + epoch reach every worker's mirror (version[shard] = epoch). Workers wait for
+ * their next token with dtf_sync_token_wait: a spin on their own mirror header.
+ * ------------------------------------------------------------------------------------------ */
+int dtf_mailbox_drain_sync(int opt, const dtf_apply_item* items, int n_items, long long slot_stride,
+                           int n_workers, int replicas_to_aggregate, const dtf_apply_hyper* hyper,
+                           dtf_ps_ctrl* ctrl /* this shard's: beta powers + epoch */,
+                           dtf_ps_ctrl* ctrl_step /* or NULL */, dtf_mbox_flags* flags,
+                           unsigned int* todo /* DTF_MAX_WORKERS + 4 words */,
+                           unsigned int* block_counter,
+                           const dtf_drain_mirror_item* mirror_items, int shard_index, int max_ctas,
+                           void* stream);
+/* Token wait: returns (on the stream) once every shard 0..n_shards-1 has completed more rounds than
+ * *last_round - i.e. the round this worker last contributed to is over - or at once when
+ * *last_round is 0xffffffff (first step). Stores the round to compute next (min over shards of
+ * version[]) into *local_step_out, which the step's pushes pass as sync_tag, and into *last_round. */
+int dtf_sync_token_wait(const dtf_mirror_hdr* my_hdr, int n_shards, unsigned int* last_round,
+                        unsigned int* local_step_out, unsigned long long* step_out, void* stream);
+
+
 /* Host-side spin on a pinned word written by a kernel (see dtf_result_sink): 0 = reached
  * `expected`, 1 = timeout. */
 int dtf_host_wait_u32(const unsigned int* word, unsigned int expected, long long timeout_us);
@@ -361,7 +390,7 @@ int dtf_mbox_daemon_start(dtf_mbox_daemon** out, int device, int opt, const dtf_
                           const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_powers,
                           dtf_ps_ctrl* ctrl_step, dtf_mbox_flags* flags, int poll_us,
                           const dtf_drain_mirror_item* mirror_items, int shard_index,
-                          int backstop_us);
+                          int backstop_us, int sync_replicas_to_aggregate /* 0 = asynchronous */);
 int dtf_mbox_daemon_set_backstop(dtf_mbox_daemon* d, int backstop_us);
 int dtf_mbox_daemon_set_max_ctas(dtf_mbox_daemon* d, int max_ctas);   /* grid cap of its drains, 0 = none */
 int dtf_mbox_daemon_pause(dtf_mbox_daemon* d, int pause);   /* 1: returns once parked; 0: resume */

@@ -291,3 +291,118 @@ def test_owner_pushes_mirror_drain_at_start_counts_every_apply():
 def _bf16_round(a):
     import torch
     return torch.from_numpy(np.ascontiguousarray(a)).to(torch.bfloat16).float().numpy()
+
+
+# ---------------------------------------------------------------------------------------------
+# synchronous rounds on the mailboxes: PS-only tasks, backup workers (csrc/kernels/mailbox.cu)
+# ---------------------------------------------------------------------------------------------
+def _sync_run(backend, n_workers, replicas, steps, num_ps=1, slow_worker=None, options=None, stop_at=None):
+    """``n_workers`` worker threads of one process against ``num_ps`` PS shards: the reference
+    template's topology (templates/00_mnist_replica.py:80-83: one PS, two workers) on one GPU."""
+    import threading
+    import time
+    import distributedtensorflow_b200 as tf
+    from distributedtensorflow_b200.models import mnist_mlp
+    tf.reset_default_graph()
+    tf.set_random_seed(0)
+    cluster = tf.train.ClusterSpec({"ps": ["h:%d" % i for i in range(num_ps)],
+                                    "worker": ["w:%d" % i for i in range(n_workers)]})
+    strategy = tf.train.FlatSlicedStrategy(num_ps) if num_ps > 1 else None
+    with tf.device(tf.train.replica_device_setter(worker_device="/job:worker/task:0", cluster=cluster,
+                                                  ps_strategy=strategy)):
+        X = tf.placeholder(tf.float32, [None, 784])
+        Y = tf.placeholder(tf.float32, [None, 10])
+        gs, loss, _ = mnist_mlp.build_model(X, Y, 100)
+        opt = tf.train.SyncReplicasOptimizer(tf.train.AdamOptimizer(0.001), replicas_to_aggregate=replicas,
+                                             total_num_replicas=n_workers)
+        train_op = opt.minimize(loss, global_step=gs)
+    server = tf.train.Server.create_local_server(num_ps=num_ps)
+    names = [v.name for v in tf.trainable_variables()]
+    out, errs, seen = {}, [], {}
+    t_start = time.time()
+    # The worker threads of this test share ONE GPU. Pinned-memory and device allocations wait for every
+    # kernel on the device, including another worker's step parked in its token wait, so every worker
+    # finishes its first step (which allocates its state and cannot block: it needs no token) before
+    # any worker starts a second one. Real deployments run one worker process per GPU.
+    first_step_done = threading.Barrier(n_workers)
+    opts = dict(cuda_graph=False, mailbox_timeout=25.0, sync_token_timeout=5.0)
+    opts.update(options or {})
+
+    def worker(i):
+        try:
+            from distributedtensorflow_b200.data import mnist
+            imgs, labels = mnist.synthetic_arrays(4 * 100, seed=50 + i)
+            x = imgs.astype(np.float32) / 255.0
+            y = np.eye(10, dtype=np.float32)[labels]
+            hooks = [opt.make_session_run_hook(i == 0, num_tokens=0)]
+            if stop_at is not None:
+                hooks.append(tf.train.StopAtStepHook(last_step=stop_at))
+            cfg = tf.ConfigProto(backend=backend, device="cuda:0" if backend == "b200" else None,
+                                 task_index=i, **(opts if backend == "b200" else {}))
+            steps_done, last_g = 0, 0
+            with tf.train.MonitoredTrainingSession(master=server.target, is_chief=(i == 0), hooks=hooks,
+                                                   config=cfg, recovery_wait_secs=0.01) as sess:
+                while (steps_done < steps) if stop_at is None else (not sess.should_stop()):
+                    k = steps_done % 4
+                    if slow_worker == i:
+                        time.sleep(0.03)
+                    _, l, g = sess.run([train_op, loss, gs], feed_dict={X: x[k * 100:(k + 1) * 100],
+                                                                        Y: y[k * 100:(k + 1) * 100]})
+                    steps_done += 1
+                    last_g = int(g)
+                    if steps_done == 1 and backend == "b200":
+                        first_step_done.wait(60)
+                raw = sess._tf_sess()
+                if i == 0 and raw is not None:
+                    if backend == "b200":
+                        raw._runner.stream.synchronize()
+                        time.sleep(0.05)          # the last round's apply runs on the PS daemon
+                        out.update({n: raw._runner.store.read_variable(n) for n in names})
+                        out["__global_step__"] = raw._runner.store.read_global_step()
+                        out["__generic__"] = raw._runner.sync_generic
+                    else:
+                        out.update(raw.ps_client.pull_all(raw.layout, names))
+            seen[i] = (steps_done, last_g)
+        except Exception as e:  # pragma: no cover
+            import traceback
+            traceback.print_exc()
+            errs.append(e)
+    ts = [threading.Thread(target=worker, args=(i,), daemon=True) for i in range(n_workers)]
+    [t.start() for t in ts]
+    [t.join(180) for t in ts]
+    server.stop()
+    assert not errs, errs
+    assert not any(t.is_alive() for t in ts), "a worker thread is stuck"
+    return out, seen
+
+
+@pytest.mark.parametrize("num_ps", [1, 2])
+def test_sync_on_mailboxes_ps_only_topology_matches_cpu_sync_replicas(num_ps):
+    """The MLP template's own topology - PS task(s) without a worker, two workers, all replicas
+    aggregated - on the device path: tagged pushes, the PS daemon's mean+apply, epoch tokens."""
+    steps = 8
+    got, seen = _sync_run("b200", 2, 2, steps, num_ps=num_ps)
+    ref, _ = _sync_run("cpu", 2, 2, steps, num_ps=num_ps)
+    assert got.pop("__generic__") is True
+    assert got.pop("__global_step__") == steps            # ONE global step per aggregated round
+    for name, r in ref.items():
+        diff = np.abs(got[name] - r)
+        assert float(diff.mean()) < 2e-3 and float(diff.max()) < 0.03, (name, float(diff.mean()), float(diff.max()))
+
+
+def test_sync_on_mailboxes_backup_worker_is_dropped_not_waited_for():
+    """replicas_to_aggregate=2 of 3 replicas, one of them slow: rounds complete with the two fast
+    gradients, the straggler's arrive stale and are retired unapplied, and when the others have
+    stopped the straggler's token wait ends like a closed token queue (clean stop)."""
+    import time
+    t0 = time.time()
+    got, seen = _sync_run("b200", 3, 2, steps=None, slow_worker=2, stop_at=12,
+                          options={"sync_token_timeout": 1.0})
+    assert got.pop("__generic__") is True
+    gstep = got.pop("__global_step__")
+    assert 12 <= gstep <= 14, gstep
+    fast = seen[0][0] + seen[1][0]
+    assert seen[0][0] >= 10 and seen[1][0] >= 10           # the fast replicas took part in (almost) every round
+    assert seen[2][0] < seen[0][0]                         # the straggler contributed to fewer
+    assert all(np.isfinite(v).all() for v in got.values())
+    assert time.time() - t0 < 120
