@@ -206,6 +206,13 @@ def main() -> int:
                 path = sv.save(raw, os.path.join(args.ckpt_dir, "model.ckpt"), global_step=final_step)
                 extra["ckpt_save_s"] = round(time.perf_counter() - t_s, 4)
                 extra["ckpt_bytes"] = sv.last_save_bytes
+                extra["ckpt_write_gbs"] = round(sv.last_save_bytes / max(extra["ckpt_save_s"], 1e-9) / 1e9, 3)
+                t_r = time.perf_counter()
+                from distributedtensorflow_b200.train import saver as S_
+                _t = S_.load_checkpoint_tensors(path)
+                extra["ckpt_read_s"] = round(time.perf_counter() - t_r, 4)
+                extra["ckpt_read_gbs"] = round(sum(v.nbytes for v in _t.values()) / max(extra["ckpt_read_s"], 1e-9) / 1e9, 3)
+                del _t
                 from distributedtensorflow_b200.ckpt import BundleReader
                 with BundleReader(path) as r:
                     extra["ckpt_shards"] = r.num_shards

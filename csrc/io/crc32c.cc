@@ -90,6 +90,45 @@ extern "C" uint32_t dtf_crc32c_extend(uint32_t crc, const void* data, size_t n) 
 
 extern "C" uint32_t dtf_crc32c(const void* data, size_t n) { return dtf_crc32c_extend(0, data, n); }
 
+// crc32c(A || B) from crc32c(A), crc32c(B) and len(B): multiplication by x^(8 len2) modulo the
+// Castagnoli polynomial, done with GF(2) matrix squaring (the scheme zlib uses for crc32_combine).
+// Lets every PS task checksum the slice of a tensor it wrote while the chief, which writes the index,
+// never touches the bytes.
+namespace {
+uint32_t gf2_times(const uint32_t* mat, uint32_t vec) {
+  uint32_t sum = 0;
+  for (int i = 0; vec; vec >>= 1, ++i)
+    if (vec & 1) sum ^= mat[i];
+  return sum;
+}
+void gf2_square(uint32_t* square, const uint32_t* mat) {
+  for (int n = 0; n < 32; ++n) square[n] = gf2_times(mat, mat[n]);
+}
+}  // namespace
+
+extern "C" uint32_t dtf_crc32c_combine(uint32_t crc1, uint32_t crc2, uint64_t len2) {
+  if (len2 == 0) return crc1;
+  uint32_t even[32], odd[32];
+  odd[0] = 0x82F63B78u;  // reflected Castagnoli polynomial: the operator for one zero bit
+  uint32_t row = 1;
+  for (int n = 1; n < 32; ++n) {
+    odd[n] = row;
+    row <<= 1;
+  }
+  gf2_square(even, odd);  // two zero bits
+  gf2_square(odd, even);  // four zero bits
+  do {                    // apply len2 zero BYTES to crc1
+    gf2_square(even, odd);
+    if (len2 & 1) crc1 = gf2_times(even, crc1);
+    len2 >>= 1;
+    if (len2 == 0) break;
+    gf2_square(odd, even);
+    if (len2 & 1) crc1 = gf2_times(odd, crc1);
+    len2 >>= 1;
+  } while (len2 != 0);
+  return crc1 ^ crc2;
+}
+
 extern "C" uint32_t dtf_crc32c_mask(uint32_t crc) {
   return ((crc >> 15) | (crc << 17)) + 0xa282ead8u;
 }

@@ -237,6 +237,65 @@ extern "C" int dtf_bundle_writer_finish(dtf_bundle_writer* w) {
   return rc;
 }
 
+// Index-only writer: the data shards were written elsewhere (every PS task pwrite()s the bytes it
+// owns straight into the final data files, in parallel); the chief only records where each tensor
+// lives. crc32c is the UNMASKED checksum of the whole tensor (see dtf_crc32c_combine).
+struct dtf_bundle_index_writer {
+  std::string prefix;
+  int num_shards = 1;
+  std::map<std::string, Entry> entries;
+};
+
+extern "C" dtf_bundle_index_writer* dtf_bundle_index_open(const char* prefix, int num_shards) {
+  if (num_shards < 1) {
+    set_error("bundle index: %d data shards", num_shards);
+    return nullptr;
+  }
+  auto* w = new dtf_bundle_index_writer();
+  w->prefix = prefix;
+  w->num_shards = num_shards;
+  return w;
+}
+
+extern "C" int dtf_bundle_index_add(dtf_bundle_index_writer* w, const char* name, int dtype, int ndim,
+                                    const int64_t* dims, int shard_id, int64_t offset, int64_t size,
+                                    uint32_t crc32c) {
+  if (w->entries.count(name)) {
+    set_error("tensor %s added twice", name);
+    return -1;
+  }
+  if (shard_id < 0 || shard_id >= w->num_shards || offset < 0 || size < 0) {
+    set_error("tensor %s: shard %d / offset %lld / size %lld out of range", name, shard_id,
+              static_cast<long long>(offset), static_cast<long long>(size));
+    return -1;
+  }
+  Entry e;
+  e.dtype = dtype;
+  e.dims.assign(dims, dims + ndim);
+  e.shard_id = shard_id;
+  e.offset = offset;
+  e.size = size;
+  e.crc = dtf_crc32c_mask(crc32c);
+  w->entries[name] = e;
+  return 0;
+}
+
+extern "C" int dtf_bundle_index_data_path(dtf_bundle_index_writer* w, int shard_id, char* buf, size_t cap) {
+  const std::string p = data_filename(w->prefix, shard_id, w->num_shards);
+  if (p.size() + 1 > cap) {
+    set_error("data file name does not fit");
+    return -1;
+  }
+  memcpy(buf, p.c_str(), p.size() + 1);
+  return 0;
+}
+
+extern "C" int dtf_bundle_index_finish(dtf_bundle_index_writer* w) {
+  const int rc = write_index(w->prefix, w->num_shards, w->entries) ? 0 : -1;
+  delete w;
+  return rc;
+}
+
 struct dtf_bundle_reader {
   std::string prefix;
   int num_shards = 0;

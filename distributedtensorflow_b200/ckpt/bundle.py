@@ -54,6 +54,43 @@ class BundleWriter:
             self.finish()
 
 
+class BundleIndexWriter:
+    """Writes only ``<prefix>.index``: the data shards were written by their owners (every PS task
+    stores the bytes it holds straight into ``<prefix>.data-0000i-of-0000N`` at planned offsets)."""
+
+    def __init__(self, prefix: str, num_shards: int):
+        self._lib = hostlib.lib()
+        self._h = self._lib.dtf_bundle_index_open(os.fsencode(prefix), int(num_shards))
+        if not self._h:
+            raise IOError(hostlib.last_error())
+        self.prefix, self.num_shards = prefix, int(num_shards)
+
+    def data_path(self, shard_id: int) -> str:
+        buf = C.create_string_buffer(4096)
+        hostlib.check(self._lib.dtf_bundle_index_data_path(self._h, int(shard_id), buf, 4096), "data path")
+        return os.fsdecode(buf.value)
+
+    def add(self, name: str, dtype_enum: int, shape: Sequence[int], shard_id: int, offset: int, size: int,
+            crc32c: int) -> None:
+        dims = (C.c_int64 * max(1, len(shape)))(*[int(d) for d in shape])
+        rc = self._lib.dtf_bundle_index_add(self._h, name.encode(), int(dtype_enum), len(shape), dims,
+                                            int(shard_id), int(offset), int(size), int(crc32c) & 0xffffffff)
+        hostlib.check(rc, f"bundle index add {name}")
+
+    def finish(self) -> None:
+        h, self._h = self._h, None
+        hostlib.check(self._lib.dtf_bundle_index_finish(h), "bundle index finish")
+
+
+def crc32c(data) -> int:
+    a = np.ascontiguousarray(data)
+    return int(hostlib.lib().dtf_crc32c(a.ctypes.data_as(C.c_void_p), a.nbytes))
+
+
+def crc32c_combine(crc_a: int, crc_b: int, len_b: int) -> int:
+    return int(hostlib.lib().dtf_crc32c_combine(int(crc_a), int(crc_b), int(len_b)))
+
+
 class BundleReader:
     def __init__(self, prefix: str):
         self._lib = hostlib.lib()

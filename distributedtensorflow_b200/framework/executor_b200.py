@@ -568,6 +568,120 @@ class B200StepRunner:
                 except Exception:
                     pass
 
+    def save_parallel(self, prefix: str, var_names) -> int:
+        """Sharded checkpoint written by the shards themselves. The chief plans where every tensor
+        lives (data file = the variable's home shard, tensors in key order), pre-sizes the data
+        files, and sends every PS task the list of byte ranges of ITS arena to store
+        (``PsShard.save_arena_ops``); all tasks copy and write in parallel and return per-range
+        checksums, which the chief combines into the index it writes last. A flat-sliced variable
+        becomes ONE contiguous tensor of the checkpoint although N tasks wrote it. Returns bytes
+        written. (Reference: templates/00_between_graph_replication_async_mnist.py:43-45.)"""
+        import threading
+        from ..ckpt import bundle as B
+        st, al = self.store, self.store.arena
+        self.stream.synchronize()
+        self.flush_pushes()
+        slot_names = self.spec.slot_names() if self.spec is not None else []
+        n_files = st.num_shards
+        # -- plan ---------------------------------------------------------------------------------
+        tensors: Dict[str, dict] = {}      # key -> dict(shape, nbytes, file, pieces=[(shard, arena_off, first, n)])
+        for name, regs in al.regions.items():
+            if name not in var_names or not regs:
+                continue
+            vl = self.layout[name]
+            regs = sorted(regs, key=lambda r: r.sl.first)
+            keys = [(name, None)] + [(f"{name}/{sn}", i) for i, sn in enumerate(slot_names) if i < len(regs[0].slot_off)]
+            for key, slot in keys:
+                pieces = [(r.shard, r.var_off if slot is None else r.slot_off[slot], r.sl.first, r.sl.n) for r in regs]
+                tensors[key] = dict(shape=tuple(vl.shape), nbytes=vl.num_elements * 4, file=regs[0].shard,
+                                    pieces=pieces, dtype=B.DT_FLOAT)
+        small: Dict[str, np.ndarray] = {}  # scalars that live in control blocks: written by the chief
+        if al.step_var:
+            vl = self.layout[al.step_var]
+            npdt = np.int64 if vl.dtype == "int64" else np.int32
+            small[al.step_var] = (np.asarray(st.read_global_step(), npdt).reshape(vl.shape), al.step_shard)
+        if self.spec is not None and self.spec.kind == "adam":
+            c = st.read_ctrl(al.powers_shard)
+            small["beta1_power"] = (np.asarray(c["beta1_power"], np.float32).reshape(()), al.powers_shard)
+            small["beta2_power"] = (np.asarray(c["beta2_power"], np.float32).reshape(()), al.powers_shard)
+        for key, (arr, shard) in small.items():
+            tensors[key] = dict(shape=tuple(arr.shape), nbytes=arr.nbytes, file=shard, pieces=None, value=arr,
+                                dtype=B._NP_TO_DT[arr.dtype])
+        offsets = [0] * n_files
+        for key in sorted(tensors):
+            t = tensors[key]
+            t["offset"] = offsets[t["file"]]
+            offsets[t["file"]] += t["nbytes"]
+        idx = B.BundleIndexWriter(prefix, n_files)
+        finals = [idx.data_path(i) for i in range(n_files)]
+        tag = ".tmp%d_%x" % (os.getpid(), int(time.time() * 1e6) & 0xffffff)
+        tmps = [p + tag for p in finals]
+        for p_, size in zip(tmps, offsets):
+            with open(p_, "wb") as f:
+                f.truncate(size)
+        ops: List[List[list]] = [[] for _ in range(n_files)]
+        op_keys: List[List[Tuple[str, int]]] = [[] for _ in range(n_files)]
+        for key, t in tensors.items():
+            if t["pieces"] is None:
+                continue
+            for k, (shard, aoff, first, n) in enumerate(t["pieces"]):
+                ops[shard].append([tmps[t["file"]], t["offset"] + first * 4, int(aoff), int(n) * 4])
+                op_keys[shard].append((key, k))
+        # -- every PS task stores its own bytes, all at once ---------------------------------------
+        paused = []
+        results: List[Optional[List[int]]] = [None] * n_files
+        errors: List[BaseException] = []
+        try:
+            if self.use_mailbox:
+                for sh in range(n_files):
+                    self.client.call(sh, "mbox_pause", True)
+                    paused.append(sh)
+
+            def work(sh):
+                try:
+                    results[sh] = self.client.call(sh, "save_arena_ops", ops[sh]) if ops[sh] else []
+                except BaseException as e:      # surfaced below
+                    errors.append(e)
+            threads = [threading.Thread(target=work, args=(sh,), daemon=True) for sh in range(n_files)]
+            [t.start() for t in threads]
+            [t.join() for t in threads]
+        finally:
+            for sh in paused:
+                try:
+                    self.client.call(sh, "mbox_pause", False)
+                except Exception:
+                    pass
+        if errors:
+            for p_ in tmps:
+                try:
+                    os.remove(p_)
+                except OSError:
+                    pass
+            raise errors[0]
+        piece_crc: Dict[Tuple[str, int], int] = {}
+        for sh in range(n_files):
+            for (key, k), crc in zip(op_keys[sh], results[sh]):
+                piece_crc[(key, k)] = int(crc)
+        total = 0
+        for key in sorted(tensors):
+            t = tensors[key]
+            if t["pieces"] is None:
+                raw = np.ascontiguousarray(t["value"]).tobytes()
+                with open(tmps[t["file"]], "r+b") as f:
+                    f.seek(t["offset"])
+                    f.write(raw)
+                crc = B.crc32c(np.frombuffer(raw, np.uint8))
+            else:
+                crc = 0
+                for k, (_shard, _aoff, _first, n) in enumerate(t["pieces"]):
+                    crc = piece_crc[(key, k)] if k == 0 else B.crc32c_combine(crc, piece_crc[(key, k)], n * 4)
+            idx.add(key, t["dtype"], t["shape"], t["file"], t["offset"], t["nbytes"], crc)
+            total += t["nbytes"]
+        for a, b in zip(tmps, finals):
+            os.replace(a, b)
+        idx.finish()
+        return total
+
     def _snapshot_shards(self) -> List[Dict[str, np.ndarray]]:
         st = self.store
         shards: List[Dict[str, np.ndarray]] = [dict() for _ in range(st.num_shards)]

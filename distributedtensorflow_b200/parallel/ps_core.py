@@ -242,6 +242,53 @@ class PsShard:
     def nvl_info(self) -> Optional[dict]:
         return self._arena
 
+    def save_arena_ops(self, ops: Sequence[Sequence]) -> List[int]:
+        """Checkpoint, PS side: this task copies the byte ranges of ITS arena named by ``ops``
+        (``[path, file_offset, arena_offset, nbytes]``) to the host and stores them straight into the
+        (pre-sized) checkpoint data files, all shards doing so in parallel; returns the unmasked
+        crc32c of every range, from which the chief - which never sees the bytes - derives each
+        tensor's checksum (``dtf_crc32c_combine``) for the index. Reference: the sharded saver of
+        templates/00_between_graph_replication_async_mnist.py:43-45, where every PS runs its own SaveV2."""
+        import ctypes as C
+        import os
+        from ..ops import _lib as L
+        from ..utils import hostlib
+        if self._arena is None:
+            raise RuntimeError("save_arena_ops before nvl_alloc")
+        lib, hl = L.lib(), hostlib.lib()
+        L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
+        base = self._arena["ptr"]
+        chunk = 32 << 20
+        stage = getattr(self, "_save_stage", None)
+        if stage is None:
+            p = C.c_void_p()
+            L.check(lib.dtf_host_alloc_pinned(C.byref(p), chunk), "pinned staging buffer")
+            stage = self._save_stage = int(p.value)
+        view = (C.c_ubyte * chunk).from_address(stage)
+        crcs: List[int] = []
+        fds: Dict[str, int] = {}
+        try:
+            for path, foff, aoff, nbytes in ops:
+                fd = fds.get(path)
+                if fd is None:
+                    fd = fds[path] = os.open(path, os.O_WRONLY)
+                crc, done = 0, 0
+                while done < nbytes:
+                    n = min(chunk, int(nbytes) - done)
+                    L.check(lib.dtf_memcpy_d2h(stage, base + int(aoff) + done, n, None), "d2h")
+                    L.check(lib.dtf_stream_sync(None), "sync")
+                    crc = int(hl.dtf_crc32c_extend(crc, stage, n))
+                    mv = memoryview(view)[:n]
+                    wrote = 0
+                    while wrote < n:
+                        wrote += os.pwrite(fd, mv[wrote:], int(foff) + done + wrote)
+                    done += n
+                crcs.append(crc)
+        finally:
+            for fd in fds.values():
+                os.close(fd)
+        return crcs
+
     # -- apply daemon ("owner applies" push, csrc/runtime/mbox_daemon.cu) ---------------------------
     def mbox_start(self, desc: dict) -> dict:
         """Start (once) the native apply daemon on this shard's arena. ``desc`` describes the

@@ -92,7 +92,7 @@ _ALLOWED = {
     "read_scalar", "heartbeat", "accum_create", "accum_apply", "accum_take", "accum_take_apply",
     "accum_set_global_step", "accum_stats", "queue_create", "queue_enqueue_many", "queue_dequeue",
     "queue_size", "queue_close", "snapshot", "declare", "nvl_alloc", "nvl_info", "request_shutdown", "ping", "kv_set", "kv_get",
-    "mbox_start", "mbox_stats", "mbox_pause", "mbox_attach", "mirror_register", "mirror_unregister",
+    "mbox_start", "mbox_stats", "mbox_pause", "mbox_attach", "mirror_register", "mirror_unregister", "save_arena_ops",
 }
 
 

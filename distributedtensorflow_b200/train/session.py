@@ -248,6 +248,10 @@ class Session:
     def save_state(self, prefix: str, var_names, sharded: bool = True) -> int:
         from . import saver as S
         self.ensure_created()
+        if sharded and hasattr(self._runner, "save_parallel") and \
+                (getattr(self.config, "b200_options", None) or {}).get("parallel_save", True):
+            # device arenas: every PS task writes its own bytes, the chief only writes the index
+            return self._runner.save_parallel(prefix, set(var_names) | {"global_step"})
         if hasattr(self._runner, "snapshot_shards"):
             shards = self._runner.snapshot_shards()
         else:

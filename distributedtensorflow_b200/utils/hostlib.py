@@ -25,6 +25,11 @@ def _declare(lib):
         ("dtf_crc32c_mask", u32, [u32]),
         ("dtf_crc32c_unmask", u32, [u32]),
         ("dtf_crc32c_is_accelerated", i, []),
+        ("dtf_crc32c_combine", u32, [u32, u32, C.c_uint64]),
+        ("dtf_bundle_index_open", vp, [cp, i]),
+        ("dtf_bundle_index_add", i, [vp, cp, i, i, C.POINTER(i64), i, i64, i64, u32]),
+        ("dtf_bundle_index_data_path", i, [vp, i, cp, sz]),
+        ("dtf_bundle_index_finish", i, [vp]),
         ("dtf_events_open", vp, [cp, cp]),
         ("dtf_events_filename", cp, [vp]),
         ("dtf_events_write_scalars", i, [vp, C.c_double, i64, i, C.POINTER(cp), C.POINTER(C.c_float)]),

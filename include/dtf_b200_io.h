@@ -23,6 +23,8 @@ uint32_t dtf_crc32c_extend(uint32_t crc, const void* data, size_t n);
 uint32_t dtf_crc32c_mask(uint32_t crc);    /* ((crc >> 15) | (crc << 17)) + 0xa282ead8 */
 uint32_t dtf_crc32c_unmask(uint32_t masked);
 int dtf_crc32c_is_accelerated(void);
+/* crc32c(A || B) from crc32c(A), crc32c(B) and len(B) (both unmasked). */
+uint32_t dtf_crc32c_combine(uint32_t crc_a, uint32_t crc_b, uint64_t len_b);
 
 /* TensorBoard event file writer: <prefix>.out.tfevents.<unix time>.<hostname>. The first record
  * is Event{file_version: "brain.Event:2"}. */
@@ -53,6 +55,20 @@ int dtf_bundle_writer_finish(dtf_bundle_writer* w); /* writes <prefix>.index, fr
  * <merged_prefix>.data-0000i-of-0000N (data files are renamed, indices re-written). */
 int dtf_bundle_merge(const char* const* part_prefixes, int n, const char* merged_prefix,
                      int delete_old_dirs);
+
+/* Index-only writer for a checkpoint whose data shards are written in parallel by the PS tasks
+ * themselves (each pwrite()s the bytes it owns into <prefix>.data-0000i-of-0000N at offsets the
+ * chief planned): the chief adds one entry per tensor - shard, offset, size, UNMASKED crc32c of the
+ * whole tensor (combined from the writers' per-slice checksums) - and writes <prefix>.index.
+ * Reference: the sharded Scaffold saver behind
+ * templates/00_between_graph_replication_async_mnist.py:43-45. */
+typedef struct dtf_bundle_index_writer dtf_bundle_index_writer;
+dtf_bundle_index_writer* dtf_bundle_index_open(const char* prefix, int num_shards);
+int dtf_bundle_index_add(dtf_bundle_index_writer* w, const char* name, int dtype, int ndim,
+                         const int64_t* dims, int shard_id, int64_t offset, int64_t size,
+                         uint32_t crc32c);
+int dtf_bundle_index_data_path(dtf_bundle_index_writer* w, int shard_id, char* buf, size_t cap);
+int dtf_bundle_index_finish(dtf_bundle_index_writer* w); /* writes <prefix>.index, frees w */
 
 typedef struct dtf_bundle_reader dtf_bundle_reader;
 dtf_bundle_reader* dtf_bundle_reader_open(const char* prefix);

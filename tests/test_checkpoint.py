@@ -225,3 +225,50 @@ def test_saver_max_to_keep(tmp_path):
     assert names == ["model.ckpt-2.index", "model.ckpt-3.index"]
     with BundleReader(str(tmp_path / "model.ckpt-3")) as r:
         assert "hid_w/Adagrad" in r.keys() and np.allclose(r.get_tensor("hid_w/Adagrad"), 0.1)
+
+
+def test_crc32c_combine_equals_checksum_of_the_concatenation():
+    """Every PS task checksums only the slice it wrote; the chief derives the tensor's crc32c for
+    the index from the pieces (dtf_crc32c_combine) without ever seeing the bytes."""
+    from distributedtensorflow_b200.ckpt import bundle as B
+    rng = np.random.RandomState(3)
+    for lens in [(1, 1), (0, 5), (5, 0), (1000, 77777, 3), (4096, 4096, 4096, 1)]:
+        parts = [rng.bytes(n) for n in lens]
+        whole = B.crc32c(np.frombuffer(b"".join(parts), np.uint8))
+        crc = B.crc32c(np.frombuffer(parts[0], np.uint8))
+        for p in parts[1:]:
+            crc = B.crc32c_combine(crc, B.crc32c(np.frombuffer(p, np.uint8)), len(p))
+        assert crc == whole, lens
+
+
+def test_index_only_writer_describes_data_files_written_elsewhere(tmp_path):
+    """The parallel sharded save: data files are filled with pwrite by their owners, the index is
+    written from (shard, offset, size, crc) alone and the result is an ordinary V2 checkpoint."""
+    from distributedtensorflow_b200.ckpt import bundle as B
+    prefix = str(tmp_path / "model.ckpt-7")
+    w = B.BundleIndexWriter(prefix, 2)
+    kernel = np.arange(24, dtype=np.float32).reshape(6, 4)
+    step = np.asarray(7, np.int64)
+    paths = [w.data_path(i) for i in range(2)]
+    assert paths[1].endswith(".data-00001-of-00002")
+    for p in paths:
+        open(p, "wb").close()
+    # two "PS tasks" each store their row slice of the kernel into shard 0, out of order
+    top, bottom = kernel[:2], kernel[2:]
+    fd = os.open(paths[0], os.O_WRONLY)
+    os.pwrite(fd, bottom.tobytes(), top.nbytes)
+    os.pwrite(fd, top.tobytes(), 0)
+    os.close(fd)
+    with open(paths[1], "r+b") as f:
+        f.write(b"\0" * 16 + step.tobytes())
+    crc = B.crc32c_combine(B.crc32c(top), B.crc32c(bottom), bottom.nbytes)
+    w.add("dense/kernel", B.DT_FLOAT, kernel.shape, 0, 0, kernel.nbytes, crc)
+    w.add("global_step", B.DT_INT64, (), 1, 16, 8, B.crc32c(step))
+    w.finish()
+    with B.BundleReader(prefix) as r:
+        assert r.num_shards == 2 and sorted(r.keys()) == ["dense/kernel", "global_step"]
+        np.testing.assert_array_equal(r.get_tensor("dense/kernel"), kernel)      # crc verified
+        assert int(r.get_tensor("global_step")) == 7
+    w2 = B.BundleIndexWriter(str(tmp_path / "bad"), 1)
+    with pytest.raises(Exception):
+        w2.add("x", B.DT_FLOAT, (1,), 3, 0, 4, 0)        # shard id outside the declared shards
