@@ -253,9 +253,29 @@ __global__ void refresh_shadow_kernel(const float* __restrict__ var,
   }
 }
 
+// Test hook: the optimizer rules' division / square root next to the compiler's IEEE ones.
+__global__ void div_sqrt_probe_kernel(const float* a, const float* b, float* q_fast, float* q_ieee,
+                                      float* s_fast, float* s_ieee, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    q_fast[i] = div_rn(a[i], b[i]);
+    q_ieee[i] = __fdiv_rn(a[i], b[i]);
+    s_fast[i] = sqrt_rn(b[i]);
+    s_ieee[i] = __fsqrt_rn(b[i]);
+  }
+}
+
 }  // namespace dtf
 
 using namespace dtf;
+
+extern "C" int dtf_debug_div_sqrt(const float* a, const float* b, float* q_fast, float* q_ieee,
+                                  float* s_fast, float* s_ieee, long long n, void* stream) {
+  div_sqrt_probe_kernel<<<296, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, b, q_fast, q_ieee,
+                                                                                   s_fast, s_ieee, n);
+  DTF_LAUNCH_CHECK();
+  return 0;
+}
 
 extern "C" int dtf_push_apply(int opt, const dtf_apply_item* items, int n_items,
                               const dtf_apply_hyper* hyper, dtf_ps_ctrl* ctrl_for_powers,

@@ -87,6 +87,10 @@ struct GemmParams {
   const unsigned int* scatter_seq;
   float* scatter_base[8];
   long long scatter_buf_stride[8];
+  // max-pool + ReLU gradient scatter (see dtf_gemm_epilogue.pool_*)
+  __nv_bfloat16* pool_out;
+  const unsigned char* pool_amax;
+  float* pool_dbias;
 };
 
 __device__ __forceinline__ void gemm_apply_one(int opt, const dtf_apply_hyper& h, float lr_t, float g,
@@ -170,9 +174,73 @@ __device__ __forceinline__ void gemm_epilogue_apply(const GemmParams& p, int m, 
 }
 
 // Applies the fused epilogue to 32 consecutive accumulator columns of row m and stores them.
-__device__ __forceinline__ void gemm_epilogue_store(const GemmParams& p, int m, int nb, float (&v)[32]) {
+// Pool-scatter mode is called by EVERY lane of the warp (valid = this lane's row exists) because its
+// bias-gradient column sums use warp shuffles; all other modes are only called with valid = true.
+__device__ __forceinline__ void gemm_epilogue_store(const GemmParams& p, int m, int nb, float (&v)[32],
+                                                    bool valid = true) {
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+  if (p.pool_out != nullptr) {
+    // The GEMM's [B, 49 x 64] result is the gradient of the 7x7x64 pooled map (NHWC): these 32 columns
+    // are channels c0..c0+31 of ONE pooled pixel. ReLU gradient (pooled activation > 0), then each
+    // value goes to the position of its 2x2 window that won the forward max (amax = dy*2 + dx), zeros
+    // to the other three: the [B,18,18,64] zero-bordered conv2 output gradient is written directly, and
+    // the conv2 bias gradient is the column sum. Replaces the dpool2 round trip + pool2_bwd kernel.
+    const int pixel = nb >> 6, c0 = nb & 63;
+    const int py = pixel / 7, px = pixel - py * 7;
+    if (!valid) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = 0.f;
+    } else {
+      const __nv_bfloat16* mrow = p.mask + static_cast<size_t>(m) * p.ldmask + nb;
+      uint32_t am[8];
+      const uint4* ap = reinterpret_cast<const uint4*>(p.pool_amax + (static_cast<size_t>(m) * 49 + pixel) * 64 + c0);
+      const uint4 a0 = ap[0], a1 = ap[1];
+      am[0] = a0.x; am[1] = a0.y; am[2] = a0.z; am[3] = a0.w;
+      am[4] = a1.x; am[5] = a1.y; am[6] = a1.z; am[7] = a1.w;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const uint4 mv = *reinterpret_cast<const uint4*>(mrow + g * 8);
+        const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (!(__bfloat162float(mb[j]) > 0.f)) v[g * 8 + j] = 0.f;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        __nv_bfloat16* orow = p.pool_out +
+            ((static_cast<size_t>(m) * 18 + 2 + 2 * py + (q >> 1)) * 18 + 2 + 2 * px + (q & 1)) * 64 + c0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float t[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int jj = g * 8 + j;
+            const uint32_t a = (am[jj >> 2] >> (8 * (jj & 3))) & 0xffu;
+            t[j] = (a == static_cast<uint32_t>(q)) ? v[jj] : 0.f;
+          }
+          *reinterpret_cast<uint4*>(orow + g * 8) =
+              make_uint4(pack_bf16x2(t[0], t[1]), pack_bf16x2(t[2], t[3]), pack_bf16x2(t[4], t[5]),
+                         pack_bf16x2(t[6], t[7]));
+        }
+      }
+    }
+    // column sums over the warp's 32 rows: a transposing butterfly (31 shuffles) leaves column L's
+    // sum in lane L
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+      const bool up = (lane & off) != 0;
+#pragma unroll
+      for (int i = 0; i < off; ++i) {
+        const float keep = up ? v[i + off] : v[i];
+        const float give = up ? v[i] : v[i + off];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, give, off);
+      }
+    }
+    if (v[0] != 0.f) atomicAdd(p.pool_dbias + c0 + lane, v[0]);
+    return;
+  }
   if (p.scatter_enable) {
     // weight-gradient rows go straight into this worker's current mailbox buffer on the shard that
     // owns them: posted stores over NVLink (or local), no gradient buffer, no copy kernel
@@ -395,14 +463,15 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
         for (int j = 0; j < 32; ++j) r[j] = 0;
       }
       const int nb = n0 + c * 32;
-      if (!row_ok || nb >= p.n_store) continue;
+      const bool pool_now = p.pool_out != nullptr && !fixup;   // called warp-wide (shuffles inside)
+      if ((!row_ok && !pool_now) || nb >= p.n_store) continue;
       float v[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
       if (p.apply_opt >= 0) {
         gemm_epilogue_apply(p, m, nb, v, lr_t);
       } else if (!fixup) {
-        gemm_epilogue_store(p, m, nb, v);
+        gemm_epilogue_store(p, m, nb, v, row_ok);
       } else {
         // partial tile -> fp32 workspace (ldws is a multiple of 4, rows are 16-byte aligned)
         float* wrow = p.ws + static_cast<size_t>(m) * p.ldws + nb;
@@ -423,17 +492,17 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (*last_flag) {
         __threadfence();
-        if (row_ok) {
+        if (row_ok || p.pool_out != nullptr) {
 #pragma unroll 1
           for (int c = 0; c < BN / 32; ++c) {
             const int nb = n0 + c * 32;
             if (nb >= p.n_store) continue;
-            const float* wrow = p.ws + static_cast<size_t>(m) * p.ldws + nb;
+            const float* wrow = p.ws + static_cast<size_t>(row_ok ? m : 0) * p.ldws + nb;
             float v[32];
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
               float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (nb + j < p.ldws) {
+              if (row_ok && nb + j < p.ldws) {
                 t = __ldcg(reinterpret_cast<const float4*>(wrow + j));
                 // self-resetting workspace: the next GEMM's partial sums start from zero again
                 if (p.ws_clean)
@@ -441,7 +510,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a,
               }
               v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
             }
-            gemm_epilogue_store(p, m, nb, v);
+            gemm_epilogue_store(p, m, nb, v, row_ok);
           }
         }
       }
@@ -680,7 +749,8 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
                              int block_n, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTF_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: bad shape M=%d N=%d K=%d", M, N, K);
-  DTF_REQUIRE(epi != nullptr && (epi->out != nullptr || epi->apply_enable || epi->scatter_enable),
+  DTF_REQUIRE(epi != nullptr && (epi->out != nullptr || epi->apply_enable || epi->scatter_enable ||
+                                 epi->pool_out != nullptr),
               "gemm: epilogue/out is null");
   DTF_REQUIRE(lda % 8 == 0 && ldb % 8 == 0,
               "gemm: lda=%d ldb=%d must be multiples of 8 elements (TMA 16 B rule)", lda, ldb);
@@ -689,7 +759,7 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
   if (splits > num_kb) splits = num_kb;
   // block_n = 256 asks for the persistent CTA-pair kernel; it is also the default for GEMMs with
   // at least one 256 x 256 tile per TPC (it has no split-K and no fused-apply epilogue)
-  const bool pair_ok = splits == 1 && !epi->apply_enable;
+  const bool pair_ok = splits == 1 && !epi->apply_enable && epi->pool_out == nullptr;
   DTF_REQUIRE(block_n != 256 || pair_ok, "gemm: block_n = 256 cannot be combined with split-K or fused apply");
   const bool use_pair = pair_ok && (block_n == 256 || (block_n == 0 && static_cast<long long>(ceil_div(M, 256)) *
                                                                            ceil_div(N, 256) >= 74 && K >= 256));
@@ -751,6 +821,20 @@ extern "C" int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, in
     // 6-20 us per GEMM on the MNIST shapes, a separate fill of the workspace is cheaper -> opt-in
     if (ws_clean < 0) ws_clean = getenv("DTF_GEMM_WS_CLEAN") ? 1 : 0;
     p.ws_clean = ws_clean;
+  }
+  if (epi->pool_out != nullptr) {
+    DTF_REQUIRE(N == 49 * 64 && !epi->apply_enable && !epi->scatter_enable && !epi->reduce && !use_pair,
+                "gemm: the pool-scatter epilogue is for the [B, 7*7*64] pooled-map gradient (N = %d)", N);
+    DTF_REQUIRE(epi->pool_amax != nullptr && epi->pool_dbias != nullptr && epi->mask != nullptr &&
+                    epi->ldmask % 8 == 0 && epi->ldmask >= N &&
+                    (reinterpret_cast<uintptr_t>(epi->pool_out) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(epi->pool_amax) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(epi->mask) & 15) == 0,
+                "gemm: pool-scatter needs amax, the bias-gradient accumulator and the pooled activation as mask (16-byte aligned)");
+    p.pool_out = reinterpret_cast<__nv_bfloat16*>(epi->pool_out);
+    p.pool_amax = epi->pool_amax;
+    p.pool_dbias = epi->pool_dbias;
+    p.n_store = N;
   }
   if (epi->scatter_enable) {
     DTF_REQUIRE(!epi->apply_enable && !epi->reduce && p.splits == 1,

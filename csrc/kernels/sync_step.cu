@@ -21,6 +21,7 @@
 // round t+1 before all shards finished round t (backup-worker mode stays on the host path).
 #include "common.cuh"
 #include "ptx.cuh"
+#include "apply_rules.cuh"
 #include "../../include/dtf_b200.h"
 
 namespace dtf {
@@ -92,11 +93,11 @@ __device__ __forceinline__ void sync_update(float g, float& var, float& s0, floa
     var -= h.use_nesterov ? (g * h.lr + s0 * h.momentum * h.lr) : h.lr * s0;
   } else if (OPT == DTF_OPT_ADAGRAD) {
     s0 += g * g;
-    var -= h.lr * g * rsqrtf(s0);
+    var -= div_rn(h.lr * g, sqrt_rn(s0));
   } else {
     s0 += (g - s0) * (1.f - h.beta1);
     s1 += (g * g - s1) * (1.f - h.beta2);
-    var -= lr_t * s0 / (sqrtf(s1) + h.epsilon);
+    var -= div_rn(lr_t * s0, sqrt_rn(s1) + h.epsilon);
   }
 }
 

@@ -37,8 +37,16 @@ NVCC_FLAGS = [
 PRECISE_SOURCES = {"apply.cu", "mailbox.cu", "sync_step.cu", "softmax_xent.cu", "head_fused.cu"}
 
 
+def _precise() -> set:
+    # DTF_B200_FAST_MATH_ALL=1 builds everything with --use_fast_math (A/B measurements only)
+    return set() if os.environ.get("DTF_B200_FAST_MATH_ALL") == "1" else PRECISE_SOURCES
+
+
 def nvcc_flags_for(src: Path) -> list:
-    return NVCC_FLAGS if src.name in PRECISE_SOURCES else NVCC_FLAGS + ["--use_fast_math"]
+    if src.name in _precise():
+        extra = os.environ.get("DTF_B200_PRECISE_EXTRA", "")
+        return NVCC_FLAGS + (extra.split() if extra else [])
+    return NVCC_FLAGS + ["--use_fast_math"]
 
 
 def _nvcc() -> str:
@@ -72,7 +80,7 @@ def _stale(lib: Path, digest: str) -> bool:
 
 def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     srcs = cuda_sources()
-    digest = _digest(srcs, " ".join(NVCC_FLAGS) + "|precise:" + ",".join(sorted(PRECISE_SOURCES)))
+    digest = _digest(srcs, " ".join(NVCC_FLAGS) + "|precise:" + ",".join(sorted(_precise())) + os.environ.get("DTF_B200_PRECISE_EXTRA", ""))
     if not force and not _stale(CUDA_LIB, digest):
         return CUDA_LIB
     LIB_DIR.mkdir(parents=True, exist_ok=True)

@@ -384,6 +384,9 @@ class B200StepRunner:
         self._pushes = 0
         self._min_consumed = 0
         self.split_k = bool(opts.get("split_k", True))
+        # conv2's pool/ReLU gradient as the epilogue of the dX GEMM in front of it (one kernel less on the
+        # backward critical path)
+        self.fused_pool_bwd = bool(opts.get("fused_pool_bwd", os.environ.get("DTF_B200_FUSED_POOL_BWD", "1") != "0"))
         # programmatic dependent launch: inside the captured multi-stream graph it measured 2-3% SLOWER
         # than plain kernel edges (the programmatic edges constrain cross-stream overlap), so off
         self.pdl = bool(opts.get("pdl", False))
@@ -1078,6 +1081,15 @@ class B200StepRunner:
                 K.colsum_bf16(s.dact[i], s.B, din, s.z[f"gb{i - 1}"])
                 dz = s.dact[i]
                 fork(side)                       # dZ_{i-1} is ready
+            elif p.kind == "cnn" and self.fused_pool_bwd:
+                # dX GEMM whose epilogue IS conv2's ReLU + max-pool gradient: the pooled-map gradient goes
+                # straight to its argmax positions in the zero-bordered conv2 output gradient (and the
+                # conv2 bias gradient is summed) - no dpool2 round trip, no pool2_bwd kernel on the chain
+                kw = self._plan_kw(s, "dx0")
+                if os.environ.get("DTF_B200_POOL_SPLITS") == "1":
+                    kw = dict(block_n=64)
+                K.gemm(dz, None, None, s.B, din, dout, b_ptr=wp, ldb=ld, mask=s.act[0],
+                       pool=dict(out=s.dconv2p, amax=s.amax2, dbias=s.z["gkb2"]), **kw)
             elif p.kind == "cnn":
                 K.gemm(dz, None, s.dpool2, s.B, din, dout, b_ptr=wp, ldb=ld, **self._plan_kw(s, "dx0"))
             small_push = (self.use_mailbox and fused is None and push_spec is None
@@ -1106,13 +1118,14 @@ class B200StepRunner:
         if p.kind == "cnn":
             c1, c2 = p.convs
             scale = 1.0 / 255.0 if s.x_dev.dtype == torch.uint8 else 1.0
-            K.pool2_bwd(s.dpool2, s.act[0].view(s.B, 7, 7, 64), s.amax2, s.dconv2p, s.z["gkb2"])
+            if not self.fused_pool_bwd:
+                K.pool2_bwd(s.dpool2, s.act[0].view(s.B, 7, 7, 64), s.amax2, s.dconv2p, s.z["gkb2"])
             fork(side)                           # dconv2p is ready
             with torch.cuda.stream(side):
+                K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
                 if clean_ws:                     # every split-K GEMM of the step is done: re-zero
                     K.fill_u32(s.zero.buf[s.zero.ws_off:], 0)   # their workspaces beside the conv backward
                     clean_ws = False
-                K.conv2_wgrad(s.pool1p, s.dconv2p, s.z["gk2"])
             K.conv2_dgrad(s.dconv2p, self.wptr[c2.k.name][0], s.dpool1)
             K.conv1_bwd(s.x_dev, s.dpool1, s.pool1p, s.amax1, s.z["gk1"], s.z["gkb1"], scale)
         if clean_ws:

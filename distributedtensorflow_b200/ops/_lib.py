@@ -84,6 +84,9 @@ class GemmEpilogue(C.Structure):
         ("scatter_seq", C.c_void_p),
         ("scatter_base", C.c_void_p * 8),
         ("scatter_buf_stride", C.c_longlong * 8),
+        ("pool_out", C.c_void_p),
+        ("pool_amax", C.c_void_p),
+        ("pool_dbias", C.c_void_p),
     ]
 
 
@@ -182,6 +185,7 @@ def _declare(lib):
         "dtf_push_apply": [i, C.POINTER(ApplyItem), i, C.POINTER(ApplyHyper), vp, vp, i, i, vp, vp, vp],
         "dtf_push_apply_ex": [i, C.POINTER(ApplyItem), i, C.POINTER(ApplyHyper), vp, vp, i, i, vp, vp,
                               C.POINTER(ResultSink), i, vp],
+        "dtf_debug_div_sqrt": [vp, vp, vp, vp, vp, vp, ll, vp],
         "dtf_pull_bulk": [C.POINTER(CopyItem), i, vp, vp, vp],
         "dtf_refresh_shadow": [vp, vp, ll, ll, i, i, vp],
         "dtf_u8_to_bf16": [vp, vp, i, i, i, f, vp],

@@ -39,14 +39,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
          a_ptr: Optional[int] = None, b_ptr: Optional[int] = None, lda: Optional[int] = None,
          ldb: Optional[int] = None, ws: Optional[torch.Tensor] = None,
          counters: Optional[torch.Tensor] = None, apply: Optional[dict] = None,
-         scatter: Optional[dict] = None) -> None:
+         scatter: Optional[dict] = None, pool: Optional[dict] = None) -> None:
     """out[M,N] = alpha * A @ B^T with the fused epilogue of ``dtf_gemm_bf16``.
 
     ``a``/``b`` are 2-D bf16 tensors whose row pitch (stride(0)) is a multiple of 8; with
     ``a_mn``/``b_mn`` they are stored transposed ([K,M] / [K,N]). ``a_ptr``/``b_ptr`` override
     the base address (peer-mapped PS memory) while ``lda``/``ldb`` give its pitch.
     """
-    if apply is None and scatter is None:
+    if apply is None and scatter is None and pool is None:
         assert out.dim() == 2 and out.stride(1) == 1
     if a_ptr is None:
         assert a.dtype == torch.bfloat16 and a.stride(1) == 1
@@ -55,7 +55,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
         assert b.dtype == torch.bfloat16 and b.stride(1) == 1
         b_ptr, ldb = b.data_ptr(), b.stride(0)
     epi = L.GemmEpilogue()
-    if scatter is not None:
+    if pool is not None:
+        # dX GEMM whose epilogue is conv2's max-pool + ReLU gradient (see dtf_gemm_epilogue.pool_*)
+        epi.out, epi.ldo, epi.out_f32 = None, N, 0
+        epi.pool_out = pool["out"].data_ptr()
+        epi.pool_amax = pool["amax"].data_ptr()
+        epi.pool_dbias = pool["dbias"].data_ptr()
+    elif scatter is not None:
         # weight-gradient GEMM whose epilogue stores straight into the owners' mailboxes
         epi.out, epi.ldo, epi.out_f32 = None, N, 1
         epi.scatter_enable = 1

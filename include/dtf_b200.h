@@ -100,6 +100,16 @@ typedef struct dtf_gemm_epilogue {
   const unsigned int* scatter_seq;
   float* scatter_base[8];
   long long scatter_buf_stride[8];
+  /* Max-pool + ReLU gradient scatter (K2 + K8 in one kernel, the dX GEMM in front of conv2's
+   * backward, run_mnist_distributed.py:59-67): with pool_out != NULL the [M, 49*64] result is the
+   * gradient of the 7x7x64 pooled map (NHWC). Each element is masked by `mask` (the pooled
+   * activation: ReLU gradient) and stored at the position of its 2x2 window that won the forward max
+   * (pool_amax u8 [M,7,7,64], value dy*2+dx), zeros at the other three, straight into the
+   * zero-bordered bf16 [M,18,18,64] gradient of conv2's output; pool_dbias[64] (fp32, accumulated)
+   * receives conv2's bias gradient. `out` is ignored. Works with split-K (fix-up). */
+  void* pool_out;
+  const unsigned char* pool_amax;
+  float* pool_dbias;
 } dtf_gemm_epilogue;
 
 int dtf_gemm_bf16(const void* A, int lda, int a_mn, const void* B, int ldb, int b_mn, int M,
@@ -188,6 +198,11 @@ int dtf_push_apply_ex(int opt, const dtf_apply_item* items, int n_items,
                       dtf_ps_ctrl* ctrl_for_step, int finish, int worker_id,
                       unsigned long long* step_out, unsigned int* block_counter,
                       const dtf_result_sink* sink, int max_ctas, void* stream);
+
+/* Test hook: q_fast = a / b and s_fast = sqrt(b) as the optimizer rules compute them (branch-free,
+ * apply_rules.cuh), q_ieee / s_ieee as IEEE round-to-nearest; n elements each. */
+int dtf_debug_div_sqrt(const float* a, const float* b, float* q_fast, float* q_ieee, float* s_fast,
+                       float* s_ieee, long long n, void* stream);
 
 /* Early step report: bumps (bump = 1) or just reads (bump = 0) global_step and fills `sink` as soon
  * as the loss is known, long before the step's applies have finished, so the host overlaps its

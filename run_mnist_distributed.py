@@ -102,7 +102,10 @@ def train_worker(cfg: TrainConfig, cluster, server, task_index: int) -> int:
             logs = logger.TensorBoardOutputFormat(dir=log_directory, flush_every=100)
             print("Logging to", log_directory)
         local_step = 0
-        while not mon_sess.should_stop():
+        warm_at = warm_t = warm_gstep = None      # steady-state clock: starts once set-up (first steps,
+        while not mon_sess.should_stop():         # CUDA-graph capture) is behind us
+            if local_step == 10:
+                warm_at, warm_t, warm_gstep = local_step, time.time(), last_step
             local_step += 1
             if is_chief:
                 _, train_loss, gstep = mon_sess.run([train_op, loss, global_step])
@@ -116,8 +119,12 @@ def train_worker(cfg: TrainConfig, cluster, server, task_index: int) -> int:
             logs.close()
         if cfg.shutdown_ps_when_done and is_chief:
             mon_sess._tf_sess().ps_client.request_shutdown()
-    elapsed = time.time() - t_begin
+    t_end = time.time()
+    elapsed = t_end - t_begin
     print("Worker %d: %d local steps, %.3f s wall clock (global step %d)" % (task_index, local_step, elapsed, last_step))
+    if warm_t is not None and is_chief and t_end > warm_t:
+        print("Worker %d steady state: %d global steps in %.4f s = %.1f global steps/s (after the first %d local steps)"
+              % (task_index, last_step - warm_gstep, t_end - warm_t, (last_step - warm_gstep) / (t_end - warm_t), warm_at))
     return 0
 
 

@@ -545,6 +545,76 @@ def test_pool2_bwd(K):
     assert (db2 - ref.sum((0, 1, 2))).abs().max().item() < 0.05
 
 
+def test_optimizer_rules_division_and_sqrt_track_ieee_rounding():
+    """The optimizer kernels are built without fast-math but use a branch-free division / sqrt
+    (apply_rules.cuh): on operands in the range optimizer state lives in they must agree with IEEE
+    round-to-nearest - bit-identical almost everywhere, never more than one ulp away."""
+    from distributedtensorflow_b200.ops import _lib as L
+    torch.manual_seed(0)
+    n = 1 << 22
+    dev = "cuda"
+    # numerators like lr_t * m, denominators like sqrt(v) + eps: 10^-12 .. 10^3, both signs upstairs
+    a = (torch.randn(n, device=dev) * torch.pow(10.0, torch.empty(n, device=dev).uniform_(-12, 3))).float()
+    b = torch.pow(10.0, torch.empty(n, device=dev).uniform_(-12, 3)).float()
+    b[:4] = torch.tensor([0.0, 1e-8, 1.0, 4.0], device=dev)
+    out = [torch.empty(n, device=dev) for _ in range(4)]
+    rc = L.lib().dtf_debug_div_sqrt(a.data_ptr(), b.data_ptr(), *[o.data_ptr() for o in out], n, L.current_stream())
+    L.check(rc, "dtf_debug_div_sqrt")
+    torch.cuda.synchronize()
+    qf, qi, sf, si = out
+    assert sf[0].item() == 0.0 and sf[2].item() == 1.0 and sf[3].item() == 2.0
+    for fast, ieee, name in ((qf[1:], qi[1:], "div"), (sf, si, "sqrt")):
+        ulp = (fast.view(torch.int32) - ieee.view(torch.int32)).abs()
+        assert ulp.max().item() <= 1, (name, ulp.max().item())
+        assert (ulp != 0).float().mean().item() < 1e-3, (name, (ulp != 0).float().mean().item())
+
+
+@pytest.mark.parametrize("B,splits", [(128, 1), (128, 3), (37, 3), (200, 2)])
+def test_gemm_pool_scatter_epilogue_equals_gemm_plus_pool2_bwd(K, B, splits):
+    """The dX GEMM with conv2's ReLU + max-pool gradient as its epilogue against the two-kernel form
+    (GEMM -> dpool2 -> pool2_bwd) and against PyTorch autograd on the same operands."""
+    torch.manual_seed(B + splits)
+    dev = "cuda"
+    Kd = 256
+    dz = (torch.randn(B, Kd, device=dev) * 0.5).to(torch.bfloat16)
+    w = (torch.randn(3136, Kd, device=dev) * 0.1).to(torch.bfloat16)          # [N, K], K contiguous
+    conv = torch.randn(B, 64, 14, 14, device=dev, requires_grad=True)
+    pooled, _ = torch.nn.functional.max_pool2d(torch.relu(conv), 2, return_indices=True)
+    convw = conv.detach().view(B, 64, 7, 2, 7, 2).permute(0, 1, 2, 4, 3, 5).reshape(B, 64, 7, 7, 4)
+    amax2 = convw.argmax(-1).permute(0, 2, 3, 1).contiguous().to(torch.uint8)
+    pool2 = pooled.detach().permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).reshape(B, 3136)
+    ws = torch.zeros(B, 3136, device=dev)
+    ct = torch.zeros(256, dtype=torch.int32, device=dev)          # one counter per 128 x 64 output tile
+    kw = dict(block_n=64)
+    if splits > 1:
+        kw.update(splits=splits, ws=ws, counters=ct)
+    # two kernels
+    dpool2 = torch.full((B, 3136), float("nan"), dtype=torch.bfloat16, device=dev)
+    K.gemm(dz, w, dpool2, B, 3136, Kd, **kw)
+    ref_out = torch.zeros(B, 18, 18, 64, dtype=torch.bfloat16, device=dev)
+    ref_db = torch.zeros(64, device=dev)
+    K.pool2_bwd(dpool2, pool2.view(B, 7, 7, 64), amax2, ref_out, ref_db)
+    # one kernel
+    ws.zero_()
+    got_out = torch.zeros(B, 18, 18, 64, dtype=torch.bfloat16, device=dev)
+    got_out[:, 2:16, 2:16, :] = float("nan")                       # every interior element must be written
+    got_db = torch.zeros(64, device=dev)
+    K.gemm(dz, w, None, B, 3136, Kd, mask=pool2, pool=dict(out=got_out, amax=amax2, dbias=got_db), **kw)
+    torch.cuda.synchronize()
+    assert torch.isfinite(got_out.float()).all()
+    assert got_out[:, :2].abs().sum() == 0 and got_out[:, 16:].abs().sum() == 0       # the zero border is untouched
+    assert got_out[:, :, :2].abs().sum() == 0 and got_out[:, :, 16:].abs().sum() == 0
+    d = (got_out.float() - ref_out.float()).abs()
+    assert d.max().item() <= 0.03 * ref_out.float().abs().max().item() + 1e-3        # one bf16 rounding vs two
+    # autograd oracle
+    g = (dz.float() @ w.float().t()).view(B, 7, 7, 64).permute(0, 3, 1, 2)
+    pooled.backward(g)
+    oracle = conv.grad.permute(0, 2, 3, 1)
+    assert _rel_err(got_out[:, 2:16, 2:16, :], oracle) < 1e-2
+    assert _rel_err(got_db, oracle.sum((0, 1, 2))) < 1e-2
+    assert _rel_err(ref_db, oracle.sum((0, 1, 2))) < 2e-2
+
+
 # ---------------------------------------------------------------------------------------------
 # "owner applies" push: mailbox_push (worker) + mailbox_drain (owner), csrc/kernels/mailbox.cu
 # ---------------------------------------------------------------------------------------------
