@@ -42,7 +42,15 @@ def main():
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     tmp = tempfile.mkdtemp(prefix="dtf_gpu_cli_")
-    cfg = {"ps": {"ps:%d" % i: "127.0.0.1:%d/gpu:%d" % (free_port(), i % args.gpus) for i in range(args.ps)},
+    # Every task is its own process. A PS task that shared a GPU with a worker PROCESS would have its
+    # drain kernels time-sliced against that worker's kernels (two contexts on one device), and a worker
+    # kernel parked in its flow control would then wait for a kernel that cannot run beside it: give the
+    # PS tasks GPUs of their own whenever there are enough devices, workers first.
+    if args.gpus >= args.workers + args.ps:
+        ps_gpu = [args.workers + i for i in range(args.ps)]
+    else:
+        ps_gpu = [i % args.gpus for i in range(args.ps)]
+    cfg = {"ps": {"ps:%d" % i: "127.0.0.1:%d/gpu:%d" % (free_port(), ps_gpu[i]) for i in range(args.ps)},
            "workers": {"worker:%d" % i: "127.0.0.1:%d/gpu:%d" % (free_port(), i % args.gpus)
                        for i in range(args.workers)}}
     path = os.path.join(tmp, "config.json")

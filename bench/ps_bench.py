@@ -74,6 +74,8 @@ def main() -> int:
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"])
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=VAL", help="extra executor option")
+    ap.add_argument("--replicas", type=int, default=0,
+                    help="sync mode: replicas_to_aggregate (default: every worker; fewer = backup workers)")
     ap.add_argument("--lockstep", action="store_true",
                     help="async correctness mode: workers take turns, one step each, and every push is "
                          "flushed before the next worker steps - the run is then a deterministic "
@@ -129,7 +131,8 @@ def main() -> int:
             loss, gs, opt = build_model(tf, args, X, Y)
             nw = len(worker_ranks)
             if args.mode == "sync":
-                opt = tf.train.SyncReplicasOptimizer(opt, replicas_to_aggregate=nw, total_num_replicas=nw)
+                opt = tf.train.SyncReplicasOptimizer(opt, replicas_to_aggregate=(args.replicas or nw),
+                                                     total_num_replicas=nw)
             train_op = opt.minimize(loss, global_step=gs)
         hooks = [opt.make_session_run_hook(wk_index == 0)] if args.mode == "sync" else []
         cfg = tf.ConfigProto(backend="b200", device="cuda:%d" % local_rank, push_mode=args.push_mode,
@@ -152,6 +155,20 @@ def main() -> int:
                         if world > 1:
                             dist.barrier()
                 args.steps_done, args.steps, args.warmup = args.warmup + args.steps, 0, 0
+            if args.mode == "sync" and args.replicas and args.replicas < nw:
+                # backup workers: train until the SHARED step reaches the target (a replica whose gradient
+                # arrived stale simply takes the next token); whoever is left waiting for a token after the
+                # others have finished gets the closed-queue signal
+                target, i, l, g = args.warmup + args.steps, 0, float("nan"), 0
+                try:
+                    while int(g) < target:
+                        bx, by = batches[i % len(batches)]
+                        _, l, g = sess.run([train_op, loss, gs], feed_dict={X: bx, Y: by})
+                        i += 1
+                except tf.errors.OutOfRangeError:
+                    pass
+                raw._runner.mark_done()
+                args.local_steps, args.steps, args.warmup = i, 0, 0
             for i in range(args.warmup):
                 bx, by = batches[i % len(batches)]
                 _, l, g = sess.run([train_op, loss, gs], feed_dict={X: bx, Y: by})
@@ -178,6 +195,9 @@ def main() -> int:
             if runner.use_mailbox:
                 runner.flush_pushes()        # my last gradients have been applied by their owners
                 extra["push"] = "mailbox"
+            if getattr(runner, "sync_generic", False):
+                extra["sync_path"] = "mailbox"
+                extra["local_steps"] = getattr(args, "local_steps", None)
             if args.dump_params:
                 if world > 1:
                     dist.barrier()           # every worker's last gradient is applied and broadcast

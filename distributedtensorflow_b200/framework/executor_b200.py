@@ -1778,6 +1778,15 @@ class B200StepRunner:
                 else:
                     self._enqueue_step(s)
 
+    def mark_done(self) -> None:
+        """Tell every owner that this worker has finished training (``done[worker]`` in its mailbox
+        flags). In synchronous mode a replica still waiting for a token learns from these words that
+        the round can never complete and stops cleanly (``_sync_token_expired``)."""
+        if self.use_mailbox and self.store is not None:
+            one = np.ones(1, np.uint32)
+            for sh in range(self.store.num_shards):
+                self.store._h2d(self.store.mbox_flags_ptr(sh) + L.MBOX_OFF_DONE + 4 * self.worker_id, one)
+
     def close(self) -> None:
         if self.use_mirror and self.store is not None and self.store.mirror_base:
             # release kernels of mine that are parked in device-side flow control (dead owner)
@@ -1795,9 +1804,7 @@ class B200StepRunner:
         if self.use_mailbox and self.store is not None:
             try:
                 self.flush_pushes()
-                one = np.ones(1, np.uint32)
-                for sh in range(self.store.num_shards):
-                    self.store._h2d(self.store.mbox_flags_ptr(sh) + L.MBOX_OFF_DONE + 4 * self.worker_id, one)
+                self.mark_done()
             except Exception:
                 pass
         if self.use_mailbox and self.store is not None:

@@ -376,8 +376,36 @@ def _sync_run(backend, n_workers, replicas, steps, num_ps=1, slow_worker=None, o
     return out, seen
 
 
+def _isolated(fn_name, *args, timeout=150):
+    """Run ``fn_name(*args)`` of this module in a process of its own. The synchronous-round tests put
+    several worker threads on ONE GPU, where a worker's token wait is a kernel that spins until another
+    worker's kernels have run: streams of one process normally run side by side, but nothing guarantees
+    it (B200_PROFILING.md). If they ever serialise, the in-kernel watchdog traps - in the child, not in
+    the pytest process whose CUDA context every later test needs. More hardware queues than streams
+    (CUDA_DEVICE_MAX_CONNECTIONS) keep unrelated streams from sharing one."""
+    import os
+    import subprocess
+    import sys
+    here = os.path.abspath(__file__)
+    code = ("import importlib.util, sys; sys.path.insert(0, %r); "
+            "spec = importlib.util.spec_from_file_location('t_exec_gpu', %r); m = importlib.util.module_from_spec(spec); "
+            "spec.loader.exec_module(m); getattr(m, %r)(*%r); print('ISOLATED-OK')"
+            % (os.path.dirname(os.path.dirname(here)), here, fn_name, tuple(args)))
+    env = dict(os.environ, CUDA_DEVICE_MAX_CONNECTIONS="32")
+    p = subprocess.run([sys.executable, "-c", code], env=env, timeout=timeout, capture_output=True, text=True)
+    assert p.returncode == 0 and "ISOLATED-OK" in p.stdout, (p.stdout[-2000:] + p.stderr[-3000:])
+
+
 @pytest.mark.parametrize("num_ps", [1, 2])
 def test_sync_on_mailboxes_ps_only_topology_matches_cpu_sync_replicas(num_ps):
+    _isolated("_impl_sync_on_mailboxes_ps_only_topology", num_ps)
+
+
+def test_sync_on_mailboxes_backup_worker_is_dropped_not_waited_for():
+    _isolated("_impl_sync_on_mailboxes_backup_worker")
+
+
+def _impl_sync_on_mailboxes_ps_only_topology(num_ps):
     """The MLP template's own topology - PS task(s) without a worker, two workers, all replicas
     aggregated - on the device path: tagged pushes, the PS daemon's mean+apply, epoch tokens."""
     steps = 8
@@ -390,7 +418,7 @@ def test_sync_on_mailboxes_ps_only_topology_matches_cpu_sync_replicas(num_ps):
         assert float(diff.mean()) < 2e-3 and float(diff.max()) < 0.03, (name, float(diff.mean()), float(diff.max()))
 
 
-def test_sync_on_mailboxes_backup_worker_is_dropped_not_waited_for():
+def _impl_sync_on_mailboxes_backup_worker():
     """replicas_to_aggregate=2 of 3 replicas, one of them slow: rounds complete with the two fast
     gradients, the straggler's arrive stale and are retired unapplied, and when the others have
     stopped the straggler's token wait ends like a closed token queue (clean stop)."""

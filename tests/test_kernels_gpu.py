@@ -856,9 +856,12 @@ def test_mailbox_push_device_flow_control_waits_for_the_owner(K):
     assert slots[:n].eq(1).all() and slots[n:].eq(2).all() and seq.item() == 2
     push(2)                       # buffer 0 again: needs consumed[owner] >= 1
     time.sleep(0.05)
-    assert not side.query() and slots[:n].eq(1).all()
+    assert not side.query() and bool((slots[:n].cpu() == 1).all())     # (read back with a copy, not a kernel)
+    # the words are moved by a COPY (copy engine), not by a kernel: a kernel queued behind the parked
+    # one could wait for it for ever, a copy cannot
+    one = torch.ones(1, dtype=torch.int32).pin_memory()
     with torch.cuda.stream(poke):
-        hdr[L.MIRROR_OFF_CONSUMED // 4 + owner] = 1
+        hdr[L.MIRROR_OFF_CONSUMED // 4 + owner: L.MIRROR_OFF_CONSUMED // 4 + owner + 1].copy_(one, non_blocking=True)
     poke.synchronize()
     side.synchronize()
     assert slots[:n].eq(3).all() and seq.item() == 3
@@ -866,7 +869,7 @@ def test_mailbox_push_device_flow_control_waits_for_the_owner(K):
     time.sleep(0.05)
     assert not side.query()
     with torch.cuda.stream(poke):
-        hdr[L.MIRROR_OFF_ABORT // 4] = 1
+        hdr[L.MIRROR_OFF_ABORT // 4: L.MIRROR_OFF_ABORT // 4 + 1].copy_(one, non_blocking=True)
     poke.synchronize()
     side.synchronize()
     assert seq.item() == 4

@@ -124,3 +124,98 @@ def test_sync_checkpoint_sharded_save(tmp_path):
                      "--ckpt-dir", str(tmp_path)], 29641)
     assert res["ckpt_shards"] == 2 and res["ckpt_roundtrip_ok"] is True
     assert res["ckpt_tensors"] == 4 * 3 + 1 + 2        # vars + Adam slots, global_step, beta powers
+
+
+def _gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+def test_async_mirror_lockstep_matches_cpu_oracle(tmp_path):
+    """Two workers + two shards on two GPUs, owner-applies push with worker mirrors and in-graph
+    drains, run in lock step (workers take turns, every push flushed): the sequence of applies is then
+    deterministic and must match a single-process CPU run that replays it; afterwards every worker's
+    mirror equals the owners' masters (fp32 exactly, bf16 after rounding) and its header carries the
+    owners' counts."""
+    steps = 6
+    pattern = str(tmp_path / "params_rank%d.npz")
+    res = _torchrun(2, "bench/ps_bench.py",
+                    ["--model", "mlp", "--placement", "flat", "--steps", str(steps), "--warmup", "0", "--lockstep",
+                     "--lr", "0.001", "--hidden", "100", "--batch", "100", "--dump-params", pattern], 29651)
+    assert res["mirror"] is True and res["graph_drain_shards"] == [0]
+    assert res["final_step"] == 2 * steps
+    got = [np.load(pattern % r) for r in range(2)]
+    import torch
+    for r in range(2):
+        assert list(got[r]["mirror_consumed"]) == [steps, steps]            # each owner applied all of MY pushes
+        assert list(got[r]["mirror_version"]) == [2 * steps, 2 * steps]     # ... and everybody's
+    names = [k for k in got[0].files if not k.startswith("mirror_")]
+    for n in names:
+        np.testing.assert_array_equal(got[0][n], got[1][n])                 # both ranks read the same masters
+        for r in range(2):
+            if "mirror_f32__" + n in got[r].files:
+                np.testing.assert_array_equal(got[r]["mirror_f32__" + n], got[r][n])
+            if "mirror_bf16__" + n in got[r].files:
+                want = torch.from_numpy(got[r][n]).to(torch.bfloat16).float().numpy()
+                np.testing.assert_array_equal(got[r]["mirror_bf16__" + n], want)
+    # CPU oracle: one process applies the same gradients in the same order (w0 step i, w1 step i, ...)
+    import distributedtensorflow_b200 as tf
+    from distributedtensorflow_b200.models import mnist_mlp
+    sys.path.insert(0, os.path.join(ROOT, "bench"))
+    import ps_bench
+
+    class A:
+        pass
+    args = A()
+    args.batch, args.model = 100, "mlp"
+    tf.reset_default_graph()
+    tf.set_random_seed(0)
+    X = tf.placeholder(tf.float32, [None, 784])
+    Y = tf.placeholder(tf.float32, [None, 10])
+    gs, loss, _ = mnist_mlp.build_model(X, Y, 100)
+    train_op = tf.train.AdamOptimizer(0.001).minimize(loss, global_step=gs)
+    server = tf.train.Server.create_local_server()
+    batches = [ps_bench.make_batches(args, w) for w in range(2)]
+    with tf.train.MonitoredTrainingSession(master=server.target, config=tf.ConfigProto(backend="cpu")) as sess:
+        for i in range(steps):
+            for w in range(2):
+                bx, by = batches[w][i % len(batches[w])]
+                sess.run(train_op, feed_dict={X: bx.astype(np.float32) / 255.0, Y: by})
+        raw = sess._tf_sess()
+        ref = raw.ps_client.pull_all(raw.layout, [v.name for v in tf.trainable_variables()])
+    server.stop()
+    for name, r in ref.items():
+        diff = np.abs(got[0][name.replace("/", "__")] - r)
+        assert float(diff.mean()) < 2e-3 and float(diff.max()) < 0.03, (name, float(diff.mean()), float(diff.max()))
+
+
+def test_sync_on_mailboxes_ps_only_task_two_gpus():
+    """The MLP template's sync mode with a PS task that has no worker (GPU 0) and a worker (GPU 1):
+    the round runs on the mailboxes - tagged push, the PS daemon's mean + apply, epoch token."""
+    res = _torchrun(2, "bench/ps_bench.py",
+                    ["--model", "mlp", "--mode", "sync", "--topology", "ps1", "--steps", "10", "--warmup", "2",
+                     "--opt", "sync_path=mailbox"], 29661)
+    assert res.get("sync_path") == "mailbox" and res["config"]["workers"] == 1
+    assert res["final_step"] == 12 and np.isfinite(res["final_loss"])
+
+
+def test_sync_backup_workers_four_gpus():
+    """1 PS task + 3 workers on 4 GPUs, replicas_to_aggregate = 2: every round is the mean of the
+    fresh gradients that arrived (>= 2), stale ones are dropped, nobody waits for a third."""
+    if _gpus() < 4:
+        pytest.skip("needs 4 GPUs")
+    res = _torchrun(4, "bench/ps_bench.py",
+                    ["--model", "mlp", "--mode", "sync", "--topology", "ps1", "--steps", "20", "--warmup", "2",
+                     "--replicas", "2", "--opt", "sync_token_timeout=2"], 29671)
+    assert res.get("sync_path") == "mailbox" and res["config"]["workers"] == 3
+    # every round applies the mean of the 2 or 3 fresh gradients that arrived; training ends at the target
+    assert 22 <= res["final_step"] <= 24 and np.isfinite(res["final_loss"])
+
+
+def test_async_eight_gpus_counts_every_apply():
+    if _gpus() < 8:
+        pytest.skip("needs 8 GPUs")
+    out = _torchrun(8, "bench.py", ["--gpus", "8", "--steps", "20", "--warmup", "3"], 29681, timeout=240)
+    assert out["n_gpus"] == 8 and out["config"]["push"].startswith("mailbox")
+    assert out["final_global_step"] == 8 * (3 + 20 + 20 + 20)
+    assert out["final_loss"] < 2.0
