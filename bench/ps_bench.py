@@ -74,6 +74,7 @@ def main() -> int:
     ap.add_argument("--no-l2-flush", action="store_true")
     ap.add_argument("--push-mode", default="auto", choices=["auto", "rmw", "mailbox"])
     ap.add_argument("--opt", action="append", default=[], metavar="KEY=VAL", help="extra executor option")
+    ap.add_argument("--timeline", default="", help="rank of the first worker: CUPTI kernel timeline of 3 more steps (json)")
     ap.add_argument("--replicas", type=int, default=0,
                     help="sync mode: replicas_to_aggregate (default: every worker; fewer = backup workers)")
     ap.add_argument("--lockstep", action="store_true",
@@ -190,6 +191,22 @@ def main() -> int:
                 dev_ms += s.elapsed_time(e)
             wall = time.perf_counter() - t0
             times[0], times[1] = dev_ms, wall * 1e3
+            if args.timeline:
+                from torch.profiler import profile, ProfilerActivity
+                bx, by = batches[0]
+                if wk_index == 0:
+                    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+                        for _ in range(3):
+                            sess.run([train_op, loss, gs], feed_dict={X: bx, Y: by})
+                        runner.stream.synchronize()
+                    evs = sorted([e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA],
+                                 key=lambda e: e.time_range.start)
+                    t00 = evs[0].time_range.start if evs else 0
+                    json.dump([dict(t_us=round(e.time_range.start - t00, 2), dur_us=round(e.time_range.end - e.time_range.start, 2),
+                                    name=e.name[:70]) for e in evs], open(args.timeline, "w"), indent=0)
+                else:
+                    for _ in range(3):
+                        sess.run([train_op, loss, gs], feed_dict={X: bx, Y: by})
             final_step, final_loss = int(g), float(l)
             extra = {}
             if runner.use_mailbox:

@@ -372,7 +372,11 @@ class B200StepRunner:
         self.drain_backstop_us = int(opts.get("drain_backstop_us", 400))
         # grid cap of the in-graph drain: it runs beside the forward pass, where a flood of CTAs
         # doubled the convolutions' time; a few dozen CTAs over a longer window are free
-        self.drain_ctas = int(opts.get("drain_ctas", os.environ.get("DTF_B200_DRAIN_CTAS", "64")))
+        # (-1 = auto: a short drain (<= 1024 chunks of 4096 elements, the MNIST models) is capped at 64 CTAs;
+        # a long one (the wide MLP: thousands of chunks) runs uncapped at low priority - capped, its few
+        # resident CTAs slowed the persistent GEMM's CTAs on the SMs they shared 3x, and the static tile
+        # schedule made the whole GEMM wait for them)
+        self.drain_ctas = int(opts.get("drain_ctas", os.environ.get("DTF_B200_DRAIN_CTAS", "-1")))
         self.use_mirror = False
         self.sync_generic = False
         self.sync_path = str(opts.get("sync_path", os.environ.get("DTF_B200_SYNC_PATH", "auto")))   # auto | mailbox
@@ -1284,11 +1288,15 @@ class B200StepRunner:
             mitems = K.make_mirror_items([tuple(m) for m in desc["mirror_items"]]) \
                 if desc.get("mirror_items") is not None else None
             scratch = self._drain_scratch.data_ptr() + 256 * k
+            cap = self.drain_ctas
+            if cap < 0:
+                chunks = sum(-(-int(it["n"]) // 4096) for it in desc["items"])
+                cap = 64 if chunks <= 1024 else 0
             K.mailbox_drain(spec.code, K.make_apply_items(entries), len(entries), int(desc["slot_stride"]),
                             int(desc["depth"]), int(desc["n_workers"]), hyper, base,
                             base if desc["owns_step"] else None, base + int(desc["flags_off"]),
                             scratch, scratch + 128, None, mirror_items=mitems, shard_index=sh,
-                            max_ctas=self.drain_ctas)
+                            max_ctas=cap)
 
     def _mbox_consumed(self) -> int:
         """min over owners of how many of MY gradients they have applied (host-side read)."""
