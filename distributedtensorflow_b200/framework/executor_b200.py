@@ -394,6 +394,8 @@ class B200StepRunner:
         # programmatic dependent launch: inside the captured multi-stream graph it measured 2-3% SLOWER
         # than plain kernel edges (the programmatic edges constrain cross-stream overlap), so off
         self.pdl = bool(opts.get("pdl", False))
+        self.pdl_chain = bool(opts.get("pdl_chain", os.environ.get("DTF_B200_PDL_CHAIN", "0") == "1"))
+        self.pdl_forward = bool(opts.get("pdl_forward", os.environ.get("DTF_B200_PDL_FORWARD", "1") == "1"))
         L.lib().dtf_set_pdl(1 if self.pdl else 0)
         self.device = torch.device(self._pick_device())
         torch.cuda.set_device(self.device)
@@ -933,6 +935,12 @@ class B200StepRunner:
                             y_bytes=s.y_bytes16)
             else:
                 K_conv1_fwd(s.x_dev, self.fptr[c1.k.name], self.fptr[c1.b.name], s.pool1p, s.amax1, scale)
+            # programmatic dependent launch for the FORWARD chain only (one stream, kernel after kernel):
+            # each kernel's prologue (TMEM allocation, mbarrier init, descriptor prefetch) overlaps its
+            # predecessor's tail. Across the multi-stream backward it measured slower, so it ends with
+            # the loss kernel.
+            if self.pdl_forward and not self.pdl:
+                L.lib().dtf_set_pdl(1)
             K_conv2_fwd(s.pool1p, self.wptr[c2.k.name][0], self.fptr[c2.b.name],
                         s.act[0].view(s.B, 7, 7, 64), s.amax2)
         else:
@@ -977,6 +985,13 @@ class B200StepRunner:
         return kw
 
     def _loss(self, s: StepState) -> None:
+        try:
+            self._loss_body(s)
+        finally:
+            if self.pdl_forward and not self.pdl:
+                L.lib().dtf_set_pdl(0)
+
+    def _loss_body(self, s: StepState) -> None:
         p = self.plan
         nl = len(p.dense)
         if getattr(s, "y_ready", None) is not None:
@@ -1446,6 +1461,19 @@ class B200StepRunner:
 
     def _enqueue_step(self, s: StepState, with_io: bool = True) -> None:
         """Everything one ``sess.run(train_op)`` does on the device, in stream order."""
+        if self.pdl_chain and not self.pdl:
+            # PDL only along the critical chain (the step's main stream): prologues overlap the
+            # predecessor's tail there; the side / apply streams keep full kernel edges
+            L.pdl_main_stream = torch.cuda.current_stream().cuda_stream
+            try:
+                self._enqueue_step_body(s, with_io)
+            finally:
+                L.pdl_main_stream = None
+                L.lib().dtf_set_pdl(0)
+            return
+        self._enqueue_step_body(s, with_io)
+
+    def _enqueue_step_body(self, s: StepState, with_io: bool = True) -> None:
         s.zero_copy = bool(with_io and self.zero_copy_input)
         s.y_ready = None
         if s.zero_copy and self.plan.kind != "cnn":

@@ -196,6 +196,8 @@ def _declare(lib):
         "dtf_conv1_fwd_ingest": [vp, vp, f, vp, vp, vp, vp, vp, vp, vp, vp, i, i, vp],
         "dtf_conv1_bwd": [vp, vp, f, vp, vp, vp, vp, vp, i, vp],
         "dtf_conv2_fwd": [vp, vp, vp, vp, vp, i, vp],
+        "dtf_conv2_fwd_halo": [vp, vp, vp, vp, vp, i, vp],
+        "dtf_conv2_dgrad_halo": [vp, vp, vp, i, vp],
         "dtf_pool2_bwd": [vp, i, vp, vp, vp, vp, i, vp],
         "dtf_conv2_wgrad": [vp, vp, vp, i, vp],
         "dtf_conv2_dgrad": [vp, vp, vp, i, vp],
@@ -265,6 +267,15 @@ def check(rc: int, what: str = "") -> None:
         raise NativeError(f"{what or 'native call'} failed ({rc}): {msg}")
 
 
+# Selective programmatic dependent launch: while set to a stream handle, kernels enqueued on THAT
+# stream are launched with the PDL attribute and kernels on any other stream without it (every
+# wrapper fetches current_stream() immediately before its launch).
+pdl_main_stream = None
+
+
 def current_stream() -> int:
     import torch
-    return torch.cuda.current_stream().cuda_stream
+    h = torch.cuda.current_stream().cuda_stream
+    if pdl_main_stream is not None:
+        lib().dtf_set_pdl(1 if h == pdl_main_stream else 0)
+    return h

@@ -7,6 +7,7 @@ reports it as ``gpu_launches``).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Sequence
 
 import torch
@@ -387,10 +388,14 @@ def conv1_bwd(x: torch.Tensor, dpool1: torch.Tensor, pool1p: torch.Tensor, amax1
     _count()
 
 
+CONV2_HALO = os.environ.get("DTF_B200_CONV2_HALO", "1") != "0"
+
+
 def conv2_fwd(pool1p: torch.Tensor, w2_ptr: int, b2: torch.Tensor, pool2: torch.Tensor,
-              amax2: torch.Tensor) -> None:
+              amax2: torch.Tensor, halo: Optional[bool] = None) -> None:
     B = pool1p.shape[0]
-    rc = L.lib().dtf_conv2_fwd(pool1p.data_ptr(), w2_ptr, b2.data_ptr(), pool2.data_ptr(),
+    fn = L.lib().dtf_conv2_fwd_halo if (CONV2_HALO if halo is None else halo) else L.lib().dtf_conv2_fwd
+    rc = fn(pool1p.data_ptr(), w2_ptr, b2.data_ptr(), pool2.data_ptr(),
                                amax2.data_ptr(), B, L.current_stream())
     L.check(rc, "dtf_conv2_fwd")
     _count()
@@ -414,9 +419,10 @@ def conv2_wgrad(pool1p: torch.Tensor, dconv2p: torch.Tensor, dw2_accum: torch.Te
     _count()
 
 
-def conv2_dgrad(dconv2p: torch.Tensor, w2_ptr: int, dpool1: torch.Tensor) -> None:
+def conv2_dgrad(dconv2p: torch.Tensor, w2_ptr: int, dpool1: torch.Tensor, halo: Optional[bool] = None) -> None:
     B = dconv2p.shape[0]
-    rc = L.lib().dtf_conv2_dgrad(dconv2p.data_ptr(), w2_ptr, dpool1.data_ptr(), B,
+    fn = L.lib().dtf_conv2_dgrad_halo if (CONV2_HALO if halo is None else halo) else L.lib().dtf_conv2_dgrad
+    rc = fn(dconv2p.data_ptr(), w2_ptr, dpool1.data_ptr(), B,
                                  L.current_stream())
     L.check(rc, "dtf_conv2_dgrad")
     _count()

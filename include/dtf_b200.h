@@ -466,6 +466,13 @@ int dtf_conv1_bwd(const unsigned char* x_u8, const float* x_f32, float scale,
  * amax2 u8 [B,7,7,64]. */
 int dtf_conv2_fwd(const void* pool1p, const void* w2, const float* b2, void* pool2,
                   unsigned char* amax2, int B, void* stream);
+/* Same results as dtf_conv2_fwd / dtf_conv2_dgrad from ONE halo tile per image in shared memory: the
+ * activation is loaded once (a 5-D TMA box re-lays it as UMMA's un-swizzled K-major operand) and the
+ * 25 filter taps are 25 shifted shared-memory descriptors; the whole filter is loaded once per CTA.
+ * A quarter of the L2 traffic of the tap-by-tap kernels. */
+int dtf_conv2_fwd_halo(const void* pool1p, const void* w2, const float* b2, void* pool2,
+                       unsigned char* amax2, int B, void* stream);
+int dtf_conv2_dgrad_halo(const void* dconv2p, const void* w2, void* dpool1, int B, void* stream);
 /* pool2 gradient + ReLU gradient: dpool2 bf16 [B,7,7,64] -> dconv2p bf16 [B,18,18,64] interior
  * (zero border kept by the caller); db2 fp32 [64] accumulated. */
 int dtf_pool2_bwd(const void* dpool2, int ld_dpool2, const void* pool2,

@@ -478,12 +478,13 @@ def _conv2_setup(B):
     return pool1p, w2, b2
 
 
+@pytest.mark.parametrize("halo", [True, False])
 @pytest.mark.parametrize("B", [128, 4, 6])
-def test_conv2_fwd(K, B):
+def test_conv2_fwd(K, B, halo):
     pool1p, w2, b2 = _conv2_setup(B)
     pool2 = torch.zeros(B, 7, 7, 64, dtype=torch.bfloat16, device="cuda")
     amax2 = torch.zeros(B, 7, 7, 64, dtype=torch.uint8, device="cuda")
-    K.conv2_fwd(pool1p, w2.data_ptr(), b2, pool2, amax2)
+    K.conv2_fwd(pool1p, w2.data_ptr(), b2, pool2, amax2, halo=halo)
     torch.cuda.synchronize()
     x = pool1p[:, 2:16, 2:16, :].float().permute(0, 3, 1, 2)
     w = w2.float().permute(3, 2, 0, 1)
@@ -501,8 +502,9 @@ def test_conv2_fwd(K, B):
     assert (got_am[clear] == ref_am[clear]).all()
 
 
+@pytest.mark.parametrize("halo", [True, False])
 @pytest.mark.parametrize("B", [128, 6])
-def test_conv2_backward(K, B):
+def test_conv2_backward(K, B, halo):
     pool1p, w2, b2 = _conv2_setup(B)
     # upstream gradient w.r.t. the conv2 pre-activation, in the zero-bordered layout
     dy = (torch.randn(B, 14, 14, 64, device="cuda") * 0.1).to(torch.bfloat16)
@@ -515,7 +517,7 @@ def test_conv2_backward(K, B):
     dw = torch.zeros(800, 64, device="cuda")
     K.conv2_wgrad(pool1p, dconv2p, dw)
     dpool1 = torch.zeros(B, 14, 14, 32, dtype=torch.bfloat16, device="cuda")
-    K.conv2_dgrad(dconv2p, w2.data_ptr(), dpool1)
+    K.conv2_dgrad(dconv2p, w2.data_ptr(), dpool1, halo=halo)
     torch.cuda.synchronize()
     dw_ref = w.grad.permute(2, 3, 1, 0).reshape(800, 64)
     assert _rel_err(dw, dw_ref) < 1e-2, f"wgrad rel err {_rel_err(dw, dw_ref)}"
