@@ -39,6 +39,9 @@ def main():
     ap.add_argument("--gpus", type=int, default=2)
     ap.add_argument("--placement", default="auto")
     ap.add_argument("--timeout", type=float, default=240.0)
+    ap.add_argument("--fault", default="", metavar="W:ACTION@N",
+                    help="fault injection for one worker, e.g. 1:kill@30 (that worker exits with code 17 at its "
+                         "30th local step; the others must finish the run)")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     tmp = tempfile.mkdtemp(prefix="dtf_gpu_cli_")
@@ -69,8 +72,10 @@ def main():
     logs = [open(os.path.join(tmp, "ps%d.log" % i), "w") for i in range(args.ps)]
     pss = [subprocess.Popen(base + ["--job_name", "ps", "--task_index", str(i)], env=env, stdout=logs[i],
                             stderr=subprocess.STDOUT, text=True) for i in range(args.ps)]
+    fault_w, _, fault_spec = args.fault.partition(":")
     ws = [subprocess.Popen(base + ["--job_name", "worker", "--task_index", str(i)] +
-                           (["--shutdown_ps_when_done", "true"] if i == 0 else []), env=env,
+                           (["--shutdown_ps_when_done", "true"] if i == 0 else []) +
+                           (["--fault_inject", fault_spec] if (args.fault and int(fault_w) == i) else []), env=env,
                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
           for i in range(args.workers)]
     outs = []
@@ -96,6 +101,9 @@ def main():
     total = time.time() - t0
     per_worker = []
     for i, out in enumerate(outs):
+        if args.fault and int(fault_w) == i:
+            per_worker.append(dict(local_steps=None, seconds=None, last_global_step=None, exit_code=ws[i].returncode))
+            continue
         m = re.search(r"Worker %d: (\d+) local steps, ([0-9.]+) s wall clock \(global step (\d+)\)" % i, out)
         if m is None:
             sys.stderr.write("---- worker %d ----\n%s\n" % (i, out[-3000:]))

@@ -219,3 +219,21 @@ def test_async_eight_gpus_counts_every_apply():
     assert out["n_gpus"] == 8 and out["config"]["push"].startswith("mailbox")
     assert out["final_global_step"] == 8 * (3 + 20 + 20 + 20)
     assert out["final_loss"] < 2.0
+
+
+def test_device_path_survives_a_worker_killed_mid_training():
+    """Three OS processes per the reference's CLI on the device data plane - PS on its own GPU, two
+    workers on theirs - and worker 1 is killed (os._exit) at its 30th step, mailboxes half-used and its
+    mirror still registered with the PS. The chief must reach max_steps, the PS must keep applying and
+    shut down cleanly (reference: a dead worker only stops contributing,
+    run_mnist_distributed.py:143-150)."""
+    if _gpus() < 3:
+        pytest.skip("needs 3 GPUs (a PS task and two workers, one process per GPU)")
+    cmd = [sys.executable, os.path.join(ROOT, "bench", "gpu_cli_baseline.py"), "--steps", "60000", "--workers", "2",
+           "--ps", "1", "--gpus", "3", "--fault", "1:kill@30", "--timeout", "150"]
+    p = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=200)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-3000:]
+    res = json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][-1])
+    assert res["global_steps"] >= 60000               # (long enough for the second worker to join: it starts ~1 s late)
+    assert res["workers"][1]["exit_code"] == 17
+    assert 25 <= res["global_steps"] - res["workers"][0]["local_steps"] <= 40     # what the dead worker contributed
