@@ -173,8 +173,13 @@ def test_sync_replicas_equals_large_batch_sgd():
                     _, step = sess.run([train_op, gs], feed_dict={x: data[i][0], y_: data[i][1]})
                 results[i] = int(step)
                 if i == 0:
-                    time.sleep(0.2)
                     raw = sess._tf_sess()
+                    # the last round's apply runs on the chief's queue-runner thread: wait for it
+                    # (bounded) instead of sleeping a fixed time - the box may be busy
+                    t_end = time.time() + 20
+                    while time.time() < t_end and raw.ps_client.read_global_step(raw.layout, "global_step") < rounds:
+                        time.sleep(0.01)
+                    time.sleep(0.05)
                     results["vars"] = raw.ps_client.pull_all(raw.layout, names)
         except Exception as e:  # pragma: no cover
             errors.append(e)
