@@ -372,7 +372,7 @@ class B200StepRunner:
         self.drain_backstop_us = int(opts.get("drain_backstop_us", 400))
         # grid cap of the in-graph drain: it runs beside the forward pass, where a flood of CTAs
         # doubled the convolutions' time; a few dozen CTAs over a longer window are free
-        # (-1 = auto: a short drain (<= 1024 chunks of 4096 elements, the MNIST models) is capped at 64 CTAs;
+        # (-1 = auto: a short drain (<= 1024 chunks of 4096 elements, the MNIST models) is capped at 148 CTAs;
         # a long one (the wide MLP: thousands of chunks) runs uncapped at low priority - capped, its few
         # resident CTAs slowed the persistent GEMM's CTAs on the SMs they shared 3x, and the static tile
         # schedule made the whole GEMM wait for them)
@@ -1308,7 +1308,10 @@ class B200StepRunner:
             cap = self.drain_ctas
             if cap < 0:
                 chunks = sum(-(-int(it["n"]) // 4096) for it in desc["items"])
-                cap = 64 if chunks <= 1024 else 0
+                # a short drain is compute-heavy (one Adam update with IEEE-grade division and sqrt per
+                # pending gradient per element): one CTA slot per SM gets it out of the way of the forward
+                # pass soonest (2 GPUs, measured: cap 64 0.139, cap 148 0.129, uncapped 0.130 ms/step)
+                cap = 148 if chunks <= 1024 else 0
             K.mailbox_drain(spec.code, K.make_apply_items(entries), len(entries), int(desc["slot_stride"]),
                             int(desc["depth"]), int(desc["n_workers"]), hyper, base,
                             base if desc["owns_step"] else None, base + int(desc["flags_off"]),
