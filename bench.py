@@ -292,6 +292,25 @@ def main() -> int:
         runner.flush_pushes()        # "owner applies" mode: my last gradients have been applied
         barrier()                    # every worker has finished: the shared counter is final
         final_step = int(sess.run(global_step))
+        # diagnostics of the data plane: every rank's loss, and whether every owner's last broadcast
+        # reached this rank's mirror (version[s] = gradients shard s had applied when it last wrote here)
+        extra_diag = {}
+        if world > 1:
+            ver = None
+            try:    # local part first: nothing in here may make one rank skip the collective below
+                if getattr(runner, "use_mirror", False):
+                    from distributedtensorflow_b200.ops import _lib as L_
+                    ver = [int(v) for v in runner.store.mirror_hdr_u32(L_.MIRROR_OFF_VERSION, runner.store.num_shards)]
+            except Exception:
+                ver = None
+            rows = [None] * world
+            dist.all_gather_object(rows, (round(final_loss, 5), ver), group=cpu_group)
+            extra_diag["final_loss_per_rank"] = [r[0] for r in rows]
+            if all(r[1] is not None for r in rows):
+                # every shard applies every worker's every push: all entries equal the final global step
+                extra_diag["mirror_versions_current"] = bool(all(x == final_step for r in rows for x in r[1]))
+                if not extra_diag["mirror_versions_current"]:
+                    extra_diag["mirror_versions"] = [r[1] for r in rows]
 
         if args.timeline:
             from torch.profiler import profile, ProfilerActivity
@@ -355,6 +374,7 @@ def main() -> int:
             "launches_per_step": int(launches_per_step),
             "clocks": clocks, "final_global_step": final_step, "final_loss": round(final_loss, 5),
             "loss_floor_label_noise": round(mnist.label_noise_xent_floor(LABEL_NOISE), 4),
+            **extra_diag,
         }
     barrier()
     if ps_server is not None:
