@@ -384,6 +384,12 @@ int dtf_sync_token_wait(const dtf_mirror_hdr* my_hdr, int n_shards, unsigned int
                         unsigned int* local_step_out, unsigned long long* step_out, void* stream);
 
 
+/* Programmatic dependent launch for every kernel launched afterwards by this library (process-wide
+ * switch; returns the previous setting). Every kernel calls griddepcontrol.wait before it touches
+ * global memory, so a dependent's prologue (TMEM allocation, mbarrier init, descriptor prefetch) may
+ * overlap its predecessor's tail. The executor turns it on for the forward chain only. */
+int dtf_set_pdl(int enabled);
+
 /* Host-side spin on a pinned word written by a kernel (see dtf_result_sink): 0 = reached
  * `expected`, 1 = timeout. */
 int dtf_host_wait_u32(const unsigned int* word, unsigned int expected, long long timeout_us);

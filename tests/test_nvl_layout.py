@@ -114,3 +114,41 @@ def test_worker_mirror_layout_holds_the_forms_the_kernels_read():
     assert ml.nbytes >= spans[-1][1] and ml.nbytes % 4096 == 0
     # the 10-column head is padded to 16 columns in its bf16 form
     assert al.regions["head/kernel"][0].shadow_ld == 16
+
+
+def test_every_ctypes_signature_matches_the_header_prototype():
+    """ABI drift guard: each function bound in ops/_lib.py exists in include/dtf_b200.h with the same
+    number of parameters (the bindings are hand-written; a missed argument shifts every pointer after it)."""
+    import inspect
+    text = open(os.path.join(ROOT, "include", "dtf_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)          # drop comments (they contain commas / parens)
+    protos = {}
+    for m in re.finditer(r"\bint\s+(dtf_\w+)\s*\(([^;{]*?)\)\s*;", text, flags=re.S):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else len([a for a in args.split(",") if a.strip()])
+    src = inspect.getsource(L._declare)
+    bound = re.findall(r'"(dtf_\w+)":\s*\[', src)
+    assert len(bound) > 40
+    ns = {"vp": C.c_void_p, "i": C.c_int, "f": C.c_float, "ll": C.c_longlong, "C": C}
+    ns.update({k: getattr(L, k) for k in dir(L)})
+    sigs_src = src[src.index("sigs = {"):src.index("for name, args in sigs.items()")]
+    exec("import ctypes as C\n" + inspect.cleandoc(sigs_src), ns)
+    for name in bound:
+        assert name in protos, "%s is bound but not declared in include/dtf_b200.h" % name
+        assert len(ns["sigs"][name]) == protos[name], (name, len(ns["sigs"][name]), protos[name])
+
+
+def test_host_library_bindings_match_their_header():
+    import inspect
+    from distributedtensorflow_b200.utils import hostlib
+    text = open(os.path.join(ROOT, "include", "dtf_b200_io.h")).read()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(dtf_\w+)\s*\(([^;{]*?)\)\s*;", text, flags=re.S):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else len([a for a in args.split(",") if a.strip()])
+    src = inspect.getsource(hostlib._declare)
+    for name, arglist in re.findall(r'\("(dtf_\w+)",\s*\w+,\s*\[(.*?)\]\),?\n', src, flags=re.S):
+        n = 0 if not arglist.strip() else len(re.sub(r"\([^()]*\)", "", arglist).split(","))
+        assert name in protos, "%s is bound but not declared in include/dtf_b200_io.h" % name
+        assert n == protos[name], (name, n, protos[name])
