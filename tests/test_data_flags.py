@@ -131,3 +131,38 @@ def test_flags_parse_defaults_booleans_and_unknown():
         F.app_run(main, ["prog", "--task_index=1", "leftover"])
     assert e.value.code == 0 and called["argv"] == ["prog", "leftover"]
     F.FLAGS._reset()
+
+
+def test_synthetic_data_label_noise_has_a_loss_floor():
+    """bench.py trains on low-contrast blobs with 10% label noise so that the final loss means
+    something: the best possible predictor cannot get below the entropy of the noisy label."""
+    from distributedtensorflow_b200.data import mnist
+    x0, y0 = mnist.synthetic_arrays(4000, seed=3)
+    x1, y1 = mnist.synthetic_arrays(4000, seed=3, contrast=90.0, label_noise=0.10)
+    assert x0.shape == x1.shape == (4000, 784) and x1.dtype == np.uint8
+    assert x1.mean() < x0.mean()                               # dimmer blobs
+    flipped = float((y0 != y1).mean())
+    assert 0.06 < flipped < 0.12                               # 10% redrawn, a tenth of those land on the same class
+    assert mnist.label_noise_xent_floor(0.0) == 0.0
+    assert abs(mnist.label_noise_xent_floor(0.10) - 0.5003) < 1e-3
+    assert mnist.label_noise_xent_floor(1.0) == pytest.approx(np.log(10.0), rel=1e-6)
+
+
+def test_synthetic_stand_in_for_mnist_is_marked(tmp_path, monkeypatch):
+    """Without network access download() falls back to generated data under the real MNIST file names;
+    a marker file says so, and loading from such a directory warns instead of passing for the real set."""
+    from distributedtensorflow_b200.data import mnist
+    import urllib.request
+
+    def no_network(*a, **k):
+        raise OSError("no route to host")
+    monkeypatch.setattr(urllib.request, "urlretrieve", no_network)
+    monkeypatch.setattr(mnist, "synthetic_mnist",
+                        lambda d, **k: mnist.write_idx(d, mnist.TRAIN_IMAGES, mnist.TRAIN_LABELS,
+                                                       *mnist.synthetic_arrays(64)))
+    d = str(tmp_path / "data")
+    assert not mnist.is_synthetic(d)
+    path = mnist.download(d, mnist.TRAIN_IMAGES)
+    assert os.path.exists(path) and mnist.is_synthetic(d)
+    with pytest.raises(OSError):
+        mnist.download(str(tmp_path / "strict"), mnist.TRAIN_IMAGES, allow_synthetic=False)

@@ -228,3 +228,24 @@ def test_sync_backup_workers_and_token_accounting():
     assert shard.accum_stats()[names[0]][0] == 0 and shard.accum_stats()[names[0]][2] == 1
     assert not opt.run_sync_op(client, layout, timeout=0.05)           # no fresh gradients: times out
     sess.close()
+
+
+def test_shard_take_is_all_or_nothing_on_timeout():
+    """accum_take_apply first waits (consuming nothing) until EVERY accumulator of the shard holds
+    enough gradients: a timeout on the second variable must not discard the first one's mean nor
+    advance its step (which would make its next gradients look stale)."""
+    from distributedtensorflow_b200.parallel.ps_core import PsShard
+    from distributedtensorflow_b200.parallel.transport import spec_to_dict
+    sh = PsShard(0)
+    spec = spec_to_dict(tf.train.GradientDescentOptimizer(0.5).spec())
+    sh.create([dict(name="a", first=0, n=2, dtype="float32"), dict(name="b", first=0, n=2, dtype="float32")], spec)
+    sh.accum_create([("a", 2), ("b", 2)])
+    sh.accum_apply({"a": np.asarray([1.0, 2.0], np.float32)}, 0)        # only `a` has a gradient
+    with pytest.raises(TimeoutError):
+        sh.accum_take_apply(["a", "b"], 1, spec, None, timeout=0.05)
+    stats = sh.accum_stats()
+    assert stats["a"][0] == 1 and stats["b"][0] == 0                    # a's gradient is still there ...
+    assert stats["a"][1] == 0                                            # ... and its step did not move
+    sh.accum_apply({"b": np.asarray([3.0, 4.0], np.float32)}, 0)
+    assert sh.accum_take_apply(["a", "b"], 1, spec, None, timeout=1.0) == 2
+    np.testing.assert_allclose(sh.pull(["a", "b"]), [[-0.5, -1.0], [-1.5, -2.0]])
