@@ -18,13 +18,14 @@ FAMILIES = {
     "gemm_umma_kernel_64_Kmajor_MNmajor": "void dtf::gemm_umma_kernel<64, false, true>",
     "gemm_umma_kernel_128_MNmajor_MNmajor": "void dtf::gemm_umma_kernel<128, true, true>",
     "gemm_umma_pair_kernel_Kmajor_MNmajor": "void dtf::gemm_umma_pair_kernel<false, true>",
+    "conv2_fwd_halo_kernel": "dtf::conv2_fwd_halo_kernel",
+    "conv2_dgrad_halo_kernel": "dtf::conv2_dgrad_halo_kernel",
     "conv2_fwd_kernel": "dtf::conv2_fwd_kernel",
     "conv2_dgrad_kernel": "dtf::conv2_dgrad_kernel",
     "conv2_wgrad_kernel": "dtf::conv2_wgrad_kernel",
     "conv1_fwd_kernel": "dtf::conv1_fwd_kernel",
     "conv1_bwd_kernel": "dtf::conv1_bwd_kernel",
     "head_fused_kernel_sparse": "void dtf::head_fused_kernel<false>",
-    "softmax_xent_sparse_kernel": "dtf::softmax_xent_sparse_kernel",
     "push_apply_kernel_adam": "void dtf::push_apply_kernel<3>",
     "mailbox_push_kernel": "dtf::mailbox_push_kernel",
     "mailbox_snapshot_kernel": "dtf::mailbox_snapshot_kernel",
