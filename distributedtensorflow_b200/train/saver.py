@@ -135,7 +135,7 @@ class Saver:
 
     # -- save ---------------------------------------------------------------------------------------
     def save(self, sess, save_path: str, global_step=None, latest_filename: Optional[str] = None,
-             write_state: bool = True) -> str:
+             write_state: bool = True, write_meta_graph: bool = True) -> str:
         t0 = time.time()
         if global_step is not None:
             if not isinstance(global_step, (int, np.integer)):
@@ -148,6 +148,9 @@ class Saver:
         os.makedirs(save_dir, exist_ok=True)
         names = {v.name for v in self._variables(sess)}
         self.last_save_bytes = sess.save_state(prefix, names, sharded=self._sharded)
+        if write_meta_graph:      # TF's Saver.save exports <prefix>.meta with every checkpoint
+            from .meta_graph import write_meta_graph as _write_meta
+            _write_meta(prefix, self._variables(sess), sharded=self._sharded, max_to_keep=self._max_to_keep or 0)
         if write_state:
             self._last_checkpoints.append(prefix)
             while self._max_to_keep and len(self._last_checkpoints) > self._max_to_keep:

@@ -272,3 +272,37 @@ def test_index_only_writer_describes_data_files_written_elsewhere(tmp_path):
     w2 = B.BundleIndexWriter(str(tmp_path / "bad"), 1)
     with pytest.raises(Exception):
         w2.add("x", B.DT_FLOAT, (1,), 3, 0, 4, 0)        # shard id outside the declared shards
+
+
+def test_saver_writes_a_meta_graph_with_the_between_graph_placement(tmp_path):
+    """Saver.save exports <prefix>.meta like TF1: one VariableV2 node per variable carrying the
+    device replica_device_setter chose, the variables / trainable_variables collections, a V2 SaverDef."""
+    from distributedtensorflow_b200.train.meta_graph import read_meta_graph
+    from distributedtensorflow_b200.models import mnist_mlp
+    tf.reset_default_graph()
+    cluster = tf.train.ClusterSpec({"ps": ["h:1", "h:2"], "worker": ["w:1"]})
+    with tf.device(tf.train.replica_device_setter(worker_device="/job:worker/task:0", cluster=cluster)):
+        x = tf.placeholder(tf.float32, [None, 784])
+        y_ = tf.placeholder(tf.float32, [None, 10])
+        gs, xent, _ = mnist_mlp.build_model(x, y_, hidden_units=100)
+        train_op = tf.train.AdamOptimizer(0.01).minimize(xent, global_step=gs)
+    server = tf.train.Server.create_local_server(num_ps=2)
+    with tf.train.MonitoredTrainingSession(master=server.target, config=tf.ConfigProto(backend="cpu")) as sess:
+        raw = sess._tf_sess()
+        path = tf.train.Saver(max_to_keep=3).save(raw, str(tmp_path / "model.ckpt"), global_step=0)
+    server.stop()
+    assert os.path.exists(path + ".meta") and os.path.exists(path + ".index")
+    mg = read_meta_graph(path + ".meta")
+    by_name = {n["name"]: n for n in mg["nodes"]}
+    assert all(n["op"] == "VariableV2" for n in mg["nodes"])
+    assert by_name["global_step"]["dtype"] == "int32" and by_name["global_step"]["shape"] == ()
+    assert by_name["hid_w"]["shape"] == (784, 100) and by_name["hid_w"]["dtype"] == "float32"
+    # round-robin in creation order over the two PS tasks (SURVEY 2.5)
+    devices = [by_name[n]["device"] for n in ("global_step", "hid_w", "hid_b", "sm_w", "sm_b")]
+    assert devices == ["/job:ps/task:0", "/job:ps/task:1", "/job:ps/task:0", "/job:ps/task:1", "/job:ps/task:0"]
+    assert mg["collections"]["trainable_variables"] == ["hid_w:0", "hid_b:0", "sm_w:0", "sm_b:0"]
+    assert "global_step:0" in mg["collections"]["variables"]
+    assert mg["saver"] == dict(max_to_keep=3, sharded=True, version=2, filename_tensor_name="save/Const:0")
+    assert mg["producer"] == 27 and mg["tags"] == ["train"]
+    S.remove_checkpoint(path)
+    assert not os.path.exists(path + ".meta")
