@@ -150,6 +150,14 @@ class PsShard:
         self.declared: set = set()           # names whose storage lives in a device arena
         self.device: Optional[str] = None    # "cuda:N" when this PS task owns a GPU arena
         self._arena: Optional[dict] = None
+        # owner-applies data plane (device arenas): the apply daemon, where its flag block lives, the
+        # workers' mirrors mapped into this process, the pinned staging buffer of the parallel save
+        self._mbox_daemon = None
+        self._mbox_sig: Optional[str] = None
+        self._mbox_flags_off: Optional[int] = None
+        self._mbox_backstop_us = 0
+        self._mirrors: Dict[int, dict] = {}
+        self._save_stage: Optional[int] = None
 
     # -- creation / init --------------------------------------------------------------------------
     def create(self, defs: Sequence[dict], spec: Optional[dict]) -> bool:
@@ -259,7 +267,7 @@ class PsShard:
         L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
         base = self._arena["ptr"]
         chunk = 32 << 20
-        stage = getattr(self, "_save_stage", None)
+        stage = self._save_stage
         if stage is None:
             p = C.c_void_p()
             L.check(lib.dtf_host_alloc_pinned(C.byref(p), chunk), "pinned staging buffer")
@@ -306,7 +314,7 @@ class PsShard:
                 raise RuntimeError("mbox_start before nvl_alloc")
             base = self._arena["ptr"]
             sig = sig + "@%x" % base
-            old = getattr(self, "_mbox_daemon", None)
+            old = self._mbox_daemon
             if old is not None:
                 if sig == self._mbox_sig:
                     return {"started": False}
@@ -327,7 +335,7 @@ class PsShard:
             zeros = (C.c_ubyte * L.MBOX_FLAGS_BYTES)()
             L.check(L.lib().dtf_memcpy_h2d(self._flags_ptr(), zeros, L.MBOX_FLAGS_BYTES, None), "h2d")
             L.check(L.lib().dtf_stream_sync(None), "sync")
-            self.__dict__.setdefault("_mirrors", {}).clear()
+            self._mirrors.clear()
             mirror_items = None
             if desc.get("mirror_items") is not None:
                 mirror_items = K.make_mirror_items([tuple(m) for m in desc["mirror_items"]])
@@ -347,7 +355,7 @@ class PsShard:
                                            base if desc["owns_step"] else None,
                                            base + int(desc["flags_off"]), int(desc.get("poll_us", 20)),
                                            mirror_items, int(desc.get("shard", self.task_index)),
-                                           int(getattr(self, "_mbox_backstop_us", 0)),
+                                           int(self._mbox_backstop_us),
                                            int(desc.get("sync_R", 0) or 0))
             L.check(rc, "dtf_mbox_daemon_start")
             self._mbox_daemon = handle
@@ -360,7 +368,7 @@ class PsShard:
         from ..ops import _lib as L
         polls, drains, applied = C.c_ulonglong(), C.c_ulonglong(), C.c_ulonglong()
         with self._lock:                       # not while mbox_stop frees the handle
-            d = getattr(self, "_mbox_daemon", None)
+            d = self._mbox_daemon
             if d is None:
                 return {"running": False}
             rc = L.lib().dtf_mbox_daemon_stats(d, C.byref(polls), C.byref(drains), C.byref(applied))
@@ -372,10 +380,10 @@ class PsShard:
         launched from a colocated worker's step graph no-ops (``flags.paused``) and waits for a
         drain in flight to retire."""
         from ..ops import _lib as L
-        d = getattr(self, "_mbox_daemon", None)
+        d = self._mbox_daemon
         if d is not None:
             L.check(L.lib().dtf_mbox_daemon_pause(d, 1 if pause else 0), "dtf_mbox_daemon_pause")
-        if self._arena is not None and getattr(self, "_mbox_flags_off", None) is not None:
+        if self._arena is not None and self._mbox_flags_off is not None:
             self._flags_write_u32(L.MBOX_OFF_PAUSED, 1 if pause else 0)
             if pause:
                 self._wait_drain_idle()
@@ -388,7 +396,7 @@ class PsShard:
         from ..ops import _lib as L
         with self._lock:
             self._mbox_backstop_us = int(backstop_us) if attach else 0
-            d = getattr(self, "_mbox_daemon", None)
+            d = self._mbox_daemon
             if d is not None:
                 L.check(L.lib().dtf_mbox_daemon_set_backstop(d, self._mbox_backstop_us), "set_backstop")
 
@@ -425,8 +433,8 @@ class PsShard:
         """Clear every registered mirror address (caller holds the lock, no drain is running)."""
         import ctypes as C
         from ..ops import _lib as L
-        mirrors = self.__dict__.get("_mirrors") or {}
-        if self._arena is None or getattr(self, "_mbox_flags_off", None) is None:
+        mirrors = self._mirrors
+        if self._arena is None or self._mbox_flags_off is None:
             mirrors.clear()
             return
         lib = L.lib()
@@ -445,13 +453,13 @@ class PsShard:
         import ctypes as C
         import os
         from ..ops import _lib as L
-        if self._arena is None or getattr(self, "_mbox_flags_off", None) is None:
+        if self._arena is None or self._mbox_flags_off is None:
             raise RuntimeError("mirror_register before mbox_start")
         if not 0 <= int(worker) < L.MAX_WORKERS:
             raise ValueError("mirror_register: worker %r out of range" % (worker,))
         lib = L.lib()
         with self._lock:
-            mirrors = self.__dict__.setdefault("_mirrors", {})
+            mirrors = self._mirrors
             L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
             imported = False
             if int(info["pid"]) == os.getpid():
@@ -477,7 +485,7 @@ class PsShard:
         from ..ops import _lib as L
         lib = L.lib()
         with self._lock:
-            ent = self.__dict__.setdefault("_mirrors", {}).pop(int(worker), None)
+            ent = self._mirrors.pop(int(worker), None)
             if ent is None or self._arena is None:
                 return
             L.check(lib.dtf_set_device(self._arena["device"]), "set_device")
@@ -493,7 +501,7 @@ class PsShard:
     def mbox_stop(self) -> None:
         from ..ops import _lib as L
         with self._lock:
-            d = getattr(self, "_mbox_daemon", None)
+            d = self._mbox_daemon
             self._mbox_daemon = None
         if d is not None:
             L.lib().dtf_mbox_daemon_stop(d)
